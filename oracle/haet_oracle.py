@@ -1,0 +1,318 @@
+"""CPU restatement of HAET's per-layer hot path.  TEST INFRASTRUCTURE ONLY.
+
+This file is the checker: only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` legs may import it.  The product (``haet_b200``)
+never does, and fails loudly when its CUDA library is missing.
+
+It restates, in plain torch-on-CPU arithmetic (fp32 by default, fp64 on request) driven by a
+``state_dict`` with the reference's parameter names:
+
+  * Physics_Attention_{Irregular_Mesh,Structured_Mesh_2D,Structured_Mesh_3D}.forward
+      /root/reference/models/PhysicsAttention/IrregularMesh.py:141-235
+      /root/reference/models/PhysicsAttention/StructuredMesh2D.py:173-189 (conv front-end)
+      /root/reference/models/PhysicsAttention/StructuredMesh3D.py:177-193 (conv front-end)
+  * ErwinTransformer.forward      models/components/erwinflash/erwin_flash.py:138-195
+  * BasicLayer / ErwinTransformerBlock  .../components/layers.py:30-32,72-92
+  * BallMSA (+compute_rel_pos)     .../components/attention.py:35-91  (flash-attn, a
+      third-party fp16 CUDA library with no pinned version, replaced by its published
+      arithmetic softmax(QK^T/sqrt(d))V in the working dtype -- SURVEY F9/F10)
+  * SwiGLU                         .../components/mlp.py:17-18
+  * BallPooling / BallUnpooling    .../components/pooling.py:25-40,58-72
+  * build_balltree_with_rotations  models/components/balltree/balltree.pyx:598-662
+      through ``oracle/balltree_oracle.c`` (ctypes)
+
+Parity status: PINNED.  ``tests/test_oracle_vs_reference.py`` runs the unmodified reference
+(imported by ``oracle/ref_loader.py``) beside this file where /root/reference exists, and
+``tests/golden/*.npz`` (made by ``tests/golden/make_golden.py`` from the reference itself)
+pin it everywhere else.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+import os
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def _lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(HERE, "libballtree_oracle.so")
+        if not os.path.exists(path):
+            from . import build_ref
+            build_ref.build_c_oracle()
+        lib = ctypes.CDLL(path)
+        lib.haet_oracle_tree_slots.restype = ctypes.c_int64
+        _LIB = lib
+    return _LIB
+
+
+def _offsets_from_batch_idx(batch_idx: np.ndarray) -> np.ndarray:
+    """balltree.pyx:444-472 -- offsets from the change points of a sorted batch index."""
+    if batch_idx.ndim != 1 or len(batch_idx) == 0:
+        raise ValueError("batch_idx must be a non-empty 1D array")
+    if batch_idx[0] != 0:
+        raise ValueError("Batch indices must start from 0")
+    n = len(batch_idx)
+    change = np.where(batch_idx[1:] != batch_idx[:-1])[0] + 1
+    nb = int(batch_idx[-1]) + 1
+    off = np.zeros(nb + 1, dtype=np.int64)
+    off[1:nb] = change
+    off[nb] = n
+    return off
+
+
+def _p(a: np.ndarray, t):
+    return a.ctypes.data_as(ctypes.POINTER(t))
+
+
+def balltree_build_with_rotations(pos: torch.Tensor, batch_idx: torch.Tensor, strides: Sequence[int],
+                                  ball_sizes: Sequence[int], angle: float = 45.0):
+    """balltree.pyx:598-662.  Returns (tree_idx int64, tree_mask bool, [rot_idx per level | None])."""
+    assert len(strides) == len(ball_sizes) - 1, "Strides must be one less than ball sizes"
+    if pos.dim() != 2 or batch_idx.dim() != 1 or pos.shape[0] != batch_idx.shape[0]:
+        raise ValueError("bad shapes")
+    p = np.ascontiguousarray(pos.detach().cpu().to(torch.float32).numpy())
+    off = _offsets_from_batch_idx(batch_idx.detach().cpu().numpy().astype(np.int64))
+    n, d = p.shape
+    nt = len(off) - 1
+    lib = _lib()
+    total = lib.haet_oracle_tree_slots(_p(off, ctypes.c_int64), ctypes.c_int64(nt))
+    if total < 0:
+        raise ValueError("every tree needs at least 2 points")
+    nl = len(ball_sizes)
+    tree_idx = np.empty(total, dtype=np.int64)
+    tree_mask = np.empty(total, dtype=np.uint8)
+    rot = np.empty(total * nl, dtype=np.int64)
+    rot_off = np.zeros(nl + 1, dtype=np.int64)
+    st = np.asarray(list(strides) + [1], dtype=np.int32)
+    bs = np.asarray(list(ball_sizes), dtype=np.int32)
+    rc = lib.haet_oracle_build_with_rotations(
+        _p(p, ctypes.c_float), ctypes.c_int64(n), ctypes.c_int(d), _p(off, ctypes.c_int64),
+        ctypes.c_int64(nt), _p(st, ctypes.c_int32), _p(bs, ctypes.c_int32), ctypes.c_int(nl),
+        ctypes.c_double(float(angle)), _p(tree_idx, ctypes.c_int64), _p(tree_mask, ctypes.c_uint8),
+        _p(rot, ctypes.c_int64), _p(rot_off, ctypes.c_int64))
+    if rc != 0:
+        raise RuntimeError(f"balltree oracle failed with code {rc}")
+    if angle > 0:
+        rots = [torch.from_numpy(rot[rot_off[i]:rot_off[i + 1]].copy()) for i in range(nl)]
+    else:
+        rots = [None] * nl
+    return torch.from_numpy(tree_idx), torch.from_numpy(tree_mask.astype(np.bool_)), rots
+
+
+# --------------------------------------------------------------------------------------
+# Erwin over the slice tokens
+# --------------------------------------------------------------------------------------
+def default_erwin_cfg(heads: int, dim_head: int, slice_num: int, dimensionality: int, rotate=45,
+                      mlp_ratio: int = 4, **over) -> dict:
+    """Defaults of Physics_Attention_*.__init__ (IrregularMesh.py:105-137)."""
+    cfg = dict(c_hidden=[dim_head, dim_head * 2],
+               ball_sizes=[min(32, slice_num), min(16, slice_num // 2)],
+               enc_num_heads=[heads // 2, heads], enc_depths=[2, 2],
+               dec_num_heads=[heads // 2], dec_depths=[2], strides=[2],
+               rotate=rotate, decode=True, mlp_ratio=mlp_ratio, dimensionality=dimensionality)
+    for k, v in over.items():
+        if v is not None:
+            cfg[k] = v
+    return cfg
+
+
+def _rmsnorm(x, w):
+    # nn.RMSNorm(dim) with eps=None -> torch.finfo(dtype).eps (layers.py:24-25)
+    eps = torch.finfo(x.dtype).eps
+    return x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + eps) * w
+
+
+def _bn(x, sd, pre, training):
+    # nn.BatchNorm1d (pooling.py:23,56): eval -> running stats; train -> biased batch stats
+    w, b = sd[pre + ".weight"], sd[pre + ".bias"]
+    if training:
+        mean, var = x.mean(0), x.var(0, unbiased=False)
+    else:
+        mean, var = sd[pre + ".running_mean"], sd[pre + ".running_var"]
+    return (x - mean) / torch.sqrt(var + 1e-5) * w + b
+
+
+def _ball_msa(x, pos, sd, pre, num_heads, ball_size):
+    """attention.py:35-91 (flash variant: no distance bias, column layout (three, head, hd))."""
+    T, dim = x.shape
+    hd = dim // num_heads
+    nb = T // ball_size
+    p = pos.view(nb, ball_size, -1)
+    rel = (p - p.mean(dim=1, keepdim=True)).view(T, -1)                      # :35-40
+    x = x + F.linear(rel, sd[pre + ".pe_proj.weight"], sd[pre + ".pe_proj.bias"])  # :59-62
+    qkv = F.linear(x, sd[pre + ".qkv.weight"], sd[pre + ".qkv.bias"])          # :65
+    qkv = qkv.view(nb, ball_size, 3, num_heads, hd)                            # :68-76
+    q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))            # [nb, h, n, hd]
+    att = torch.softmax(q @ k.transpose(-1, -2) * (1.0 / math.sqrt(hd)), dim=-1)  # :79-84
+    o = (att @ v).permute(0, 2, 1, 3).reshape(T, dim)                          # :87
+    return F.linear(o, sd[pre + ".proj.weight"], sd[pre + ".proj.bias"])       # :88
+
+
+def _swiglu(x, sd, pre):
+    """mlp.py:17-18"""
+    return F.linear(F.linear(x, sd[pre + ".w2.weight"], sd[pre + ".w2.bias"])
+                    * F.silu(F.linear(x, sd[pre + ".w1.weight"], sd[pre + ".w1.bias"])),
+                    sd[pre + ".w3.weight"], sd[pre + ".w3.bias"])
+
+
+def _block(x, pos, sd, pre, num_heads, ball_size):
+    """layers.py:30-32"""
+    x = x + _ball_msa(_rmsnorm(x, sd[pre + ".norm1.weight"]), pos, sd, pre + ".BMSA", num_heads, ball_size)
+    return x + _swiglu(_rmsnorm(x, sd[pre + ".norm2.weight"]), sd, pre + ".swiglu")
+
+
+def _blocks(x, pos, rot, sd, pre, depth, num_heads, ball_size, rotate):
+    """layers.py:74-91: odd blocks run on the rotated permutation and are permuted back."""
+    inv = torch.argsort(rot) if (rotate and depth > 1) else None
+    for i in range(depth):
+        if rotate and i % 2 == 1:
+            x = _block(x[rot], pos[rot], sd, f"{pre}.blocks.{i}", num_heads, ball_size)[inv]
+        else:
+            x = _block(x, pos, sd, f"{pre}.blocks.{i}", num_heads, ball_size)
+    return x
+
+
+def erwin_forward(sd: Dict[str, torch.Tensor], cfg: dict, x: torch.Tensor, pos: torch.Tensor,
+                  batch_idx: torch.Tensor, tree=None, bn_training: bool = False, taps: Optional[dict] = None):
+    """erwin_flash.py:138-195 with embed=False, mp_steps=0 (the only mode HAET uses).
+
+    ``sd`` holds the ``erwin.*`` entries with the prefix stripped.  ``tree`` may carry a
+    pre-built (tree_idx, tree_mask, rot_list) triple."""
+    strides, balls = cfg["strides"], cfg["ball_sizes"]
+    rotate = cfg["rotate"] > 0
+    if tree is None:
+        tree = balltree_build_with_rotations(pos, batch_idx, strides, balls, cfg["rotate"])
+    tree_idx, tree_mask, rots = tree
+    rots = list(rots)
+    if taps is not None:
+        taps.update(tree_idx=tree_idx, tree_mask=tree_mask, rot_idx=list(rots))
+    nlev = len(cfg["enc_depths"]) - 1
+    xs, ps, rs = [], [], []                      # encoder skip state (node.children chain)
+    x, p = x[tree_idx], pos[tree_idx]            # :176-181
+    for i in range(nlev):                        # encoder :183-185
+        rot = rots.pop(0)
+        x = _blocks(x, p, rot, sd, f"encoder.{i}", cfg["enc_depths"][i], cfg["enc_num_heads"][i], balls[i], rotate)
+        xs.append(x); ps.append(p); rs.append(rot)
+        s = strides[i]                           # BallPooling pooling.py:25-40
+        if s != 1:
+            n = x.shape[0] // s
+            centers = p.view(n, s, -1).mean(1)
+            rel = (p.view(n, s, -1) - centers[:, None]).reshape(n, -1)
+            cat = torch.cat([x.view(n, -1), rel], dim=1)
+            x = _bn(F.linear(cat, sd[f"encoder.{i}.pool.proj.weight"], sd[f"encoder.{i}.pool.proj.bias"]),
+                    sd, f"encoder.{i}.pool.norm", bn_training)
+            p = centers
+    rot = rots.pop(0)                            # bottleneck :187-188
+    x = _blocks(x, p, rot, sd, "bottleneck", cfg["enc_depths"][-1], cfg["enc_num_heads"][-1], balls[-1], rotate)
+    if not cfg.get("decode", True):
+        return x
+    for j, i in enumerate(range(nlev - 1, -1, -1)):   # decoder :190-192
+        s = strides[i]                           # BallUnpooling pooling.py:58-72
+        cx, cp, crot = xs[i], ps[i], rs[i]
+        n = x.shape[0]
+        rel = (cp.view(n, s, -1) - p[:, None]).reshape(n, -1)
+        up = F.linear(torch.cat([x, rel], dim=-1), sd[f"decoder.{j}.unpool.proj.weight"],
+                      sd[f"decoder.{j}.unpool.proj.bias"]).view(n * s, -1)
+        x = _bn(cx + up, sd, f"decoder.{j}.unpool.norm", bn_training)
+        p = cp
+        x = _blocks(x, p, crot, sd, f"decoder.{j}", cfg["dec_depths"][i], cfg["dec_num_heads"][i], balls[i], rotate)
+    return x[tree_mask][torch.argsort(tree_idx[tree_mask])]   # :193
+
+
+# --------------------------------------------------------------------------------------
+# PhysicsAttention layer (slicing -> Erwin -> deslicing)
+# --------------------------------------------------------------------------------------
+def split_state_dict(sd: Dict[str, torch.Tensor], dtype=torch.float32):
+    """Split a Physics_Attention_* state_dict into (own params, erwin.* params w/o prefix)."""
+    own, erw = {}, {}
+    for k, v in sd.items():
+        v = v.detach().cpu()
+        if v.is_floating_point():
+            v = v.to(dtype)
+        if k.startswith("erwin."):
+            erw[k[len("erwin."):]] = v
+        else:
+            own[k] = v
+    return own, erw
+
+
+def in_project(own, x, heads, dim_head, grid=None):
+    """IrregularMesh.py:157-164 (Linear) / StructuredMesh2D.py:173-189 / StructuredMesh3D.py:177-193
+    (Conv2d/Conv3d k=3 pad=1 on the reshaped grid).  Returns x_proj [B, H, N, C]."""
+    B, N, D = x.shape
+    w, b = own["in_project_x.weight"], own["in_project_x.bias"]
+    if w.dim() == 2:
+        xp = F.linear(x, w, b)
+    elif w.dim() == 4:
+        H, W = grid
+        xg = x.reshape(B, H, W, D).permute(0, 3, 1, 2)
+        xp = F.conv2d(xg, w, b, stride=1, padding=w.shape[-1] // 2).permute(0, 2, 3, 1).reshape(B, N, -1)
+    else:
+        H, W, Dz = grid
+        xg = x.reshape(B, H, W, Dz, D).permute(0, 4, 1, 2, 3)
+        xp = F.conv3d(xg, w, b, stride=1, padding=w.shape[-1] // 2).permute(0, 2, 3, 4, 1).reshape(B, N, -1)
+    return xp.reshape(B, N, heads, dim_head).permute(0, 2, 1, 3).contiguous()
+
+
+def slice_weights_and_states(own, x_proj, base_temp=0.5, epsilon=1e-6):
+    """IrregularMesh.py:168-188.  Returns (W [B,H,N,G], S [B,H,G,C], tau [B,H,N,1])."""
+    tau = base_temp + F.linear(x_proj, own["ada_temp_linear.weight"], own["ada_temp_linear.bias"]).clamp(-0.4, 0.4)
+    c = torch.log(-torch.log(torch.tensor(epsilon, dtype=torch.float32))).to(x_proj.dtype)   # :172 (fp32 scalar)
+    logits = F.linear(x_proj, own["in_project_slice.weight"], own["in_project_slice.bias"]) - c
+    W = torch.softmax(logits / tau, dim=2)                       # over the N points
+    mass = W.sum(2)                                              # :177
+    S = torch.einsum("bhnc,bhng->bhgc", x_proj, W)               # :181-183
+    S = S / (mass + 1e-5)[:, :, :, None]                         # :186-188
+    return W, S, tau
+
+
+def slice_positions(S_flat, dimensionality):
+    """IrregularMesh.py:204-209 -- min/max over ALL rows jointly, first d channels."""
+    fmin = S_flat.min(dim=0, keepdim=True)[0]
+    fmax = S_flat.max(dim=0, keepdim=True)[0]
+    rng = fmax - fmin + 1e-8
+    d = dimensionality
+    return (S_flat[:, :d] - fmin[:, :d]) / rng[:, :d]
+
+
+def physics_attention_forward(sd: Dict[str, torch.Tensor], x: torch.Tensor, *, heads: int, dim_head: int,
+                              slice_num: int, dimensionality: int = 3, grid=None, base_temp: float = 0.5,
+                              epsilon: float = 1e-6, erwin_cfg: Optional[dict] = None, mlp_ratio: int = 4,
+                              rotate=45, dtype=torch.float32, bn_training: bool = False,
+                              taps: Optional[dict] = None, tree=None, pos_override=None):
+    """Whole layer: Physics_Attention_*.forward (IrregularMesh.py:141-235).
+
+    ``taps`` (optional dict) receives the intermediates x_proj, tau, W (only when N*G is small),
+    S, pos, tree_idx, tree_mask, rot_idx, S_out.  ``tree`` / ``pos_override`` let a test feed the
+    exact positions / tree the device path used (SURVEY 7.3 hard part 2)."""
+    own, erw = split_state_dict(sd, dtype)
+    x = x.detach().cpu().to(dtype)
+    B, N, _ = x.shape
+    cfg = erwin_cfg or default_erwin_cfg(heads, dim_head, slice_num, dimensionality, rotate=rotate,
+                                         mlp_ratio=mlp_ratio)
+    xp = in_project(own, x, heads, dim_head, grid)
+    W, S, tau = slice_weights_and_states(own, xp, base_temp, epsilon)
+    G = S.shape[2]
+    S_flat = S.reshape(B * heads * G, dim_head)
+    pos = slice_positions(S_flat, dimensionality) if pos_override is None else pos_override.to(dtype)
+    batch_idx = torch.arange(B * heads).repeat_interleave(G)     # :213
+    et = {} if taps is not None else None
+    # the tree is always built from the fp32 value of pos (balltree.pyx:542 promotes fp32 -> fp64)
+    S_out = erwin_forward(erw, cfg, S_flat, pos, batch_idx, tree=tree, bn_training=bn_training, taps=et)
+    out_x = torch.einsum("bhgc,bhng->bhnc", S_out.reshape(B, heads, G, dim_head), W)   # :228
+    out_x = out_x.permute(0, 2, 1, 3).reshape(B, N, heads * dim_head)                  # :232
+    out = F.linear(out_x, own["to_out.0.weight"], own["to_out.0.bias"])                # :235
+    if taps is not None:
+        taps.update(x_proj=xp, tau=tau, S=S, pos=pos, S_out=S_out, **et)
+        if N * G * B * heads <= (1 << 26):
+            taps["W"] = W
+    return out

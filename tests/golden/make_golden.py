@@ -1,0 +1,110 @@
+"""Generate the committed golden vectors from the UNMODIFIED reference.
+
+Run in the build container only (needs /root/reference):
+    python tests/golden/make_golden.py
+It imports the reference through oracle/ref_loader.py (shims documented there), runs it on
+seeded inputs on the CPU in fp32 and stores inputs, weights and outputs as small .npz files.
+The GPU box never runs this script; tests only read the .npz files.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import ref_loader  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def trained_like_(module, seed):
+    """Make the softmax over points peaky and drive tau into both clamps:
+    scale in_project_slice / ada_temp_linear, randomise biases and BatchNorm running stats."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for n, p in module.named_parameters():
+            if n.startswith("in_project_slice.weight"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.6)
+            elif n.startswith("ada_temp_linear.weight"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.5)
+            elif n.endswith(".bias") and "norm" not in n:
+                p.copy_(torch.randn(p.shape, generator=g) * 0.1)
+            elif n.startswith("erwin.") and n.endswith(".weight") and p.dim() == 2:
+                p.copy_(torch.randn(p.shape, generator=g) * (1.0 / p.shape[1] ** 0.5))
+            elif "norm" in n and n.endswith(".weight"):
+                p.copy_(1 + 0.2 * torch.randn(p.shape, generator=g))
+            elif "norm" in n and n.endswith(".bias"):
+                p.copy_(0.1 * torch.randn(p.shape, generator=g))
+        for n, b in module.named_buffers():
+            if n.endswith("running_mean"):
+                b.copy_(0.2 * torch.randn(b.shape, generator=g))
+            elif n.endswith("running_var"):
+                b.copy_(0.5 + torch.rand(b.shape, generator=g))
+
+
+def save_layer(name, cls_name, kwargs, B, N, seed, trained=True):
+    ref = ref_loader.load_reference()
+    torch.manual_seed(seed)
+    m = getattr(ref.PhysicsAttention, cls_name)(**kwargs).eval()
+    if trained:
+        trained_like_(m, seed + 1)
+    x = torch.randn(B, N, kwargs["dim"])
+    x = torch.nn.functional.layer_norm(x, (kwargs["dim"],))
+    with torch.no_grad():
+        out = m(x)
+    blob = {"x": x.numpy(), "out": out.numpy(),
+            "cfg": np.frombuffer(json.dumps({"cls": cls_name, "kwargs": kwargs}).encode(), dtype=np.uint8)}
+    for k, v in m.state_dict().items():
+        blob["sd/" + k] = v.numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **blob)
+    print(name, "out absmax", float(out.abs().max()), "bytes", os.path.getsize(os.path.join(OUT, name + ".npz")))
+
+
+def save_balltree(name, d, n_trees, G, angle, mode, seed):
+    bt = ref_loader.load_reference_balltree()
+    g = torch.Generator().manual_seed(seed)
+    T = n_trees * G
+    if mode == "rand":
+        pos = torch.rand(T, d, generator=g)
+    elif mode == "ties":
+        pos = torch.randint(0, 4, (T, d), generator=g).float() / 4
+    else:  # sorted / organ-pipe: stresses the introselect pivoting
+        base = torch.arange(G).float() / G
+        col = torch.cat([base[::2], base[1::2].flip(0)]) if mode == "pipe" else base
+        pos = col.repeat(n_trees)[:, None].repeat(1, d).contiguous()
+    bidx = torch.arange(n_trees).repeat_interleave(G)
+    balls = [min(32, G), min(16, max(G // 2, 1))]
+    tree_idx, tree_mask, rots = bt.build_balltree_with_rotations(pos, bidx, [2], balls, angle)
+    blob = {"pos": pos.numpy(), "n_trees": np.int64(n_trees), "G": np.int64(G), "angle": np.float64(angle),
+            "ball_sizes": np.asarray(balls), "strides": np.asarray([2]),
+            "tree_idx": tree_idx.numpy(), "tree_mask": tree_mask.numpy()}
+    for i, r in enumerate(rots):
+        if r is not None:
+            blob[f"rot{i}"] = r.numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **blob)
+
+
+if __name__ == "__main__":
+    save_layer("layer_irregular_small", "Physics_Attention_Irregular_Mesh",
+               dict(dim=64, heads=4, dim_head=16, slice_num=32, rotate=45, mlp_ratio=2), B=2, N=1031, seed=10)
+    save_layer("layer_irregular_g64_fresh", "Physics_Attention_Irregular_Mesh",
+               dict(dim=64, heads=8, dim_head=8, slice_num=64, rotate=45, mlp_ratio=1), B=1, N=2050, seed=11,
+               trained=False)
+    save_layer("layer_2d_small", "Physics_Attention_Structured_Mesh_2D",
+               dict(dim=32, heads=4, dim_head=8, slice_num=32, H=17, W=13, rotate=45, mlp_ratio=2), B=2, N=17 * 13,
+               seed=12)
+    save_layer("layer_3d_small", "Physics_Attention_Structured_Mesh_3D",
+               dict(dim=32, heads=4, dim_head=8, slice_num=32, H=6, W=5, D=7, rotate=45, mlp_ratio=2), B=1,
+               N=6 * 5 * 7, seed=13)
+    k = 0
+    for d in (2, 3):
+        for (nt, G) in ((8, 32), (3, 100), (8, 256), (2, 512), (4, 5)):
+            for mode in ("rand", "ties", "pipe"):
+                save_balltree(f"balltree_{k:02d}", d, nt, G, 45.0 if k % 4 else 0.0, mode, 100 + k)
+                k += 1
+    print("balltree goldens:", k)
