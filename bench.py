@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""Benchmark of the HAET layer hot path (BASELINE.json metric: mesh points/sec per HAET layer forward @1M points).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--points P] [--slices G]
+
+A "step" is one PhysicsAttention layer forward (slice -> merge -> ball tree -> Erwin -> deslice + to_out) over
+one synthetic mesh: BASELINE config 4's layer (irregular mesh, 1,000,000 points per GPU, 256 hidden, 8 heads,
+256 slices, Erwin defaults, mlp_ratio 2 as in the reference's velocity-mem-checker).  With N > 1 (torchrun, one
+rank per GPU) the mesh has N x 1M points, point-sharded, with one all-gather of the packed slice state per
+layer (weak scaling).  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+HIDDEN, HEADS, DIM_HEAD, MLP_RATIO, ROTATE = 256, 8, 32, 2, 45
+METRIC = "mesh points/sec per HAET layer fwd"
+UNIT = "points/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf=d["bf16_tflops"], tf_sus=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                    src="measured")
+    return dict(hbm=6650.0, tf=1590.0, tf_sus=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                    str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([c.strip() for c in o.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active")
+                                                         for r in self.rows)]
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ----------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (a port of the reference's PyTorch path; the reference's Python cannot travel to the box)
+# ----------------------------------------------------------------------------------------------------
+def make_module(slices, device=None):
+    import haet_b200 as hb
+    from tests.helpers import trained_like_
+    torch.manual_seed(0)
+    m = hb.Physics_Attention_Irregular_Mesh(HIDDEN, heads=HEADS, dim_head=DIM_HEAD, slice_num=slices, rotate=ROTATE,
+                                            mlp_ratio=MLP_RATIO).eval()
+    trained_like_(m, 1)   # throughput is weight independent; peaky weights exercise the rescale path
+    return m.to(device) if device is not None else m
+
+
+def cpu_layer_time(slices, n_sample, steps, warmup):
+    """Seconds per forward of the oracle layer on n_sample points with all host threads."""
+    from oracle import haet_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    m = make_module(slices)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    x = torch.nn.functional.layer_norm(torch.randn(1, n_sample, HIDDEN, generator=torch.Generator().manual_seed(0)),
+                                       (HIDDEN,))
+    kw = dict(heads=HEADS, dim_head=DIM_HEAD, slice_num=slices, dimensionality=3, rotate=ROTATE, mlp_ratio=MLP_RATIO)
+    ts = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            O.physics_attention_forward(sd, x, **kw)
+            if i >= warmup:
+                ts.append(time.perf_counter() - t0)
+    return sum(ts) / len(ts), torch.get_num_threads()
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_sample = args.cpu_points
+    sec, cores = cpu_layer_time(args.slices, n_sample, args.steps, min(args.warmup, 1))
+    v = n_sample / sec
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": min(args.warmup, 1), "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, cpu=True),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"oracle (CPU restatement of the reference PyTorch layer) on {n_sample} of the "
+                                       f"{args.points} points per step, {args.slices} slices"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, cpu=False):
+    return {"workload": f"HAETransolver_Irregular_Mesh PhysicsAttention layer forward, synthetic mesh, "
+                        f"{args.points} points per GPU, {HIDDEN} hidden, {HEADS} heads, {args.slices} slices "
+                        f"(BASELINE config 4, single layer)",
+            "points_per_gpu": args.points, "slices": args.slices, "hidden": HIDDEN, "heads": HEADS,
+            "mlp_ratio": MLP_RATIO, "parallelism": f"point-sharded x{args.gpus}" if args.gpus > 1 else "single GPU",
+            "l2": "inputs (1 GB of points per step) are larger than the 126 MB L2; no explicit flush",
+            **({"cpu_sample_points": args.cpu_points} if cpu else {})}
+
+
+# ----------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------
+def stage_times(m, x, iters=3):
+    """CUDA-event time of each C-ABI stage of one layer forward (ms, mean of iters) on the current stream."""
+    from haet_b200 import _lib
+    from haet_b200.balltree import balltree_device
+    from haet_b200.erwin import erwin_device
+    l = _lib.lib()
+    B, N, _ = x.shape
+    sh = m._shape(B, N)
+    psh = C.byref(sh)
+    dev = x.device
+    st = torch.cuda.current_stream(dev).cuda_stream
+    H, G, Cc = m.heads, m.slice_num, m.dim_head
+    T = B * H * G
+    wx, bx = m._wx().float(), m.in_project_x.bias.detach()
+    ws, bs = m.in_project_slice.weight.detach().contiguous(), m.in_project_slice.bias.detach()
+    wt, bt = m.ada_temp_linear.weight.detach().view(-1).contiguous(), m._bt()
+    wo, bo = m.to_out[0].weight.detach().contiguous(), m.to_out[0].bias.detach()
+    spill = torch.empty(l.haet_spill_bytes(psh), dtype=torch.uint8, device=dev)
+    work = torch.empty(max(l.haet_slice_workspace_bytes(psh), l.haet_deslice_workspace_bytes(psh)), dtype=torch.uint8,
+                       device=dev)
+    part = torch.empty(l.haet_partial_floats(psh), device=dev)
+    eid = torch.empty(T, Cc, device=dev); lse = torch.empty(T, device=dev); pos = torch.empty(T, 3, device=dev)
+    out = torch.empty(B, N, m.dim, device=dev)
+    acc = {k: 0.0 for k in ("slice_reduce", "slice_merge", "balltree", "erwin", "deslice_out")}
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    for it in range(iters + 1):
+        e = [ev() for _ in range(6)]
+        e[0].record()
+        _lib.check(l.haet_slice_reduce(psh, x.data_ptr(), wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(),
+                                       wt.data_ptr(), bt, spill.data_ptr(), part.data_ptr(), work.data_ptr(), st))
+        e[1].record()
+        _lib.check(l.haet_slice_merge(psh, part.data_ptr(), 1, eid.data_ptr(), lse.data_ptr(), pos.data_ptr(), st))
+        e[2].record()
+        tree_idx, tree_mask, rots = balltree_device(pos, B * H, G, m.erwin.strides, m.erwin.ball_sizes,
+                                                    float(m.erwin.rotate))
+        e[3].record()
+        states = erwin_device(m.erwin, eid, pos, tree_idx, tree_mask, rots)
+        e[4].record()
+        _lib.check(l.haet_deslice_out(psh, spill.data_ptr(), lse.data_ptr(), states.data_ptr(), ws.data_ptr(),
+                                      bs.data_ptr(), wt.data_ptr(), bt, wo.data_ptr(), bo.data_ptr(), out.data_ptr(),
+                                      work.data_ptr(), st))
+        e[5].record()
+        torch.cuda.synchronize()
+        if it == 0:
+            continue   # warm-up
+        for i, k in enumerate(acc):
+            acc[k] += e[i].elapsed_time(e[i + 1]) / iters
+    return acc
+
+
+def roofline_for(stages, args, pk):
+    """Roofline of the dominant stage.  Algorithmic work per point (DESIGN.md "algorithmic work"):
+       slice_reduce: 2*D^2 (in-projection) + 2*D*G (logits) + 2*D*G (W^T x) flop; reads x (4*D B)
+       deslice_out : 2*D*G (W.S') + 2*D^2 (to_out) flop;            writes out (4*D B)
+    (the recomputed logits of pass 2 and the spill traffic are implementation cost, not counted)."""
+    D, G, N = HIDDEN, args.slices, args.points
+    work = {"slice_reduce": (N * (2 * D * D + 4 * D * G), N * 4 * D),
+            "deslice_out": (N * (2 * D * D + 2 * D * G), N * 4 * D)}
+    name = max(("slice_reduce", "deslice_out"), key=lambda k: stages[k])
+    flops, byts = work[name]
+    sec = stages[name] * 1e-3
+    t_tensor, t_hbm = flops / (pk["tf"] * 1e12), byts / (pk["hbm"] * 1e9)
+    if t_tensor >= t_hbm:
+        ach = flops / sec / 1e12
+        r = {"bound": "tensor", "achieved": ach, "peak": pk["tf"], "unit": "TFLOP/s", "frac": ach / pk["tf"]}
+    else:
+        ach = byts / sec / 1e9
+        r = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"]}
+    r.update(kernel=name, kernel_ms=stages[name], peak_source=pk["src"], traffic=None)
+    return r
+
+
+def layer_roofline_ms(args, pk):
+    """t_roof of the whole layer: max(F_alg / P_bf16, Bytes_alg / BW_hbm)."""
+    D, G, N = HIDDEN, args.slices, args.points
+    f = N * (4 * D * D + 6 * D * G + 2 * D)
+    b = N * 8 * D
+    return max(f / (pk["tf"] * 1e12), b / (pk["hbm"] * 1e9)) * 1e3
+
+
+def run_gpu_arm(args):
+    import torch.distributed as dist
+    from haet_b200 import _lib
+    from haet_b200.distributed import init_from_env
+    rank, local, world = init_from_env("nccl")
+    if world != args.gpus:
+        if rank == 0:
+            print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; launch with torchrun", file=sys.stderr)
+        args.gpus = world
+    dev = torch.device("cuda", local)
+    _lib.check(_lib.lib().haet_device_check())
+    m = make_module(args.slices, dev)
+    if world > 1:
+        m.point_group = dist.group.WORLD
+    N = args.points
+    g = torch.Generator(device=dev).manual_seed(rank)
+    x = torch.nn.functional.layer_norm(torch.randn(1, N, HIDDEN, device=dev, generator=g), (HIDDEN,))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        m(x)
+    barrier()
+    lib = _lib.lib()
+    n0 = lib.haet_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        e0.record()
+        for _ in range(args.steps):
+            out = m(x)
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = lib.haet_launch_count() - n0
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+    value = N * world / (ms * 1e-3)
+
+    # ---- end to end through the public module API with HOST buffers (pinned): H2D + forward + D2H per step ----
+    xh = x.cpu().pin_memory()
+    oh = torch.empty_like(xh).pin_memory()
+    def e2e_step():
+        xd = xh.to(dev, non_blocking=True)
+        oh.copy_(m(xd), non_blocking=True)
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    k2 = max(2, min(args.steps, 5))
+    e0.record()
+    for _ in range(k2):
+        e2e_step()
+    e1.record()
+    barrier()
+    ms2 = e0.elapsed_time(e1) / k2
+    if world > 1:
+        t = torch.tensor([ms2], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms2 = float(t)
+    e2e = {"value": N * world / (ms2 * 1e-3), "unit": UNIT, "ms_per_step": ms2,
+           "h2d_bytes_per_step": xh.numel() * 4, "d2h_bytes_per_step": oh.numel() * 4}
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    stages = stage_times(m, x)
+    roof = roofline_for(stages, args, pk)
+    t_roof = layer_roofline_ms(args, pk)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(args), "clocks": clk.summary(), "e2e": e2e,
+            "gpu_launches": int(launches), "roofline": roof,
+            "layer_roofline": {"t_roof_ms": t_roof, "frac": t_roof / ms, "peak_source": pk["src"]},
+            "stages_ms": stages}
+    if world == 1 and not args.no_cpu:
+        sec, cores = cpu_layer_time(args.slices, args.cpu_points, 2, 1)
+        line["cpu_baseline"] = {"value": args.cpu_points / sec, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"oracle (CPU restatement of the reference PyTorch layer) on "
+                                          f"{args.cpu_points} of the {N} points, {args.slices} slices, mean of 2"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="haet_b200", choices=["haet_b200", "reference"])
+    ap.add_argument("--points", type=int, default=1_000_000, help="points per GPU")
+    ap.add_argument("--slices", type=int, default=256)
+    ap.add_argument("--cpu-points", type=int, default=131072, help="bounded CPU sample (points)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,16 @@
+"""haet_b200 -- B200-native (sm_100a) implementation of the HAET per-layer hot path.
+
+Public surface (mirrors the reference's ``models.PhysicsAttention`` and ``balltree`` modules):
+    Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D, Physics_Attention_Structured_Mesh_3D
+    ErwinTransformer, build_balltree_with_rotations, build_balltree, patch_model
+All arithmetic runs in libhaet_b200.so (hand-written CUDA behind the C-ABI of include/haet_b200.h).
+"""
+from ._lib import HaetError, lib  # noqa: F401
+from .balltree import build_balltree, build_balltree_with_rotations  # noqa: F401
+from .erwin import ErwinTransformer  # noqa: F401
+from .physics_attention import (Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D,  # noqa: F401
+                                Physics_Attention_Structured_Mesh_3D, from_reference, patch_model)
+
+__all__ = ["Physics_Attention_Irregular_Mesh", "Physics_Attention_Structured_Mesh_2D",
+           "Physics_Attention_Structured_Mesh_3D", "ErwinTransformer", "build_balltree_with_rotations",
+           "build_balltree", "patch_model", "from_reference", "HaetError", "lib"]

@@ -1,0 +1,201 @@
+// extern "C" entry points of libhaet_b200.so (see include/haet_b200.h).
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace haet {
+
+static thread_local char g_err[512] = "";
+int64_t g_launches = 0;
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static int check_shape(const haet_layer_shape *s) {
+    HAET_CHECK_ARG(s != nullptr, "null shape");
+    HAET_CHECK_ARG(s->B >= 0 && s->N >= 0, "negative B or N");
+    HAET_CHECK_ARG(s->dim > 0 && s->heads > 0 && s->dim_head > 0 && s->slice_num > 0, "non-positive dimension");
+    HAET_CHECK_ARG(s->dim_head == 4 || s->dim_head == 8 || s->dim_head == 16 || s->dim_head == 32 || s->dim_head == 64,
+                   "dim_head %d not supported (4, 8, 16, 32, 64)", s->dim_head);
+    HAET_CHECK_ARG(s->B * s->heads <= 65535, "B*heads > 65535 not supported");
+    HAET_CHECK_ARG(s->dimensionality >= 1 && s->dimensionality <= 3 && s->dimensionality <= s->dim_head,
+                   "dimensionality must be 1..3 and <= dim_head");
+    HAET_CHECK_ARG(s->base_temp > 0.4f, "base_temp must exceed the 0.4 clamp (tau > 0)");
+    HAET_CHECK_ARG(s->epsilon > 0.f && s->epsilon < 1.f, "epsilon must be in (0, 1)");
+    return HAET_OK;
+}
+
+struct Carver {
+    char *p;
+    explicit Carver(void *base) : p((char *)base) {}
+    template <typename T> T *take(int64_t n) {
+        T *r = (T *)p;
+        p += align_up(n * (int64_t)sizeof(T), 256);
+        return r;
+    }
+};
+
+static int64_t deslice_ws_bytes(const haet_layer_shape *s) {
+    return align_up(s->B * s->N * (int64_t)s->heads * s->dim_head * (int64_t)sizeof(float), 256);
+}
+
+struct LayerBuf {
+    void *spill; void *ws; float *partial, *eidetic, *lse2, *pos, *states; int64_t *tree_idx; uint8_t *tree_mask;
+    int64_t *rot[HAET_MAX_LEVELS]; void *erwin_ws; float *xdev, *odev; int64_t slots; int64_t total;
+};
+
+static int carve_layer(const haet_layer_shape *s, const haet_erwin_cfg *c, void *base, bool host_io, LayerBuf &b) {
+    const int64_t T = s->B * s->heads * s->slice_num;
+    b.slots = haet_balltree_slots(s->B * s->heads, s->slice_num);
+    HAET_CHECK_ARG(b.slots >= 0, "slice_num must be >= 2");
+    Carver cv(base);
+    b.spill = cv.take<char>(haet_spill_bytes(s));
+    int64_t w1 = haet_slice_workspace_bytes(s), w2 = deslice_ws_bytes(s);
+    b.ws = cv.take<char>(w1 > w2 ? w1 : w2);
+    b.partial = cv.take<float>(haet_partial_floats(s));
+    b.eidetic = cv.take<float>(T * s->dim_head);
+    b.lse2 = cv.take<float>(T);
+    b.pos = cv.take<float>(T * 3);
+    b.states = cv.take<float>(T * s->dim_head);
+    b.tree_idx = cv.take<int64_t>(b.slots);
+    b.tree_mask = cv.take<uint8_t>(b.slots);
+    for (int i = 0; i < HAET_MAX_LEVELS; ++i) b.rot[i] = i < c->n_levels ? cv.take<int64_t>(b.slots) : nullptr;
+    int64_t ew = haet_erwin_workspace_bytes(c, b.slots);
+    HAET_CHECK_ARG(ew >= 0, "bad erwin config");
+    b.erwin_ws = cv.take<char>(ew);
+    b.xdev = b.odev = nullptr;
+    if (host_io) {
+        b.xdev = cv.take<float>(s->B * s->N * (int64_t)s->dim);
+        b.odev = cv.take<float>(s->B * s->N * (int64_t)s->dim);
+    }
+    b.total = cv.p - (char *)base;
+    return HAET_OK;
+}
+
+}  // namespace haet
+
+using namespace haet;
+
+extern "C" {
+
+int haet_version(void) { return 1; }
+const char *haet_last_error(void) { return g_err; }
+int64_t haet_launch_count(void) { return g_launches; }
+
+int haet_device_check(void) {
+    int dev = 0;
+    cudaDeviceProp p;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&p, dev) != cudaSuccess) {
+        set_error("no CUDA device");
+        return HAET_ENODEV;
+    }
+    if (p.major != 10) {
+        set_error("device %s is sm_%d%d; libhaet_b200 is built for sm_100a only", p.name, p.major, p.minor);
+        return HAET_ENODEV;
+    }
+    return HAET_OK;
+}
+
+int64_t haet_spill_bytes(const haet_layer_shape *s) {
+    return align_up(s->B * s->N * (int64_t)s->heads * s->dim_head * (int64_t)sizeof(float), 256);
+}
+int64_t haet_partial_floats(const haet_layer_shape *s) {
+    return s->B * s->heads * (int64_t)s->slice_num * (s->dim_head + 2);
+}
+int64_t haet_slice_workspace_bytes(const haet_layer_shape *s) {
+    return align_up(slice_chunks(s) * haet_partial_floats(s) * (int64_t)sizeof(float), 256);
+}
+int64_t haet_deslice_workspace_bytes(const haet_layer_shape *s) { return deslice_ws_bytes(s); }
+
+int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *wx_d, const float *bx_d,
+                      const float *ws_d, const float *bs_d, const float *wt_d, float bt, void *spill_d,
+                      float *partial_d, void *workspace_d, void *stream) {
+    int rc = check_shape(s);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *xp = (float *)spill_d;
+    if (s->B == 0) return HAET_OK;
+    HAET_CHECK_ARG(s->N > 0, "a rank needs at least one point (N == 0)");
+    if ((rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st))) return rc;
+    float *parts = (float *)workspace_d;
+    if ((rc = launch_slice_partial(s, xp, ws_d, bs_d, wt_d, bt, parts, st))) return rc;
+    return launch_slice_merge(s, parts, slice_chunks(s), partial_d, nullptr, nullptr, st);
+}
+
+int haet_slice_merge(const haet_layer_shape *s, const float *partials_d, int32_t n_ranks, float *eidetic_d,
+                     float *lse2_d, float *pos_d, void *stream) {
+    int rc = check_shape(s);
+    if (rc) return rc;
+    HAET_CHECK_ARG(n_ranks >= 1, "n_ranks must be >= 1");
+    if (s->B == 0) return HAET_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if ((rc = launch_slice_merge(s, partials_d, n_ranks, nullptr, eidetic_d, lse2_d, st))) return rc;
+    return launch_slice_pos(s, eidetic_d, pos_d, st);
+}
+
+int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float *lse2_d, const float *states_d,
+                     const float *ws_d, const float *bs_d, const float *wt_d, float bt, const float *wo_d,
+                     const float *bo_d, float *out_d, void *workspace_d, void *stream) {
+    int rc = check_shape(s);
+    if (rc) return rc;
+    if (s->B == 0 || s->N == 0) return HAET_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *o = (float *)workspace_d;
+    if ((rc = launch_deslice(s, (const float *)spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st))) return rc;
+    return launch_linear(o, wo_d, bo_d, out_d, s->B * s->N, s->heads * s->dim_head, s->dim, st);
+}
+
+int64_t haet_layer_scratch_bytes(const haet_layer_shape *s, const haet_erwin_cfg *c) {
+    LayerBuf b;
+    if (check_shape(s) || carve_layer(s, c, nullptr, true, b)) return -1;
+    return b.total;
+}
+
+static int layer_forward_impl(const haet_layer_shape *s, const haet_erwin_cfg *c, const haet_layer_weights *w,
+                              const float *x_d, float *out_d, LayerBuf &b, cudaStream_t st) {
+    int rc;
+    if ((rc = haet_slice_reduce(s, x_d, w->wx_d, w->bx_d, w->ws_d, w->bs_d, w->wt_d, w->bt, b.spill, b.partial, b.ws, st))) return rc;
+    if ((rc = haet_slice_merge(s, b.partial, 1, b.eidetic, b.lse2, b.pos, st))) return rc;
+    if (s->B == 0) return HAET_OK;
+    const int64_t T = s->B * s->heads * s->slice_num;
+    if ((rc = haet_balltree_build(b.pos, s->B * s->heads, s->slice_num, s->dimensionality, c->strides, c->ball_sizes,
+                                  c->n_levels, (double)c->rotate, b.tree_idx, b.tree_mask, b.rot, st))) return rc;
+    if ((rc = haet_erwin_forward(c, b.eidetic, b.pos, T, b.tree_idx, b.tree_mask, b.slots, b.rot, w->erwin_d, b.erwin_ws,
+                                 b.states, st))) return rc;
+    return haet_deslice_out(s, b.spill, b.lse2, b.states, w->ws_d, w->bs_d, w->wt_d, w->bt, w->wo_d, w->bo_d, out_d, b.ws, st);
+}
+
+int haet_layer_forward(const haet_layer_shape *s, const haet_erwin_cfg *c, const haet_layer_weights *w,
+                       const float *x_d, float *out_d, void *scratch_d, void *stream) {
+    int rc = check_shape(s);
+    if (rc) return rc;
+    HAET_CHECK_ARG(c->dimensionality == s->dimensionality && c->c_hidden[0] == s->dim_head,
+                   "erwin config does not match the layer (dimensionality / c_hidden[0])");
+    LayerBuf b;
+    if ((rc = carve_layer(s, c, scratch_d, false, b))) return rc;
+    return layer_forward_impl(s, c, w, x_d, out_d, b, (cudaStream_t)stream);
+}
+
+int haet_layer_forward_host(const haet_layer_shape *s, const haet_erwin_cfg *c, const haet_layer_weights *w,
+                            const float *x_h, float *out_h, void *scratch_d, void *stream) {
+    int rc = check_shape(s);
+    if (rc) return rc;
+    HAET_CHECK_ARG(c->dimensionality == s->dimensionality && c->c_hidden[0] == s->dim_head,
+                   "erwin config does not match the layer (dimensionality / c_hidden[0])");
+    LayerBuf b;
+    if ((rc = carve_layer(s, c, scratch_d, true, b))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t bytes = sizeof(float) * (size_t)(s->B * s->N) * s->dim;
+    if (bytes == 0) return HAET_OK;
+    HAET_CUDA(cudaMemcpyAsync(b.xdev, x_h, bytes, cudaMemcpyHostToDevice, st));
+    if ((rc = layer_forward_impl(s, c, w, b.xdev, b.odev, b, st))) return rc;
+    HAET_CUDA(cudaMemcpyAsync(out_h, b.odev, bytes, cudaMemcpyDeviceToHost, st));
+    return HAET_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,368 @@
+// Erwin ball-tree transformer over the slice tokens (eval mode).
+//
+// Reference: models/components/erwinflash/erwin_flash.py:138-195 (forward), components/layers.py:30-32
+// (block), :72-92 (BasicLayer, rotated odd blocks), components/attention.py:35-91 (BallMSA, flash
+// variant: no distance bias, qkv columns laid out (three, head, head_dim)), components/mlp.py:17-18
+// (SwiGLU), components/pooling.py:25-40, 58-72 (BallPooling / BallUnpooling, BatchNorm1d eval).
+//
+// Everything inside one ErwinTransformerBlock is local to a ball (ball_size consecutive tokens of
+// the -- possibly rotated -- sequence), so a block is ONE kernel with one CTA per ball: the ball's
+// tokens are gathered through the permutation into shared memory, RMSNorm -> PE -> qkv -> attention
+// -> proj -> RMSNorm -> SwiGLU all run there, and the result is scattered back in place.
+#include "common.cuh"
+
+namespace haet {
+
+struct BlockW {  // float offsets into the packed weights
+    int norm1, norm2, pe_w, pe_b, qkv_w, qkv_b, proj_w, proj_b, w1, b1, w2, b2, w3, b3;
+};
+struct PoolW { int w, b, scale, shift; };
+
+__device__ __forceinline__ int pad_dim(int n) { return n | 1; }  // odd row stride: conflict-free columns
+
+// out[i][o] (+)= sum_k in[i][k] * W[o][k] + b[o], i < rows; consecutive threads take consecutive rows
+// so W reads are warp-uniform and the smem reads hit distinct banks (odd stride).
+template <bool ACC>
+__device__ void ball_linear(const float *in, int in_ld, const float *__restrict__ W, const float *__restrict__ b,
+                            float *out, int out_ld, int rows, int K, int O) {
+    for (int t = threadIdx.x; t < rows * O; t += blockDim.x) {
+        const int i = t % rows, o = t / rows;
+        const float *wr = W + (size_t)o * K;
+        const float *ir = in + i * in_ld;
+        float acc = b ? b[o] : 0.f;
+        for (int k = 0; k < K; ++k) acc = fmaf(ir[k], __ldg(wr + k), acc);
+        if (ACC) out[i * out_ld + o] += acc; else out[i * out_ld + o] = acc;
+    }
+}
+
+__device__ void ball_rmsnorm(const float *in, int ld, const float *__restrict__ gamma, float *out, int rows, int dim) {
+    // nn.RMSNorm(dim), eps=None -> torch.finfo(float32).eps (layers.py:24-25)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int i = warp; i < rows; i += nw) {
+        float ss = 0.f;
+        for (int k = lane; k < dim; k += 32) { float v = in[i * ld + k]; ss = fmaf(v, v, ss); }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        const float r = rsqrtf(ss / (float)dim + 1.1920928955078125e-07f);
+        for (int k = lane; k < dim; k += 32) out[i * ld + k] = in[i * ld + k] * r * gamma[k];
+    }
+}
+
+__global__ void __launch_bounds__(128) erwin_block_kernel(float *__restrict__ x, const float *__restrict__ pos,
+                                                          const int64_t *__restrict__ perm,
+                                                          const float *__restrict__ wts, BlockW w, int bs, int dim,
+                                                          int heads, int hidden, int d) {
+    extern __shared__ float sm[];
+    const int ld = pad_dim(dim), ldq = pad_dim(3 * dim), ldh = pad_dim(hidden);
+    float *xs = sm;                    // [bs][ld]   residual stream
+    float *us = xs + bs * ld;          // [bs][ld]   normed / attention output
+    float *qkv = us + bs * ld;         // [bs][ldq]
+    float *hid = qkv + bs * ldq;       // [bs][ldh]  (holds w1 branch, then the gated product)
+    float *hid2 = hid + bs * ldh;      // [bs][ldh]
+    float *rel = hid2 + bs * ldh;      // [bs][4]
+    float *cen = rel + bs * 4;         // [4]
+    int *tok = reinterpret_cast<int *>(cen + 4);  // [bs]
+    const int tid = threadIdx.x;
+    const int64_t base = (int64_t)blockIdx.x * bs;
+
+    for (int i = tid; i < bs; i += blockDim.x) tok[i] = perm ? (int)perm[base + i] : (int)(base + i);
+    __syncthreads();
+    for (int t = tid; t < bs * dim; t += blockDim.x) {
+        const int i = t / dim, k = t - i * dim;
+        xs[i * ld + k] = x[(int64_t)tok[i] * dim + k];
+    }
+    for (int t = tid; t < bs * d; t += blockDim.x) {
+        const int i = t / d, j = t - i * d;
+        rel[i * 4 + j] = pos[(int64_t)tok[i] * d + j];
+    }
+    __syncthreads();
+    if (tid < d) {  // ball centre: mean over the ball (attention.py:35-40)
+        float s = 0.f;
+        for (int i = 0; i < bs; ++i) s += rel[i * 4 + tid];
+        cen[tid] = s / (float)bs;
+    }
+    __syncthreads();
+    for (int t = tid; t < bs * d; t += blockDim.x) { const int i = t / d, j = t - i * d; rel[i * 4 + j] -= cen[j]; }
+    ball_rmsnorm(xs, ld, wts + w.norm1, us, bs, dim);
+    __syncthreads();
+    ball_linear<true>(rel, 4, wts + w.pe_w, wts + w.pe_b, us, ld, bs, d, dim);        // x + pe_proj(rel_pos)
+    __syncthreads();
+    ball_linear<false>(us, ld, wts + w.qkv_w, wts + w.qkv_b, qkv, ldq, bs, dim, 3 * dim);
+    __syncthreads();
+    {   // softmax(q k^T / sqrt(hd)) v inside the ball, one (query, head) per thread
+        const int hd = dim / heads;
+        const float scale = rsqrtf((float)hd) * kLog2e;
+        for (int t = tid; t < bs * heads; t += blockDim.x) {
+            const int i = t % bs, h = t / bs;
+            const float *q = qkv + i * ldq + h * hd;
+            float mx = -INFINITY;
+            for (int j = 0; j < bs; ++j) {
+                const float *k = qkv + j * ldq + dim + h * hd;
+                float s = 0.f;
+                for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
+                mx = fmaxf(mx, s * scale);
+            }
+            float *o = us + i * ld + h * hd;
+            for (int c = 0; c < hd; ++c) o[c] = 0.f;
+            float den = 0.f;
+            for (int j = 0; j < bs; ++j) {
+                const float *k = qkv + j * ldq + dim + h * hd;
+                const float *v = qkv + j * ldq + 2 * dim + h * hd;
+                float s = 0.f;
+                for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
+                const float p = exp2f(s * scale - mx);
+                den += p;
+                for (int c = 0; c < hd; ++c) o[c] = fmaf(p, v[c], o[c]);
+            }
+            const float inv = 1.f / den;
+            for (int c = 0; c < hd; ++c) o[c] *= inv;
+        }
+    }
+    __syncthreads();
+    ball_linear<true>(us, ld, wts + w.proj_w, wts + w.proj_b, xs, ld, bs, dim, dim);   // x + BMSA(...)
+    __syncthreads();
+    ball_rmsnorm(xs, ld, wts + w.norm2, us, bs, dim);
+    __syncthreads();
+    ball_linear<false>(us, ld, wts + w.w1, wts + w.b1, hid, ldh, bs, dim, hidden);
+    ball_linear<false>(us, ld, wts + w.w2, wts + w.b2, hid2, ldh, bs, dim, hidden);
+    __syncthreads();
+    for (int t = tid; t < bs * hidden; t += blockDim.x) {   // w2(x) * silu(w1(x))   (mlp.py:17-18)
+        const int i = t / hidden, k = t - i * hidden;
+        const float a = hid[i * ldh + k];
+        hid[i * ldh + k] = hid2[i * ldh + k] * (a / (1.f + __expf(-a)));
+    }
+    __syncthreads();
+    ball_linear<true>(hid, ldh, wts + w.w3, wts + w.b3, xs, ld, bs, hidden, dim);
+    __syncthreads();
+    for (int t = tid; t < bs * dim; t += blockDim.x) {
+        const int i = t / dim, k = t - i * dim;
+        x[(int64_t)tok[i] * dim + k] = xs[i * ld + k];
+    }
+}
+
+static size_t block_smem(int bs, int dim, int hidden) {
+    auto pd = [](int n) { return n | 1; };
+    return sizeof(float) * ((size_t)bs * (2 * pd(dim) + pd(3 * dim) + 2 * pd(hidden)) + bs * 4 + 4) + sizeof(int) * bs;
+}
+
+__global__ void erwin_gather_kernel(const float *__restrict__ x, const float *__restrict__ pos,
+                                    const int64_t *__restrict__ tree_idx, int64_t n_slots, int dim, int d,
+                                    float *__restrict__ x0, float *__restrict__ p0) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int W = dim + d;
+    if (t >= n_slots * W) return;
+    const int64_t i = t / W; const int k = (int)(t - i * W);
+    const int64_t src = tree_idx[i];
+    if (k < dim) x0[i * dim + k] = x[src * dim + k];
+    else p0[i * d + (k - dim)] = pos[src * d + (k - dim)];
+}
+
+// erwin_flash.py:193: x[tree_mask][argsort(tree_idx[tree_mask])]  ==  out[tree_idx[i]] = x[i] where mask[i]
+__global__ void erwin_scatter_kernel(const float *__restrict__ x0, const int64_t *__restrict__ tree_idx,
+                                     const uint8_t *__restrict__ mask, int64_t n_slots, int dim,
+                                     float *__restrict__ out) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_slots * dim) return;
+    const int64_t i = t / dim; const int k = (int)(t - i * dim);
+    if (mask[i]) out[tree_idx[i] * dim + k] = x0[t];
+}
+
+// BallPooling (pooling.py:25-40) with eval BatchNorm folded to scale/shift
+__global__ void erwin_pool_kernel(const float *__restrict__ xc, const float *__restrict__ pc, int64_t n_par, int s,
+                                  int in_dim, int out_dim, int d, const float *__restrict__ wts, PoolW w,
+                                  float *__restrict__ xo, float *__restrict__ po) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_par * out_dim) return;
+    const int64_t n = t / out_dim; const int o = (int)(t - n * out_dim);
+    const int K = s * in_dim + s * d;
+    const float *wr = wts + w.w + (size_t)o * K;
+    float acc = wts[w.b + o];
+    const float *xr = xc + n * s * in_dim;
+    for (int k = 0; k < s * in_dim; ++k) acc = fmaf(xr[k], wr[k], acc);
+    for (int j = 0; j < d; ++j) {
+        float c = 0.f;
+        for (int m = 0; m < s; ++m) c += pc[(n * s + m) * d + j];
+        c = c / (float)s;
+        if (o == 0) po[n * d + j] = c;
+        for (int m = 0; m < s; ++m) acc = fmaf(pc[(n * s + m) * d + j] - c, wr[s * in_dim + m * d + j], acc);
+    }
+    xo[t] = fmaf(acc, wts[w.scale + o], wts[w.shift + o]);
+}
+
+// BallUnpooling (pooling.py:58-72): children.x = BN(children.x + proj([x_parent | rel_children]))
+__global__ void erwin_unpool_kernel(const float *__restrict__ xp, const float *__restrict__ pp, int64_t n_par, int s,
+                                    int in_dim, int out_dim, int d, const float *__restrict__ wts, PoolW w,
+                                    float *__restrict__ xc, const float *__restrict__ pc) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_par * s * out_dim) return;
+    const int64_t tokc = t / out_dim; const int c = (int)(t - tokc * out_dim);
+    const int64_t n = tokc / s; const int m = (int)(tokc - n * s);
+    const int K = in_dim + s * d;
+    const int row = m * out_dim + c;
+    const float *wr = wts + w.w + (size_t)row * K;
+    float acc = wts[w.b + row];
+    const float *xr = xp + n * in_dim;
+    for (int k = 0; k < in_dim; ++k) acc = fmaf(xr[k], wr[k], acc);
+    for (int mm = 0; mm < s; ++mm)
+        for (int j = 0; j < d; ++j)
+            acc = fmaf(pc[(n * s + mm) * d + j] - pp[n * d + j], wr[in_dim + mm * d + j], acc);
+    xc[t] = fmaf(xc[t] + acc, wts[w.scale + c], wts[w.shift + c]);
+}
+
+// ---- host walker: the packed-weight order (mirrored by haet_b200/erwin_pack.py) ------------
+struct Walker {
+    int64_t off = 0;
+    int take(int64_t n) { int64_t o = off; off += (n + 3) / 4 * 4; return (int)o; }
+    BlockW block(int dim, int hidden, int d) {
+        BlockW b;
+        b.norm1 = take(dim); b.norm2 = take(dim);
+        b.pe_w = take((int64_t)dim * d); b.pe_b = take(dim);
+        b.qkv_w = take((int64_t)3 * dim * dim); b.qkv_b = take(3 * dim);
+        b.proj_w = take((int64_t)dim * dim); b.proj_b = take(dim);
+        b.w1 = take((int64_t)hidden * dim); b.b1 = take(hidden);
+        b.w2 = take((int64_t)hidden * dim); b.b2 = take(hidden);
+        b.w3 = take((int64_t)dim * hidden); b.b3 = take(dim);
+        return b;
+    }
+    PoolW pool(int64_t rows, int64_t K, int bn) {
+        PoolW p;
+        p.w = take(rows * K); p.b = take(rows); p.scale = take(bn); p.shift = take(bn);
+        return p;
+    }
+};
+
+static int check_cfg(const haet_erwin_cfg *c) {
+    HAET_CHECK_ARG(c->n_levels >= 1 && c->n_levels <= HAET_MAX_LEVELS, "erwin n_levels out of range");
+    HAET_CHECK_ARG(c->dimensionality >= 1 && c->dimensionality <= 3, "erwin dimensionality must be 1..3");
+    for (int i = 0; i < c->n_levels; ++i) {
+        HAET_CHECK_ARG(c->c_hidden[i] > 0 && c->enc_num_heads[i] > 0 && c->c_hidden[i] % c->enc_num_heads[i] == 0,
+                       "dim must be divisible by num_heads (level %d)", i);
+        HAET_CHECK_ARG(c->ball_sizes[i] > 0 && c->enc_depths[i] >= 0, "bad ball size / depth at level %d", i);
+    }
+    for (int i = 0; i + 1 < c->n_levels; ++i) {
+        HAET_CHECK_ARG(c->strides[i] >= 1, "bad stride at level %d", i);
+        HAET_CHECK_ARG(c->dec_num_heads[i] > 0 && c->c_hidden[i] % c->dec_num_heads[i] == 0,
+                       "dim must be divisible by num_heads (decoder %d)", i);
+    }
+    return HAET_OK;
+}
+
+}  // namespace haet
+
+using namespace haet;
+
+extern "C" int64_t haet_erwin_weight_floats(const haet_erwin_cfg *c) {
+    if (check_cfg(c) != HAET_OK) return -1;
+    Walker wk;
+    const int d = c->dimensionality, L = c->n_levels - 1;
+    for (int i = 0; i < L; ++i) {
+        for (int k = 0; k < c->enc_depths[i]; ++k) wk.block(c->c_hidden[i], c->c_hidden[i] * c->mlp_ratio, d);
+        if (c->strides[i] != 1)  // stride 1: BallPooling is the identity (pooling.py:26-27); its params are unused
+            wk.pool(c->c_hidden[i + 1], (int64_t)c->strides[i] * (c->c_hidden[i] + d), c->c_hidden[i + 1]);
+    }
+    for (int k = 0; k < c->enc_depths[L]; ++k) wk.block(c->c_hidden[L], c->c_hidden[L] * c->mlp_ratio, d);
+    if (c->decode)
+        for (int i = L - 1; i >= 0; --i) {
+            wk.pool((int64_t)c->strides[i] * c->c_hidden[i], c->c_hidden[i + 1] + (int64_t)c->strides[i] * d, c->c_hidden[i]);
+            for (int k = 0; k < c->dec_depths[i]; ++k) wk.block(c->c_hidden[i], c->c_hidden[i] * c->mlp_ratio, d);
+        }
+    return wk.off;
+}
+
+extern "C" int64_t haet_erwin_workspace_bytes(const haet_erwin_cfg *c, int64_t n_slots) {
+    if (check_cfg(c) != HAET_OK) return -1;
+    int64_t fl = 0, n = n_slots;
+    for (int i = 0; i < c->n_levels; ++i) {
+        fl += align_up(n * c->c_hidden[i], 4) + align_up(n * c->dimensionality, 4);
+        if (i + 1 < c->n_levels) n /= c->strides[i];
+    }
+    return fl * (int64_t)sizeof(float);
+}
+
+static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64_t n, int level, int depth, int heads,
+                      const int64_t *rot, const float *wts, Walker &wk, cudaStream_t st) {
+    const int dim = c->c_hidden[level], hidden = dim * c->mlp_ratio, bs = c->ball_sizes[level], d = c->dimensionality;
+    HAET_CHECK_ARG(n % bs == 0, "level %d: %lld tokens are not a multiple of ball size %d", level, (long long)n, bs);
+    const size_t smem = block_smem(bs, dim, hidden);
+    HAET_CHECK_ARG(smem <= 200 * 1024, "ball of %d tokens x dim %d does not fit shared memory", bs, dim);
+    static size_t smem_set = 0;
+    if (smem > 48 * 1024 && smem > smem_set) {
+        HAET_CUDA(cudaFuncSetAttribute(erwin_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set = smem;
+    }
+    const bool rotate = c->rotate > 0 && depth > 1;   // layers.py:74-91
+    for (int k = 0; k < depth; ++k) {
+        BlockW bw = wk.block(dim, hidden, d);
+        const int64_t *perm = (rotate && (k & 1)) ? rot : nullptr;
+        if (rotate && (k & 1)) HAET_CHECK_ARG(rot != nullptr, "tree_idx_rot must be provided for rotation");
+        if (n == 0) continue;
+        erwin_block_kernel<<<(unsigned)(n / bs), 128, smem, st>>>(x, pos, perm, wts, bw, bs, dim, heads, hidden, d);
+        HAET_LAUNCHED();
+    }
+    return HAET_OK;
+}
+
+extern "C" int haet_erwin_forward(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T,
+                                  const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                                  int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
+                                  float *out_d, void *stream) {
+    int rc = check_cfg(c);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int d = c->dimensionality, L = c->n_levels - 1;
+    float *xs[HAET_MAX_LEVELS], *ps[HAET_MAX_LEVELS];
+    int64_t ns[HAET_MAX_LEVELS];
+    {
+        float *p = (float *)workspace_d;
+        int64_t n = n_slots;
+        for (int i = 0; i < c->n_levels; ++i) {
+            ns[i] = n; xs[i] = p; p += align_up(n * c->c_hidden[i], 4); ps[i] = p; p += align_up(n * d, 4);
+            if (i < L) {
+                HAET_CHECK_ARG(n % c->strides[i] == 0, "stride %d does not divide %lld tokens", c->strides[i], (long long)n);
+                n /= c->strides[i];
+            }
+        }
+    }
+    if (n_slots == 0) return HAET_OK;
+    const int dim0 = c->c_hidden[0];
+    {
+        const int64_t tot = n_slots * (dim0 + d);
+        erwin_gather_kernel<<<(unsigned)cdiv(tot, 256), 256, 0, st>>>(x_d, pos_d, tree_idx_d, n_slots, dim0, d, xs[0], ps[0]);
+        HAET_LAUNCHED();
+    }
+    Walker wk;
+    auto rot = [&](int i) -> const int64_t * { return (c->rotate > 0 && rot_idx_d) ? rot_idx_d[i] : nullptr; };
+    for (int i = 0; i < L; ++i) {   // encoder (erwin_flash.py:183-185)
+        rc = run_blocks(c, xs[i], ps[i], ns[i], i, c->enc_depths[i], c->enc_num_heads[i], rot(i), weights_d, wk, st);
+        if (rc) return rc;
+        const int s = c->strides[i];
+        if (s != 1) {
+            PoolW pw = wk.pool(c->c_hidden[i + 1], (int64_t)s * (c->c_hidden[i] + d), c->c_hidden[i + 1]);
+            const int64_t tot = ns[i + 1] * c->c_hidden[i + 1];
+            erwin_pool_kernel<<<(unsigned)cdiv(tot, 128), 128, 0, st>>>(xs[i], ps[i], ns[i + 1], s, c->c_hidden[i],
+                                                                       c->c_hidden[i + 1], d, weights_d, pw, xs[i + 1], ps[i + 1]);
+            HAET_LAUNCHED();
+        } else {
+            HAET_CHECK_ARG(c->c_hidden[i] == c->c_hidden[i + 1], "stride 1 needs equal dims");
+            HAET_CUDA(cudaMemcpyAsync(xs[i + 1], xs[i], sizeof(float) * ns[i] * c->c_hidden[i], cudaMemcpyDeviceToDevice, st));
+            HAET_CUDA(cudaMemcpyAsync(ps[i + 1], ps[i], sizeof(float) * ns[i] * d, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    rc = run_blocks(c, xs[L], ps[L], ns[L], L, c->enc_depths[L], c->enc_num_heads[L], rot(L), weights_d, wk, st);
+    if (rc) return rc;
+    HAET_CHECK_ARG(c->decode, "decode=False is not used by the HAET layer (the deslice needs token-level states)");
+    for (int i = L - 1; i >= 0; --i) {   // decoder (erwin_flash.py:190-192)
+        const int s = c->strides[i];
+        PoolW pw = wk.pool((int64_t)s * c->c_hidden[i], c->c_hidden[i + 1] + (int64_t)s * d, c->c_hidden[i]);
+        const int64_t tot = ns[i + 1] * s * c->c_hidden[i];
+        erwin_unpool_kernel<<<(unsigned)cdiv(tot, 128), 128, 0, st>>>(xs[i + 1], ps[i + 1], ns[i + 1], s, c->c_hidden[i + 1],
+                                                                     c->c_hidden[i], d, weights_d, pw, xs[i], ps[i]);
+        HAET_LAUNCHED();
+        rc = run_blocks(c, xs[i], ps[i], ns[i], i, c->dec_depths[i], c->dec_num_heads[i], rot(i), weights_d, wk, st);
+        if (rc) return rc;
+    }
+    (void)T;
+    erwin_scatter_kernel<<<(unsigned)cdiv(n_slots * dim0, 256), 256, 0, st>>>(xs[0], tree_idx_d, tree_mask_d, n_slots, dim0, out_d);
+    HAET_LAUNCHED();
+    return HAET_OK;
+}

@@ -1,0 +1,168 @@
+/*
+ * haet_b200.h -- C-ABI of the B200-native HAET layer hot path (libhaet_b200.so).
+ *
+ * Plain pointers and sizes only: no torch types.  Every pointer named *_d is a
+ * DEVICE pointer on the current CUDA device; `stream` is a cudaStream_t passed
+ * as void*.  All entry points only enqueue work on `stream` (no host sync, CUDA
+ * graph capturable) and return 0 on success or a negative HAET_E* code;
+ * haet_last_error() gives the message.  The caller owns every buffer; inputs
+ * are never written.  There is no CPU fallback: without an sm_100 device the
+ * calls fail with HAET_ENODEV.
+ *
+ * Which reference interface each entry point replaces (paths relative to
+ * /root/reference, the pedrocurvo/HAET checkout):
+ *
+ *   haet_slice_reduce      models/PhysicsAttention/IrregularMesh.py:157-188
+ *                          (in_project_x, Ada-Temp, Rep-Slice softmax over the
+ *                          N points, W^T x), conv front-ends of
+ *                          StructuredMesh2D.py:173-189 / StructuredMesh3D.py:177-193
+ *   haet_slice_merge       IrregularMesh.py:177-209 (mass normalisation, eidetic
+ *                          states, slice positions) + the cross-rank merge of the
+ *                          point-sharded multi-GPU layout (new)
+ *   haet_balltree_build    models/components/balltree/balltree.pyx:598-662
+ *                          build_balltree_with_rotations (and balltree.h)
+ *   haet_erwin_forward     models/components/erwinflash/erwin_flash.py:138-195
+ *                          (+ components/{layers,attention,mlp,pooling}.py)
+ *   haet_deslice_out       IrregularMesh.py:221-235 (deslice W.S' + to_out)
+ *   haet_layer_forward_host  the whole Physics_Attention_*.forward
+ *                          (IrregularMesh.py:141-235) on HOST buffers
+ */
+#ifndef HAET_B200_H
+#define HAET_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HAET_OK 0
+#define HAET_EINVAL (-1)  /* bad argument (the reference raises ValueError / AssertionError) */
+#define HAET_ECUDA (-2)   /* a CUDA call failed */
+#define HAET_ENODEV (-3)  /* no sm_100 device */
+#define HAET_ENOSUP (-4)  /* shape outside what the kernels support */
+
+#define HAET_MAX_LEVELS 8
+
+/* Shape of one PhysicsAttention layer (IrregularMesh.py:41-63 constructor arguments). */
+typedef struct haet_layer_shape {
+    int64_t B;          /* batch */
+    int64_t N;          /* points per batch item (H*W[*D] for structured meshes) */
+    int32_t dim;        /* input/output channels (n_hidden) */
+    int32_t heads;      /* H */
+    int32_t dim_head;   /* C; inner_dim = heads*dim_head */
+    int32_t slice_num;  /* G */
+    int32_t conv_nd;    /* 0: Linear in_project_x; 2: Conv2d; 3: Conv3d (kernel k, pad k/2) */
+    int32_t grid[3];    /* structured grid extents (H, W, D); unused when conv_nd == 0 */
+    int32_t kernel;     /* conv kernel size (3) */
+    int32_t dimensionality; /* 3 irregular/3D, 2 for 2D: #channels used as slice positions */
+    float base_temp;    /* 0.5 */
+    float epsilon;      /* 1e-6 */
+} haet_layer_shape;
+
+/* Hyper-parameters of the Erwin transformer over the slice tokens
+ * (erwin_flash.py:42-58 constructor arguments; embed=False, mp_steps=0). */
+typedef struct haet_erwin_cfg {
+    int32_t n_levels;                    /* len(ball_sizes) = encoder levels + bottleneck */
+    int32_t c_hidden[HAET_MAX_LEVELS];
+    int32_t ball_sizes[HAET_MAX_LEVELS];
+    int32_t enc_num_heads[HAET_MAX_LEVELS];
+    int32_t enc_depths[HAET_MAX_LEVELS];
+    int32_t dec_num_heads[HAET_MAX_LEVELS]; /* n_levels-1 entries */
+    int32_t dec_depths[HAET_MAX_LEVELS];
+    int32_t strides[HAET_MAX_LEVELS];
+    float rotate;                        /* rotation angle in degrees; > 0 enables the rotated permutation */
+    int32_t decode;
+    int32_t mlp_ratio;
+    int32_t dimensionality;
+} haet_erwin_cfg;
+
+int haet_version(void);
+const char *haet_last_error(void);
+/* 0 when the current device is sm_100 and the kernels can run, else HAET_ENODEV. */
+int haet_device_check(void);
+
+/* ---- sizes of the caller-allocated buffers ---------------------------------------- */
+/* bytes of the opaque per-point spill written by haet_slice_reduce and read by haet_deslice_out */
+int64_t haet_spill_bytes(const haet_layer_shape *s);
+/* bytes of scratch haet_slice_reduce / haet_deslice_out need */
+int64_t haet_slice_workspace_bytes(const haet_layer_shape *s);
+int64_t haet_deslice_workspace_bytes(const haet_layer_shape *s);
+/* floats in one packed rank-partial slice state: B*heads*G*(C+2)  [(m2, l, S[C]) per slice] */
+int64_t haet_partial_floats(const haet_layer_shape *s);
+/* number of floats of the packed Erwin weights / of its scratch, for T input tokens */
+int64_t haet_erwin_weight_floats(const haet_erwin_cfg *c);
+int64_t haet_erwin_workspace_bytes(const haet_erwin_cfg *c, int64_t n_slots);
+/* slots of the main ball tree for n_trees trees of pts points each (2^ceil(log2 pts) each) */
+int64_t haet_balltree_slots(int64_t n_trees, int64_t pts);
+
+/* ---- slicing (pass 1 over the points) ---------------------------------------------
+ * x_d      [B, N, dim] fp32
+ * wx_d     Linear: [inner, dim];  conv: [inner, taps, dim] (taps = k^nd, tap-major repack of
+ *          the torch [inner, dim, k, k(, k)] weight -- done once by the host module)
+ * ws_d     in_project_slice.weight [G, C];  bs_d [G];  wt_d ada_temp_linear.weight [C]; bt scalar
+ * spill_d  haet_spill_bytes() bytes (projected points kept for the deslice pass)
+ * partial_d haet_partial_floats() floats: this rank's un-normalised slice state in the
+ *          base-2 log domain: m2 = max_n z*log2e, l = sum_n 2^(z2-m2), S = sum_n 2^(z2-m2) x_proj
+ */
+int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *wx_d, const float *bx_d,
+                      const float *ws_d, const float *bs_d, const float *wt_d, float bt,
+                      void *spill_d, float *partial_d, void *workspace_d, void *stream);
+
+/* Merge R packed rank-partials (rank-major, fixed order => bit-reproducible on every rank) into
+ *   eidetic_d [B*heads*G, C]  = (S/l)/(1+1e-5)          (IrregularMesh.py:181-188; sum_n W == 1)
+ *   lse2_d    [B*heads*G]     = m2 + log2(l)            (global softmax normaliser, base 2)
+ *   pos_d     [B*heads*G, dimensionality]               (IrregularMesh.py:204-209)
+ */
+int haet_slice_merge(const haet_layer_shape *s, const float *partials_d, int32_t n_ranks,
+                     float *eidetic_d, float *lse2_d, float *pos_d, void *stream);
+
+/* ---- ball tree (balltree.pyx:598-662) ----------------------------------------------
+ * pos_d [n_trees*pts, d] fp32; every tree has `pts` >= 2 consecutive rows (batch_idx = row / pts).
+ * tree_idx_d int64[slots], tree_mask_d uint8[slots]; rot_idx_d[i] int64[slots / prod(strides[:i])]
+ * for i < n_levels (ignored when angle_deg <= 0); rot_idx_d itself is a HOST array of n_levels
+ * device pointers.  Bit-exact with the reference extension,
+ * including the element order std::nth_element leaves behind. */
+int haet_balltree_build(const float *pos_d, int64_t n_trees, int64_t pts, int32_t d,
+                        const int32_t *strides, const int32_t *ball_sizes, int32_t n_levels,
+                        double angle_deg, int64_t *tree_idx_d, uint8_t *tree_mask_d,
+                        int64_t *const *rot_idx_d, void *stream);
+
+/* ---- Erwin over the slice tokens (erwin_flash.py:138-195, eval-mode BatchNorm) -------
+ * x_d [T, c_hidden[0]], pos_d [T, d]; tree from haet_balltree_build (n_slots entries);
+ * weights_d: packed fp32 parameters in the order documented in haet_b200/erwin_pack.py;
+ * out_d [T, c_hidden[0]] in the original token order (erwin_flash.py:193). */
+int haet_erwin_forward(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T,
+                       const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                       int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
+                       float *out_d, void *stream);
+
+/* ---- deslice + to_out (pass 2 over the points) -------------------------------------
+ * states_d [B*heads*G, C] = Erwin output; lse2_d from haet_slice_merge; out_d [B, N, dim]. */
+int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float *lse2_d,
+                     const float *states_d, const float *ws_d, const float *bs_d, const float *wt_d,
+                     float bt, const float *wo_d, const float *bo_d, float *out_d,
+                     void *workspace_d, void *stream);
+
+/* ---- whole layer on HOST buffers (copies inside) ------------------------------------
+ * The call a non-torch host (C, C++, ctypes) makes: x_h / out_h are host pointers (pinned for
+ * full speed); weights are device pointers prepared once.  Allocates nothing: scratch_d must
+ * hold haet_layer_scratch_bytes() bytes. */
+typedef struct haet_layer_weights {
+    const float *wx_d, *bx_d, *ws_d, *bs_d, *wt_d, *wo_d, *bo_d, *erwin_d;
+    float bt;
+} haet_layer_weights;
+int64_t haet_layer_scratch_bytes(const haet_layer_shape *s, const haet_erwin_cfg *c);
+int haet_layer_forward_host(const haet_layer_shape *s, const haet_erwin_cfg *c, const haet_layer_weights *w,
+                            const float *x_h, float *out_h, void *scratch_d, void *stream);
+/* Same with device x/out (what the torch module calls when it does not need the stages). */
+int haet_layer_forward(const haet_layer_shape *s, const haet_erwin_cfg *c, const haet_layer_weights *w,
+                       const float *x_d, float *out_d, void *scratch_d, void *stream);
+
+/* number of kernels launched by this library since load (bench.py's gpu_launches) */
+int64_t haet_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HAET_B200_H */

@@ -1,0 +1,352 @@
+"""GPU parity tests: the CUDA path (through the drop-in modules / the C-ABI) against the oracle and the
+golden vectors made from the unmodified reference.  Tolerances: bit-exact for tree indices; rel-L2 <= 1e-3
+for floating point (north_star: "within 1e-3 relative error"), most stages are far tighter and say so."""
+import ctypes as C
+import itertools
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import haet_oracle as O
+from tests.helpers import balltree_goldens, load_layer_golden, oracle_kwargs, rel_l2, trained_like_
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-3          # the north_star tolerance for layer outputs
+TOL_FP32 = 2e-5     # what the exact-fp32 stages are held to
+
+LAYERS = ["layer_irregular_small", "layer_irregular_g64_fresh", "layer_2d_small", "layer_3d_small"]
+
+
+def _module(name):
+    import haet_b200 as hb
+    cfg, sd, x, out = load_layer_golden(name)
+    m = getattr(hb, cfg["cls"])(**cfg["kwargs"])
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda().eval()
+    m.keep_taps = True
+    return cfg, sd, x, out, m
+
+
+# ------------------------------------------------------------------------------------------------
+# ball tree: bit-exact
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("path", balltree_goldens())
+def test_balltree_golden_bit_exact(path):
+    import haet_b200 as hb
+    z = np.load(path)
+    nt, G = int(z["n_trees"]), int(z["G"])
+    pos = torch.from_numpy(z["pos"]).cuda()
+    bidx = torch.arange(nt).repeat_interleave(G).cuda()
+    ti, tm, rots = hb.build_balltree_with_rotations(pos, bidx, z["strides"].tolist(), z["ball_sizes"].tolist(),
+                                                    float(z["angle"]))
+    assert ti.dtype == torch.int64 and tm.dtype == torch.bool and ti.is_cuda
+    assert np.array_equal(ti.cpu().numpy(), z["tree_idx"])
+    assert np.array_equal(tm.cpu().numpy(), z["tree_mask"])
+    for i, r in enumerate(rots):
+        if float(z["angle"]) > 0:
+            assert np.array_equal(r.cpu().numpy(), z[f"rot{i}"]), f"level {i}"
+        else:
+            assert r is None
+
+
+@pytest.mark.parametrize("d,nt,G", list(itertools.product([2, 3], [1, 8, 32], [2, 3, 7, 32, 64, 100, 256, 512, 1000])))
+def test_balltree_vs_oracle_bit_exact(d, nt, G):
+    from haet_b200.balltree import balltree_device
+    g = torch.Generator().manual_seed(d * 7919 + nt * 31 + G)
+    for angle, mode in itertools.product([0.0, 45.0, 30.0], ["rand", "ties", "sorted"]):
+        T = nt * G
+        if mode == "rand":
+            pos = torch.rand(T, d, generator=g)
+        elif mode == "ties":
+            pos = torch.randint(0, 4, (T, d), generator=g).float() / 4
+        else:
+            pos = (torch.arange(T).float() % G / G)[:, None].repeat(1, d).contiguous()
+        bidx = torch.arange(nt).repeat_interleave(G)
+        balls = [min(32, G), min(16, max(G // 2, 1))]
+        want = O.balltree_build_with_rotations(pos, bidx, [2], balls, angle)
+        got = balltree_device(pos.cuda(), nt, G, [2], balls, angle)
+        assert torch.equal(got[0].cpu(), want[0]) and torch.equal(got[1].cpu(), want[1]), (angle, mode)
+        for a, b in zip(got[2], want[2]):
+            assert (a is None and b is None) or torch.equal(a.cpu(), b), (angle, mode)
+
+
+def test_balltree_three_levels_and_errors():
+    from haet_b200.balltree import balltree_device
+    import haet_b200 as hb
+    g = torch.Generator().manual_seed(5)
+    pos = torch.rand(4 * 128, 3, generator=g)
+    bidx = torch.arange(4).repeat_interleave(128)
+    want = O.balltree_build_with_rotations(pos, bidx, [2, 2], [32, 16, 8], 45.0)
+    got = balltree_device(pos.cuda(), 4, 128, [2, 2], [32, 16, 8], 45.0)
+    assert torch.equal(got[0].cpu(), want[0])
+    for a, b in zip(got[2], want[2]):
+        assert torch.equal(a.cpu(), b)
+    with pytest.raises(ValueError):
+        hb.build_balltree_with_rotations(pos.cuda(), (bidx + 1).cuda(), [2], [32, 16], 45.0)   # must start at 0
+    with pytest.raises(ValueError):
+        balltree_device(pos[:4].cuda(), 4, 1, [2], [32, 16], 45.0)                                  # < 2 points
+    with pytest.raises(AssertionError):
+        balltree_device(pos.cuda(), 4, 128, [2, 2], [32, 16], 45.0)                                 # list lengths
+
+
+# ------------------------------------------------------------------------------------------------
+# stages of the layer against the oracle's taps
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", LAYERS)
+def test_slice_state_matches_oracle(name):
+    cfg, sd, x, out, m = _module(name)
+    taps = {}
+    O.physics_attention_forward(sd, x, taps=taps, **oracle_kwargs(cfg))
+    m(x.cuda())
+    got = m.last_taps
+    assert rel_l2(got["S"], taps["S"]) < TOL_FP32
+    assert rel_l2(got["pos"], taps["pos"]) < 1e-4
+    # global softmax normaliser: lse2 = log2 sum_n exp(z)
+    if "W" in taps:
+        B, H, N, G = taps["W"].shape
+        own, _ = O.split_state_dict(sd)
+        kw = oracle_kwargs(cfg)
+        xp = O.in_project(own, x.float(), kw["heads"], kw["dim_head"], kw.get("grid"))
+        tau = 0.5 + torch.nn.functional.linear(xp, own["ada_temp_linear.weight"], own["ada_temp_linear.bias"]).clamp(-0.4, 0.4)
+        c = torch.log(-torch.log(torch.tensor(1e-6)))
+        z = (torch.nn.functional.linear(xp.double(), own["in_project_slice.weight"].double(),
+                                        own["in_project_slice.bias"].double()) - c.double()) / tau.double()
+        lse2 = torch.logsumexp(z, dim=2) / np.log(2.0)
+        assert float((got["lse2"].cpu().double() - lse2).abs().max()) < 1e-3
+
+
+@pytest.mark.parametrize("name", LAYERS)
+def test_erwin_stage_matches_oracle_given_same_tree(name):
+    cfg, sd, x, out, m = _module(name)
+    m(x.cuda())
+    t = m.last_taps
+    _, erw = O.split_state_dict(sd)
+    kw = oracle_kwargs(cfg)
+    ecfg = O.default_erwin_cfg(kw["heads"], kw["dim_head"], kw["slice_num"], kw["dimensionality"],
+                               rotate=kw["rotate"], mlp_ratio=kw["mlp_ratio"])
+    S_flat = t["S"].reshape(-1, kw["dim_head"]).cpu()
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    bidx = torch.arange(S_flat.shape[0] // kw["slice_num"]).repeat_interleave(kw["slice_num"])
+    want = O.erwin_forward(erw, ecfg, S_flat, t["pos"].cpu(), bidx, tree=tree)
+    assert rel_l2(t["S_out"], want) < 5e-5
+    # and the device tree is what the oracle builds from the device positions (bit-exact)
+    otree = O.balltree_build_with_rotations(t["pos"].cpu(), bidx, ecfg["strides"], ecfg["ball_sizes"], ecfg["rotate"])
+    assert torch.equal(otree[0], tree[0]) and torch.equal(otree[1], tree[1])
+    for a, b in zip(otree[2], tree[2]):
+        assert (a is None and b is None) or torch.equal(a, b)
+
+
+# ------------------------------------------------------------------------------------------------
+# whole layer
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", LAYERS)
+def test_layer_matches_reference_golden(name):
+    """Output vs the unmodified reference's output on the same inputs and weights."""
+    cfg, sd, x, out, m = _module(name)
+    got = m(x.cuda())
+    assert got.shape == out.shape and got.dtype == torch.float32
+    # feeding the oracle the device's positions removes the only discontinuity (a near-tie median flipping a
+    # tree split, SURVEY 7.3 hard part 2); against the golden itself the same bound must hold when no split flips
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    want = O.physics_attention_forward(sd, x, tree=tree, pos_override=t["pos"].cpu(), **oracle_kwargs(cfg))
+    assert rel_l2(got, want) < TOL
+    taps = {}
+    O.physics_attention_forward(sd, x, taps=taps, **oracle_kwargs(cfg))
+    if torch.equal(taps["tree_idx"], tree[0]) and all(
+            (a is None and b is None) or torch.equal(a, b) for a, b in zip(taps["rot_idx"], tree[2])):
+        assert rel_l2(got, out) < TOL
+
+
+def test_layer_deterministic_and_noncontiguous_input():
+    cfg, sd, x, out, m = _module("layer_irregular_small")
+    a = m(x.cuda())
+    b = m(x.cuda())
+    assert torch.equal(a, b)
+    xt = x.cuda().transpose(0, 1).contiguous().transpose(0, 1)   # non-contiguous view
+    assert torch.equal(m(xt), a)
+
+
+@pytest.mark.parametrize("variant,B,N,kw", [
+    ("Physics_Attention_Irregular_Mesh", 1, 4099, dict(dim=256, heads=8, dim_head=32, slice_num=32, rotate=45, mlp_ratio=2)),
+    ("Physics_Attention_Irregular_Mesh", 2, 1500, dict(dim=128, heads=8, dim_head=16, slice_num=100, rotate=45, mlp_ratio=2)),
+    ("Physics_Attention_Irregular_Mesh", 1, 3000, dict(dim=256, heads=8, dim_head=32, slice_num=512, rotate=45, mlp_ratio=1)),
+    ("Physics_Attention_Irregular_Mesh", 1, 777, dict(dim=128, heads=2, dim_head=64, slice_num=64, rotate=0, mlp_ratio=4)),
+    ("Physics_Attention_Structured_Mesh_2D", 4, 85 * 85, dict(dim=128, heads=8, dim_head=16, slice_num=64, H=85, W=85, rotate=45, mlp_ratio=1)),
+    ("Physics_Attention_Structured_Mesh_3D", 1, 16 * 12 * 10, dict(dim=64, heads=8, dim_head=8, slice_num=64, H=16, W=12, D=10, rotate=45, mlp_ratio=2)),
+])
+def test_layer_matches_oracle_trained_like(variant, B, N, kw):
+    """Bigger / odd shapes (N not tile aligned, non power-of-two slice_num, 512 slices, rotate off, BASELINE
+    config 2's Darcy grid) with trained-like weights (peaky softmax, tau in both clamps)."""
+    import haet_b200 as hb
+    torch.manual_seed(N)
+    m = getattr(hb, variant)(**kw).eval()
+    trained_like_(m, N + 1)
+    x = torch.nn.functional.layer_norm(torch.randn(B, N, kw["dim"]), (kw["dim"],))
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    m = m.cuda()
+    m.keep_taps = True
+    got = m(x.cuda())
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    okw = dict(heads=kw["heads"], dim_head=kw["dim_head"], slice_num=kw["slice_num"], rotate=kw["rotate"],
+               mlp_ratio=kw["mlp_ratio"], dimensionality=2 if variant.endswith("2D") else 3)
+    if variant.endswith("2D"):
+        okw["grid"] = (kw["H"], kw["W"])
+    if variant.endswith("3D"):
+        okw["grid"] = (kw["H"], kw["W"], kw["D"])
+    taps = {}
+    want = O.physics_attention_forward(sd, x, tree=tree, pos_override=t["pos"].cpu(), taps=taps, **okw)
+    assert rel_l2(t["S"], taps["S"]) < TOL
+    assert rel_l2(got, want) < TOL
+
+
+def test_errors_are_loud():
+    import haet_b200 as hb
+    m = hb.Physics_Attention_Irregular_Mesh(64, heads=4, dim_head=16, slice_num=32, rotate=45)
+    with pytest.raises(hb.HaetError):
+        m.eval()(torch.randn(1, 10, 64))                 # CPU tensor: no fallback
+    m = m.cuda()
+    with pytest.raises(NotImplementedError):
+        m.train()(torch.randn(1, 100, 64).cuda())        # train-mode BatchNorm statistics
+    with pytest.raises(ValueError):
+        m.eval()(torch.randn(1, 100, 32).cuda())         # wrong channel count
+    with pytest.raises(NotImplementedError):
+        hb.ErwinTransformer(16, [16, 32], [32, 16], [2, 4], [2, 2], [2], [2], [2], 45, embed=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# C-ABI on host buffers, point sharding, full-size properties
+# ------------------------------------------------------------------------------------------------
+def _host_layer_call(m, x_host):
+    from haet_b200 import _lib
+    l = _lib.lib()
+    B, N, dim = x_host.shape
+    sh = m._shape(B, N)
+    dev = torch.device("cuda")
+    keep = [m._wx().float(), m.in_project_x.bias.detach().float(), m.in_project_slice.weight.detach().float().contiguous(),
+            m.in_project_slice.bias.detach().float(), m.ada_temp_linear.weight.detach().float().view(-1).contiguous(),
+            m.to_out[0].weight.detach().float().contiguous(), m.to_out[0].bias.detach().float(),
+            m.erwin.packed_weights(dev)]
+    w = _lib.LayerWeights(*[t.data_ptr() for t in keep], m._bt())
+    nbytes = l.haet_layer_scratch_bytes(C.byref(sh), C.byref(m.erwin.cfg))
+    assert nbytes > 0
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    out = torch.empty_like(x_host).pin_memory()
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(l.haet_layer_forward_host(C.byref(sh), C.byref(m.erwin.cfg), C.byref(w), x_host.data_ptr(),
+                                         out.data_ptr(), scratch.data_ptr(), st))
+    torch.cuda.synchronize()
+    return out
+
+
+@pytest.mark.parametrize("name", ["layer_irregular_small", "layer_2d_small"])
+def test_c_abi_host_call_equals_module(name):
+    cfg, sd, x, out, m = _module(name)
+    want = m(x.cuda()).cpu()
+    got = _host_layer_call(m, x.contiguous().pin_memory())
+    assert torch.equal(got, want)
+
+
+def test_point_sharded_equals_single(monkeypatch):
+    """R rank-partials merged in rank order == one rank over all points (emulated on one GPU: the ranks'
+    slice_reduce calls run back to back and their packed partials are concatenated rank-major, exactly what
+    all_gather_into_tensor produces)."""
+    from haet_b200 import _lib
+    cfg, sd, x, out, m = _module("layer_irregular_small")
+    l = _lib.lib()
+    xg = x.cuda()
+    B, N, dim = xg.shape
+    m(xg)
+    full = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in m.last_taps.items()}
+    st = torch.cuda.current_stream().cuda_stream
+    wx, bx = m._wx().float(), m.in_project_x.bias.detach()
+    ws, bs = m.in_project_slice.weight.detach().contiguous(), m.in_project_slice.bias.detach()
+    wt, bt = m.ada_temp_linear.weight.detach().view(-1).contiguous(), m._bt()
+    for R in (2, 3):
+        parts = []
+        bounds = [N * r // R for r in range(R + 1)]
+        for r in range(R):
+            xs = xg[:, bounds[r]:bounds[r + 1]].contiguous()
+            sh = m._shape(B, xs.shape[1])
+            spill = torch.empty(l.haet_spill_bytes(C.byref(sh)), dtype=torch.uint8, device="cuda")
+            work = torch.empty(l.haet_slice_workspace_bytes(C.byref(sh)), dtype=torch.uint8, device="cuda")
+            part = torch.empty(l.haet_partial_floats(C.byref(sh)), device="cuda")
+            _lib.check(l.haet_slice_reduce(C.byref(sh), xs.data_ptr(), wx.data_ptr(), bx.data_ptr(), ws.data_ptr(),
+                                           bs.data_ptr(), wt.data_ptr(), bt, spill.data_ptr(), part.data_ptr(),
+                                           work.data_ptr(), st))
+            parts.append(part)
+        allp = torch.cat(parts)
+        sh = m._shape(B, N)
+        T = B * m.heads * m.slice_num
+        eid = torch.empty(T, m.dim_head, device="cuda")
+        lse = torch.empty(T, device="cuda")
+        pos = torch.empty(T, 3, device="cuda")
+        _lib.check(l.haet_slice_merge(C.byref(sh), allp.data_ptr(), R, eid.data_ptr(), lse.data_ptr(), pos.data_ptr(), st))
+        assert rel_l2(eid, full["S"].reshape(T, -1)) < 1e-5
+        assert float((lse - full["lse2"].reshape(-1)).abs().max()) < 1e-4
+
+
+@pytest.mark.parametrize("N,G", [(1_000_000, 256)])
+def test_full_size_properties(N, G):
+    """BASELINE config 4 shape (1M points, 256 hidden, 8 heads, 256 slices): size-independent properties.
+       (1) sum_n W[n, g] = 1  =>  sum_n deslice(states)[n, h, :] = sum_g states[h, g, :]   (to_out = identity)
+       (2) deslice is linear in the states
+       (3) the eidetic states are convex combinations of the projected points: inside their min/max box
+       (4) two runs are bitwise identical"""
+    import haet_b200 as hb
+    from haet_b200 import _lib
+    torch.manual_seed(0)
+    m = hb.Physics_Attention_Irregular_Mesh(256, heads=8, dim_head=32, slice_num=G, rotate=45, mlp_ratio=2).eval()
+    trained_like_(m, 3)
+    with torch.no_grad():
+        m.to_out[0].weight.copy_(torch.eye(256))
+        m.to_out[0].bias.zero_()
+    m = m.cuda()
+    m.keep_taps = True
+    x = torch.nn.functional.layer_norm(torch.randn(1, N, 256, device="cuda"), (256,))
+    out1 = m(x)
+    S = m.last_taps["S"].clone()
+    out2 = m(x)
+    assert torch.equal(out1, out2)
+    assert torch.isfinite(out1).all()
+    l = _lib.lib()
+    sh = m._shape(1, N)
+    st = torch.cuda.current_stream().cuda_stream
+    # re-run the two passes by hand to get at the spill and feed chosen states
+    spill = torch.empty(l.haet_spill_bytes(C.byref(sh)), dtype=torch.uint8, device="cuda")
+    work = torch.empty(max(l.haet_slice_workspace_bytes(C.byref(sh)), l.haet_deslice_workspace_bytes(C.byref(sh))),
+                       dtype=torch.uint8, device="cuda")
+    part = torch.empty(l.haet_partial_floats(C.byref(sh)), device="cuda")
+    wx, bx = m._wx().float(), m.in_project_x.bias.detach()
+    ws, bs = m.in_project_slice.weight.detach().contiguous(), m.in_project_slice.bias.detach()
+    wt, bt = m.ada_temp_linear.weight.detach().view(-1).contiguous(), m._bt()
+    wo, bo = m.to_out[0].weight.detach().contiguous(), m.to_out[0].bias.detach()
+    _lib.check(l.haet_slice_reduce(C.byref(sh), x.data_ptr(), wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(),
+                                   wt.data_ptr(), bt, spill.data_ptr(), part.data_ptr(), work.data_ptr(), st))
+    T = 8 * G
+    eid = torch.empty(T, 32, device="cuda"); lse = torch.empty(T, device="cuda"); pos = torch.empty(T, 3, device="cuda")
+    _lib.check(l.haet_slice_merge(C.byref(sh), part.data_ptr(), 1, eid.data_ptr(), lse.data_ptr(), pos.data_ptr(), st))
+    assert torch.equal(eid.view_as(S), S)
+
+    def deslice(states):
+        o = torch.empty(1, N, 256, device="cuda")
+        _lib.check(l.haet_deslice_out(C.byref(sh), spill.data_ptr(), lse.data_ptr(), states.data_ptr(), ws.data_ptr(),
+                                      bs.data_ptr(), wt.data_ptr(), bt, wo.data_ptr(), bo.data_ptr(), o.data_ptr(),
+                                      work.data_ptr(), st))
+        return o
+    g = torch.Generator(device="cuda").manual_seed(1)
+    s1 = torch.randn(T, 32, device="cuda", generator=g)
+    s2 = torch.randn(T, 32, device="cuda", generator=g)
+    o1, o2 = deslice(s1), deslice(s2)
+    colsum = o1.double().sum(1).view(8, 32)                       # [h, c]
+    want = s1.double().view(8, G, 32).sum(1)
+    assert float((colsum - want).abs().max() / want.abs().max()) < 1e-3          # (1)
+    o12 = deslice(s1 + 2 * s2)
+    assert rel_l2(o12, o1 + 2 * o2) < 1e-4                                       # (2)
+    xp = torch.nn.functional.linear(x[0], m.in_project_x.weight, m.in_project_x.bias).view(N, 8, 32)
+    lo, hi = xp.amin(0), xp.amax(0)                                              # [h, c]
+    Sv = S.view(8, G, 32)
+    tol = 1e-3 * (hi - lo).max()
+    assert bool((Sv >= lo[:, None] - tol).all()) and bool((Sv <= hi[:, None] + tol).all())   # (3)
