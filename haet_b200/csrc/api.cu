@@ -8,6 +8,7 @@ namespace haet {
 
 static thread_local char g_err[512] = "";
 int64_t g_launches = 0;
+int g_path = 0;
 
 void set_error(const char *fmt, ...) {
     va_list ap;
@@ -40,8 +41,16 @@ struct Carver {
     }
 };
 
-static int64_t deslice_ws_bytes(const haet_layer_shape *s) {
+static int64_t image_bytes(const haet_layer_shape *s) {   // packed-weight scratch of the tcgen05 GEMM
+    const int inner = s->heads * s->dim_head;
+    return align_up(4 * (int64_t)(inner > s->dim ? inner : s->dim) * (inner > s->dim ? inner : s->dim), 256);
+}
+static int64_t deslice_o_bytes(const haet_layer_shape *s) {
     return align_up(s->B * s->N * (int64_t)s->heads * s->dim_head * (int64_t)sizeof(float), 256);
+}
+static int64_t deslice_ws_bytes(const haet_layer_shape *s) { return deslice_o_bytes(s) + image_bytes(s); }
+static int64_t slice_parts_bytes(const haet_layer_shape *s) {
+    return align_up(slice_chunks(s) * haet_partial_floats(s) * (int64_t)sizeof(float), 256);
 }
 
 struct LayerBuf {
@@ -107,8 +116,16 @@ int64_t haet_spill_bytes(const haet_layer_shape *s) {
 int64_t haet_partial_floats(const haet_layer_shape *s) {
     return s->B * s->heads * (int64_t)s->slice_num * (s->dim_head + 2);
 }
-int64_t haet_slice_workspace_bytes(const haet_layer_shape *s) {
-    return align_up(slice_chunks(s) * haet_partial_floats(s) * (int64_t)sizeof(float), 256);
+int64_t haet_slice_workspace_bytes(const haet_layer_shape *s) { return slice_parts_bytes(s) + image_bytes(s); }
+int haet_set_path(int path) {
+    if (path != 0 && path != 1) { set_error("path must be 0 (tensor core) or 1 (fp32 SIMT)"); return HAET_EINVAL; }
+    g_path = path;
+    return HAET_OK;
+}
+int haet_debug_gemm(const float *x_d, const float *w_d, const float *bias_d, float *y_d, int64_t M, int32_t K, int32_t Nn,
+                    void *img_d, void *stream) {
+    if (g_path == 0 && gemm_tc_supported(K, Nn)) return launch_gemm_tc(x_d, w_d, bias_d, y_d, M, K, Nn, img_d, (cudaStream_t)stream);
+    return launch_linear(x_d, w_d, bias_d, y_d, M, K, Nn, (cudaStream_t)stream);
 }
 int64_t haet_deslice_workspace_bytes(const haet_layer_shape *s) { return deslice_ws_bytes(s); }
 
@@ -121,8 +138,14 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
     float *xp = (float *)spill_d;
     if (s->B == 0) return HAET_OK;
     HAET_CHECK_ARG(s->N > 0, "a rank needs at least one point (N == 0)");
-    if ((rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st))) return rc;
     float *parts = (float *)workspace_d;
+    void *img = (char *)workspace_d + slice_parts_bytes(s);
+    const int inner = s->heads * s->dim_head;
+    if (g_path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
+        rc = launch_gemm_tc(x_d, wx_d, bx_d, xp, s->B * s->N, s->dim, inner, img, st);
+    else
+        rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
+    if (rc) return rc;
     if ((rc = launch_slice_partial(s, xp, ws_d, bs_d, wt_d, bt, parts, st))) return rc;
     return launch_slice_merge(s, parts, slice_chunks(s), partial_d, nullptr, nullptr, st);
 }
@@ -147,7 +170,10 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
     cudaStream_t st = (cudaStream_t)stream;
     float *o = (float *)workspace_d;
     if ((rc = launch_deslice(s, (const float *)spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st))) return rc;
-    return launch_linear(o, wo_d, bo_d, out_d, s->B * s->N, s->heads * s->dim_head, s->dim, st);
+    const int inner = s->heads * s->dim_head;
+    if (g_path == 0 && gemm_tc_supported(inner, s->dim))
+        return launch_gemm_tc(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, (char *)workspace_d + deslice_o_bytes(s), st);
+    return launch_linear(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, st);
 }
 
 int64_t haet_layer_scratch_bytes(const haet_layer_shape *s, const haet_erwin_cfg *c) {

@@ -159,6 +159,15 @@ int haet_layer_forward_host(const haet_layer_shape *s, const haet_erwin_cfg *c, 
 int haet_layer_forward(const haet_layer_shape *s, const haet_erwin_cfg *c, const haet_layer_weights *w,
                        const float *x_d, float *out_d, void *scratch_d, void *stream);
 
+/* ---- switches and test hooks -------------------------------------------------------
+ * haet_set_path(0): tcgen05 tensor-core kernels wherever the shape allows (default);
+ * haet_set_path(1): the exact-fp32 SIMT CUDA kernels everywhere (device-side cross-check).
+ * haet_debug_gemm: Y[M,Nn] = X[M,K].W[Nn,K]^T + bias through the path selected above;
+ * img_d: scratch of 4*Nn*K bytes. */
+int haet_set_path(int path);
+int haet_debug_gemm(const float *x_d, const float *w_d, const float *bias_d, float *y_d, int64_t M, int32_t K,
+                    int32_t Nn, void *img_d, void *stream);
+
 /* number of kernels launched by this library since load (bench.py's gpu_launches) */
 int64_t haet_launch_count(void);
 
