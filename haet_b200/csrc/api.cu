@@ -50,7 +50,9 @@ static int64_t deslice_o_bytes(const haet_layer_shape *s) {
 }
 static int64_t deslice_ws_bytes(const haet_layer_shape *s) { return deslice_o_bytes(s) + image_bytes(s); }
 static int64_t slice_parts_bytes(const haet_layer_shape *s) {
-    return align_up(slice_chunks(s) * haet_partial_floats(s) * (int64_t)sizeof(float), 256);
+    int64_t c = slice_chunks(s);
+    if (slice_tc_supported(s) && slice_tc_chunks(s) > c) c = slice_tc_chunks(s);
+    return align_up(c * haet_partial_floats(s) * (int64_t)sizeof(float), 256);
 }
 
 struct LayerBuf {
@@ -146,6 +148,10 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
     else
         rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
     if (rc) return rc;
+    if (g_path == 0 && slice_tc_supported(s)) {
+        if ((rc = launch_slice_tc(s, xp, ws_d, bs_d, wt_d, bt, parts, st))) return rc;
+        return launch_slice_merge(s, parts, slice_tc_chunks(s), partial_d, nullptr, nullptr, st);
+    }
     if ((rc = launch_slice_partial(s, xp, ws_d, bs_d, wt_d, bt, parts, st))) return rc;
     return launch_slice_merge(s, parts, slice_chunks(s), partial_d, nullptr, nullptr, st);
 }

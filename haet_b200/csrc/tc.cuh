@@ -113,14 +113,26 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
 //   K-major : row = M/N index, 128 B along K;  SBO = bytes between 8-row groups;  K advance = +32 B on the start
 //   MN-major: row = K index, 128 B along M/N;  LBO = bytes between 128-B blocks along M/N, SBO = between 8-k groups
 // bits [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version = 1, [61,64) layout (2 = SWIZZLE_128B)
-__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr >> 4) & 0x3FFF);
     d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
     d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
     d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
+    d |= (uint64_t)layout << 61;
     return d;
+}
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return smem_desc(saddr, lbo_bytes, sbo_bytes, 2);
+}
+// MN-major 32-bit (tf32) operands have ONE legal layout: SWIZZLE_128B_BASE32B (layout 1).  Rows are the K index,
+// 128 B (32 floats) along M/N; the 32-byte chunk index is XORed with (row % 4); atoms are 4 rows = 512 B, so one
+// K = 8 instruction spans two atoms SBO bytes apart.
+__device__ __forceinline__ uint64_t smem_desc_mn32(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return smem_desc(saddr, lbo_bytes, sbo_bytes, 1);
+}
+__device__ __forceinline__ uint32_t mn32_off(int row, int chunk32) {   // byte offset of (k row, 32-B chunk)
+    return (uint32_t)(row * 128 + ((chunk32 ^ (row & 3)) << 5));
 }
 
 // Instruction descriptor (upper 32 bits of idescE): c_format [4,6) 1 = F32; a_format [7,10), b_format [10,13):
@@ -165,6 +177,12 @@ __device__ __forceinline__ bool elect_one() {
     asm volatile(
         "{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
     return pred != 0;
+}
+
+__device__ __forceinline__ float fast_ex2(float x) {   // MUFU.EX2 (2 ulp), flushes denormals
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
 // split an fp32 into bf16 hi + bf16 lo (hi + lo carries ~16 mantissa bits)
