@@ -175,7 +175,11 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
     if (s->B == 0 || s->N == 0) return HAET_OK;
     cudaStream_t st = (cudaStream_t)stream;
     float *o = (float *)workspace_d;
-    if ((rc = launch_deslice(s, (const float *)spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st))) return rc;
+    if (g_path == 0 && deslice_tc_supported(s))
+        rc = launch_deslice_tc(s, (const float *)spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
+    else
+        rc = launch_deslice(s, (const float *)spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
+    if (rc) return rc;
     const int inner = s->heads * s->dim_head;
     if (g_path == 0 && gemm_tc_supported(inner, s->dim))
         return launch_gemm_tc(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, (char *)workspace_d + deslice_o_bytes(s), st);

@@ -57,6 +57,9 @@ bool slice_tc_supported(const haet_layer_shape *s);
 int64_t slice_tc_chunks(const haet_layer_shape *s);
 int launch_slice_tc(const haet_layer_shape *s, const float *xp, const float *ws, const float *bs, const float *wt,
                     float bt, float *chunk_parts, cudaStream_t st);
+bool deslice_tc_supported(const haet_layer_shape *s);
+int launch_deslice_tc(const haet_layer_shape *s, const float *xp, const float *lse2, const float *states,
+                      const float *ws, const float *bs, const float *wt, float bt, float *o, cudaStream_t st);
 extern int g_path;   // 0: tensor-core kernels where supported; 1: fp32 SIMT kernels everywhere
 int64_t slice_chunks(const haet_layer_shape *s);
 int launch_slice_partial(const haet_layer_shape *s, const float *xp, const float *ws, const float *bs,

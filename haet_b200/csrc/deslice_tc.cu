@@ -1,0 +1,275 @@
+// Pass 2 on tcgen05: o[b, n, h*C + c] = sum_g W[n,g] S'[b,h,g,c],  W[n,g] = 2^(z2[n,g] - lse2[g])
+// (IrregularMesh.py:221-232; the N x G weight matrix is recomputed tile by tile, never materialised).
+//
+// Points on the TMEM lanes (thread = point, so s_n = log2e / tau_n is a register):
+//   MMA1 (kind::f16, 3-term bf16 split): D[n, g] = x_proj[n,:] . Ws[g,:]      M = 128 points, N = 64 slices, K' = 96
+//   softmax warps: P = 2^((D + bc_g) * s_n - lse2_g) -> TMEM in place (per-column constants from shared memory)
+//   MMA2 (kind::tf32, A = P from TMEM, B = S'_h as MN-major fp32): O[n, c] += sum_g P[n, g] S'[g, c]
+// CTA = (b, h, chunk of points): the Ws and S'_h operand images are built once and stay resident; the x_proj
+// head slice streams through a 4-stage ring; O is double-buffered in TMEM and stored by the producer warps.
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace haet {
+using namespace tc;
+
+constexpr int DT_C = 32;
+constexpr int DT_TILE = 128;        // points per tile (UMMA M)
+constexpr int DT_GC = 64;           // slices per item (UMMA N of MMA1, K of MMA2)
+constexpr int DT_STAGES = 4;
+constexpr int DT_THREADS = 416;
+constexpr int DT_MAX_G = 512;
+constexpr int DT_TILE_BYTES = DT_TILE * 128;
+constexpr int DT_EPI_LAG = 3;       // the producer warps store tile t - 3 after producing tile t
+
+struct DesliceCtl {
+    uint64_t a_full[DT_STAGES], a_empty[DT_STAGES];
+    uint64_t d_full[2][2], p_full[2][2];
+    uint64_t o_full[2], o_empty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint32_t dt_dbuf_col(int wg, int buf) { return 128u + (uint32_t)(wg * 2 + buf) * DT_GC; }
+
+__global__ void __launch_bounds__(DT_THREADS, 1)
+deslice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ lse2, const float *__restrict__ states,
+                  const float *__restrict__ ws, const float *__restrict__ bs, const float *__restrict__ wt, float bt,
+                  float base_temp, float shift, int64_t N, int H, int G, int64_t chunk_pts, float *__restrict__ o) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int n_gc = (G + DT_GC - 1) / DT_GC;
+    const int g_pad = n_gc * DT_GC;
+    uint8_t *sW = smem;                                     // [g_pad rows][hi(32 bf16) | lo(32 bf16)]  K-major SW128
+    uint8_t *sV = sW + (size_t)g_pad * 128;                 // [g_pad rows][32 fp32]  S'_h, MN-major SW128_BASE32B
+    uint8_t *sA = sV + (size_t)g_pad * 128;                 // [stages][128 rows][hi | lo]
+    float2 *sC = reinterpret_cast<float2 *>(sA + (size_t)DT_STAGES * DT_TILE_BYTES);   // [g_pad] {bc_g, -lse2_g}
+    float *sS = reinterpret_cast<float *>(sC + g_pad);                                 // [stages][128] s_n
+    DesliceCtl *ctl = reinterpret_cast<DesliceCtl *>(sS + DT_STAGES * DT_TILE);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
+    const int inner = H * DT_C;
+    const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
+    const int64_t n_end = min(N, n_begin + chunk_pts);
+    const int n_tiles = (int)((n_end - n_begin + DT_TILE - 1) / DT_TILE);
+
+    if (warp == 12) {
+        if (lane == 0) {
+            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 128); mbar_init(&ctl->a_empty[s], 1); }
+            for (int w = 0; w < 2; ++w) {
+                for (int k = 0; k < 2; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
+                mbar_init(&ctl->o_full[w], 1);
+                mbar_init(&ctl->o_empty[w], 128);
+            }
+            fence_barrier_init();
+        }
+        __syncwarp();
+        tmem_alloc<512>(&ctl->tmem_base);
+    }
+    // resident operand images: Ws rows [hi | lo] and S'_h rows (tf32-rounded), per-column constants
+    for (int idx = threadIdx.x; idx < g_pad * 4; idx += DT_THREADS) {
+        const int g = idx >> 2, ck = idx & 3;
+        __align__(16) __nv_bfloat16 hi[8], lo[8];
+        __align__(16) float sv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float v = g < G ? ws[(size_t)g * DT_C + ck * 8 + i] : 0.f;
+            split_bf16(v, hi[i], lo[i]);
+            const float s = g < G ? states[((size_t)bh * G + g) * DT_C + ck * 8 + i] : 0.f;
+            uint32_t u;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(s));
+            sv[i] = __uint_as_float(u);
+        }
+        *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(hi);
+        *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck + 4)) = *reinterpret_cast<const uint4 *>(lo);
+        *reinterpret_cast<uint4 *>(sV + mn32_off(g, ck)) = reinterpret_cast<const uint4 *>(sv)[0];
+        *reinterpret_cast<uint4 *>(sV + mn32_off(g, ck) + 16) = reinterpret_cast<const uint4 *>(sv)[1];
+    }
+    for (int g = threadIdx.x; g < g_pad; g += DT_THREADS)
+        sC[g] = g < G ? make_float2(bs[g] - shift, -lse2[(size_t)bh * G + g]) : make_float2(0.f, -INFINITY);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = ctl->tmem_base;
+
+    if (warp >= 8 && warp < 12) {
+        // =========================== producers + O epilogue ===========================
+        const int r = threadIdx.x - 256;   // row of the tile == TMEM lane
+        const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+        float wtr[DT_C];
+#pragma unroll
+        for (int i = 0; i < DT_C; ++i) wtr[i] = wt[i];
+        const float *src = xp + ((int64_t)b * N) * inner + h * DT_C;
+        float *dst = o + ((int64_t)b * N) * inner + h * DT_C;
+        auto epilogue = [&](int te) {
+            const int ob = te & 1;
+            mbar_wait(&ctl->o_full[ob], (uint32_t)((te >> 1) & 1));
+            tc_fence_after();
+            uint32_t v[32];
+            tmem_ld32(tmem_base + lane_base + (uint32_t)ob * DT_C, v);
+            tmem_wait_ld();
+            tc_fence_before();
+            mbar_arrive(&ctl->o_empty[ob]);
+            const int64_t n = n_begin + (int64_t)te * DT_TILE + r;
+            if (n < n_end) {
+                float4 *p = reinterpret_cast<float4 *>(dst + n * inner);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    p[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
+                                       __uint_as_float(v[4 * i + 3]));
+            }
+        };
+        float4 cur[8], nxt[8];
+        auto load = [&](int t, float4 (&v)[8]) {
+            const int64_t n = n_begin + (int64_t)t * DT_TILE + r;
+            if (t < n_tiles && n < n_end) {
+                const float4 *p = reinterpret_cast<const float4 *>(src + n * inner);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = __ldg(p + i);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        };
+        load(0, cur);
+        int stage = 0, phase = 0;
+        for (int t = 0; t < n_tiles; ++t) {
+            load(t + 1, nxt);
+            mbar_wait(&ctl->a_empty[stage], phase ^ 1);
+            const bool valid = n_begin + (int64_t)t * DT_TILE + r < n_end;
+            const float *f = reinterpret_cast<const float *>(cur);
+            float d = bt;
+#pragma unroll
+            for (int i = 0; i < DT_C; ++i) d = fmaf(f[i], wtr[i], d);
+            const float tau = base_temp + fminf(fmaxf(d, -0.4f), 0.4f);
+            sS[stage * DT_TILE + r] = valid ? kLog2e / tau : 0.f;
+            uint8_t *a = sA + (size_t)stage * DT_TILE_BYTES;
+            __align__(16) __nv_bfloat16 hi[DT_C], lo[DT_C];
+#pragma unroll
+            for (int i = 0; i < DT_C; ++i) split_bf16(f[i], hi[i], lo[i]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                *reinterpret_cast<uint4 *>(a + sw128_off(r, c)) = reinterpret_cast<const uint4 *>(hi)[c];
+                *reinterpret_cast<uint4 *>(a + sw128_off(r, 4 + c)) = reinterpret_cast<const uint4 *>(lo)[c];
+            }
+            fence_proxy_async();
+            mbar_arrive(&ctl->a_full[stage]);
+            if (++stage == DT_STAGES) { stage = 0; phase ^= 1; }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
+            if (t >= DT_EPI_LAG) epilogue(t - DT_EPI_LAG);
+        }
+        for (int te = max(0, n_tiles - DT_EPI_LAG); te < n_tiles; ++te) epilogue(te);
+    } else if (warp == 12) {
+        // =========================== MMA issuer ===========================
+        if (lane == 0) {
+            const uint32_t id1 = instr_desc(FMT_BF16, DT_TILE, DT_GC, false, false);
+            const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
+            const uint32_t wbase = smem_u32(sW), vbase = smem_u32(sV);
+            const int Q = n_tiles * n_gc;
+            int cnt1[2] = {0, 0}, cnt2[2] = {0, 0};
+            for (int q = 0; q < Q + 2; ++q) {
+                if (q >= 2) {   // ---- MMA2 of item q-2: O += P . S'_h[g-chunk]
+                    const int qq = q - 2, t = qq / n_gc, j = qq - t * n_gc, w = j & 1, k = cnt2[w]++;
+                    const int buf = k & 1, stage = t % DT_STAGES, ob = t & 1;
+                    if (j == 0) { mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t >> 1) & 1) ^ 1)); }
+                    mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
+                    tc_fence_after();
+                    const uint32_t pa = tmem_base + dt_dbuf_col(w, buf), od = tmem_base + (uint32_t)ob * DT_C;
+                    const uint32_t vb = vbase + (uint32_t)j * DT_GC * 128;
+#pragma unroll
+                    for (int ks = 0; ks < DT_GC / 8; ++ks)
+                        mma_tf32_ts(od, pa + ks * 8, smem_desc_mn32(vb + ks * 1024, 512, 512), id2, (j | ks) != 0);
+                    if (j == n_gc - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[stage]); }
+                }
+                if (q < Q) {    // ---- MMA1 of item q: D = x_proj . Ws[g-chunk]^T  (hi.hi + lo.hi + hi.lo)
+                    const int t = q / n_gc, j = q - t * n_gc, w = j & 1, k = cnt1[w]++;
+                    const int buf = k & 1, stage = t % DT_STAGES;
+                    if (j == 0) { mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1)); tc_fence_after(); }
+                    const uint32_t a = smem_u32(sA + (size_t)stage * DT_TILE_BYTES);
+                    const uint32_t wb = wbase + (uint32_t)j * DT_GC * 128;
+                    const uint32_t d = tmem_base + dt_dbuf_col(w, buf);
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        mma_bf16_ss(d, smem_desc_sw128(a + ks * 32, 16, 1024), smem_desc_sw128(wb + ks * 32, 16, 1024), id1, ks != 0);
+                        mma_bf16_ss(d, smem_desc_sw128(a + 64 + ks * 32, 16, 1024), smem_desc_sw128(wb + ks * 32, 16, 1024), id1, true);
+                        mma_bf16_ss(d, smem_desc_sw128(a + ks * 32, 16, 1024), smem_desc_sw128(wb + 64 + ks * 32, 16, 1024), id1, true);
+                    }
+                    tc_commit(&ctl->d_full[w][buf]);
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // =========================== softmax warpgroups ===========================
+        const int w = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;
+        const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
+        int k = 0;
+        for (int t = 0; t < n_tiles; ++t) {
+            const int stage = t % DT_STAGES;
+            if (w < n_gc) mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1));
+            const float sn = sS[stage * DT_TILE + row];
+#pragma unroll 1
+            for (int j = w; j < n_gc; j += 2, ++k) {
+                const int buf = k & 1;
+                mbar_wait(&ctl->d_full[w][buf], (uint32_t)((k >> 1) & 1));
+                tc_fence_after();
+                const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(w, buf);
+                const float4 *cc = reinterpret_cast<const float4 *>(sC + j * DT_GC);
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                    uint32_t r[32];
+                    tmem_ld32(dcol + hh * 32, r);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int c = 0; c < 32; c += 2) {
+                        const float4 k2 = cc[hh * 16 + (c >> 1)];   // {bc, -lse} of two slices
+                        r[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c]) + k2.x, sn, k2.y)));
+                        r[c + 1] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 1]) + k2.z, sn, k2.w)));
+                    }
+                    tmem_st32(dcol + hh * 32, r);
+                }
+                tmem_wait_st();
+                tc_fence_before();
+                mbar_arrive(&ctl->p_full[w][buf]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 12) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+bool deslice_tc_supported(const haet_layer_shape *s) { return s->dim_head == DT_C && s->slice_num <= DT_MAX_G; }
+
+int launch_deslice_tc(const haet_layer_shape *s, const float *xp, const float *lse2, const float *states,
+                      const float *ws, const float *bs, const float *wt, float bt, float *o, cudaStream_t st) {
+    if (s->N == 0 || s->B == 0) return HAET_OK;
+    const int n_gc = (s->slice_num + DT_GC - 1) / DT_GC, g_pad = n_gc * DT_GC;
+    const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + sizeof(float2) * g_pad +
+                        sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        HAET_CUDA(cudaFuncSetAttribute(deslice_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set = smem;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t BH = s->B * s->heads;
+    int64_t n_chunks = sms / BH;
+    if (n_chunks < 1) n_chunks = 1;
+    const int64_t max_chunks = cdiv(s->N, DT_TILE);
+    if (n_chunks > max_chunks) n_chunks = max_chunks;
+    const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
+    dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
+    deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(xp, lse2, states, ws, bs, wt, bt, s->base_temp,
+                                                       rep_slice_shift(s->epsilon), s->N, s->heads, s->slice_num, chunk_pts, o);
+    HAET_LAUNCHED();
+    return HAET_OK;
+}
+
+}  // namespace haet

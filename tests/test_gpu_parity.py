@@ -344,7 +344,7 @@ def test_full_size_properties(N, G):
     want = s1.double().view(8, G, 32).sum(1)
     assert float((colsum - want).abs().max() / want.abs().max()) < 1e-3          # (1)
     o12 = deslice(s1 + 2 * s2)
-    assert rel_l2(o12, o1 + 2 * o2) < 1e-4                                       # (2)
+    assert rel_l2(o12, o1 + 2 * o2) < 1e-3   # (2) exact up to the tf32 rounding of the states operand
     xp = torch.nn.functional.linear(x[0], m.in_project_x.weight, m.in_project_x.bias).view(N, 8, 32)
     lo, hi = xp.amin(0), xp.amax(0)                                              # [h, c]
     Sv = S.view(8, G, 32)
