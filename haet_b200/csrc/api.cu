@@ -113,7 +113,10 @@ int haet_device_check(void) {
 }
 
 int64_t haet_spill_bytes(const haet_layer_shape *s) {
-    return align_up(s->B * s->N * (int64_t)s->heads * s->dim_head * (int64_t)sizeof(float), 256);
+    SpillView v = spill_view(s, nullptr);
+    int64_t bytes = (char *)v.xp - (char *)nullptr;
+    if (spill_needs_xp(s)) bytes += align_up(s->B * s->N * (int64_t)s->heads * s->dim_head * (int64_t)sizeof(float), 256);
+    return bytes;
 }
 int64_t haet_partial_floats(const haet_layer_shape *s) {
     return s->B * s->heads * (int64_t)s->slice_num * (s->dim_head + 2);
@@ -137,7 +140,8 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
     int rc = check_shape(s);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    float *xp = (float *)spill_d;
+    const SpillView sv = spill_view(s, spill_d);
+    float *xp = sv.xp;
     if (s->B == 0) return HAET_OK;
     HAET_CHECK_ARG(s->N > 0, "a rank needs at least one point (N == 0)");
     float *parts = (float *)workspace_d;
@@ -149,7 +153,8 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
         rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
     if (rc) return rc;
     if (g_path == 0 && slice_tc_supported(s)) {
-        if ((rc = launch_slice_tc(s, xp, ws_d, bs_d, wt_d, bt, parts, st))) return rc;
+        if ((rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st))) return rc;
+        if ((rc = launch_slice_tc(s, sv.img, sv.scale, ws_d, bs_d, parts, st))) return rc;
         return launch_slice_merge(s, parts, slice_tc_chunks(s), partial_d, nullptr, nullptr, st);
     }
     if ((rc = launch_slice_partial(s, xp, ws_d, bs_d, wt_d, bt, parts, st))) return rc;
@@ -175,10 +180,11 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
     if (s->B == 0 || s->N == 0) return HAET_OK;
     cudaStream_t st = (cudaStream_t)stream;
     float *o = (float *)workspace_d;
+    const SpillView sv = spill_view(s, const_cast<void *>(spill_d));
     if (g_path == 0 && deslice_tc_supported(s))
-        rc = launch_deslice_tc(s, (const float *)spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
+        rc = launch_deslice_tc(s, sv.xp, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
     else
-        rc = launch_deslice(s, (const float *)spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
+        rc = launch_deslice(s, sv.xp, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
     if (rc) return rc;
     const int inner = s->heads * s->dim_head;
     if (g_path == 0 && gemm_tc_supported(inner, s->dim))

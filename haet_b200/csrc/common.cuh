@@ -44,6 +44,27 @@ constexpr float kLog2e = 1.4426950408889634f;
 // log(-log(eps)) evaluated like the reference does (fp32 tensor ops, IrregularMesh.py:172)
 static inline float rep_slice_shift(float eps) { return logf(-logf(eps)); }
 
+// ---- the per-point spill between pass 1 and pass 2 (opaque to the caller; haet_spill_bytes) ----------
+// Tensor-core path: the projected points are kept as a ready-made UMMA operand image
+//   img  [B*H][Npad rows][128 B]: row n of head h = 32 fp16 "hi" then 32 fp16 "lo" (x_proj = hi + lo to ~2^-22);
+//        the 16-byte chunk j of a row sits at chunk position j ^ (n & 7), i.e. any run of rows starting at a
+//        multiple of 8 IS a SWIZZLE_128B shared-memory tile (K-major for the logits MMA, MN-major for P.x) and
+//        is brought in by one bulk copy.  Npad = N rounded up to 128; pad rows are zero.
+//   scale[B*H][Npad] fp32: s_n = log2(e) / tau_n (Ada-Temp, IrregularMesh.py:168); 0 on pad rows.
+//   xp   [B][N][H*C] fp32: only for the fp32 SIMT kernels and the conv front-ends (which pack img from it).
+constexpr int XPI_ROW_BYTES = 128;
+static inline int64_t xpi_npad(int64_t N) { return align_up(N, 128); }
+struct SpillView {
+    uint8_t *img;
+    float *scale;
+    float *xp;
+    int64_t npad;
+};
+bool spill_needs_xp(const haet_layer_shape *s);
+SpillView spill_view(const haet_layer_shape *s, void *base);
+int launch_xpi_pack(const haet_layer_shape *s, const float *xp, const float *wt, float bt, uint8_t *img, float *scale,
+                    cudaStream_t st);
+
 // ---- stage entry points implemented in the .cu files ------------------------------------
 int launch_in_project(const haet_layer_shape *s, const float *x, const float *wx, const float *bx,
                       float *xp, cudaStream_t st);
@@ -55,8 +76,8 @@ int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, 
                    cudaStream_t st);
 bool slice_tc_supported(const haet_layer_shape *s);
 int64_t slice_tc_chunks(const haet_layer_shape *s);
-int launch_slice_tc(const haet_layer_shape *s, const float *xp, const float *ws, const float *bs, const float *wt,
-                    float bt, float *chunk_parts, cudaStream_t st);
+int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,
+                    const float *bs, float *chunk_parts, cudaStream_t st);
 bool deslice_tc_supported(const haet_layer_shape *s);
 int launch_deslice_tc(const haet_layer_shape *s, const float *xp, const float *lse2, const float *states,
                       const float *ws, const float *bs, const float *wt, float bt, float *o, cudaStream_t st);

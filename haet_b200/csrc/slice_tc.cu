@@ -3,16 +3,18 @@
 // with z2 = ((x_proj . Ws_g + bs_g - log(-log eps)) / tau_n) log2 e     (IrregularMesh.py:168-183).
 //
 // Flash-attention-shaped, with the SLICES on the TMEM lanes so that the softmax over the points
-// is a per-thread reduction:
-//   MMA1 (kind::f16, 3-term bf16 split = fp32-class logits; precision_study.py):
+// is a per-thread reduction.  The projected points arrive as the ready-made operand image of the spill
+// (common.cuh: rows of [32 fp16 hi | 32 fp16 lo], pre-swizzled), one bulk copy per 64-point tile, and the SAME
+// shared-memory tile feeds both MMAs:
+//   MMA1 (kind::f16, 3-term fp16 split = fp32-class logits; precision_study.py), tile read K-major:
 //        D[g, n] = Ws[g,:] . x_proj[n,:]          M = 128 slices, N = 64 points, K' = 96
-//   softmax warps (thread = slice row g): t = (D + bc_g) * s_n - m_run, P = 2^t, l += P, P -> TMEM in place.
-//        m_run is a LAZY running max: it is only raised when a tile exceeds it by 2^32 (P stays finite in fp32 /
-//        tf32), so the TMEM accumulator rescale is off the common path.
-//   MMA2 (kind::tf32, A = P from TMEM, B = x_proj tile as MN-major fp32):
-//        S[g, c] += sum_n P[g, n] x_proj[n, c]     M = 128, N = 32, K = 64
-// Warp roles: 2 softmax warpgroups (slice blocks j = w, w+2, ..), 4 producer warps (x_proj tile -> bf16 hi/lo
-// K-major rows, tf32-rounded fp32 rows, s_n = log2e / tau_n), 1 MMA-issuing warp.  All hand-offs are mbarriers.
+//   softmax warps (thread = slice row g): t = (D + bc_g) * s_n - m_run, P = 2^t, l += P, P -> TMEM as packed fp16.
+//        m_run is a LAZY running max: it is only raised when a tile exceeds it by 2^8 (P stays inside fp16),
+//        so the TMEM accumulator rescale is off the common path.
+//   MMA2 (kind::f16, A = P from TMEM, B = the tile read MN-major: 64 columns = [hi c | lo c]):
+//        S2[g, 0:32] += sum_n P[g,n] hi[n,:],  S2[g, 32:64] += sum_n P[g,n] lo[n,:];   S = S2[:, :32] + S2[:, 32:]
+// Warp roles: 2 softmax warpgroups (slice blocks j = w, w+2, ..), 1 loader warp (bulk copies), 1 MMA-issuing warp.
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -23,13 +25,13 @@ using namespace tc;
 
 constexpr int ST_C = 32;            // dim_head handled by this kernel
 constexpr int ST_TILE = 64;         // points per tile
-constexpr int ST_STAGES = 4;
-constexpr int ST_THREADS = 416;     // 8 softmax warps + 4 producer warps + 1 MMA warp
+constexpr int ST_STAGES = 6;
+constexpr int ST_THREADS = 320;     // 8 softmax warps + loader warp + MMA warp
 constexpr int ST_GB = 128;          // slices per block (UMMA M)
 constexpr int ST_MAX_GB = 4;        // up to 512 slices
 constexpr int ST_TILE_BYTES = ST_TILE * 128;   // one operand tile: 64 rows x 128 B
-constexpr float ST_RAISE = 32.0f;   // lazy-max threshold (log2 units)
-constexpr float ST_TF32_BIAS = 1.0f + 1.0f / 4096.0f;   // centres the tensor core's tf32 truncation of P
+constexpr int ST_SCOLS = 64;        // TMEM columns of one slice block's accumulator ([hi | lo] halves)
+constexpr float ST_RAISE = 8.0f;    // lazy-max threshold (log2 units): P <= 2^8 fits fp16
 
 struct SliceCtl {
     uint64_t b_full[ST_STAGES], b_empty[ST_STAGES];
@@ -39,31 +41,30 @@ struct SliceCtl {
     uint32_t tmem_base;
 };
 
-__device__ __forceinline__ uint32_t st_dbuf_col(int wg, int buf) { return 128u + (uint32_t)(wg * 2 + buf) * ST_TILE; }
+__device__ __forceinline__ uint32_t st_dbuf_col(int wg, int buf) { return 256u + (uint32_t)(wg * 2 + buf) * ST_TILE; }
 
 __global__ void __launch_bounds__(ST_THREADS, 1)
-slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, const float *__restrict__ bs,
-                const float *__restrict__ wt, float bt, float base_temp, float shift, int64_t N, int H, int G,
-                int64_t chunk_pts, float raise_thr, float *__restrict__ parts) {
+slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
+                const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int64_t chunk_pts,
+                float raise_thr, float *__restrict__ parts) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int n_gb = (G + ST_GB - 1) / ST_GB;
     uint8_t *sW = smem;                                              // [n_gb][2][16 KB]: [hi|hi] rows, [lo|0] rows
-    uint8_t *sB = sW + (size_t)n_gb * 2 * (ST_GB * 128);             // [stages][B1 8 KB | B2 8 KB]
-    float *sS = reinterpret_cast<float *>(sB + (size_t)ST_STAGES * 2 * ST_TILE_BYTES);   // [stages][64] s_n
+    uint8_t *sB = sW + (size_t)n_gb * 2 * (ST_GB * 128);             // [stages][8 KB] point tiles
+    float *sS = reinterpret_cast<float *>(sB + (size_t)ST_STAGES * ST_TILE_BYTES);   // [stages][64] s_n
     SliceCtl *ctl = reinterpret_cast<SliceCtl *>(sS + ST_STAGES * ST_TILE);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
-    const int inner = H * ST_C;
+    const int bh = blockIdx.y;
     const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
     const int64_t n_end = min(N, n_begin + chunk_pts);
     const int n_tiles = (int)((n_end - n_begin + ST_TILE - 1) / ST_TILE);
     const int64_t BH = gridDim.y;
 
     // ---- one-time setup: barriers, TMEM, the Ws operand images ----
-    if (warp == 12) {
+    if (warp == 9) {
         if (lane == 0) {
-            for (int s = 0; s < ST_STAGES; ++s) { mbar_init(&ctl->b_full[s], 128); mbar_init(&ctl->b_empty[s], 1); }
+            for (int s = 0; s < ST_STAGES; ++s) { mbar_init(&ctl->b_full[s], 1); mbar_init(&ctl->b_empty[s], 1); }
             for (int w = 0; w < 2; ++w) {
                 for (int k = 0; k < 2; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
                 mbar_init(&ctl->mma2_done[w], 1);
@@ -76,11 +77,12 @@ slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, cons
     }
     for (int idx = threadIdx.x; idx < n_gb * ST_GB * 4; idx += ST_THREADS) {   // one 16-B chunk (8 k) per step
         const int row = idx >> 2, ck = idx & 3, g = row, j = row / ST_GB, r = row % ST_GB;
-        __align__(16) __nv_bfloat16 hi[8], lo[8];
+        __align__(16) __half hi[8], lo[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            float v = g < G ? ws[(size_t)g * ST_C + ck * 8 + i] : 0.f;
-            split_bf16(v, hi[i], lo[i]);
+            const float v = g < G ? ws[(size_t)g * ST_C + ck * 8 + i] : 0.f;
+            hi[i] = __float2half_rn(v);
+            lo[i] = __float2half_rn(v - __half2float(hi[i]));
         }
         uint8_t *w1 = sW + (size_t)j * 2 * (ST_GB * 128), *w2 = w1 + ST_GB * 128;
         *reinterpret_cast<uint4 *>(w1 + sw128_off(r, ck)) = *reinterpret_cast<const uint4 *>(hi);
@@ -94,82 +96,39 @@ slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, cons
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
 
-    if (warp >= 8 && warp < 12) {
-        // =========================== producers ===========================
-        const int tid = threadIdx.x - 256, r = tid >> 1, hf = tid & 1;
-        float wtr[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) wtr[i] = wt[hf * 16 + i];
-        const float *src = xp + ((int64_t)b * N) * inner + h * ST_C + hf * 16;
-        float4 cur[4], nxt[4];
-        auto load = [&](int t, float4 (&v)[4]) {
-            const int64_t n = n_begin + (int64_t)t * ST_TILE + r;
-            if (t < n_tiles && n < n_end) {
-                const float4 *p = reinterpret_cast<const float4 *>(src + n * inner);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) v[i] = __ldg(p + i);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (warp == 8) {
+        // =========================== loader: one bulk copy per tile (+ its s_n) ===========================
+        if (lane == 0) {
+            const uint8_t *src = img + ((int64_t)bh * npad + n_begin) * XPI_ROW_BYTES;
+            const float *ssrc = scale + (int64_t)bh * npad + n_begin;
+            int stage = 0, phase = 0;
+            for (int t = 0; t < n_tiles; ++t) {
+                mbar_wait(&ctl->b_empty[stage], phase ^ 1);
+                mbar_arrive_expect_tx(&ctl->b_full[stage], ST_TILE_BYTES + ST_TILE * 4);
+                bulk_g2s(sB + (size_t)stage * ST_TILE_BYTES, src + (size_t)t * ST_TILE_BYTES, ST_TILE_BYTES, &ctl->b_full[stage]);
+                bulk_g2s(sS + stage * ST_TILE, ssrc + (size_t)t * ST_TILE, ST_TILE * 4, &ctl->b_full[stage]);
+                if (++stage == ST_STAGES) { stage = 0; phase ^= 1; }
             }
-        };
-        load(0, cur);
-        int stage = 0, phase = 0;
-        for (int t = 0; t < n_tiles; ++t) {
-            load(t + 1, nxt);
-            mbar_wait(&ctl->b_empty[stage], phase ^ 1);
-            const bool valid = n_begin + (int64_t)t * ST_TILE + r < n_end;
-            const float *f = reinterpret_cast<const float *>(cur);
-            float d = 0.f;
-#pragma unroll
-            for (int i = 0; i < 16; ++i) d = fmaf(f[i], wtr[i], d);
-            d += __shfl_xor_sync(0xffffffffu, d, 1);
-            if (hf == 0) {
-                const float tau = base_temp + fminf(fmaxf(d + bt, -0.4f), 0.4f);   // Ada-Temp (:168)
-                sS[stage * ST_TILE + r] = valid ? kLog2e / tau : 0.f;
-            }
-            uint8_t *b1 = sB + (size_t)stage * 2 * ST_TILE_BYTES, *b2 = b1 + ST_TILE_BYTES;
-            __align__(16) __nv_bfloat16 hi[16], lo[16];
-            __align__(16) float tf[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                split_bf16(f[i], hi[i], lo[i]);
-                uint32_t u;
-                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(f[i]));
-                tf[i] = __uint_as_float(u);
-            }
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                *reinterpret_cast<uint4 *>(b1 + sw128_off(r, hf * 2 + c)) = reinterpret_cast<const uint4 *>(hi)[c];
-                *reinterpret_cast<uint4 *>(b1 + sw128_off(r, 4 + hf * 2 + c)) = reinterpret_cast<const uint4 *>(lo)[c];
-            }
-#pragma unroll
-            for (int c = 0; c < 4; ++c)   // MN-major tf32 tile: SWIZZLE_128B_BASE32B
-                *reinterpret_cast<uint4 *>(b2 + mn32_off(r, hf * 2 + (c >> 1)) + (c & 1) * 16) = reinterpret_cast<const uint4 *>(tf)[c];
-            fence_proxy_async();
-            mbar_arrive(&ctl->b_full[stage]);
-            if (++stage == ST_STAGES) { stage = 0; phase ^= 1; }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
         }
-    } else if (warp == 12) {
+        __syncwarp();
+    } else if (warp == 9) {
         // =========================== MMA issuer ===========================
         if (lane == 0) {
-            const uint32_t id1 = instr_desc(FMT_BF16, ST_GB, ST_TILE, false, false);
-            const uint32_t id2 = instr_desc(FMT_TF32, ST_GB, ST_C, false, true);
+            const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
+            const uint32_t id2 = instr_desc(FMT_F16, ST_GB, ST_SCOLS, false, true);
             const int Q = n_tiles * n_gb;
             int cnt1[2] = {0, 0}, cnt2[2] = {0, 0};
             for (int q = 0; q < Q + 2; ++q) {
-                if (q >= 2) {   // ---- MMA2 of item q-2: S_j += P . x_proj
+                if (q >= 2) {   // ---- MMA2 of item q-2: S2_j += P . [hi | lo]
                     const int qq = q - 2, t = qq / n_gb, j = qq - t * n_gb, w = j & 1, k = cnt2[w]++;
                     const int buf = k & 1, stage = t % ST_STAGES;
                     mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
                     tc_fence_after();
-                    const uint32_t b2 = smem_u32(sB + (size_t)stage * 2 * ST_TILE_BYTES + ST_TILE_BYTES);
-                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf), sd = tmem_base + (uint32_t)j * ST_C;
+                    const uint32_t b2 = smem_u32(sB + (size_t)stage * ST_TILE_BYTES);
+                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf), sd = tmem_base + (uint32_t)j * ST_SCOLS;
 #pragma unroll
-                    for (int ks = 0; ks < ST_TILE / 8; ++ks)
-                        mma_tf32_ts(sd, pa + ks * 8, smem_desc_mn32(b2 + ks * 1024, 512, 512), id2, (t | ks) != 0);
+                    for (int ks = 0; ks < ST_TILE / 16; ++ks)   // K = 16 points = two 8-row swizzle atoms
+                        mma_f16_ts(sd, pa + ks * 8, smem_desc_sw128(b2 + ks * 2048, 1024, 1024), id2, (t | ks) != 0);
                     tc_commit(&ctl->mma2_done[w]);
                     if (j == n_gb - 1) tc_commit(&ctl->b_empty[stage]);
                 }
@@ -177,7 +136,7 @@ slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, cons
                     const int t = q / n_gb, j = q - t * n_gb, w = j & 1, k = cnt1[w]++;
                     const int buf = k & 1, stage = t % ST_STAGES;
                     if (j == 0) { mbar_wait(&ctl->b_full[stage], (uint32_t)((t / ST_STAGES) & 1)); tc_fence_after(); }
-                    const uint32_t b1 = smem_u32(sB + (size_t)stage * 2 * ST_TILE_BYTES);
+                    const uint32_t b1 = smem_u32(sB + (size_t)stage * ST_TILE_BYTES);
                     const uint32_t a1 = smem_u32(sW + (size_t)j * 2 * (ST_GB * 128)), a2 = a1 + ST_GB * 128;
                     const uint32_t d = tmem_base + st_dbuf_col(w, buf);
 #pragma unroll
@@ -203,11 +162,13 @@ slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, cons
             m_run[n_my] = 0.f; l_run[n_my] = 0.f;
             bc[n_my] = g < G ? bs[g] - shift : 0.f;
         }
+        const int last_valid = (int)(n_end - n_begin) - (n_tiles - 1) * ST_TILE;   // points in the last tile
         int k = 0;   // item counter of this warpgroup
         for (int t = 0; t < n_tiles && n_my > 0; ++t) {
             const int stage = t % ST_STAGES;
             mbar_wait(&ctl->b_full[stage], (uint32_t)((t / ST_STAGES) & 1));
             const float4 *s4 = reinterpret_cast<const float4 *>(sS + stage * ST_TILE);
+            const bool ragged = (t == n_tiles - 1) && last_valid < ST_TILE;
 #pragma unroll 1
             for (int jj = 0; jj < n_my; ++jj, ++k) {
                 const int j = w + 2 * jj, buf = k & 1;
@@ -233,7 +194,16 @@ slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, cons
                     v = fmaf(__uint_as_float(r1[c + 2]) + bcj, sb.z, -mr); r1[c + 2] = __float_as_uint(v); tmax = fmaxf(tmax, v);
                     v = fmaf(__uint_as_float(r1[c + 3]) + bcj, sb.w, -mr); r1[c + 3] = __float_as_uint(v); tmax = fmaxf(tmax, v);
                 }
-                // lazy running max: the first tile fixes it, later tiles raise it only past 2^ST_RAISE
+                if (ragged) {   // columns past the chunk's last point: weight 0 (their image rows are zero or foreign)
+                    tmax = -INFINITY;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        if (c >= last_valid) r0[c] = __float_as_uint(-INFINITY);
+                        if (c + 32 >= last_valid) r1[c] = __float_as_uint(-INFINITY);
+                        tmax = fmaxf(tmax, fmaxf(__uint_as_float(r0[c]), __uint_as_float(r1[c])));
+                    }
+                }
+                // lazy running max: the first tile fixes it, later tiles raise it only past 2^raise_thr
                 const bool first = (t == 0);
                 const bool need = first || tmax > raise_thr;
                 if (__any_sync(0xffffffffu, need)) {
@@ -249,29 +219,36 @@ slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, cons
                     if (!first) {   // rescale the TMEM accumulator of this slice block (all earlier MMA2s are done)
                         mbar_wait(&ctl->mma2_done[w], (uint32_t)((k - 1) & 1));
                         tc_fence_after();
-                        uint32_t sr[32];
-                        const uint32_t scol = tmem_base + lane_base + (uint32_t)j * ST_C;
-                        tmem_ld32(scol, sr);
-                        tmem_wait_ld();
+                        const uint32_t scol = tmem_base + lane_base + (uint32_t)j * ST_SCOLS;
+#pragma unroll 1
+                        for (int hh = 0; hh < 2; ++hh) {
+                            uint32_t sr[32];
+                            tmem_ld32(scol + hh * 32, sr);
+                            tmem_wait_ld();
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) sr[c] = __float_as_uint(__uint_as_float(sr[c]) * sc);
-                        tmem_st32(scol, sr);
+                            for (int c = 0; c < 32; ++c) sr[c] = __float_as_uint(__uint_as_float(sr[c]) * sc);
+                            tmem_st32(scol + hh * 32, sr);
+                        }
                     }
                 }
                 float l = l_run[jj];
+                uint32_t pk[32];   // P as packed fp16: word i = points (2i, 2i+1)
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const float p = fast_ex2(__uint_as_float(r0[c]));
-                    l += p; r0[c] = __float_as_uint(p);
+                for (int c = 0; c < 32; c += 2) {
+                    const float p0 = fast_ex2(__uint_as_float(r0[c])), p1 = fast_ex2(__uint_as_float(r0[c + 1]));
+                    l += p0; l += p1;
+                    const __half2 h2 = __floats2half2_rn(p0, p1);
+                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&h2);
                 }
 #pragma unroll
-                for (int c = 0; c < 32; ++c) {
-                    const float p = fast_ex2(__uint_as_float(r1[c]));
-                    l += p; r1[c] = __float_as_uint(p);
+                for (int c = 0; c < 32; c += 2) {
+                    const float p0 = fast_ex2(__uint_as_float(r1[c])), p1 = fast_ex2(__uint_as_float(r1[c + 1]));
+                    l += p0; l += p1;
+                    const __half2 h2 = __floats2half2_rn(p0, p1);
+                    pk[16 + (c >> 1)] = *reinterpret_cast<const uint32_t *>(&h2);
                 }
                 l_run[jj] = l;
-                tmem_st32(dcol, r0);
-                tmem_st32(dcol + 32, r1);
+                tmem_st32(dcol, pk);
                 tmem_wait_st();
                 tc_fence_before();
                 mbar_arrive(&ctl->p_full[w][buf]);
@@ -282,26 +259,24 @@ slice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ ws, cons
             // (mma2_done may be two phases behind here, so its parity is ambiguous: use the dedicated barrier)
             mbar_wait(&ctl->all_done, 0);
             tc_fence_after();
-            const int64_t n_pad = (int64_t)n_tiles * ST_TILE - (n_end - n_begin);   // masked columns of the last tile
             for (int jj = 0; jj < n_my; ++jj) {
                 const int j = w + 2 * jj, g = j * ST_GB + row;
-                uint32_t sr[32];
-                tmem_ld32(tmem_base + lane_base + (uint32_t)j * ST_C, sr);
+                uint32_t s0[32], s1[32];
+                tmem_ld32(tmem_base + lane_base + (uint32_t)j * ST_SCOLS, s0);
+                tmem_ld32(tmem_base + lane_base + (uint32_t)j * ST_SCOLS + 32, s1);
                 tmem_wait_ld();
                 if (g < G) {
-                    // masked points entered with s_n = 0 and zero rows: each added exactly 2^(-m_run) to l, 0 to S
-                    const float l = l_run[jj] - (float)n_pad * fast_ex2(-m_run[jj]);
                     float *o = parts + (((int64_t)blockIdx.x * BH + bh) * G + g) * (ST_C + 2);
-                    o[0] = m_run[jj]; o[1] = l;
+                    o[0] = m_run[jj]; o[1] = l_run[jj];
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) o[2 + c] = __uint_as_float(sr[c]);
+                    for (int c = 0; c < 32; ++c) o[2 + c] = __uint_as_float(s0[c]) + __uint_as_float(s1[c]);
                 }
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 12) {
+    if (warp == 9) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }
@@ -322,10 +297,10 @@ static int64_t slice_tc_chunk_pts(const haet_layer_shape *s) {
 }
 int64_t slice_tc_chunks(const haet_layer_shape *s) { return s->N > 0 ? cdiv(s->N, slice_tc_chunk_pts(s)) : 0; }
 
-int launch_slice_tc(const haet_layer_shape *s, const float *xp, const float *ws, const float *bs, const float *wt,
-                    float bt, float *chunk_parts, cudaStream_t st) {
+int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,
+                    const float *bs, float *chunk_parts, cudaStream_t st) {
     const int n_gb = (s->slice_num + ST_GB - 1) / ST_GB;
-    const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)ST_STAGES * 2 * ST_TILE_BYTES +
+    const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)ST_STAGES * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
     static size_t smem_set = 0;
     if (smem > smem_set) {
@@ -336,8 +311,8 @@ int launch_slice_tc(const haet_layer_shape *s, const float *xp, const float *ws,
     const char *env = getenv("HAET_ST_RAISE");   // test hook: force the accumulator-rescale path
     const float raise_thr = env ? (float)atof(env) : ST_RAISE;
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads));
-    slice_tc_kernel<<<grid, ST_THREADS, smem, st>>>(xp, ws, bs, wt, bt, s->base_temp, rep_slice_shift(s->epsilon), s->N,
-                                                     s->heads, s->slice_num, chunk_pts, raise_thr, chunk_parts);
+    slice_tc_kernel<<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
+                                                     s->slice_num, chunk_pts, raise_thr, chunk_parts);
     HAET_LAUNCHED();
     return HAET_OK;
 }

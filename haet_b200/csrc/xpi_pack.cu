@@ -1,0 +1,86 @@
+// The per-point spill of the tensor-core path (layout in common.cuh) and the SIMT packer that builds it from
+// fp32 projected points (used behind the conv front-ends; the Linear front-end writes the image straight from
+// the in-projection GEMM's epilogue, gemm_tc.cu).
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+
+namespace haet {
+
+bool spill_needs_xp(const haet_layer_shape *s) {
+    const int inner = s->heads * s->dim_head;
+    return true ||   // TRANSITION: the deslice kernel still reads fp32 x_proj
+           g_path != 0 || s->conv_nd != 0 || !slice_tc_supported(s) || !deslice_tc_supported(s) ||
+           !gemm_tc_supported(s->dim, inner);
+}
+
+static bool spill_has_image(const haet_layer_shape *s) { return slice_tc_supported(s) && deslice_tc_supported(s); }
+
+SpillView spill_view(const haet_layer_shape *s, void *base) {
+    SpillView v;
+    v.npad = xpi_npad(s->N);
+    const int64_t rows = spill_has_image(s) ? s->B * s->heads * v.npad : 0;
+    char *p = (char *)base;
+    v.img = (uint8_t *)p;
+    p += align_up(rows * XPI_ROW_BYTES, 256);
+    v.scale = (float *)p;
+    p += align_up(rows * (int64_t)sizeof(float), 256);
+    v.xp = (float *)p;
+    return v;
+}
+
+// one thread per (b, h, row): 32 projected channels -> hi/lo fp16 image row + s_n
+__global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__ xp, const float *__restrict__ wt, float bt,
+                                                       float base_temp, int64_t N, int64_t npad, int H, int64_t rows,
+                                                       uint8_t *__restrict__ img, float *__restrict__ scale) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= rows) return;
+    const int64_t bh = t / npad, n = t - bh * npad;
+    const int b = (int)(bh / H), h = (int)(bh - (int64_t)b * H);
+    uint4 out[8];
+    float sn = 0.f;
+    if (n < N) {
+        const float4 *src = reinterpret_cast<const float4 *>(xp + ((int64_t)b * N + n) * (H * 32) + h * 32);
+        float d = bt;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {   // chunk j: channels 8j .. 8j+7
+            const float4 a = __ldg(src + 2 * j), c = __ldg(src + 2 * j + 1);
+            const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                d = fmaf(v[2 * i], __ldg(wt + 8 * j + 2 * i), d);
+                d = fmaf(v[2 * i + 1], __ldg(wt + 8 * j + 2 * i + 1), d);
+                const __half2 hh = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+                const float2 hf = __half22float2(hh);
+                const __half2 ll = __floats2half2_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
+                hi[i] = *reinterpret_cast<const uint32_t *>(&hh);
+                lo[i] = *reinterpret_cast<const uint32_t *>(&ll);
+            }
+            out[j] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            out[4 + j] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+        const float tau = base_temp + fminf(fmaxf(d, -0.4f), 0.4f);   // Ada-Temp (IrregularMesh.py:168)
+        sn = kLog2e / tau;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) out[j] = make_uint4(0, 0, 0, 0);
+    }
+    uint8_t *row = img + t * XPI_ROW_BYTES;
+    const int sw = (int)(n & 7);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4 *>(row + ((j ^ sw) << 4)) = out[j];
+    scale[t] = sn;
+}
+
+int launch_xpi_pack(const haet_layer_shape *s, const float *xp, const float *wt, float bt, uint8_t *img, float *scale,
+                    cudaStream_t st) {
+    HAET_CHECK_ARG(s->dim_head == 32, "the operand image needs dim_head == 32");
+    const int64_t npad = xpi_npad(s->N), rows = s->B * s->heads * npad;
+    if (rows == 0) return HAET_OK;
+    xpi_pack_kernel<<<(unsigned)cdiv(rows, 256), 256, 0, st>>>(xp, wt, bt, s->base_temp, s->N, npad, s->heads, rows, img, scale);
+    HAET_LAUNCHED();
+    return HAET_OK;
+}
+
+}  // namespace haet
