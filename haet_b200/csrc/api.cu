@@ -147,13 +147,19 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
     float *parts = (float *)workspace_d;
     void *img = (char *)workspace_d + slice_parts_bytes(s);
     const int inner = s->heads * s->dim_head;
-    if (g_path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
-        rc = launch_gemm_tc(x_d, wx_d, bx_d, xp, s->B * s->N, s->dim, inner, img, st);
-    else
-        rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
+    const bool tc = g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s);
+    if (tc && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner)) {
+        // Linear front-end: the GEMM epilogue writes the operand image directly
+        rc = launch_inproj_tc(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st);
+    } else {
+        if (g_path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
+            rc = launch_gemm_tc(x_d, wx_d, bx_d, xp, s->B * s->N, s->dim, inner, img, st);
+        else
+            rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
+        if (!rc && tc) rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st);
+    }
     if (rc) return rc;
-    if (g_path == 0 && slice_tc_supported(s)) {
-        if ((rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st))) return rc;
+    if (tc) {
         if ((rc = launch_slice_tc(s, sv.img, sv.scale, ws_d, bs_d, parts, st))) return rc;
         return launch_slice_merge(s, parts, slice_tc_chunks(s), partial_d, nullptr, nullptr, st);
     }
@@ -181,8 +187,8 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
     cudaStream_t st = (cudaStream_t)stream;
     float *o = (float *)workspace_d;
     const SpillView sv = spill_view(s, const_cast<void *>(spill_d));
-    if (g_path == 0 && deslice_tc_supported(s))
-        rc = launch_deslice_tc(s, sv.xp, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
+    if (g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s))
+        rc = launch_deslice_tc(s, sv.img, sv.scale, lse2_d, states_d, ws_d, bs_d, o, st);
     else
         rc = launch_deslice(s, sv.xp, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
     if (rc) return rc;

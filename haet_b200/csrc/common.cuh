@@ -74,13 +74,15 @@ bool gemm_tc_supported(int K, int Nn);
 int64_t gemm_tc_image_bytes(int K, int Nn);
 int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
                    cudaStream_t st);
+int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
+                     uint8_t *xpi, float *scale, void *img, cudaStream_t st);
 bool slice_tc_supported(const haet_layer_shape *s);
 int64_t slice_tc_chunks(const haet_layer_shape *s);
 int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,
                     const float *bs, float *chunk_parts, cudaStream_t st);
 bool deslice_tc_supported(const haet_layer_shape *s);
-int launch_deslice_tc(const haet_layer_shape *s, const float *xp, const float *lse2, const float *states,
-                      const float *ws, const float *bs, const float *wt, float bt, float *o, cudaStream_t st);
+int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
+                      const float *states, const float *ws, const float *bs, float *o, cudaStream_t st);
 extern int g_path;   // 0: tensor-core kernels where supported; 1: fp32 SIMT kernels everywhere
 int64_t slice_chunks(const haet_layer_shape *s);
 int launch_slice_partial(const haet_layer_shape *s, const float *xp, const float *ws, const float *bs,

@@ -2,11 +2,14 @@
 // (IrregularMesh.py:221-232; the N x G weight matrix is recomputed tile by tile, never materialised).
 //
 // Points on the TMEM lanes (thread = point, so s_n = log2e / tau_n is a register):
-//   MMA1 (kind::f16, 3-term bf16 split): D[n, g] = x_proj[n,:] . Ws[g,:]      M = 128 points, N = 64 slices, K' = 96
+//   MMA1 (kind::f16, 3-term fp16 split): D[n, g] = x_proj[n,:] . Ws[g,:]      M = 128 points, N = 64 slices, K' = 96
+//        (A = a 128-point tile of the spill's operand image, common.cuh, brought in by one bulk copy)
 //   softmax warps: P = 2^((D + bc_g) * s_n - lse2_g) -> TMEM in place (per-column constants from shared memory)
 //   MMA2 (kind::tf32, A = P from TMEM, B = S'_h as MN-major fp32): O[n, c] += sum_g P[n, g] S'[g, c]
 // CTA = (b, h, chunk of points): the Ws and S'_h operand images are built once and stay resident; the x_proj
-// head slice streams through a 4-stage ring; O is double-buffered in TMEM and stored by the producer warps.
+// head slice streams through a 4-stage ring of bulk copies; O is double-buffered in TMEM and stored by 4 epilogue warps.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -17,10 +20,9 @@ constexpr int DT_C = 32;
 constexpr int DT_TILE = 128;        // points per tile (UMMA M)
 constexpr int DT_GC = 64;           // slices per item (UMMA N of MMA1, K of MMA2)
 constexpr int DT_STAGES = 4;
-constexpr int DT_THREADS = 416;
+constexpr int DT_THREADS = 448;     // 8 softmax warps + 4 epilogue warps + MMA warp + loader warp
 constexpr int DT_MAX_G = 512;
 constexpr int DT_TILE_BYTES = DT_TILE * 128;
-constexpr int DT_EPI_LAG = 3;       // the producer warps store tile t - 3 after producing tile t
 
 struct DesliceCtl {
     uint64_t a_full[DT_STAGES], a_empty[DT_STAGES];
@@ -32,14 +34,14 @@ struct DesliceCtl {
 __device__ __forceinline__ uint32_t dt_dbuf_col(int wg, int buf) { return 128u + (uint32_t)(wg * 2 + buf) * DT_GC; }
 
 __global__ void __launch_bounds__(DT_THREADS, 1)
-deslice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ lse2, const float *__restrict__ states,
-                  const float *__restrict__ ws, const float *__restrict__ bs, const float *__restrict__ wt, float bt,
-                  float base_temp, float shift, int64_t N, int H, int G, int64_t chunk_pts, float *__restrict__ o) {
+deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
+                  const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
+                  int64_t N, int64_t npad, int H, int G, int64_t chunk_pts, float *__restrict__ o) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int n_gc = (G + DT_GC - 1) / DT_GC;
     const int g_pad = n_gc * DT_GC;
-    uint8_t *sW = smem;                                     // [g_pad rows][hi(32 bf16) | lo(32 bf16)]  K-major SW128
+    uint8_t *sW = smem;                                     // [g_pad rows][hi(32 fp16) | lo(32 fp16)]  K-major SW128
     uint8_t *sV = sW + (size_t)g_pad * 128;                 // [g_pad rows][32 fp32]  S'_h, MN-major SW128_BASE32B
     uint8_t *sA = sV + (size_t)g_pad * 128;                 // [stages][128 rows][hi | lo]
     float2 *sC = reinterpret_cast<float2 *>(sA + (size_t)DT_STAGES * DT_TILE_BYTES);   // [g_pad] {bc_g, -lse2_g}
@@ -54,7 +56,7 @@ deslice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ lse2, 
 
     if (warp == 12) {
         if (lane == 0) {
-            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 128); mbar_init(&ctl->a_empty[s], 1); }
+            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 1); }
             for (int w = 0; w < 2; ++w) {
                 for (int k = 0; k < 2; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
                 mbar_init(&ctl->o_full[w], 1);
@@ -68,12 +70,13 @@ deslice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ lse2, 
     // resident operand images: Ws rows [hi | lo] and S'_h rows (tf32-rounded), per-column constants
     for (int idx = threadIdx.x; idx < g_pad * 4; idx += DT_THREADS) {
         const int g = idx >> 2, ck = idx & 3;
-        __align__(16) __nv_bfloat16 hi[8], lo[8];
+        __align__(16) __half hi[8], lo[8];
         __align__(16) float sv[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const float v = g < G ? ws[(size_t)g * DT_C + ck * 8 + i] : 0.f;
-            split_bf16(v, hi[i], lo[i]);
+            hi[i] = __float2half_rn(v);
+            lo[i] = __float2half_rn(v - __half2float(hi[i]));
             const float s = g < G ? states[((size_t)bh * G + g) * DT_C + ck * 8 + i] : 0.f;
             uint32_t u;
             asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(s));
@@ -93,15 +96,11 @@ deslice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ lse2, 
     const uint32_t tmem_base = ctl->tmem_base;
 
     if (warp >= 8 && warp < 12) {
-        // =========================== producers + O epilogue ===========================
+        // =========================== O epilogue: TMEM -> global ===========================
         const int r = threadIdx.x - 256;   // row of the tile == TMEM lane
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-        float wtr[DT_C];
-#pragma unroll
-        for (int i = 0; i < DT_C; ++i) wtr[i] = wt[i];
-        const float *src = xp + ((int64_t)b * N) * inner + h * DT_C;
         float *dst = o + ((int64_t)b * N) * inner + h * DT_C;
-        auto epilogue = [&](int te) {
+        for (int te = 0; te < n_tiles; ++te) {
             const int ob = te & 1;
             mbar_wait(&ctl->o_full[ob], (uint32_t)((te >> 1) & 1));
             tc_fence_after();
@@ -118,59 +117,34 @@ deslice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ lse2, 
                     p[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
                                        __uint_as_float(v[4 * i + 3]));
             }
-        };
-        float4 cur[8], nxt[8];
-        auto load = [&](int t, float4 (&v)[8]) {
-            const int64_t n = n_begin + (int64_t)t * DT_TILE + r;
-            if (t < n_tiles && n < n_end) {
-                const float4 *p = reinterpret_cast<const float4 *>(src + n * inner);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = __ldg(p + i);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        };
-        load(0, cur);
-        int stage = 0, phase = 0;
-        for (int t = 0; t < n_tiles; ++t) {
-            load(t + 1, nxt);
-            mbar_wait(&ctl->a_empty[stage], phase ^ 1);
-            const bool valid = n_begin + (int64_t)t * DT_TILE + r < n_end;
-            const float *f = reinterpret_cast<const float *>(cur);
-            float d = bt;
-#pragma unroll
-            for (int i = 0; i < DT_C; ++i) d = fmaf(f[i], wtr[i], d);
-            const float tau = base_temp + fminf(fmaxf(d, -0.4f), 0.4f);
-            sS[stage * DT_TILE + r] = valid ? kLog2e / tau : 0.f;
-            uint8_t *a = sA + (size_t)stage * DT_TILE_BYTES;
-            __align__(16) __nv_bfloat16 hi[DT_C], lo[DT_C];
-#pragma unroll
-            for (int i = 0; i < DT_C; ++i) split_bf16(f[i], hi[i], lo[i]);
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                *reinterpret_cast<uint4 *>(a + sw128_off(r, c)) = reinterpret_cast<const uint4 *>(hi)[c];
-                *reinterpret_cast<uint4 *>(a + sw128_off(r, 4 + c)) = reinterpret_cast<const uint4 *>(lo)[c];
-            }
-            fence_proxy_async();
-            mbar_arrive(&ctl->a_full[stage]);
-            if (++stage == DT_STAGES) { stage = 0; phase ^= 1; }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
-            if (t >= DT_EPI_LAG) epilogue(t - DT_EPI_LAG);
         }
-        for (int te = max(0, n_tiles - DT_EPI_LAG); te < n_tiles; ++te) epilogue(te);
+    } else if (warp == 13) {
+        // =========================== loader: one bulk copy per 128-point tile (+ its s_n) ===========================
+        if (lane == 0) {
+            const uint8_t *src = img + ((int64_t)bh * npad + n_begin) * XPI_ROW_BYTES;
+            const float *ssrc = scale + (int64_t)bh * npad + n_begin;
+            int stage = 0, phase = 0;
+            for (int t = 0; t < n_tiles; ++t) {
+                mbar_wait(&ctl->a_empty[stage], phase ^ 1);
+                mbar_arrive_expect_tx(&ctl->a_full[stage], DT_TILE_BYTES + DT_TILE * 4);
+                bulk_g2s(sA + (size_t)stage * DT_TILE_BYTES, src + (size_t)t * DT_TILE_BYTES, DT_TILE_BYTES, &ctl->a_full[stage]);
+                bulk_g2s(sS + stage * DT_TILE, ssrc + (size_t)t * DT_TILE, DT_TILE * 4, &ctl->a_full[stage]);
+                if (++stage == DT_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+        __syncwarp();
     } else if (warp == 12) {
         // =========================== MMA issuer ===========================
         if (lane == 0) {
-            const uint32_t id1 = instr_desc(FMT_BF16, DT_TILE, DT_GC, false, false);
+            const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, DT_GC, false, false);
             const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
             const uint32_t wbase = smem_u32(sW), vbase = smem_u32(sV);
             const int Q = n_tiles * n_gc;
+            const int LAG = (n_gc & 1) ? (n_gc == 1 ? 2 : 3) : 4;   // see slice_tc.cu
             int cnt1[2] = {0, 0}, cnt2[2] = {0, 0};
-            for (int q = 0; q < Q + 2; ++q) {
-                if (q >= 2) {   // ---- MMA2 of item q-2: O += P . S'_h[g-chunk]
-                    const int qq = q - 2, t = qq / n_gc, j = qq - t * n_gc, w = j & 1, k = cnt2[w]++;
+            for (int q = 0; q < Q + LAG; ++q) {
+                if (q >= LAG) {   // ---- MMA2 of item q-LAG: O += P . S'_h[g-chunk]
+                    const int qq = q - LAG, t = qq / n_gc, j = qq - t * n_gc, w = j & 1, k = cnt2[w]++;
                     const int buf = k & 1, stage = t % DT_STAGES, ob = t & 1;
                     if (j == 0) { mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t >> 1) & 1) ^ 1)); }
                     mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
@@ -245,8 +219,8 @@ deslice_tc_kernel(const float *__restrict__ xp, const float *__restrict__ lse2, 
 
 bool deslice_tc_supported(const haet_layer_shape *s) { return s->dim_head == DT_C && s->slice_num <= DT_MAX_G; }
 
-int launch_deslice_tc(const haet_layer_shape *s, const float *xp, const float *lse2, const float *states,
-                      const float *ws, const float *bs, const float *wt, float bt, float *o, cudaStream_t st) {
+int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
+                      const float *states, const float *ws, const float *bs, float *o, cudaStream_t st) {
     if (s->N == 0 || s->B == 0) return HAET_OK;
     const int n_gc = (s->slice_num + DT_GC - 1) / DT_GC, g_pad = n_gc * DT_GC;
     const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + sizeof(float2) * g_pad +
@@ -266,8 +240,8 @@ int launch_deslice_tc(const haet_layer_shape *s, const float *xp, const float *l
     if (n_chunks > max_chunks) n_chunks = max_chunks;
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
-    deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(xp, lse2, states, ws, bs, wt, bt, s->base_temp,
-                                                       rep_slice_shift(s->epsilon), s->N, s->heads, s->slice_num, chunk_pts, o);
+    deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
+                                                       xpi_npad(s->N), s->heads, s->slice_num, chunk_pts, o);
     HAET_LAUNCHED();
     return HAET_OK;
 }

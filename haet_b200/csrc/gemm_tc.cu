@@ -1,4 +1,4 @@
-// tcgen05 GEMM with fp32-class accuracy: Y[M, Nn] = X[M, K] . W[Nn, K]^T + bias, X / Y fp32 in HBM.
+// tcgen05 GEMM with fp32-class accuracy: Y[M, Nn] = X[M, K] . W[Nn, K]^T + bias, X fp32 in HBM.
 // Used for in_project_x (IrregularMesh.py:157) and to_out (:235).
 //
 // Accuracy: the Rep-Slice softmax divides the logits by tau >= 0.1 and exponentiates, so rounding the
@@ -8,10 +8,15 @@
 //
 // Mapping (persistent, one CTA per SM): CTA = (worker, column half).  The CTA's half of W (hi and lo,
 // <= 128 KB) is bulk-copied ONCE into shared memory as ready-made SWIZZLE_128B K-major panels and stays
-// resident; the CTA then walks 128-row tiles of X.  Warp roles: 4 producer warps (coalesced LDG of fp32
-// X, hi/lo split, swizzled STS), 1 MMA warp (one thread issues tcgen05.mma, accumulators double-buffered
-// in TMEM), 4 epilogue warps (tcgen05.ld, + bias, store).  mbarrier pipelines: a_full/a_empty per stage,
-// t_full/t_empty per accumulator buffer.
+// resident; the CTA then walks 128-row tiles of X.  Warp roles: 8 producer warps (coalesced LDG of fp32 X two
+// panels ahead in registers, hi/lo split, swizzled STS), 1 MMA warp (one thread issues tcgen05.mma, accumulators
+// double-buffered in TMEM), 4 epilogue warps (tcgen05.ld, + bias, store).  mbarrier pipelines: a_full/a_empty
+// per stage, t_full/t_empty per accumulator buffer.
+// Epilogues: EPI_F32 stores fp32 rows (to_out); EPI_IMG is the in-projection of the tensor-core path: per head it
+// adds the bias, evaluates Ada-Temp (s_n = log2 e / tau_n) and writes the spill's fp16 hi/lo operand image
+// (common.cuh) instead of fp32 rows, so that passes 1 and 2 bulk-copy their MMA operands.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -21,9 +26,12 @@ using namespace tc;
 constexpr int GT_M = 128;          // rows per tile (UMMA M)
 constexpr int GT_N = 128;          // output columns per CTA (UMMA N)
 constexpr int GT_KP = 64;          // k per panel: 64 bf16 = one 128-byte swizzle row
-constexpr int GT_STAGES = 2;
+constexpr int GT_STAGES = 3;
 constexpr int GT_PANEL_BYTES = GT_M * 128;   // 16 KB: 128 rows x 128 B
-constexpr int GT_THREADS = 288;
+constexpr int GT_PROD = 256;       // producer threads (warps 0-7)
+constexpr int GT_THREADS = GT_PROD + 32 + 128;   // + MMA warp (8) + epilogue warps (9-12)
+constexpr int GT_LD = GT_M * GT_KP / 4 / GT_PROD;   // float4 per producer thread per panel (8)
+enum { EPI_F32 = 0, EPI_IMG = 1 };
 
 // W [Nn, K] fp32 -> image [Nn/128 halves][K/64 panels][hi, lo][128 rows x 128 B swizzled]
 __global__ void gemm_tc_pack_kernel(const float *__restrict__ w, int Nn, int K, uint8_t *__restrict__ img) {
@@ -42,6 +50,26 @@ __global__ void gemm_tc_pack_kernel(const float *__restrict__ w, int Nn, int K, 
     *reinterpret_cast<uint4 *>(base + GT_PANEL_BYTES) = *reinterpret_cast<const uint4 *>(lo);
 }
 
+// zero the pad rows [N, npad) of every (b, h) of the spill image and their scales
+__global__ void xpi_pad_kernel(uint8_t *__restrict__ img, float *__restrict__ scale, int64_t N, int64_t npad, int64_t bh_count) {
+    const int64_t pad = npad - N;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // one thread per 16-B chunk of a pad row
+    if (t >= bh_count * pad * 8) return;
+    const int64_t rowi = t >> 3, bh = rowi / pad, n = N + (rowi - bh * pad);
+    const int64_t row = bh * npad + n;
+    *reinterpret_cast<uint4 *>(img + row * XPI_ROW_BYTES + ((t & 7) << 4)) = make_uint4(0, 0, 0, 0);
+    if ((t & 7) == 0) scale[row] = 0.f;
+}
+
+struct GemmEpi {   // EPI_IMG arguments
+    uint8_t *img;
+    float *scale;
+    const float *wt;
+    float bt, base_temp;
+    int64_t N, npad;   // rows m = b * N + n
+    int H;
+};
+
 struct GemmSmem {   // control block placed after the tiles
     uint64_t w_full;
     uint64_t a_full[GT_STAGES], a_empty[GT_STAGES];
@@ -49,9 +77,10 @@ struct GemmSmem {   // control block placed after the tiles
     uint32_t tmem_base;
 };
 
+template <int EPI>
 __global__ void __launch_bounds__(GT_THREADS, 1)
 gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
-               float *__restrict__ Y, int64_t M, int K, int Nn, int n_workers) {
+               float *__restrict__ Y, int64_t M, int K, int Nn, int n_workers, GemmEpi ep) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const int panels = K / GT_KP;
@@ -62,11 +91,12 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int half = blockIdx.x % n_halves, worker = blockIdx.x / n_halves;
     const int64_t n_tiles = (M + GT_M - 1) / GT_M;
+    const int64_t my_tiles = worker < n_tiles ? (n_tiles - worker + n_workers - 1) / n_workers : 0;
 
-    if (warp == 4) {
+    if (warp == 8) {
         if (lane == 0) {
             mbar_init(&cb->w_full, 1);
-            for (int s = 0; s < GT_STAGES; ++s) { mbar_init(&cb->a_full[s], 128); mbar_init(&cb->a_empty[s], 1); }
+            for (int s = 0; s < GT_STAGES; ++s) { mbar_init(&cb->a_full[s], GT_PROD); mbar_init(&cb->a_empty[s], 1); }
             for (int b = 0; b < 2; ++b) { mbar_init(&cb->t_full[b], 1); mbar_init(&cb->t_empty[b], 128); }
             fence_barrier_init();
         }
@@ -78,44 +108,58 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     tc_fence_after();
     const uint32_t tmem_base = cb->tmem_base;
 
-    if (warp < 4) {
+    if (warp < 8) {
         // ---------------- producers: X tile panel -> bf16 hi/lo, SWIZZLE_128B K-major ----------------
         const int tid = threadIdx.x;
+        const int64_t total = my_tiles * panels;   // (tile, panel) items of this CTA, in order
+        auto load = [&](int64_t it, float4 (&v)[GT_LD]) {
+            if (it >= total) return;
+            const int64_t tile = worker + (it / panels) * n_workers;
+            const int p = (int)(it % panels);
+#pragma unroll
+            for (int i = 0; i < GT_LD; ++i) {
+                const int idx = i * GT_PROD + tid, row = idx >> 4, c4 = idx & 15;
+                const int64_t m = tile * GT_M + row;
+                v[i] = (m < M) ? __ldg(reinterpret_cast<const float4 *>(X + m * K + p * GT_KP + c4 * 4))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        };
         int stage = 0, phase = 0;
-        for (int64_t tile = worker; tile < n_tiles; tile += n_workers) {
-            for (int p = 0; p < panels; ++p) {
-                mbar_wait(&cb->a_empty[stage], phase ^ 1);
-                uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
-                float4 v[16];
+        auto store = [&](const float4 (&v)[GT_LD]) {
+            mbar_wait(&cb->a_empty[stage], phase ^ 1);
+            uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int idx = i * 128 + tid, row = idx >> 4, c4 = idx & 15;
-                    const int64_t m = tile * GT_M + row;
-                    v[i] = (m < M) ? __ldg(reinterpret_cast<const float4 *>(X + m * K + p * GT_KP + c4 * 4))
-                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const int idx = i * 128 + tid, row = idx >> 4, c4 = idx & 15;
-                    __nv_bfloat16 h0, h1, h2, h3, l0, l1, l2, l3;
-                    split_bf16(v[i].x, h0, l0); split_bf16(v[i].y, h1, l1);
-                    split_bf16(v[i].z, h2, l2); split_bf16(v[i].w, h3, l3);
-                    __nv_bfloat162 ha = __halves2bfloat162(h0, h1), hb = __halves2bfloat162(h2, h3);
-                    __nv_bfloat162 la = __halves2bfloat162(l0, l1), lb = __halves2bfloat162(l2, l3);
-                    const uint32_t off = sw128_off(row, c4 >> 1) + (c4 & 1) * 8;
-                    uint2 hv = make_uint2(*reinterpret_cast<uint32_t *>(&ha), *reinterpret_cast<uint32_t *>(&hb));
-                    uint2 lv = make_uint2(*reinterpret_cast<uint32_t *>(&la), *reinterpret_cast<uint32_t *>(&lb));
-                    *reinterpret_cast<uint2 *>(hi_base + off) = hv;
-                    *reinterpret_cast<uint2 *>(hi_base + GT_PANEL_BYTES + off) = lv;
-                }
-                fence_proxy_async();
-                mbar_arrive(&cb->a_full[stage]);
-                if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+            for (int i = 0; i < GT_LD; ++i) {
+                const int idx = i * GT_PROD + tid, row = idx >> 4, c4 = idx & 15;
+                const __nv_bfloat162 ha = __floats2bfloat162_rn(v[i].x, v[i].y), hb = __floats2bfloat162_rn(v[i].z, v[i].w);
+                const uint32_t ua = *reinterpret_cast<const uint32_t *>(&ha), ub = *reinterpret_cast<const uint32_t *>(&hb);
+                const __nv_bfloat162 la = __floats2bfloat162_rn(v[i].x - __uint_as_float(ua << 16),
+                                                                v[i].y - __uint_as_float(ua & 0xffff0000u));
+                const __nv_bfloat162 lb = __floats2bfloat162_rn(v[i].z - __uint_as_float(ub << 16),
+                                                                v[i].w - __uint_as_float(ub & 0xffff0000u));
+                const uint32_t off = sw128_off(row, c4 >> 1) + (c4 & 1) * 8;
+                *reinterpret_cast<uint2 *>(hi_base + off) = make_uint2(ua, ub);
+                *reinterpret_cast<uint2 *>(hi_base + GT_PANEL_BYTES + off) =
+                    make_uint2(*reinterpret_cast<const uint32_t *>(&la), *reinterpret_cast<const uint32_t *>(&lb));
+            }
+            fence_proxy_async();
+            mbar_arrive(&cb->a_full[stage]);
+            if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+        };
+        float4 va[GT_LD], vb[GT_LD];
+        load(0, va);
+        load(1, vb);
+        for (int64_t it = 0; it < total; it += 2) {
+            store(va);
+            load(it + 2, va);
+            if (it + 1 < total) {
+                store(vb);
+                load(it + 3, vb);
             }
         }
-    } else if (warp == 4) {
+    } else if (warp == 8) {
         // ---------------- MMA issuer ----------------
-        if (lane == 0) {
+        if (lane == 0 && my_tiles > 0) {
             const uint32_t wbytes = (uint32_t)panels * 2 * GT_PANEL_BYTES;
             mbar_arrive_expect_tx(&cb->w_full, wbytes);
             const uint8_t *src = Wimg + (size_t)half * wbytes;
@@ -124,8 +168,7 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
             mbar_wait(&cb->w_full, 0);
             const uint32_t idesc = instr_desc(FMT_BF16, GT_M, GT_N, false, false);
             int stage = 0, phase = 0;
-            int64_t it = 0;
-            for (int64_t tile = worker; tile < n_tiles; tile += n_workers, ++it) {
+            for (int64_t it = 0; it < my_tiles; ++it) {
                 const int buf = (int)(it & 1);
                 mbar_wait(&cb->t_empty[buf], (uint32_t)(((it >> 1) & 1) ^ 1));
                 tc_fence_after();
@@ -154,28 +197,69 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
         __syncwarp();
     } else {
         // ---------------- epilogue: TMEM -> registers -> + bias -> global ----------------
-        const int q = warp & 3;   // TMEM lane quarter this warp may access
-        int64_t it = 0;
-        for (int64_t tile = worker; tile < n_tiles; tile += n_workers, ++it) {
+        const int q = warp & 3;   // TMEM lane quarter this warp may access (warps 9..12 -> 1, 2, 3, 0)
+        float wtr[32];
+        if (EPI == EPI_IMG) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) wtr[i] = __ldg(ep.wt + i);
+        }
+        for (int64_t it = 0; it < my_tiles; ++it) {
+            const int64_t tile = worker + it * n_workers;
             const int buf = (int)(it & 1);
             mbar_wait(&cb->t_full[buf], (uint32_t)((it >> 1) & 1));
             tc_fence_after();
             const int64_t m = tile * GT_M + q * 32 + lane;
-            float *yrow = Y + m * Nn + half * GT_N;
+            int64_t bi = 0, n = 0;
+            if (EPI == EPI_IMG) { bi = m / ep.N; n = m - bi * ep.N; }
 #pragma unroll 1
             for (int c0 = 0; c0 < GT_N; c0 += 32) {
                 uint32_t r[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * GT_N + c0), r);
                 tmem_wait_ld();
                 if (m < M) {
+                    const float4 *b4 = reinterpret_cast<const float4 *>(bias + half * GT_N + c0);
+                    if (EPI == EPI_F32) {
+                        float *yrow = Y + m * Nn + half * GT_N;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        float4 o;
-                        o.x = __uint_as_float(r[j]) + __ldg(bias + half * GT_N + c0 + j);
-                        o.y = __uint_as_float(r[j + 1]) + __ldg(bias + half * GT_N + c0 + j + 1);
-                        o.z = __uint_as_float(r[j + 2]) + __ldg(bias + half * GT_N + c0 + j + 2);
-                        o.w = __uint_as_float(r[j + 3]) + __ldg(bias + half * GT_N + c0 + j + 3);
-                        *reinterpret_cast<float4 *>(yrow + c0 + j) = o;
+                        for (int j = 0; j < 32; j += 4) {
+                            const float4 bb = __ldg(b4 + (j >> 2));
+                            float4 o;
+                            o.x = __uint_as_float(r[j]) + bb.x;
+                            o.y = __uint_as_float(r[j + 1]) + bb.y;
+                            o.z = __uint_as_float(r[j + 2]) + bb.z;
+                            o.w = __uint_as_float(r[j + 3]) + bb.w;
+                            *reinterpret_cast<float4 *>(yrow + c0 + j) = o;
+                        }
+                    } else {
+                        // one head: + bias, Ada-Temp, fp16 hi/lo image row (chunk j -> position j ^ (n & 7))
+                        const int h = (half * GT_N + c0) >> 5;
+                        const int64_t row = (bi * ep.H + h) * ep.npad + n;
+                        uint8_t *dst = ep.img + row * XPI_ROW_BYTES;
+                        const int sw = (int)(n & 7);
+                        float d = ep.bt;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float4 ba = __ldg(b4 + 2 * j), bb = __ldg(b4 + 2 * j + 1);
+                            const float v[8] = {__uint_as_float(r[8 * j]) + ba.x,     __uint_as_float(r[8 * j + 1]) + ba.y,
+                                                __uint_as_float(r[8 * j + 2]) + ba.z, __uint_as_float(r[8 * j + 3]) + ba.w,
+                                                __uint_as_float(r[8 * j + 4]) + bb.x, __uint_as_float(r[8 * j + 5]) + bb.y,
+                                                __uint_as_float(r[8 * j + 6]) + bb.z, __uint_as_float(r[8 * j + 7]) + bb.w};
+                            uint32_t hi[4], lo[4];
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                d = fmaf(v[2 * i], wtr[8 * j + 2 * i], d);
+                                d = fmaf(v[2 * i + 1], wtr[8 * j + 2 * i + 1], d);
+                                const __half2 hh = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+                                const float2 hf = __half22float2(hh);
+                                const __half2 ll = __floats2half2_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
+                                hi[i] = *reinterpret_cast<const uint32_t *>(&hh);
+                                lo[i] = *reinterpret_cast<const uint32_t *>(&ll);
+                            }
+                            *reinterpret_cast<uint4 *>(dst + ((j ^ sw) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                            *reinterpret_cast<uint4 *>(dst + (((4 + j) ^ sw) << 4)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                        }
+                        const float tau = ep.base_temp + fminf(fmaxf(d, -0.4f), 0.4f);   // Ada-Temp (IrregularMesh.py:168)
+                        ep.scale[row] = kLog2e / tau;
                     }
                 }
             }
@@ -185,7 +269,7 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == 8) {
         tc_fence_after();
         tmem_dealloc<256>(tmem_base);
     }
@@ -207,8 +291,9 @@ static int sm_count() {
 }
 
 // img: scratch of gemm_tc_image_bytes(K, Nn) bytes (the packed weights; rebuilt each call, ~2 us)
-int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
-                   cudaStream_t st) {
+template <int EPI>
+static int launch_gemm_impl(const float *x, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
+                            const GemmEpi &ep, cudaStream_t st) {
     if (M == 0) return HAET_OK;
     HAET_CHECK_ARG(gemm_tc_supported(K, Nn), "gemm_tc: unsupported K=%d Nn=%d", K, Nn);
     const int chunks = Nn * (K / 8);
@@ -218,16 +303,37 @@ int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, 
     const size_t smem = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + sizeof(GemmSmem);
     static size_t smem_set = 0;
     if (smem > smem_set) {
-        HAET_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        HAET_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set = smem;
     }
     const int64_t n_tiles = (M + GT_M - 1) / GT_M;
     int n_workers = sm_count() / n_halves;
     if (n_workers < 1) n_workers = 1;
     if (n_workers > n_tiles) n_workers = (int)n_tiles;
-    gemm_tc_kernel<<<n_workers * n_halves, GT_THREADS, smem, st>>>(x, (const uint8_t *)img, bias, y, M, K, Nn, n_workers);
+    gemm_tc_kernel<EPI><<<n_workers * n_halves, GT_THREADS, smem, st>>>(x, (const uint8_t *)img, bias, y, M, K, Nn, n_workers, ep);
     HAET_LAUNCHED();
     return HAET_OK;
+}
+
+int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
+                   cudaStream_t st) {
+    GemmEpi ep{};
+    return launch_gemm_impl<EPI_F32>(x, w, bias, y, M, K, Nn, img, ep, st);
+}
+
+// in_project_x of the tensor-core path: X [B*N, dim] -> the spill's operand image + scales (no fp32 x_proj)
+int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
+                     uint8_t *xpi, float *scale, void *img, cudaStream_t st) {
+    HAET_CHECK_ARG(s->dim_head == 32, "the operand image needs dim_head == 32");
+    GemmEpi ep{};
+    ep.img = xpi; ep.scale = scale; ep.wt = wt; ep.bt = bt; ep.base_temp = s->base_temp;
+    ep.N = s->N; ep.npad = xpi_npad(s->N); ep.H = s->heads;
+    const int64_t pad = ep.npad - ep.N, bh = s->B * s->heads;
+    if (pad > 0 && bh > 0) {
+        xpi_pad_kernel<<<(unsigned)cdiv(bh * pad * 8, 256), 256, 0, st>>>(xpi, scale, ep.N, ep.npad, bh);
+        HAET_LAUNCHED();
+    }
+    return launch_gemm_impl<EPI_IMG>(x, wx, bx, nullptr, s->B * s->N, s->dim, s->heads * s->dim_head, img, ep, st);
 }
 
 }  // namespace haet

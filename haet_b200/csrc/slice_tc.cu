@@ -117,10 +117,13 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
             const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
             const uint32_t id2 = instr_desc(FMT_F16, ST_GB, ST_SCOLS, false, true);
             const int Q = n_tiles * n_gb;
+            // MMA1 runs LAG items ahead of MMA2: far enough that both D buffers of a warpgroup are in flight, never so
+            // far that MMA1 would overwrite a D/P buffer whose MMA2 has not been issued yet
+            const int LAG = (n_gb & 1) ? (n_gb == 1 ? 2 : 3) : 4;
             int cnt1[2] = {0, 0}, cnt2[2] = {0, 0};
-            for (int q = 0; q < Q + 2; ++q) {
-                if (q >= 2) {   // ---- MMA2 of item q-2: S2_j += P . [hi | lo]
-                    const int qq = q - 2, t = qq / n_gb, j = qq - t * n_gb, w = j & 1, k = cnt2[w]++;
+            for (int q = 0; q < Q + LAG; ++q) {
+                if (q >= LAG) {   // ---- MMA2 of item q-LAG: S2_j += P . [hi | lo]
+                    const int qq = q - LAG, t = qq / n_gb, j = qq - t * n_gb, w = j & 1, k = cnt2[w]++;
                     const int buf = k & 1, stage = t % ST_STAGES;
                     mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
                     tc_fence_after();

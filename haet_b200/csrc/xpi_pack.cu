@@ -9,8 +9,7 @@ namespace haet {
 
 bool spill_needs_xp(const haet_layer_shape *s) {
     const int inner = s->heads * s->dim_head;
-    return true ||   // TRANSITION: the deslice kernel still reads fp32 x_proj
-           g_path != 0 || s->conv_nd != 0 || !slice_tc_supported(s) || !deslice_tc_supported(s) ||
+    return g_path != 0 || s->conv_nd != 0 || !slice_tc_supported(s) || !deslice_tc_supported(s) ||
            !gemm_tc_supported(s->dim, inner);
 }
 
