@@ -20,7 +20,7 @@ constexpr int DT_C = 32;
 constexpr int DT_TILE = 128;        // points per tile (UMMA M)
 constexpr int DT_GC = 64;           // slices per item (UMMA N of MMA1, K of MMA2)
 constexpr int DT_STAGES = 4;
-constexpr int DT_THREADS = 448;     // 8 softmax warps + 4 epilogue warps + MMA warp + loader warp
+constexpr int DT_THREADS = 480;     // 8 softmax warps + 4 epilogue warps + MMA warp 0 + loader warp + MMA warp 1
 constexpr int DT_MAX_G = 512;
 constexpr int DT_TILE_BYTES = DT_TILE * 128;
 
@@ -31,6 +31,7 @@ struct DesliceCtl {
     uint32_t tmem_base;
 };
 
+// TMEM columns: O accumulators [issuer][buffer] x 32 at 0..127, D / P buffers [warpgroup][buffer] x 64 at 128..383
 __device__ __forceinline__ uint32_t dt_dbuf_col(int wg, int buf) { return 128u + (uint32_t)(wg * 2 + buf) * DT_GC; }
 
 __global__ void __launch_bounds__(DT_THREADS, 1)
@@ -47,7 +48,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     float2 *sC = reinterpret_cast<float2 *>(sA + (size_t)DT_STAGES * DT_TILE_BYTES);   // [g_pad] {bc_g, -lse2_g}
     float *sS = reinterpret_cast<float *>(sC + g_pad);                                 // [stages][128] s_n
     DesliceCtl *ctl = reinterpret_cast<DesliceCtl *>(sS + DT_STAGES * DT_TILE);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
     const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
     const int inner = H * DT_C;
     const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
@@ -56,10 +57,11 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
 
     if (warp == 12) {
         if (lane == 0) {
-            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 1); }
+            const uint32_t n_issuers = n_gc > 1 ? 2 : 1;
+            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], n_issuers); }
             for (int w = 0; w < 2; ++w) {
                 for (int k = 0; k < 2; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
-                mbar_init(&ctl->o_full[w], 1);
+                mbar_init(&ctl->o_full[w], n_issuers);
                 mbar_init(&ctl->o_empty[w], 128);
             }
             fence_barrier_init();
@@ -106,7 +108,15 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             tc_fence_after();
             uint32_t v[32];
             tmem_ld32(tmem_base + lane_base + (uint32_t)ob * DT_C, v);
-            tmem_wait_ld();
+            if (n_gc > 1) {   // the second issue stream's share of the slices
+                uint32_t v1[32];
+                tmem_ld32(tmem_base + lane_base + (uint32_t)(2 + ob) * DT_C, v1);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v1[i]));
+            } else {
+                tmem_wait_ld();
+            }
             tc_fence_before();
             mbar_arrive(&ctl->o_empty[ob]);
             const int64_t n = n_begin + (int64_t)te * DT_TILE + r;
@@ -133,47 +143,55 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
         }
         __syncwarp();
-    } else if (warp == 12) {
-        // =========================== MMA issuer ===========================
-        if (lane == 0) {
-            const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, DT_GC, false, false);
-            const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
-            const uint32_t wbase = smem_u32(sW), vbase = smem_u32(sV);
-            const int Q = n_tiles * n_gc;
-            const int LAG = (n_gc & 1) ? (n_gc == 1 ? 2 : 3) : 4;   // see slice_tc.cu
-            int cnt1[2] = {0, 0}, cnt2[2] = {0, 0};
-            for (int q = 0; q < Q + LAG; ++q) {
-                if (q >= LAG) {   // ---- MMA2 of item q-LAG: O += P . S'_h[g-chunk]
-                    const int qq = q - LAG, t = qq / n_gc, j = qq - t * n_gc, w = j & 1, k = cnt2[w]++;
-                    const int buf = k & 1, stage = t % DT_STAGES, ob = t & 1;
-                    if (j == 0) { mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t >> 1) & 1) ^ 1)); }
-                    mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
-                    tc_fence_after();
-                    const uint32_t pa = tmem_base + dt_dbuf_col(w, buf), od = tmem_base + (uint32_t)ob * DT_C;
-                    const uint32_t vb = vbase + (uint32_t)j * DT_GC * 128;
+    } else if (warp == 12 || warp == 14) {
+        // =========================== MMA issuers ===========================
+        // warp 12 issues for softmax warpgroup 0 (slice chunks j = 0, 2, ..), warp 14 for warpgroup 1 (j = 1, 3, ..); each
+        // stream accumulates its chunks into its own O buffers (summed by the epilogue).  The whole warp runs the
+        // warp-uniform loop and one elected lane issues (see slice_tc.cu).
+        const int w = warp == 12 ? 0 : 1;
+        const int pw = (n_gc + 1 - w) >> 1;
+        const int Qw = n_tiles * pw;
+        const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, DT_GC, false, false);
+        const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
+        const uint32_t wbase = smem_u32(sW) >> 4, vbase = smem_u32(sV) >> 4, abase = smem_u32(sA) >> 4;
+        int t1 = 0, jj1 = 0, st1 = 0, ph1 = 0;   // MMA1 cursor
+        int t2 = 0, jj2 = 0, st2 = 0;            // MMA2 cursor
+        for (int q = 0; q < Qw + 2; ++q) {
+            if (q >= 2) {   // ---- MMA2 of this warpgroup's item q-2: O_w += P . S'_h[g-chunk]
+                const int k = q - 2, buf = k & 1, ob = t2 & 1;
+                if (jj2 == 0) mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t2 >> 1) & 1) ^ 1));
+                mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t pa = tmem_base + dt_dbuf_col(w, buf), od = tmem_base + (uint32_t)(w * 2 + ob) * DT_C;
+                    const uint32_t vb = vbase + (uint32_t)(w + 2 * jj2) * (DT_GC * 128 >> 4);
 #pragma unroll
                     for (int ks = 0; ks < DT_GC / 8; ++ks)
-                        mma_tf32_ts(od, pa + ks * 8, smem_desc_mn32(vb + ks * 1024, 512, 512), id2, (j | ks) != 0);
-                    if (j == n_gc - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[stage]); }
+                        mma_tf32_ts(od, pa + ks * 8, desc_u(vb + ks * 64, 512, 512, 1), id2, (jj2 | ks) != 0);
+                    if (jj2 == pw - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
                 }
-                if (q < Q) {    // ---- MMA1 of item q: D = x_proj . Ws[g-chunk]^T  (hi.hi + lo.hi + hi.lo)
-                    const int t = q / n_gc, j = q - t * n_gc, w = j & 1, k = cnt1[w]++;
-                    const int buf = k & 1, stage = t % DT_STAGES;
-                    if (j == 0) { mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1)); tc_fence_after(); }
-                    const uint32_t a = smem_u32(sA + (size_t)stage * DT_TILE_BYTES);
-                    const uint32_t wb = wbase + (uint32_t)j * DT_GC * 128;
+                __syncwarp();
+                if (++jj2 == pw) { jj2 = 0; ++t2; if (++st2 == DT_STAGES) st2 = 0; }
+            }
+            if (q < Qw) {    // ---- MMA1 of item q: D = x_proj . Ws[g-chunk]^T  (hi.hi + lo.hi + hi.lo)
+                const int buf = q & 1;
+                if (jj1 == 0) { mbar_wait(&ctl->a_full[st1], (uint32_t)ph1); tc_fence_after(); }
+                if (elect_one()) {
+                    const uint32_t a = abase + (uint32_t)st1 * (DT_TILE_BYTES >> 4);
+                    const uint32_t wb = wbase + (uint32_t)(w + 2 * jj1) * (DT_GC * 128 >> 4);
                     const uint32_t d = tmem_base + dt_dbuf_col(w, buf);
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks) {
-                        mma_bf16_ss(d, smem_desc_sw128(a + ks * 32, 16, 1024), smem_desc_sw128(wb + ks * 32, 16, 1024), id1, ks != 0);
-                        mma_bf16_ss(d, smem_desc_sw128(a + 64 + ks * 32, 16, 1024), smem_desc_sw128(wb + ks * 32, 16, 1024), id1, true);
-                        mma_bf16_ss(d, smem_desc_sw128(a + ks * 32, 16, 1024), smem_desc_sw128(wb + 64 + ks * 32, 16, 1024), id1, true);
+                        mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, ks != 0);
+                        mma_bf16_ss(d, desc_sw128_u(a + 4 + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, true);
+                        mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + 4 + ks * 2, 16, 1024), id1, true);
                     }
                     tc_commit(&ctl->d_full[w][buf]);
                 }
+                __syncwarp();
+                if (++jj1 == pw) { jj1 = 0; ++t1; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
             }
         }
-        __syncwarp();
     } else {
         // =========================== softmax warpgroups ===========================
         const int w = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;

@@ -13,7 +13,8 @@
 //        so the TMEM accumulator rescale is off the common path.
 //   MMA2 (kind::f16, A = P from TMEM, B = the tile read MN-major: 64 columns = [hi c | lo c]):
 //        S2[g, 0:32] += sum_n P[g,n] hi[n,:],  S2[g, 32:64] += sum_n P[g,n] lo[n,:];   S = S2[:, :32] + S2[:, 32:]
-// Warp roles: 2 softmax warpgroups (slice blocks j = w, w+2, ..), 1 loader warp (bulk copies), 1 MMA-issuing warp.
+// Warp roles: 2 softmax warpgroups (slice blocks j = w, w+2, ..), 1 loader warp (bulk copies), 2 MMA-issuing warps
+// (one per warpgroup: the single-thread issue stream was the bottleneck of the first version).
 #include <cuda_fp16.h>
 #include <stdlib.h>
 
@@ -26,7 +27,7 @@ using namespace tc;
 constexpr int ST_C = 32;            // dim_head handled by this kernel
 constexpr int ST_TILE = 64;         // points per tile
 constexpr int ST_STAGES = 6;
-constexpr int ST_THREADS = 320;     // 8 softmax warps + loader warp + MMA warp
+constexpr int ST_THREADS = 352;     // 8 softmax warps + loader warp + 2 MMA-issuing warps
 constexpr int ST_GB = 128;          // slices per block (UMMA M)
 constexpr int ST_MAX_GB = 4;        // up to 512 slices
 constexpr int ST_TILE_BYTES = ST_TILE * 128;   // one operand tile: 64 rows x 128 B
@@ -37,7 +38,7 @@ struct SliceCtl {
     uint64_t b_full[ST_STAGES], b_empty[ST_STAGES];
     uint64_t d_full[2][2], p_full[2][2];
     uint64_t mma2_done[2];
-    uint64_t all_done;
+    uint64_t all_done[2];
     uint32_t tmem_base;
 };
 
@@ -54,7 +55,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     uint8_t *sB = sW + (size_t)n_gb * 2 * (ST_GB * 128);             // [stages][8 KB] point tiles
     float *sS = reinterpret_cast<float *>(sB + (size_t)ST_STAGES * ST_TILE_BYTES);   // [stages][64] s_n
     SliceCtl *ctl = reinterpret_cast<SliceCtl *>(sS + ST_STAGES * ST_TILE);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
     const int bh = blockIdx.y;
     const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
     const int64_t n_end = min(N, n_begin + chunk_pts);
@@ -64,12 +65,13 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     // ---- one-time setup: barriers, TMEM, the Ws operand images ----
     if (warp == 9) {
         if (lane == 0) {
-            for (int s = 0; s < ST_STAGES; ++s) { mbar_init(&ctl->b_full[s], 1); mbar_init(&ctl->b_empty[s], 1); }
+            for (int s = 0; s < ST_STAGES; ++s) { mbar_init(&ctl->b_full[s], 1); mbar_init(&ctl->b_empty[s], n_gb > 1 ? 2 : 1); }
             for (int w = 0; w < 2; ++w) {
                 for (int k = 0; k < 2; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
                 mbar_init(&ctl->mma2_done[w], 1);
             }
-            mbar_init(&ctl->all_done, 1);
+            mbar_init(&ctl->all_done[0], 1);
+            mbar_init(&ctl->all_done[1], 1);
             fence_barrier_init();
         }
         __syncwarp();
@@ -111,48 +113,56 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
             }
         }
         __syncwarp();
-    } else if (warp == 9) {
-        // =========================== MMA issuer ===========================
-        if (lane == 0) {
-            const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
-            const uint32_t id2 = instr_desc(FMT_F16, ST_GB, ST_SCOLS, false, true);
-            const int Q = n_tiles * n_gb;
-            // MMA1 runs LAG items ahead of MMA2: far enough that both D buffers of a warpgroup are in flight, never so
-            // far that MMA1 would overwrite a D/P buffer whose MMA2 has not been issued yet
-            const int LAG = (n_gb & 1) ? (n_gb == 1 ? 2 : 3) : 4;
-            int cnt1[2] = {0, 0}, cnt2[2] = {0, 0};
-            for (int q = 0; q < Q + LAG; ++q) {
-                if (q >= LAG) {   // ---- MMA2 of item q-LAG: S2_j += P . [hi | lo]
-                    const int qq = q - LAG, t = qq / n_gb, j = qq - t * n_gb, w = j & 1, k = cnt2[w]++;
-                    const int buf = k & 1, stage = t % ST_STAGES;
-                    mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
-                    tc_fence_after();
-                    const uint32_t b2 = smem_u32(sB + (size_t)stage * ST_TILE_BYTES);
-                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf), sd = tmem_base + (uint32_t)j * ST_SCOLS;
+    } else if (warp >= 9) {
+        // =========================== MMA issuers ===========================
+        // warp 9 issues for softmax warpgroup 0 (slice blocks j = 0, 2), warp 10 for warpgroup 1 (j = 1, 3): two
+        // instruction streams, each MMA1 one item ahead of its warpgroup.  The whole warp runs the (warp-uniform)
+        // loop and one elected lane issues, so operands stay in uniform registers.
+        const int w = warp - 9;
+        const int pw = (n_gb + 1 - w) >> 1;   // slice blocks of this warpgroup
+        const int Qw = n_tiles * pw;
+        const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
+        const uint32_t id2 = instr_desc(FMT_F16, ST_GB, ST_SCOLS, false, true);
+        const uint32_t sW_a = smem_u32(sW) >> 4, sB_a = smem_u32(sB) >> 4;
+        int t1 = 0, jj1 = 0, st1 = 0, ph1 = 0;   // MMA1 cursor: tile, block within the warpgroup, stage, stage phase
+        int t2 = 0, jj2 = 0, st2 = 0;            // MMA2 cursor
+        for (int q = 0; q < Qw + 2; ++q) {
+            if (q >= 2) {   // ---- MMA2 of this warpgroup's item q-2: S2_j += P . [hi | lo]
+                const int k = q - 2, buf = k & 1;
+                mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t b2 = sB_a + (uint32_t)st2 * (ST_TILE_BYTES >> 4);
+                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf), sd = tmem_base + (uint32_t)(w + 2 * jj2) * ST_SCOLS;
 #pragma unroll
                     for (int ks = 0; ks < ST_TILE / 16; ++ks)   // K = 16 points = two 8-row swizzle atoms
-                        mma_f16_ts(sd, pa + ks * 8, smem_desc_sw128(b2 + ks * 2048, 1024, 1024), id2, (t | ks) != 0);
+                        mma_f16_ts(sd, pa + ks * 8, desc_sw128_u(b2 + ks * 128, 1024, 1024), id2, (t2 | ks) != 0);
                     tc_commit(&ctl->mma2_done[w]);
-                    if (j == n_gb - 1) tc_commit(&ctl->b_empty[stage]);
+                    if (jj2 == pw - 1) tc_commit(&ctl->b_empty[st2]);
                 }
-                if (q < Q) {    // ---- MMA1 of item q: D = Ws_j . x_proj^T (hi.hi + hi.lo + lo.hi)
-                    const int t = q / n_gb, j = q - t * n_gb, w = j & 1, k = cnt1[w]++;
-                    const int buf = k & 1, stage = t % ST_STAGES;
-                    if (j == 0) { mbar_wait(&ctl->b_full[stage], (uint32_t)((t / ST_STAGES) & 1)); tc_fence_after(); }
-                    const uint32_t b1 = smem_u32(sB + (size_t)stage * ST_TILE_BYTES);
-                    const uint32_t a1 = smem_u32(sW + (size_t)j * 2 * (ST_GB * 128)), a2 = a1 + ST_GB * 128;
+                __syncwarp();
+                if (++jj2 == pw) { jj2 = 0; ++t2; if (++st2 == ST_STAGES) st2 = 0; }
+            }
+            if (q < Qw) {    // ---- MMA1 of item q: D = Ws_j . x_proj^T (hi.hi + hi.lo + lo.hi)
+                const int buf = q & 1;
+                if (jj1 == 0) { mbar_wait(&ctl->b_full[st1], (uint32_t)ph1); tc_fence_after(); }
+                if (elect_one()) {
+                    const uint32_t b1 = sB_a + (uint32_t)st1 * (ST_TILE_BYTES >> 4);
+                    const uint32_t a1 = sW_a + (uint32_t)(w + 2 * jj1) * (2 * ST_GB * 128 >> 4), a2 = a1 + (ST_GB * 128 >> 4);
                     const uint32_t d = tmem_base + st_dbuf_col(w, buf);
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)
-                        mma_bf16_ss(d, smem_desc_sw128(a1 + ks * 32, 16, 1024), smem_desc_sw128(b1 + ks * 32, 16, 1024), id1, ks != 0);
+                        mma_bf16_ss(d, desc_sw128_u(a1 + ks * 2, 16, 1024), desc_sw128_u(b1 + ks * 2, 16, 1024), id1, ks != 0);
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks)
-                        mma_bf16_ss(d, smem_desc_sw128(a2 + ks * 32, 16, 1024), smem_desc_sw128(b1 + ks * 32, 16, 1024), id1, true);
+                        mma_bf16_ss(d, desc_sw128_u(a2 + ks * 2, 16, 1024), desc_sw128_u(b1 + ks * 2, 16, 1024), id1, true);
                     tc_commit(&ctl->d_full[w][buf]);
                 }
+                __syncwarp();
+                if (++jj1 == pw) { jj1 = 0; ++t1; if (++st1 == ST_STAGES) { st1 = 0; ph1 ^= 1; } }
             }
-            tc_commit(&ctl->all_done);   // every MMA of this CTA has completed when this phase flips
         }
+        if (elect_one()) tc_commit(&ctl->all_done[w]);   // every MMA of this stream has completed when this phase flips
         __syncwarp();
     } else {
         // =========================== softmax warpgroups ===========================
@@ -260,7 +270,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         // ---- write this CTA's partial (m2, l, S[C]) per slice ----
         if (n_my > 0 && n_tiles > 0) {
             // (mma2_done may be two phases behind here, so its parity is ambiguous: use the dedicated barrier)
-            mbar_wait(&ctl->all_done, 0);
+            mbar_wait(&ctl->all_done[w], 0);
             tc_fence_after();
             for (int jj = 0; jj < n_my; ++jj) {
                 const int j = w + 2 * jj, g = j * ST_GB + row;

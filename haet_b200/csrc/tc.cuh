@@ -125,6 +125,15 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
     return smem_desc(saddr, lbo_bytes, sbo_bytes, 2);
 }
+// same, from the start address already shifted right by 4 (cheap to advance inside an issue loop)
+__device__ __forceinline__ uint64_t desc_u(uint32_t saddr16, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+    const uint32_t lo = (saddr16 & 0x3FFFu) | ((lbo_bytes >> 4) << 16);
+    const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) | (layout << 29);
+    return ((uint64_t)hi << 32) | lo;
+}
+__device__ __forceinline__ uint64_t desc_sw128_u(uint32_t saddr16, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return desc_u(saddr16, lbo_bytes, sbo_bytes, 2);
+}
 // MN-major 32-bit (tf32) operands have ONE legal layout: SWIZZLE_128B_BASE32B (layout 1).  Rows are the K index,
 // 128 B (32 floats) along M/N; the 32-byte chunk index is XORed with (row % 4); atoms are 4 rows = 512 B, so one
 // K = 8 instruction spans two atoms SBO bytes apart.
