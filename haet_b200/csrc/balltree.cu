@@ -160,17 +160,116 @@ __device__ __forceinline__ void node_range(int j, int level, int n, int &s, int 
     }
 }
 
+// ---- warp-cooperative versions for the large nodes near the root ------------------------------------------
+// find_split_dimension: min / max are order independent, so a strided scan + shuffle reduction is exact.
+__device__ int warp_find_split_dimension(const float *key, const int *idx, int s, int e, int d) {
+    if (e - s <= 1) return 0;
+    const int lane = threadIdx.x & 31;
+    int best = 0;
+    double max_spread = 0;
+    for (int dim = 0; dim < d; ++dim) {
+        float mn = INFINITY, mx = -INFINITY;
+        for (int i = s + lane; i < e; i += 32) {
+            const float v = key[idx[i] * d + dim];
+            mn = v < mn ? v : mn;
+            mx = mx < v ? v : mx;
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            const float a = __shfl_xor_sync(0xffffffffu, mn, o), b = __shfl_xor_sync(0xffffffffu, mx, o);
+            mn = a < mn ? a : mn;
+            mx = mx < b ? b : mx;
+        }
+        const double spread = (double)mx - (double)mn;
+        if (spread > max_spread) { max_spread = spread; best = dim; }
+    }
+    return best;
+}
+
+// std::nth_element with the Hoare partition of every introselect round done by the whole warp.
+// __unguarded_partition(f, last, pivot) is a deterministic function of the range: with A = positions (ascending,
+// from f) whose key is >= pivot and B = positions (descending, from last - 1) whose key is <= pivot, the
+// sequential loop swaps A[k] <-> B[k] for k < K, K = #{k : A[k] < B[k]} (a swapped position is never visited
+// again), and returns min(A[K], B[K-1]).  Ranks come from ballots; the result is bit-identical to the sequential
+// code (the median-of-3, the heap-select fallback and the final insertion sort stay sequential on lane 0).
+__device__ void warp_nth_element(const KeyCtx &c, int *idx, int first, int nth, int last, int *Apos, int *Bpos) {
+    const int lane = threadIdx.x & 31;
+    if (first == last || nth == last) return;
+    int depth_limit = 2 * (31 - __clz(last - first));
+    while (last - first > 3) {
+        if (depth_limit == 0) {
+            if (lane == 0) {
+                heap_select_(c, idx + first, idx + nth + 1, idx + last);
+                SWAPI(idx + first, idx + nth);
+            }
+            __syncwarp();
+            return;
+        }
+        --depth_limit;
+        if (lane == 0) move_median_to_first(c, idx + first, idx + first + 1, idx + first + (last - first) / 2, idx + last - 1);
+        __syncwarp();
+        const float pv = KEY(c, idx[first]);
+        const int f = first + 1;
+        int cntA = 0, cntB = 0;
+        for (int base = f; base < last; base += 32) {
+            const int p = base + lane;
+            const bool in = p < last;
+            const float k = in ? KEY(c, idx[p]) : 0.f;
+            const bool isA = in && !(k < pv), isB = in && !(pv < k);
+            const unsigned mA = __ballot_sync(0xffffffffu, isA), mB = __ballot_sync(0xffffffffu, isB);
+            const unsigned lt = (1u << lane) - 1u;
+            if (isA) Apos[first + cntA + __popc(mA & lt)] = p;
+            if (isB) Bpos[first + cntB + __popc(mB & lt)] = p;   // ascending; B[k] (descending) = Bpos[first + cntB - 1 - k]
+            cntA += __popc(mA);
+            cntB += __popc(mB);
+        }
+        __syncwarp();
+        const int lim = cntA < cntB ? cntA : cntB;
+        int K = 0;
+        for (int base = 0; base < lim; base += 32) {
+            const int k = base + lane;
+            const bool ok = k < lim && Apos[first + k] < Bpos[first + cntB - 1 - k];
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            K += __popc(m);
+            if (m != 0xffffffffu) break;   // A ascending, B descending: the predicate is monotone in k
+        }
+        const int aK = K < cntA ? Apos[first + K] : 0x7fffffff;
+        const int bK1 = K >= 1 ? Bpos[first + cntB - K] : 0x7fffffff;
+        const int cut = aK < bK1 ? aK : bK1;
+        for (int k = lane; k < K; k += 32) SWAPI(idx + Apos[first + k], idx + Bpos[first + cntB - 1 - k]);
+        __syncwarp();
+        if (cut <= nth) first = cut;
+        else last = cut;
+    }
+    if (lane == 0) insertion_sort_(c, idx + first, idx + last);
+    __syncwarp();
+}
+
+constexpr int BT_WARP_NODE = 24;   // nodes of at least this many points are split by a whole warp
+
 // Split every node of levels [0, n_levels) of the implicit median tree over idx[0, n).
 // stop_small: partition_ball_tree stops at <= 1 point (balltree.h:219); build_tree always splits.
-__device__ void split_levels(const float *key, int *idx, int n, int d, int n_levels) {
+__device__ void split_levels(const float *key, int *idx, int n, int d, int n_levels, int *Apos, int *Bpos) {
+    const int warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     for (int level = 0; level < n_levels; ++level) {
         const int nodes = 1 << level;
-        for (int j = threadIdx.x; j < nodes; j += blockDim.x) {
-            int s, e;
-            node_range(j, level, n, s, e);
-            if (e - s > 1) {
-                KeyCtx c{key, d, find_split_dimension(key, idx, s, e, d)};
-                nth_element_(c, idx + s, idx + (s + e) / 2, idx + e);
+        if ((n >> level) >= BT_WARP_NODE) {
+            for (int j = warp; j < nodes; j += n_warps) {
+                int s, e;
+                node_range(j, level, n, s, e);
+                if (e - s > 1) {
+                    KeyCtx c{key, d, warp_find_split_dimension(key, idx, s, e, d)};
+                    warp_nth_element(c, idx, s, (s + e) / 2, e, Apos, Bpos);
+                }
+            }
+        } else {
+            for (int j = threadIdx.x; j < nodes; j += blockDim.x) {
+                int s, e;
+                node_range(j, level, n, s, e);
+                if (e - s > 1) {
+                    KeyCtx c{key, d, find_split_dimension(key, idx, s, e, d)};
+                    nth_element_(c, idx + s, idx + (s + e) / 2, idx + e);
+                }
             }
         }
         __syncthreads();
@@ -197,6 +296,7 @@ __global__ void __launch_bounds__(256) balltree_kernel(BallTreeArgs a) {
     float *rotB = rotA + (size_t)slots * d;               // [slots * d]
     int *idx = reinterpret_cast<int *>(rotB + (size_t)slots * d);  // [slots]
     int *leaf = idx + slots;                              // [slots]
+    int *Apos = leaf + slots, *Bpos = Apos + slots;       // [slots] each: scratch of the warp-parallel partition
     const int tid = threadIdx.x;
     const int64_t tree = blockIdx.x;
     const int64_t row0 = tree * a.pts;
@@ -206,7 +306,7 @@ __global__ void __launch_bounds__(256) balltree_kernel(BallTreeArgs a) {
     __syncthreads();
 
     // ---- main tree (balltree.h:121-186) ----
-    split_levels(P, idx, n, d, a.max_level);
+    split_levels(P, idx, n, d, a.max_level, Apos, Bpos);
     for (int j = tid; j < (1 << a.max_level); j += blockDim.x) {
         int s, e;
         node_range(j, a.max_level, n, s, e);
@@ -238,7 +338,7 @@ __global__ void __launch_bounds__(256) balltree_kernel(BallTreeArgs a) {
         int lv = a.targets[lvl];
         int maxlv = cur > 1 ? 32 - __clz(cur - 1) : 0;
         if (lv > maxlv) lv = maxlv;
-        split_levels(rotA, idx, cur, d, lv);
+        split_levels(rotA, idx, cur, d, lv, Apos, Bpos);
         int64_t *out = a.rot_idx[lvl] + tree * cur;
         for (int i = tid; i < cur; i += blockDim.x) out[i] = tree * cur + idx[i];
         if (lvl < a.n_levels - 1) {
@@ -310,7 +410,7 @@ extern "C" int haet_balltree_build(const float *pos_d, int64_t n_trees, int64_t 
         a.R[3] = (float)(s * c); a.R[4] = (float)(s * s * s + c * c); a.R[5] = (float)(s * c * (s - 1));
         a.R[6] = (float)(-s); a.R[7] = (float)(s * c); a.R[8] = (float)(c * c);
     }
-    const size_t smem = (size_t)a.slots * d * 3 * sizeof(float) + (size_t)a.slots * 2 * sizeof(int);
+    const size_t smem = (size_t)a.slots * d * 3 * sizeof(float) + (size_t)a.slots * 4 * sizeof(int);
     static size_t smem_set = 0;
     if (smem > 48 * 1024 && smem > smem_set) {
         HAET_CUDA(cudaFuncSetAttribute(balltree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -18,10 +18,10 @@ struct BlockW {  // float offsets into the packed weights
 };
 struct PoolW { int w, b, scale, shift; };
 
-__device__ __forceinline__ int pad_dim(int n) { return n | 1; }  // odd row stride: conflict-free columns
+__device__ __forceinline__ int pad_dim(int n) { return n + 4; }  // rows stay 16-byte aligned; LDS.128 conflict-free
 
 // out[i][o] (+)= sum_k in[i][k] * W[o][k] + b[o], i < rows; consecutive threads take consecutive rows
-// so W reads are warp-uniform and the smem reads hit distinct banks (odd stride).
+// so W reads are warp-uniform (scalar variant: any K / O, used for the K = d positional projection)
 template <bool ACC>
 __device__ void ball_linear(const float *in, int in_ld, const float *__restrict__ W, const float *__restrict__ b,
                             float *out, int out_ld, int rows, int K, int O) {
@@ -32,6 +32,53 @@ __device__ void ball_linear(const float *in, int in_ld, const float *__restrict_
         float acc = b ? b[o] : 0.f;
         for (int k = 0; k < K; ++k) acc = fmaf(ir[k], __ldg(wr + k), acc);
         if (ACC) out[i * out_ld + o] += acc; else out[i * out_ld + o] = acc;
+    }
+}
+
+// Register-blocked variant (K, O multiples of 4; rows 16-byte aligned): one thread = one row x 4 outputs, float4
+// loads of the activations (shared) and of 4 weight rows (warp-uniform, L1-resident), 16 FMAs per step.
+// GATE: out = (W2 x + b2) * silu(W x + b)   (SwiGLU, mlp.py:17-18), W2 / b2 the second weight pair.
+template <bool ACC, bool GATE>
+__device__ void ball_linear4(const float *in, int in_ld, const float *__restrict__ W, const float *__restrict__ b,
+                             const float *__restrict__ W2, const float *__restrict__ b2, float *out, int out_ld, int rows,
+                             int K, int O) {
+    const int og = O >> 2, k4 = K >> 2;
+    for (int t = threadIdx.x; t < rows * og; t += blockDim.x) {
+        const int i = t % rows, o = (t / rows) << 2;
+        const float4 *x = reinterpret_cast<const float4 *>(in + i * in_ld);
+        const float4 *w = reinterpret_cast<const float4 *>(W + (size_t)o * K);
+        const float4 bb = __ldg(reinterpret_cast<const float4 *>(b + o));
+        float a0 = bb.x, a1 = bb.y, a2 = bb.z, a3 = bb.w;
+        float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;
+        const float4 *w2 = nullptr;
+        if (GATE) {
+            w2 = reinterpret_cast<const float4 *>(W2 + (size_t)o * K);
+            const float4 b2v = __ldg(reinterpret_cast<const float4 *>(b2 + o));
+            g0 = b2v.x; g1 = b2v.y; g2 = b2v.z; g3 = b2v.w;
+        }
+#pragma unroll 4
+        for (int k = 0; k < k4; ++k) {
+            const float4 xv = x[k];
+            const float4 p = __ldg(w + k), q = __ldg(w + k4 + k), r = __ldg(w + 2 * k4 + k), s = __ldg(w + 3 * k4 + k);
+            a0 = fmaf(xv.x, p.x, a0); a0 = fmaf(xv.y, p.y, a0); a0 = fmaf(xv.z, p.z, a0); a0 = fmaf(xv.w, p.w, a0);
+            a1 = fmaf(xv.x, q.x, a1); a1 = fmaf(xv.y, q.y, a1); a1 = fmaf(xv.z, q.z, a1); a1 = fmaf(xv.w, q.w, a1);
+            a2 = fmaf(xv.x, r.x, a2); a2 = fmaf(xv.y, r.y, a2); a2 = fmaf(xv.z, r.z, a2); a2 = fmaf(xv.w, r.w, a2);
+            a3 = fmaf(xv.x, s.x, a3); a3 = fmaf(xv.y, s.y, a3); a3 = fmaf(xv.z, s.z, a3); a3 = fmaf(xv.w, s.w, a3);
+            if (GATE) {
+                const float4 p2 = __ldg(w2 + k), q2 = __ldg(w2 + k4 + k), r2 = __ldg(w2 + 2 * k4 + k), s2 = __ldg(w2 + 3 * k4 + k);
+                g0 = fmaf(xv.x, p2.x, g0); g0 = fmaf(xv.y, p2.y, g0); g0 = fmaf(xv.z, p2.z, g0); g0 = fmaf(xv.w, p2.w, g0);
+                g1 = fmaf(xv.x, q2.x, g1); g1 = fmaf(xv.y, q2.y, g1); g1 = fmaf(xv.z, q2.z, g1); g1 = fmaf(xv.w, q2.w, g1);
+                g2 = fmaf(xv.x, r2.x, g2); g2 = fmaf(xv.y, r2.y, g2); g2 = fmaf(xv.z, r2.z, g2); g2 = fmaf(xv.w, r2.w, g2);
+                g3 = fmaf(xv.x, s2.x, g3); g3 = fmaf(xv.y, s2.y, g3); g3 = fmaf(xv.z, s2.z, g3); g3 = fmaf(xv.w, s2.w, g3);
+            }
+        }
+        if (GATE) {
+            a0 = g0 * (a0 / (1.f + __expf(-a0))); a1 = g1 * (a1 / (1.f + __expf(-a1)));
+            a2 = g2 * (a2 / (1.f + __expf(-a2))); a3 = g3 * (a3 / (1.f + __expf(-a3)));
+        }
+        float4 *op = reinterpret_cast<float4 *>(out + i * out_ld + o);
+        if (ACC) { const float4 c = *op; a0 += c.x; a1 += c.y; a2 += c.z; a3 += c.w; }
+        *op = make_float4(a0, a1, a2, a3);
     }
 }
 
@@ -48,28 +95,112 @@ __device__ void ball_rmsnorm(const float *in, int ld, const float *__restrict__ 
     }
 }
 
-__global__ void __launch_bounds__(128) erwin_block_kernel(float *__restrict__ x, const float *__restrict__ pos,
-                                                          const int64_t *__restrict__ perm,
-                                                          const float *__restrict__ wts, BlockW w, int bs, int dim,
-                                                          int heads, int hidden, int d) {
-    extern __shared__ float sm[];
+// softmax(q k^T / sqrt(hd)) v inside the ball, one (query, head) per thread; HD4 = head_dim / 4 (1 or 2) fast paths
+template <int HD4>
+__device__ void ball_attention(const float *qkv, int ldq, float *us, int ld, int bs, int dim, int heads) {
+    const int hd = HD4 * 4;
+    const float scale = rsqrtf((float)hd) * kLog2e;
+    for (int t = threadIdx.x; t < bs * heads; t += blockDim.x) {
+        const int i = t % bs, h = t / bs;
+        float4 q[HD4], o[HD4];
+#pragma unroll
+        for (int c = 0; c < HD4; ++c) {
+            q[c] = *reinterpret_cast<const float4 *>(qkv + i * ldq + h * hd + 4 * c);
+            q[c].x *= scale; q[c].y *= scale; q[c].z *= scale; q[c].w *= scale;
+            o[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        float mx = -INFINITY, den = 0.f;
+        for (int j = 0; j < bs; ++j) {   // online softmax over the ball's keys (k / v rows are warp-uniform reads)
+            const float4 *kr = reinterpret_cast<const float4 *>(qkv + j * ldq + dim + h * hd);
+            const float4 *vr = reinterpret_cast<const float4 *>(qkv + j * ldq + 2 * dim + h * hd);
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < HD4; ++c) {
+                const float4 kv = kr[c];
+                s = fmaf(q[c].x, kv.x, s); s = fmaf(q[c].y, kv.y, s); s = fmaf(q[c].z, kv.z, s); s = fmaf(q[c].w, kv.w, s);
+            }
+            const float mn = fmaxf(mx, s);
+            const float corr = exp2f(mx - mn), p = exp2f(s - mn);
+            mx = mn;
+            den = fmaf(den, corr, p);
+#pragma unroll
+            for (int c = 0; c < HD4; ++c) {
+                const float4 vv = vr[c];
+                o[c].x = fmaf(o[c].x, corr, p * vv.x); o[c].y = fmaf(o[c].y, corr, p * vv.y);
+                o[c].z = fmaf(o[c].z, corr, p * vv.z); o[c].w = fmaf(o[c].w, corr, p * vv.w);
+            }
+        }
+        const float inv = 1.f / den;
+#pragma unroll
+        for (int c = 0; c < HD4; ++c)
+            *reinterpret_cast<float4 *>(us + i * ld + h * hd + 4 * c) =
+                make_float4(o[c].x * inv, o[c].y * inv, o[c].z * inv, o[c].w * inv);
+    }
+}
+
+// generic head_dim (scalar two-pass)
+__device__ void ball_attention_any(const float *qkv, int ldq, float *us, int ld, int bs, int dim, int heads) {
+    const int hd = dim / heads;
+    const float scale = rsqrtf((float)hd) * kLog2e;
+    for (int t = threadIdx.x; t < bs * heads; t += blockDim.x) {
+        const int i = t % bs, h = t / bs;
+        const float *q = qkv + i * ldq + h * hd;
+        float mx = -INFINITY;
+        for (int j = 0; j < bs; ++j) {
+            const float *k = qkv + j * ldq + dim + h * hd;
+            float s = 0.f;
+            for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
+            mx = fmaxf(mx, s * scale);
+        }
+        float *o = us + i * ld + h * hd;
+        for (int c = 0; c < hd; ++c) o[c] = 0.f;
+        float den = 0.f;
+        for (int j = 0; j < bs; ++j) {
+            const float *k = qkv + j * ldq + dim + h * hd;
+            const float *v = qkv + j * ldq + 2 * dim + h * hd;
+            float s = 0.f;
+            for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
+            const float p = exp2f(s * scale - mx);
+            den += p;
+            for (int c = 0; c < hd; ++c) o[c] = fmaf(p, v[c], o[c]);
+        }
+        const float inv = 1.f / den;
+        for (int c = 0; c < hd; ++c) o[c] *= inv;
+    }
+}
+
+constexpr int EB_THREADS = 256;
+
+__global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restrict__ x, const float *__restrict__ pos,
+                                                                 const int64_t *__restrict__ perm,
+                                                                 const float *__restrict__ wts, BlockW w, int bs, int dim,
+                                                                 int heads, int hidden, int d) {
+    extern __shared__ __align__(16) float sm[];
     const int ld = pad_dim(dim), ldq = pad_dim(3 * dim), ldh = pad_dim(hidden);
     float *xs = sm;                    // [bs][ld]   residual stream
     float *us = xs + bs * ld;          // [bs][ld]   normed / attention output
     float *qkv = us + bs * ld;         // [bs][ldq]
-    float *hid = qkv + bs * ldq;       // [bs][ldh]  (holds w1 branch, then the gated product)
-    float *hid2 = hid + bs * ldh;      // [bs][ldh]
-    float *rel = hid2 + bs * ldh;      // [bs][4]
+    float *hid = qkv + bs * ldq;       // [bs][ldh]  gated SwiGLU product
+    float *rel = hid + bs * ldh;       // [bs][4]
     float *cen = rel + bs * 4;         // [4]
     int *tok = reinterpret_cast<int *>(cen + 4);  // [bs]
     const int tid = threadIdx.x;
     const int64_t base = (int64_t)blockIdx.x * bs;
+    const bool vec = (dim & 3) == 0 && (hidden & 3) == 0;   // float4 paths
 
     for (int i = tid; i < bs; i += blockDim.x) tok[i] = perm ? (int)perm[base + i] : (int)(base + i);
     __syncthreads();
-    for (int t = tid; t < bs * dim; t += blockDim.x) {
-        const int i = t / dim, k = t - i * dim;
-        xs[i * ld + k] = x[(int64_t)tok[i] * dim + k];
+    if (vec) {
+        const int d4 = dim >> 2;
+        for (int t = tid; t < bs * d4; t += blockDim.x) {
+            const int i = t / d4, k = t - i * d4;
+            *reinterpret_cast<float4 *>(xs + i * ld + 4 * k) = __ldg(reinterpret_cast<const float4 *>(x + (int64_t)tok[i] * dim) + k);
+        }
+    } else {
+        for (int t = tid; t < bs * dim; t += blockDim.x) {
+            const int i = t / dim, k = t - i * dim;
+            xs[i * ld + k] = x[(int64_t)tok[i] * dim + k];
+        }
     }
     for (int t = tid; t < bs * d; t += blockDim.x) {
         const int i = t / d, j = t - i * d;
@@ -81,68 +212,62 @@ __global__ void __launch_bounds__(128) erwin_block_kernel(float *__restrict__ x,
         for (int i = 0; i < bs; ++i) s += rel[i * 4 + tid];
         cen[tid] = s / (float)bs;
     }
+    ball_rmsnorm(xs, ld, wts + w.norm1, us, bs, dim);
     __syncthreads();
     for (int t = tid; t < bs * d; t += blockDim.x) { const int i = t / d, j = t - i * d; rel[i * 4 + j] -= cen[j]; }
-    ball_rmsnorm(xs, ld, wts + w.norm1, us, bs, dim);
     __syncthreads();
     ball_linear<true>(rel, 4, wts + w.pe_w, wts + w.pe_b, us, ld, bs, d, dim);        // x + pe_proj(rel_pos)
     __syncthreads();
-    ball_linear<false>(us, ld, wts + w.qkv_w, wts + w.qkv_b, qkv, ldq, bs, dim, 3 * dim);
+    if (vec) ball_linear4<false, false>(us, ld, wts + w.qkv_w, wts + w.qkv_b, nullptr, nullptr, qkv, ldq, bs, dim, 3 * dim);
+    else ball_linear<false>(us, ld, wts + w.qkv_w, wts + w.qkv_b, qkv, ldq, bs, dim, 3 * dim);
     __syncthreads();
-    {   // softmax(q k^T / sqrt(hd)) v inside the ball, one (query, head) per thread
+    {
         const int hd = dim / heads;
-        const float scale = rsqrtf((float)hd) * kLog2e;
-        for (int t = tid; t < bs * heads; t += blockDim.x) {
-            const int i = t % bs, h = t / bs;
-            const float *q = qkv + i * ldq + h * hd;
-            float mx = -INFINITY;
-            for (int j = 0; j < bs; ++j) {
-                const float *k = qkv + j * ldq + dim + h * hd;
-                float s = 0.f;
-                for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
-                mx = fmaxf(mx, s * scale);
-            }
-            float *o = us + i * ld + h * hd;
-            for (int c = 0; c < hd; ++c) o[c] = 0.f;
-            float den = 0.f;
-            for (int j = 0; j < bs; ++j) {
-                const float *k = qkv + j * ldq + dim + h * hd;
-                const float *v = qkv + j * ldq + 2 * dim + h * hd;
-                float s = 0.f;
-                for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
-                const float p = exp2f(s * scale - mx);
-                den += p;
-                for (int c = 0; c < hd; ++c) o[c] = fmaf(p, v[c], o[c]);
-            }
-            const float inv = 1.f / den;
-            for (int c = 0; c < hd; ++c) o[c] *= inv;
-        }
+        if (vec && hd == 8) ball_attention<2>(qkv, ldq, us, ld, bs, dim, heads);
+        else if (vec && hd == 4) ball_attention<1>(qkv, ldq, us, ld, bs, dim, heads);
+        else ball_attention_any(qkv, ldq, us, ld, bs, dim, heads);
     }
     __syncthreads();
-    ball_linear<true>(us, ld, wts + w.proj_w, wts + w.proj_b, xs, ld, bs, dim, dim);   // x + BMSA(...)
+    if (vec) ball_linear4<true, false>(us, ld, wts + w.proj_w, wts + w.proj_b, nullptr, nullptr, xs, ld, bs, dim, dim);
+    else ball_linear<true>(us, ld, wts + w.proj_w, wts + w.proj_b, xs, ld, bs, dim, dim);   // x + BMSA(...)
     __syncthreads();
     ball_rmsnorm(xs, ld, wts + w.norm2, us, bs, dim);
     __syncthreads();
-    ball_linear<false>(us, ld, wts + w.w1, wts + w.b1, hid, ldh, bs, dim, hidden);
-    ball_linear<false>(us, ld, wts + w.w2, wts + w.b2, hid2, ldh, bs, dim, hidden);
-    __syncthreads();
-    for (int t = tid; t < bs * hidden; t += blockDim.x) {   // w2(x) * silu(w1(x))   (mlp.py:17-18)
-        const int i = t / hidden, k = t - i * hidden;
-        const float a = hid[i * ldh + k];
-        hid[i * ldh + k] = hid2[i * ldh + k] * (a / (1.f + __expf(-a)));
+    if (vec) {
+        ball_linear4<false, true>(us, ld, wts + w.w1, wts + w.b1, wts + w.w2, wts + w.b2, hid, ldh, bs, dim, hidden);
+    } else {
+        ball_linear<false>(us, ld, wts + w.w1, wts + w.b1, hid, ldh, bs, dim, hidden);
+        float *hid2 = reinterpret_cast<float *>(tok + bs);   // [bs][ldh], only carved for the scalar path (block_smem)
+        ball_linear<false>(us, ld, wts + w.w2, wts + w.b2, hid2, ldh, bs, dim, hidden);
+        __syncthreads();
+        for (int t = tid; t < bs * hidden; t += blockDim.x) {   // w2(x) * silu(w1(x))   (mlp.py:17-18)
+            const int i = t / hidden, k = t - i * hidden;
+            const float a = hid[i * ldh + k];
+            hid[i * ldh + k] = hid2[i * ldh + k] * (a / (1.f + __expf(-a)));
+        }
     }
     __syncthreads();
-    ball_linear<true>(hid, ldh, wts + w.w3, wts + w.b3, xs, ld, bs, hidden, dim);
+    if (vec) ball_linear4<true, false>(hid, ldh, wts + w.w3, wts + w.b3, nullptr, nullptr, xs, ld, bs, hidden, dim);
+    else ball_linear<true>(hid, ldh, wts + w.w3, wts + w.b3, xs, ld, bs, hidden, dim);
     __syncthreads();
-    for (int t = tid; t < bs * dim; t += blockDim.x) {
-        const int i = t / dim, k = t - i * dim;
-        x[(int64_t)tok[i] * dim + k] = xs[i * ld + k];
+    if (vec) {
+        const int d4 = dim >> 2;
+        for (int t = tid; t < bs * d4; t += blockDim.x) {
+            const int i = t / d4, k = t - i * d4;
+            reinterpret_cast<float4 *>(x + (int64_t)tok[i] * dim)[k] = *reinterpret_cast<const float4 *>(xs + i * ld + 4 * k);
+        }
+    } else {
+        for (int t = tid; t < bs * dim; t += blockDim.x) {
+            const int i = t / dim, k = t - i * dim;
+            x[(int64_t)tok[i] * dim + k] = xs[i * ld + k];
+        }
     }
 }
 
 static size_t block_smem(int bs, int dim, int hidden) {
-    auto pd = [](int n) { return n | 1; };
-    return sizeof(float) * ((size_t)bs * (2 * pd(dim) + pd(3 * dim) + 2 * pd(hidden)) + bs * 4 + 4) + sizeof(int) * bs;
+    auto pd = [](int n) { return n + 4; };
+    const size_t scalar_extra = ((dim | hidden) & 3) ? (size_t)bs * pd(hidden) : 0;   // hid2 of the non-float4 path
+    return sizeof(float) * ((size_t)bs * (2 * pd(dim) + pd(3 * dim) + pd(hidden)) + bs * 4 + 4 + scalar_extra) + sizeof(int) * bs;
 }
 
 __global__ void erwin_gather_kernel(const float *__restrict__ x, const float *__restrict__ pos,
@@ -296,7 +421,7 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
         const int64_t *perm = (rotate && (k & 1)) ? rot : nullptr;
         if (rotate && (k & 1)) HAET_CHECK_ARG(rot != nullptr, "tree_idx_rot must be provided for rotation");
         if (n == 0) continue;
-        erwin_block_kernel<<<(unsigned)(n / bs), 128, smem, st>>>(x, pos, perm, wts, bw, bs, dim, heads, hidden, d);
+        erwin_block_kernel<<<(unsigned)(n / bs), EB_THREADS, smem, st>>>(x, pos, perm, wts, bw, bs, dim, heads, hidden, d);
         HAET_LAUNCHED();
     }
     return HAET_OK;
