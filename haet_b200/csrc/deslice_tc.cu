@@ -39,7 +39,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
                   int64_t N, int64_t npad, int H, int G, int64_t chunk_pts, float *__restrict__ o) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int n_gc = (G + DT_GC - 1) / DT_GC;
     const int g_pad = n_gc * DT_GC;
     uint8_t *sW = smem;                                     // [g_pad rows][hi(32 fp16) | lo(32 fp16)]  K-major SW128

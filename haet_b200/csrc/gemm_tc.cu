@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1)
 gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
                float *__restrict__ Y, int64_t M, int K, int Nn, int n_workers, GemmEpi ep) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int panels = K / GT_KP;
     const int n_halves = Nn / GT_N;
     uint8_t *sW = smem;                                         // [panels][hi|lo][16 KB]
@@ -117,11 +117,16 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
             const int64_t tile = worker + (it / panels) * n_workers;
             const int p = (int)(it % panels);
 #pragma unroll
-            for (int i = 0; i < GT_LD; ++i) {
-                const int idx = i * GT_PROD + tid, row = idx >> 4, c4 = idx & 15;
+            for (int i = 0; i < GT_LD / 2; ++i) {   // 8 consecutive k (32 B) per item: one 16-B bf16 chunk of the row
+                const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
                 const int64_t m = tile * GT_M + row;
-                v[i] = (m < M) ? __ldg(reinterpret_cast<const float4 *>(X + m * K + p * GT_KP + c4 * 4))
-                               : make_float4(0.f, 0.f, 0.f, 0.f);
+                if (m < M) {
+                    const float4 *src = reinterpret_cast<const float4 *>(X + m * K + p * GT_KP + c8 * 8);
+                    v[2 * i] = __ldg(src);
+                    v[2 * i + 1] = __ldg(src + 1);
+                } else {
+                    v[2 * i] = v[2 * i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
             }
         };
         int stage = 0, phase = 0;
@@ -129,18 +134,22 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
             mbar_wait(&cb->a_empty[stage], phase ^ 1);
             uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
 #pragma unroll
-            for (int i = 0; i < GT_LD; ++i) {
-                const int idx = i * GT_PROD + tid, row = idx >> 4, c4 = idx & 15;
-                const __nv_bfloat162 ha = __floats2bfloat162_rn(v[i].x, v[i].y), hb = __floats2bfloat162_rn(v[i].z, v[i].w);
-                const uint32_t ua = *reinterpret_cast<const uint32_t *>(&ha), ub = *reinterpret_cast<const uint32_t *>(&hb);
-                const __nv_bfloat162 la = __floats2bfloat162_rn(v[i].x - __uint_as_float(ua << 16),
-                                                                v[i].y - __uint_as_float(ua & 0xffff0000u));
-                const __nv_bfloat162 lb = __floats2bfloat162_rn(v[i].z - __uint_as_float(ub << 16),
-                                                                v[i].w - __uint_as_float(ub & 0xffff0000u));
-                const uint32_t off = sw128_off(row, c4 >> 1) + (c4 & 1) * 8;
-                *reinterpret_cast<uint2 *>(hi_base + off) = make_uint2(ua, ub);
-                *reinterpret_cast<uint2 *>(hi_base + GT_PANEL_BYTES + off) =
-                    make_uint2(*reinterpret_cast<const uint32_t *>(&la), *reinterpret_cast<const uint32_t *>(&lb));
+            for (int i = 0; i < GT_LD / 2; ++i) {
+                const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const float4 f = v[2 * i + j];
+                    const __nv_bfloat162 ha = __floats2bfloat162_rn(f.x, f.y), hb = __floats2bfloat162_rn(f.z, f.w);
+                    const uint32_t ua = *reinterpret_cast<const uint32_t *>(&ha), ub = *reinterpret_cast<const uint32_t *>(&hb);
+                    const __nv_bfloat162 la = __floats2bfloat162_rn(f.x - __uint_as_float(ua << 16), f.y - __uint_as_float(ua & 0xffff0000u));
+                    const __nv_bfloat162 lb = __floats2bfloat162_rn(f.z - __uint_as_float(ub << 16), f.w - __uint_as_float(ub & 0xffff0000u));
+                    hi[2 * j] = ua; hi[2 * j + 1] = ub;
+                    lo[2 * j] = *reinterpret_cast<const uint32_t *>(&la); lo[2 * j + 1] = *reinterpret_cast<const uint32_t *>(&lb);
+                }
+                const uint32_t off = sw128_off(row, c8);
+                *reinterpret_cast<uint4 *>(hi_base + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4 *>(hi_base + GT_PANEL_BYTES + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             }
             fence_proxy_async();
             mbar_arrive(&cb->a_full[stage]);

@@ -49,7 +49,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int64_t chunk_pts,
                 float raise_thr, float *__restrict__ parts) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int n_gb = (G + ST_GB - 1) / ST_GB;
     uint8_t *sW = smem;                                              // [n_gb][2][16 KB]: [hi|hi] rows, [lo|0] rows
     uint8_t *sB = sW + (size_t)n_gb * 2 * (ST_GB * 128);             // [stages][8 KB] point tiles
