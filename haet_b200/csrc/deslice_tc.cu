@@ -20,7 +20,7 @@ constexpr int DT_C = 32;
 constexpr int DT_TILE = 128;        // points per tile (UMMA M)
 constexpr int DT_GC = 64;           // slices per item (UMMA N of MMA1, K of MMA2)
 constexpr int DT_STAGES = 4;
-constexpr int DT_THREADS = 480;     // 8 softmax warps + 4 epilogue warps + MMA warp 0 + loader warp + MMA warp 1
+constexpr int DT_THREADS = 736;     // 16 softmax warps + 4 epilogue warps + MMA warp 0 + loader warp + MMA warp 1
 constexpr int DT_MAX_G = 512;
 constexpr int DT_TILE_BYTES = DT_TILE * 128;
 
@@ -55,7 +55,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     const int64_t n_end = min(N, n_begin + chunk_pts);
     const int n_tiles = (int)((n_end - n_begin + DT_TILE - 1) / DT_TILE);
 
-    if (warp == 12) {
+    if (warp == 20) {
         if (lane == 0) {
             const uint32_t n_issuers = n_gc > 1 ? 2 : 1;
             for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], n_issuers); }
@@ -97,9 +97,9 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
 
-    if (warp >= 8 && warp < 12) {
+    if (warp >= 16 && warp < 20) {
         // =========================== O epilogue: TMEM -> global ===========================
-        const int r = threadIdx.x - 256;   // row of the tile == TMEM lane
+        const int r = threadIdx.x - 512;   // row of the tile == TMEM lane
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
         float *dst = o + ((int64_t)b * N) * inner + h * DT_C;
         for (int te = 0; te < n_tiles; ++te) {
@@ -128,7 +128,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                                        __uint_as_float(v[4 * i + 3]));
             }
         }
-    } else if (warp == 13) {
+    } else if (warp == 21) {
         // =========================== loader: one bulk copy per 128-point tile (+ its s_n) ===========================
         if (lane == 0) {
             const uint8_t *src = img + ((int64_t)bh * npad + n_begin) * XPI_ROW_BYTES;
@@ -143,12 +143,12 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
         }
         __syncwarp();
-    } else if (warp == 12 || warp == 14) {
+    } else if (warp == 20 || warp == 22) {
         // =========================== MMA issuers ===========================
-        // warp 12 issues for softmax warpgroup 0 (slice chunks j = 0, 2, ..), warp 14 for warpgroup 1 (j = 1, 3, ..); each
+        // warp 20 issues the slice chunks j = 0, 2, .. (softmax warpgroups 0 and 2), warp 22 j = 1, 3, .. (warpgroups 1, 3); each
         // stream accumulates its chunks into its own O buffers (summed by the epilogue).  The whole warp runs the
         // warp-uniform loop and one elected lane issues (see slice_tc.cu).
-        const int w = warp == 12 ? 0 : 1;
+        const int w = warp == 20 ? 0 : 1;
         const int pw = (n_gc + 1 - w) >> 1;
         const int Qw = n_tiles * pw;
         const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, DT_GC, false, false);
@@ -194,42 +194,44 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         }
     } else {
         // =========================== softmax warpgroups ===========================
-        const int w = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;
+        // 4 warpgroups: wg & 1 = the issue stream it serves, wg >> 1 = which of that stream's two D / P buffers it owns
+        // (it takes every other item of the stream), so each scheduler has 4 softmax warps to hide latencies.
+        const int wg = warp >> 2, w = wg & 1, sub = wg >> 1, q4 = warp & 3, row = q4 * 32 + lane;
         const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
-        int k = 0;
-        for (int t = 0; t < n_tiles; ++t) {
+        const int pw = (n_gc + 1 - w) >> 1, Qw = n_tiles * pw;
+        const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(w, sub);
+        int t = 0, jj = sub;   // item k = t * pw + jj of the stream
+        while (jj >= pw && pw > 0) { jj -= pw; ++t; }
+        for (int k = sub; k < Qw; k += 2) {
             const int stage = t % DT_STAGES;
-            if (w < n_gc) mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1));
+            mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1));
             const float sn = sS[stage * DT_TILE + row];
-#pragma unroll 1
-            for (int j = w; j < n_gc; j += 2, ++k) {
-                const int buf = k & 1;
-                mbar_wait(&ctl->d_full[w][buf], (uint32_t)((k >> 1) & 1));
-                tc_fence_after();
-                const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(w, buf);
-                const float4 *cc = reinterpret_cast<const float4 *>(sC + j * DT_GC);
+            mbar_wait(&ctl->d_full[w][sub], (uint32_t)((k >> 1) & 1));
+            tc_fence_after();
+            const float4 *cc = reinterpret_cast<const float4 *>(sC + (w + 2 * jj) * DT_GC);
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    uint32_t r[32];
-                    tmem_ld32(dcol + hh * 32, r);
-                    tmem_wait_ld();
+            for (int hh = 0; hh < 2; ++hh) {
+                uint32_t r[32];
+                tmem_ld32(dcol + hh * 32, r);
+                tmem_wait_ld();
 #pragma unroll
-                    for (int c = 0; c < 32; c += 2) {
-                        const float4 k2 = cc[hh * 16 + (c >> 1)];   // {bc, -lse} of two slices
-                        r[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c]) + k2.x, sn, k2.y)));
-                        r[c + 1] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 1]) + k2.z, sn, k2.w)));
-                    }
-                    tmem_st32(dcol + hh * 32, r);
+                for (int c = 0; c < 32; c += 2) {
+                    const float4 k2 = cc[hh * 16 + (c >> 1)];   // {bc, -lse} of two slices
+                    r[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c]) + k2.x, sn, k2.y)));
+                    r[c + 1] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 1]) + k2.z, sn, k2.w)));
                 }
-                tmem_wait_st();
-                tc_fence_before();
-                mbar_arrive(&ctl->p_full[w][buf]);
+                tmem_st32(dcol + hh * 32, r);
             }
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(&ctl->p_full[w][sub]);
+            jj += 2;
+            while (jj >= pw) { jj -= pw; ++t; }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 12) {
+    if (warp == 20) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }

@@ -13,8 +13,8 @@
 //        so the TMEM accumulator rescale is off the common path.
 //   MMA2 (kind::f16, A = P from TMEM, B = the tile read MN-major: 64 columns = [hi c | lo c]):
 //        S2[g, 0:32] += sum_n P[g,n] hi[n,:],  S2[g, 32:64] += sum_n P[g,n] lo[n,:];   S = S2[:, :32] + S2[:, 32:]
-// Warp roles: 2 softmax warpgroups (slice blocks j = w, w+2, ..), 1 loader warp (bulk copies), 2 MMA-issuing warps
-// (one per warpgroup: the single-thread issue stream was the bottleneck of the first version).
+// Warp roles: 4 softmax warpgroups (4 warps per scheduler hide the TMEM / MUFU latencies), 1 loader warp (bulk copies),
+// 2 MMA-issuing warps (a single issuing thread was the bottleneck of the first version).
 #include <cuda_fp16.h>
 #include <stdlib.h>
 
@@ -27,7 +27,7 @@ using namespace tc;
 constexpr int ST_C = 32;            // dim_head handled by this kernel
 constexpr int ST_TILE = 64;         // points per tile
 constexpr int ST_STAGES = 6;
-constexpr int ST_THREADS = 352;     // 8 softmax warps + loader warp + 2 MMA-issuing warps
+constexpr int ST_THREADS = 608;     // 16 softmax warps + loader warp + 2 MMA-issuing warps
 constexpr int ST_GB = 128;          // slices per block (UMMA M)
 constexpr int ST_MAX_GB = 4;        // up to 512 slices
 constexpr int ST_TILE_BYTES = ST_TILE * 128;   // one operand tile: 64 rows x 128 B
@@ -37,7 +37,7 @@ constexpr float ST_RAISE = 8.0f;    // lazy-max threshold (log2 units): P <= 2^8
 struct SliceCtl {
     uint64_t b_full[ST_STAGES], b_empty[ST_STAGES];
     uint64_t d_full[2][2], p_full[2][2];
-    uint64_t mma2_done[2];
+    uint64_t mma2_done[2][2];
     uint64_t all_done[2];
     uint32_t tmem_base;
 };
@@ -63,12 +63,13 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     const int64_t BH = gridDim.y;
 
     // ---- one-time setup: barriers, TMEM, the Ws operand images ----
-    if (warp == 9) {
+    if (warp == 17) {
         if (lane == 0) {
             for (int s = 0; s < ST_STAGES; ++s) { mbar_init(&ctl->b_full[s], 1); mbar_init(&ctl->b_empty[s], n_gb > 1 ? 2 : 1); }
             for (int w = 0; w < 2; ++w) {
-                for (int k = 0; k < 2; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
-                mbar_init(&ctl->mma2_done[w], 1);
+                for (int k = 0; k < 2; ++k) {
+                    mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); mbar_init(&ctl->mma2_done[w][k], 1);
+                }
             }
             mbar_init(&ctl->all_done[0], 1);
             mbar_init(&ctl->all_done[1], 1);
@@ -98,7 +99,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
 
-    if (warp == 8) {
+    if (warp == 16) {
         // =========================== loader: one bulk copy per tile (+ its s_n) ===========================
         if (lane == 0) {
             const uint8_t *src = img + ((int64_t)bh * npad + n_begin) * XPI_ROW_BYTES;
@@ -113,12 +114,12 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
             }
         }
         __syncwarp();
-    } else if (warp >= 9) {
+    } else if (warp >= 17) {
         // =========================== MMA issuers ===========================
-        // warp 9 issues for softmax warpgroup 0 (slice blocks j = 0, 2), warp 10 for warpgroup 1 (j = 1, 3): two
-        // instruction streams, each MMA1 one item ahead of its warpgroup.  The whole warp runs the (warp-uniform)
+        // warp 17 issues stream 0 (slice blocks j = 0, 2), warp 18 stream 1 (j = 1, 3): two instruction streams, each
+        // MMA1 two items ahead of MMA2; item k of a stream uses D / P buffer k & 1 = softmax warpgroup (w, k & 1).  The whole warp runs the (warp-uniform)
         // loop and one elected lane issues, so operands stay in uniform registers.
-        const int w = warp - 9;
+        const int w = warp - 17;
         const int pw = (n_gb + 1 - w) >> 1;   // slice blocks of this warpgroup
         const int Qw = n_tiles * pw;
         const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
@@ -133,11 +134,12 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 tc_fence_after();
                 if (elect_one()) {
                     const uint32_t b2 = sB_a + (uint32_t)st2 * (ST_TILE_BYTES >> 4);
-                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf), sd = tmem_base + (uint32_t)(w + 2 * jj2) * ST_SCOLS;
+                    // the accumulator belongs to the softmax warpgroup that owns D / P buffer `buf` of this stream
+                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf), sd = tmem_base + (uint32_t)(w * 2 + buf) * ST_SCOLS;
 #pragma unroll
                     for (int ks = 0; ks < ST_TILE / 16; ++ks)   // K = 16 points = two 8-row swizzle atoms
-                        mma_f16_ts(sd, pa + ks * 8, desc_sw128_u(b2 + ks * 128, 1024, 1024), id2, (t2 | ks) != 0);
-                    tc_commit(&ctl->mma2_done[w]);
+                        mma_f16_ts(sd, pa + ks * 8, desc_sw128_u(b2 + ks * 128, 1024, 1024), id2, ((k >> 1) | ks) != 0);
+                    tc_commit(&ctl->mma2_done[w][buf]);
                     if (jj2 == pw - 1) tc_commit(&ctl->b_empty[st2]);
                 }
                 __syncwarp();
@@ -166,130 +168,138 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         __syncwarp();
     } else {
         // =========================== softmax warpgroups ===========================
-        const int w = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;   // TMEM lane = slice row within its block
+        // 4 warpgroups: w = wg & 1 is the issue stream it serves, sub = wg >> 1 the D / P buffer of that stream it owns
+        // (every other item).  With 2 blocks per stream that is always the same slice block; with 1 block the two
+        // warpgroups split its tiles.  Either way a warpgroup owns ONE block j, one running (m, l) per thread (slice
+        // row) and one TMEM accumulator, and writes one chunk partial.  The 64 columns of an item are processed as two
+        // halves of 32 (registers), each with its own lazy-max check.
+        const int wg = warp >> 2, w = wg & 1, sub = wg >> 1, q4 = warp & 3, row = q4 * 32 + lane;
         const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
-        float m_run[2], l_run[2], bc[2];
-        int n_my = 0;
-        for (int j = w; j < n_gb; j += 2, ++n_my) {
-            const int g = j * ST_GB + row;
-            m_run[n_my] = 0.f; l_run[n_my] = 0.f;
-            bc[n_my] = g < G ? bs[g] - shift : 0.f;
-        }
+        const int pw = (n_gb + 1 - w) >> 1, Qw = n_tiles * pw;
+        const int j = w + (pw == 2 ? 2 * sub : 0), g = j * ST_GB + row;
+        const uint32_t dcol = tmem_base + lane_base + st_dbuf_col(w, sub);
+        const uint32_t scol = tmem_base + lane_base + (uint32_t)(w * 2 + sub) * ST_SCOLS;
+        float m_run = 0.f, l_run = 0.f;
+        const float bcj = (pw > 0 && g < G) ? bs[g] - shift : 0.f;
         const int last_valid = (int)(n_end - n_begin) - (n_tiles - 1) * ST_TILE;   // points in the last tile
-        int k = 0;   // item counter of this warpgroup
-        for (int t = 0; t < n_tiles && n_my > 0; ++t) {
+        int t = 0, jj = sub, i = 0;   // item k = t * pw + jj of the stream; i = items this warpgroup has done
+        while (pw > 0 && jj >= pw) { jj -= pw; ++t; }
+        for (int k = sub; k < Qw; k += 2, ++i) {
             const int stage = t % ST_STAGES;
             mbar_wait(&ctl->b_full[stage], (uint32_t)((t / ST_STAGES) & 1));
             const float4 *s4 = reinterpret_cast<const float4 *>(sS + stage * ST_TILE);
             const bool ragged = (t == n_tiles - 1) && last_valid < ST_TILE;
+            mbar_wait(&ctl->d_full[w][sub], (uint32_t)(i & 1));
+            tc_fence_after();
 #pragma unroll 1
-            for (int jj = 0; jj < n_my; ++jj, ++k) {
-                const int j = w + 2 * jj, buf = k & 1;
-                mbar_wait(&ctl->d_full[w][buf], (uint32_t)((k >> 1) & 1));
-                tc_fence_after();
-                const uint32_t dcol = tmem_base + lane_base + st_dbuf_col(w, buf);
-                uint32_t r0[32], r1[32];
-                tmem_ld32(dcol, r0);
-                tmem_ld32(dcol + 32, r1);
+            for (int hh = 0; hh < 2; ++hh) {
+                uint32_t r[32];
+                tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
-                const float mr = m_run[jj], bcj = bc[jj];
                 float tmax = -INFINITY;
 #pragma unroll
                 for (int c = 0; c < 32; c += 4) {
-                    const float4 sa = s4[c >> 2], sb = s4[8 + (c >> 2)];
+                    const float4 sa = s4[hh * 8 + (c >> 2)];
                     float v;
-                    v = fmaf(__uint_as_float(r0[c]) + bcj, sa.x, -mr); r0[c] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r0[c + 1]) + bcj, sa.y, -mr); r0[c + 1] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r0[c + 2]) + bcj, sa.z, -mr); r0[c + 2] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r0[c + 3]) + bcj, sa.w, -mr); r0[c + 3] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r1[c]) + bcj, sb.x, -mr); r1[c] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r1[c + 1]) + bcj, sb.y, -mr); r1[c + 1] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r1[c + 2]) + bcj, sb.z, -mr); r1[c + 2] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r1[c + 3]) + bcj, sb.w, -mr); r1[c + 3] = __float_as_uint(v); tmax = fmaxf(tmax, v);
+                    v = fmaf(__uint_as_float(r[c]) + bcj, sa.x, -m_run); r[c] = __float_as_uint(v); tmax = fmaxf(tmax, v);
+                    v = fmaf(__uint_as_float(r[c + 1]) + bcj, sa.y, -m_run); r[c + 1] = __float_as_uint(v); tmax = fmaxf(tmax, v);
+                    v = fmaf(__uint_as_float(r[c + 2]) + bcj, sa.z, -m_run); r[c + 2] = __float_as_uint(v); tmax = fmaxf(tmax, v);
+                    v = fmaf(__uint_as_float(r[c + 3]) + bcj, sa.w, -m_run); r[c + 3] = __float_as_uint(v); tmax = fmaxf(tmax, v);
                 }
-                if (ragged) {   // columns past the chunk's last point: weight 0 (their image rows are zero or foreign)
+                if (ragged) {   // columns past the chunk's last point: weight 0 (their image rows are zero)
                     tmax = -INFINITY;
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
-                        if (c >= last_valid) r0[c] = __float_as_uint(-INFINITY);
-                        if (c + 32 >= last_valid) r1[c] = __float_as_uint(-INFINITY);
-                        tmax = fmaxf(tmax, fmaxf(__uint_as_float(r0[c]), __uint_as_float(r1[c])));
+                        if (hh * 32 + c >= last_valid) r[c] = __float_as_uint(-INFINITY);
+                        tmax = fmaxf(tmax, __uint_as_float(r[c]));
                     }
                 }
-                // lazy running max: the first tile fixes it, later tiles raise it only past 2^raise_thr
-                const bool first = (t == 0);
+                // lazy running max: the very first half fixes it, later ones raise it only past 2^raise_thr
+                const bool first = (i == 0 && hh == 0);
                 const bool need = first || tmax > raise_thr;
                 if (__any_sync(0xffffffffu, need)) {
                     const float delta = need ? tmax : 0.f;   // m_new = m_run + delta
                     const float sc = first ? 0.f : fast_ex2(-delta);
-                    m_run[jj] = mr + delta;
-                    l_run[jj] *= sc;
+                    m_run += delta;
+                    l_run *= sc;
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        r0[c] = __float_as_uint(__uint_as_float(r0[c]) - delta);
-                        r1[c] = __float_as_uint(__uint_as_float(r1[c]) - delta);
-                    }
-                    if (!first) {   // rescale the TMEM accumulator of this slice block (all earlier MMA2s are done)
-                        mbar_wait(&ctl->mma2_done[w], (uint32_t)((k - 1) & 1));
+                    for (int c = 0; c < 32; ++c) r[c] = __float_as_uint(__uint_as_float(r[c]) - delta);
+                    if (i > 0) {   // rescale this warpgroup's TMEM accumulator (its earlier MMA2s are done)
+                        mbar_wait(&ctl->mma2_done[w][sub], (uint32_t)((i - 1) & 1));
                         tc_fence_after();
-                        const uint32_t scol = tmem_base + lane_base + (uint32_t)j * ST_SCOLS;
 #pragma unroll 1
-                        for (int hh = 0; hh < 2; ++hh) {
+                        for (int q = 0; q < 2; ++q) {
                             uint32_t sr[32];
-                            tmem_ld32(scol + hh * 32, sr);
+                            tmem_ld32(scol + q * 32, sr);
                             tmem_wait_ld();
 #pragma unroll
                             for (int c = 0; c < 32; ++c) sr[c] = __float_as_uint(__uint_as_float(sr[c]) * sc);
-                            tmem_st32(scol + hh * 32, sr);
+                            tmem_st32(scol + q * 32, sr);
                         }
                     }
+                    if (hh == 1) {   // the first half's P of this item is already in TMEM at the old scale
+                        uint32_t ph[16];
+                        tmem_ld16(dcol, ph);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) {
+                            const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&ph[c]));
+                            const __half2 h2 = __floats2half2_rn(f.x * sc, f.y * sc);
+                            ph[c] = *reinterpret_cast<const uint32_t *>(&h2);
+                        }
+                        tmem_st16(dcol, ph);
+                    }
                 }
-                float l = l_run[jj];
-                uint32_t pk[32];   // P as packed fp16: word i = points (2i, 2i+1)
+                float l = l_run;
+                uint32_t pk[16];   // P as packed fp16: word c = points (2c, 2c+1) of this half
 #pragma unroll
                 for (int c = 0; c < 32; c += 2) {
-                    const float p0 = fast_ex2(__uint_as_float(r0[c])), p1 = fast_ex2(__uint_as_float(r0[c + 1]));
+                    const float p0 = fast_ex2(__uint_as_float(r[c])), p1 = fast_ex2(__uint_as_float(r[c + 1]));
                     l += p0; l += p1;
                     const __half2 h2 = __floats2half2_rn(p0, p1);
                     pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&h2);
                 }
-#pragma unroll
-                for (int c = 0; c < 32; c += 2) {
-                    const float p0 = fast_ex2(__uint_as_float(r1[c])), p1 = fast_ex2(__uint_as_float(r1[c + 1]));
-                    l += p0; l += p1;
-                    const __half2 h2 = __floats2half2_rn(p0, p1);
-                    pk[16 + (c >> 1)] = *reinterpret_cast<const uint32_t *>(&h2);
-                }
-                l_run[jj] = l;
-                tmem_st32(dcol, pk);
-                tmem_wait_st();
-                tc_fence_before();
-                mbar_arrive(&ctl->p_full[w][buf]);
+                l_run = l;
+                tmem_st16(dcol + hh * 16, pk);
             }
+            tmem_wait_st();
+            tc_fence_before();
+            mbar_arrive(&ctl->p_full[w][sub]);
+            jj += 2;
+            while (jj >= pw) { jj -= pw; ++t; }
         }
-        // ---- write this CTA's partial (m2, l, S[C]) per slice ----
-        if (n_my > 0 && n_tiles > 0) {
-            // (mma2_done may be two phases behind here, so its parity is ambiguous: use the dedicated barrier)
-            mbar_wait(&ctl->all_done[w], 0);
-            tc_fence_after();
-            for (int jj = 0; jj < n_my; ++jj) {
-                const int j = w + 2 * jj, g = j * ST_GB + row;
+        // ---- write this warpgroup's partial (m2, l, S[C]) per slice of its block: chunk slot 2 * blockIdx.x + c ----
+        if (pw > 0) {
+            const int slot = pw == 1 ? sub : 0;
+            float *o = parts + ((((int64_t)blockIdx.x * 2 + slot) * BH + bh) * G + g) * (ST_C + 2);
+            if (i > 0) {
+                mbar_wait(&ctl->all_done[w], 0);
+                tc_fence_after();
                 uint32_t s0[32], s1[32];
-                tmem_ld32(tmem_base + lane_base + (uint32_t)j * ST_SCOLS, s0);
-                tmem_ld32(tmem_base + lane_base + (uint32_t)j * ST_SCOLS + 32, s1);
+                tmem_ld32(scol, s0);
+                tmem_ld32(scol + 32, s1);
                 tmem_wait_ld();
                 if (g < G) {
-                    float *o = parts + (((int64_t)blockIdx.x * BH + bh) * G + g) * (ST_C + 2);
-                    o[0] = m_run[jj]; o[1] = l_run[jj];
+                    o[0] = m_run; o[1] = l_run;
 #pragma unroll
                     for (int c = 0; c < 32; ++c) o[2 + c] = __uint_as_float(s0[c]) + __uint_as_float(s1[c]);
                 }
+            } else if (g < G) {   // no tile for this warpgroup: neutral partial
+                o[0] = -INFINITY; o[1] = 0.f;
+#pragma unroll
+                for (int c = 0; c < 32; ++c) o[2 + c] = 0.f;
+            }
+            if (pw == 2 && g < G) {   // the other slot of this block's rows is nobody's: neutral
+                float *o2 = o + BH * (int64_t)G * (ST_C + 2);
+                o2[0] = -INFINITY; o2[1] = 0.f;
+#pragma unroll
+                for (int c = 0; c < 32; ++c) o2[2 + c] = 0.f;
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) {
+    if (warp == 17) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }
@@ -308,7 +318,7 @@ static int64_t slice_tc_chunk_pts(const haet_layer_shape *s) {
     if (n_chunks > max_chunks) n_chunks = max_chunks;
     return align_up(cdiv(s->N, n_chunks), ST_TILE);
 }
-int64_t slice_tc_chunks(const haet_layer_shape *s) { return s->N > 0 ? cdiv(s->N, slice_tc_chunk_pts(s)) : 0; }
+int64_t slice_tc_chunks(const haet_layer_shape *s) { return s->N > 0 ? 2 * cdiv(s->N, slice_tc_chunk_pts(s)) : 0; }   // 2 partial slots per CTA
 
 int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,
                     const float *bs, float *chunk_parts, cudaStream_t st) {
