@@ -22,17 +22,18 @@ constexpr int DT_GC = 64;           // slices per item (UMMA N of MMA1, K of MMA
 constexpr int DT_STAGES = 4;
 constexpr int DT_THREADS = 736;     // 16 softmax warps + 4 epilogue warps + MMA warp 0 + loader warp + MMA warp 1
 constexpr int DT_MAX_G = 512;
+constexpr int DT_NBUF = 3;          // D / P buffers per issue stream
 constexpr int DT_TILE_BYTES = DT_TILE * 128;
 
 struct DesliceCtl {
     uint64_t a_full[DT_STAGES], a_empty[DT_STAGES];
-    uint64_t d_full[2][2], p_full[2][2];
+    uint64_t d_full[2][DT_NBUF], p_full[2][DT_NBUF];
     uint64_t o_full[2], o_empty[2];
     uint32_t tmem_base;
 };
 
-// TMEM columns: O accumulators [issuer][buffer] x 32 at 0..127, D / P buffers [warpgroup][buffer] x 64 at 128..383
-__device__ __forceinline__ uint32_t dt_dbuf_col(int wg, int buf) { return 128u + (uint32_t)(wg * 2 + buf) * DT_GC; }
+// TMEM columns: O accumulators [issuer][buffer] x 32 at 0..127, D / P buffers [stream][3] x 64 at 128..511
+__device__ __forceinline__ uint32_t dt_dbuf_col(int w, int buf) { return 128u + (uint32_t)(w * DT_NBUF + buf) * DT_GC; }
 
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
@@ -60,7 +61,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             const uint32_t n_issuers = n_gc > 1 ? 2 : 1;
             for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], n_issuers); }
             for (int w = 0; w < 2; ++w) {
-                for (int k = 0; k < 2; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
+                for (int k = 0; k < DT_NBUF; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
                 mbar_init(&ctl->o_full[w], n_issuers);
                 mbar_init(&ctl->o_empty[w], 128);
             }
@@ -154,16 +155,16 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, DT_GC, false, false);
         const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
         const uint32_t wbase = smem_u32(sW) >> 4, vbase = smem_u32(sV) >> 4, abase = smem_u32(sA) >> 4;
-        int t1 = 0, jj1 = 0, st1 = 0, ph1 = 0;   // MMA1 cursor
-        int t2 = 0, jj2 = 0, st2 = 0;            // MMA2 cursor
-        for (int q = 0; q < Qw + 2; ++q) {
-            if (q >= 2) {   // ---- MMA2 of this warpgroup's item q-2: O_w += P . S'_h[g-chunk]
-                const int k = q - 2, buf = k & 1, ob = t2 & 1;
+        int jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;            // MMA1 cursor: chunk within the stream, stage (+phase), D buffer
+        int t2 = 0, jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;    // MMA2 cursor
+        for (int q = 0; q < Qw + DT_NBUF; ++q) {
+            if (q >= DT_NBUF) {   // ---- MMA2 of this stream's item q-3: O_w += P . S'_h[g-chunk]
+                const int ob = t2 & 1;
                 if (jj2 == 0) mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t2 >> 1) & 1) ^ 1));
-                mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
+                mbar_wait(&ctl->p_full[w][buf2], (uint32_t)ph2);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint32_t pa = tmem_base + dt_dbuf_col(w, buf), od = tmem_base + (uint32_t)(w * 2 + ob) * DT_C;
+                    const uint32_t pa = tmem_base + dt_dbuf_col(w, buf2), od = tmem_base + (uint32_t)(w * 2 + ob) * DT_C;
                     const uint32_t vb = vbase + (uint32_t)(w + 2 * jj2) * (DT_GC * 128 >> 4);
 #pragma unroll
                     for (int ks = 0; ks < DT_GC / 8; ++ks)
@@ -171,43 +172,45 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                     if (jj2 == pw - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
                 }
                 __syncwarp();
+                if (++buf2 == DT_NBUF) { buf2 = 0; ph2 ^= 1; }
                 if (++jj2 == pw) { jj2 = 0; ++t2; if (++st2 == DT_STAGES) st2 = 0; }
             }
             if (q < Qw) {    // ---- MMA1 of item q: D = x_proj . Ws[g-chunk]^T  (hi.hi + lo.hi + hi.lo)
-                const int buf = q & 1;
                 if (jj1 == 0) { mbar_wait(&ctl->a_full[st1], (uint32_t)ph1); tc_fence_after(); }
                 if (elect_one()) {
                     const uint32_t a = abase + (uint32_t)st1 * (DT_TILE_BYTES >> 4);
                     const uint32_t wb = wbase + (uint32_t)(w + 2 * jj1) * (DT_GC * 128 >> 4);
-                    const uint32_t d = tmem_base + dt_dbuf_col(w, buf);
+                    const uint32_t d = tmem_base + dt_dbuf_col(w, buf1);
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks) {
                         mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, ks != 0);
                         mma_bf16_ss(d, desc_sw128_u(a + 4 + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, true);
                         mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + 4 + ks * 2, 16, 1024), id1, true);
                     }
-                    tc_commit(&ctl->d_full[w][buf]);
+                    tc_commit(&ctl->d_full[w][buf1]);
                 }
                 __syncwarp();
-                if (++jj1 == pw) { jj1 = 0; ++t1; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
+                if (++buf1 == DT_NBUF) buf1 = 0;
+                if (++jj1 == pw) { jj1 = 0; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
             }
         }
     } else {
         // =========================== softmax warpgroups ===========================
-        // 4 warpgroups: wg & 1 = the issue stream it serves, wg >> 1 = which of that stream's two D / P buffers it owns
-        // (it takes every other item of the stream), so each scheduler has 4 softmax warps to hide latencies.
+        // 4 warpgroups: wg & 1 = the issue stream it serves; it takes every other item of the stream (items cycle through
+        // the stream's 3 D / P buffers), so each scheduler has 4 softmax warps and MMA1 runs 3 items ahead.
         const int wg = warp >> 2, w = wg & 1, sub = wg >> 1, q4 = warp & 3, row = q4 * 32 + lane;
         const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
         const int pw = (n_gc + 1 - w) >> 1, Qw = n_tiles * pw;
-        const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(w, sub);
         int t = 0, jj = sub;   // item k = t * pw + jj of the stream
+        int buf = sub, bph = 0;   // D / P buffer k % 3 of the current item and its phase (k / 3) & 1
         while (jj >= pw && pw > 0) { jj -= pw; ++t; }
         for (int k = sub; k < Qw; k += 2) {
             const int stage = t % DT_STAGES;
             mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1));
             const float sn = sS[stage * DT_TILE + row];
-            mbar_wait(&ctl->d_full[w][sub], (uint32_t)((k >> 1) & 1));
+            mbar_wait(&ctl->d_full[w][buf], (uint32_t)bph);
             tc_fence_after();
+            const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(w, buf);
             const float4 *cc = reinterpret_cast<const float4 *>(sC + (w + 2 * jj) * DT_GC);
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
@@ -224,7 +227,9 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
             tmem_wait_st();
             tc_fence_before();
-            mbar_arrive(&ctl->p_full[w][sub]);
+            mbar_arrive(&ctl->p_full[w][buf]);
+            buf += 2;
+            if (buf >= DT_NBUF) { buf -= DT_NBUF; bph ^= 1; }
             jj += 2;
             while (jj >= pw) { jj -= pw; ++t; }
         }

@@ -11,8 +11,8 @@
 //   softmax warps (thread = slice row g): t = (D + bc_g) * s_n - m_run, P = 2^t, l += P, P -> TMEM as packed fp16.
 //        m_run is a LAZY running max: it is only raised when a tile exceeds it by 2^8 (P stays inside fp16),
 //        so the TMEM accumulator rescale is off the common path.
-//   MMA2 (kind::f16, A = P from TMEM, B = the tile read MN-major: 64 columns = [hi c | lo c]):
-//        S2[g, 0:32] += sum_n P[g,n] hi[n,:],  S2[g, 32:64] += sum_n P[g,n] lo[n,:];   S = S2[:, :32] + S2[:, 32:]
+//   MMA2 (kind::f16, A = P from TMEM, B = the hi half of the tile read MN-major: 32 columns):
+//        S[g, c] += sum_n P[g,n] hi[n,c]      M = 128, N = 32, K = 64   (hi carries x_proj to 2^-12: ample for S)
 // Warp roles: 4 softmax warpgroups (4 warps per scheduler hide the TMEM / MUFU latencies), 1 loader warp (bulk copies),
 // 2 MMA-issuing warps (a single issuing thread was the bottleneck of the first version).
 #include <cuda_fp16.h>
@@ -31,18 +31,20 @@ constexpr int ST_THREADS = 608;     // 16 softmax warps + loader warp + 2 MMA-is
 constexpr int ST_GB = 128;          // slices per block (UMMA M)
 constexpr int ST_MAX_GB = 4;        // up to 512 slices
 constexpr int ST_TILE_BYTES = ST_TILE * 128;   // one operand tile: 64 rows x 128 B
-constexpr int ST_SCOLS = 64;        // TMEM columns of one slice block's accumulator ([hi | lo] halves)
+constexpr int ST_SCOLS = 32;        // TMEM columns of one warpgroup's accumulator (P . hi; the fp16 hi half carries x_proj to 2^-12)
+constexpr int ST_NBUF = 3;          // D / P buffers per issue stream
 constexpr float ST_RAISE = 8.0f;    // lazy-max threshold (log2 units): P <= 2^8 fits fp16
 
 struct SliceCtl {
     uint64_t b_full[ST_STAGES], b_empty[ST_STAGES];
-    uint64_t d_full[2][2], p_full[2][2];
+    uint64_t d_full[2][ST_NBUF], p_full[2][ST_NBUF];
     uint64_t mma2_done[2][2];
     uint64_t all_done[2];
     uint32_t tmem_base;
 };
 
-__device__ __forceinline__ uint32_t st_dbuf_col(int wg, int buf) { return 256u + (uint32_t)(wg * 2 + buf) * ST_TILE; }
+// TMEM columns: accumulators of the 4 softmax warpgroups at 0..127, D / P buffers [stream][3] x 64 at 128..511
+__device__ __forceinline__ uint32_t st_dbuf_col(int w, int buf) { return 128u + (uint32_t)(w * ST_NBUF + buf) * ST_TILE; }
 
 __global__ void __launch_bounds__(ST_THREADS, 1)
 slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
@@ -67,9 +69,8 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         if (lane == 0) {
             for (int s = 0; s < ST_STAGES; ++s) { mbar_init(&ctl->b_full[s], 1); mbar_init(&ctl->b_empty[s], n_gb > 1 ? 2 : 1); }
             for (int w = 0; w < 2; ++w) {
-                for (int k = 0; k < 2; ++k) {
-                    mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); mbar_init(&ctl->mma2_done[w][k], 1);
-                }
+                for (int k = 0; k < ST_NBUF; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
+                for (int k = 0; k < 2; ++k) mbar_init(&ctl->mma2_done[w][k], 1);
             }
             mbar_init(&ctl->all_done[0], 1);
             mbar_init(&ctl->all_done[1], 1);
@@ -117,7 +118,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     } else if (warp >= 17) {
         // =========================== MMA issuers ===========================
         // warp 17 issues stream 0 (slice blocks j = 0, 2), warp 18 stream 1 (j = 1, 3): two instruction streams, each
-        // MMA1 two items ahead of MMA2; item k of a stream uses D / P buffer k & 1 = softmax warpgroup (w, k & 1).  The whole warp runs the (warp-uniform)
+        // MMA1 three items ahead of MMA2; item k of a stream uses D / P buffer k % 3 and belongs to softmax warpgroup (w, k & 1).  The whole warp runs the (warp-uniform)
         // loop and one elected lane issues, so operands stay in uniform registers.
         const int w = warp - 17;
         const int pw = (n_gb + 1 - w) >> 1;   // slice blocks of this warpgroup
@@ -125,42 +126,42 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
         const uint32_t id2 = instr_desc(FMT_F16, ST_GB, ST_SCOLS, false, true);
         const uint32_t sW_a = smem_u32(sW) >> 4, sB_a = smem_u32(sB) >> 4;
-        int t1 = 0, jj1 = 0, st1 = 0, ph1 = 0;   // MMA1 cursor: tile, block within the warpgroup, stage, stage phase
-        int t2 = 0, jj2 = 0, st2 = 0;            // MMA2 cursor
-        for (int q = 0; q < Qw + 2; ++q) {
-            if (q >= 2) {   // ---- MMA2 of this warpgroup's item q-2: S2_j += P . [hi | lo]
-                const int k = q - 2, buf = k & 1;
-                mbar_wait(&ctl->p_full[w][buf], (uint32_t)((k >> 1) & 1));
+        int t1 = 0, jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;   // MMA1 cursor: tile, block within the stream, stage (+phase), D buffer
+        int jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;           // MMA2 cursor
+        for (int q = 0; q < Qw + ST_NBUF; ++q) {
+            if (q >= ST_NBUF) {   // ---- MMA2 of this stream's item k = q - 3: S_wg += P . hi   (wg = k & 1)
+                const int k = q - ST_NBUF;
+                mbar_wait(&ctl->p_full[w][buf2], (uint32_t)ph2);
                 tc_fence_after();
                 if (elect_one()) {
                     const uint32_t b2 = sB_a + (uint32_t)st2 * (ST_TILE_BYTES >> 4);
-                    // the accumulator belongs to the softmax warpgroup that owns D / P buffer `buf` of this stream
-                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf), sd = tmem_base + (uint32_t)(w * 2 + buf) * ST_SCOLS;
+                    const uint32_t pa = tmem_base + st_dbuf_col(w, buf2), sd = tmem_base + (uint32_t)(w * 2 + (k & 1)) * ST_SCOLS;
 #pragma unroll
                     for (int ks = 0; ks < ST_TILE / 16; ++ks)   // K = 16 points = two 8-row swizzle atoms
                         mma_f16_ts(sd, pa + ks * 8, desc_sw128_u(b2 + ks * 128, 1024, 1024), id2, ((k >> 1) | ks) != 0);
-                    tc_commit(&ctl->mma2_done[w][buf]);
+                    tc_commit(&ctl->mma2_done[w][k & 1]);
                     if (jj2 == pw - 1) tc_commit(&ctl->b_empty[st2]);
                 }
                 __syncwarp();
-                if (++jj2 == pw) { jj2 = 0; ++t2; if (++st2 == ST_STAGES) st2 = 0; }
+                if (++buf2 == ST_NBUF) { buf2 = 0; ph2 ^= 1; }
+                if (++jj2 == pw) { jj2 = 0; if (++st2 == ST_STAGES) st2 = 0; }
             }
             if (q < Qw) {    // ---- MMA1 of item q: D = Ws_j . x_proj^T (hi.hi + hi.lo + lo.hi)
-                const int buf = q & 1;
                 if (jj1 == 0) { mbar_wait(&ctl->b_full[st1], (uint32_t)ph1); tc_fence_after(); }
                 if (elect_one()) {
                     const uint32_t b1 = sB_a + (uint32_t)st1 * (ST_TILE_BYTES >> 4);
                     const uint32_t a1 = sW_a + (uint32_t)(w + 2 * jj1) * (2 * ST_GB * 128 >> 4), a2 = a1 + (ST_GB * 128 >> 4);
-                    const uint32_t d = tmem_base + st_dbuf_col(w, buf);
+                    const uint32_t d = tmem_base + st_dbuf_col(w, buf1);
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)
                         mma_bf16_ss(d, desc_sw128_u(a1 + ks * 2, 16, 1024), desc_sw128_u(b1 + ks * 2, 16, 1024), id1, ks != 0);
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks)
                         mma_bf16_ss(d, desc_sw128_u(a2 + ks * 2, 16, 1024), desc_sw128_u(b1 + ks * 2, 16, 1024), id1, true);
-                    tc_commit(&ctl->d_full[w][buf]);
+                    tc_commit(&ctl->d_full[w][buf1]);
                 }
                 __syncwarp();
+                if (++buf1 == ST_NBUF) buf1 = 0;
                 if (++jj1 == pw) { jj1 = 0; ++t1; if (++st1 == ST_STAGES) { st1 = 0; ph1 ^= 1; } }
             }
         }
@@ -177,8 +178,8 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
         const int pw = (n_gb + 1 - w) >> 1, Qw = n_tiles * pw;
         const int j = w + (pw == 2 ? 2 * sub : 0), g = j * ST_GB + row;
-        const uint32_t dcol = tmem_base + lane_base + st_dbuf_col(w, sub);
         const uint32_t scol = tmem_base + lane_base + (uint32_t)(w * 2 + sub) * ST_SCOLS;
+        int buf = sub, bph = 0;   // D / P buffer k % 3 of the current item and its phase (k / 3) & 1
         float m_run = 0.f, l_run = 0.f;
         const float bcj = (pw > 0 && g < G) ? bs[g] - shift : 0.f;
         const int last_valid = (int)(n_end - n_begin) - (n_tiles - 1) * ST_TILE;   // points in the last tile
@@ -189,8 +190,9 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
             mbar_wait(&ctl->b_full[stage], (uint32_t)((t / ST_STAGES) & 1));
             const float4 *s4 = reinterpret_cast<const float4 *>(sS + stage * ST_TILE);
             const bool ragged = (t == n_tiles - 1) && last_valid < ST_TILE;
-            mbar_wait(&ctl->d_full[w][sub], (uint32_t)(i & 1));
+            mbar_wait(&ctl->d_full[w][buf], (uint32_t)bph);
             tc_fence_after();
+            const uint32_t dcol = tmem_base + lane_base + st_dbuf_col(w, buf);
 #pragma unroll 1
             for (int hh = 0; hh < 2; ++hh) {
                 uint32_t r[32];
@@ -227,15 +229,12 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                     if (i > 0) {   // rescale this warpgroup's TMEM accumulator (its earlier MMA2s are done)
                         mbar_wait(&ctl->mma2_done[w][sub], (uint32_t)((i - 1) & 1));
                         tc_fence_after();
-#pragma unroll 1
-                        for (int q = 0; q < 2; ++q) {
-                            uint32_t sr[32];
-                            tmem_ld32(scol + q * 32, sr);
-                            tmem_wait_ld();
+                        uint32_t sr[32];
+                        tmem_ld32(scol, sr);
+                        tmem_wait_ld();
 #pragma unroll
-                            for (int c = 0; c < 32; ++c) sr[c] = __float_as_uint(__uint_as_float(sr[c]) * sc);
-                            tmem_st32(scol + q * 32, sr);
-                        }
+                        for (int c = 0; c < 32; ++c) sr[c] = __float_as_uint(__uint_as_float(sr[c]) * sc);
+                        tmem_st32(scol, sr);
                     }
                     if (hh == 1) {   // the first half's P of this item is already in TMEM at the old scale
                         uint32_t ph[16];
@@ -264,7 +263,9 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
             }
             tmem_wait_st();
             tc_fence_before();
-            mbar_arrive(&ctl->p_full[w][sub]);
+            mbar_arrive(&ctl->p_full[w][buf]);
+            buf += 2;
+            if (buf >= ST_NBUF) { buf -= ST_NBUF; bph ^= 1; }
             jj += 2;
             while (jj >= pw) { jj -= pw; ++t; }
         }
@@ -275,14 +276,13 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
             if (i > 0) {
                 mbar_wait(&ctl->all_done[w], 0);
                 tc_fence_after();
-                uint32_t s0[32], s1[32];
+                uint32_t s0[32];
                 tmem_ld32(scol, s0);
-                tmem_ld32(scol + 32, s1);
                 tmem_wait_ld();
                 if (g < G) {
                     o[0] = m_run; o[1] = l_run;
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) o[2 + c] = __uint_as_float(s0[c]) + __uint_as_float(s1[c]);
+                    for (int c = 0; c < 32; ++c) o[2 + c] = __uint_as_float(s0[c]);
                 }
             } else if (g < G) {   // no tile for this warpgroup: neutral partial
                 o[0] = -INFINITY; o[1] = 0.f;
