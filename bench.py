@@ -143,8 +143,9 @@ def workload_config(args, cpu=False):
 # ----------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------
-def stage_times(m, x, iters=3):
-    """CUDA-event time of each C-ABI stage of one layer forward (ms, mean of iters) on the current stream."""
+def stage_times(m, x, iters=5):
+    """CUDA-event time of each kernel group of one layer forward (ms, mean of iters) on the current stream, through the
+    C-ABI entry points (haet_set_stage_mask selects which kernels an entry point launches)."""
     from haet_b200 import _lib
     from haet_b200.balltree import balltree_device
     from haet_b200.erwin import erwin_device
@@ -166,42 +167,71 @@ def stage_times(m, x, iters=3):
     part = torch.empty(l.haet_partial_floats(psh), device=dev)
     eid = torch.empty(T, Cc, device=dev); lse = torch.empty(T, device=dev); pos = torch.empty(T, 3, device=dev)
     out = torch.empty(B, N, m.dim, device=dev)
-    acc = {k: 0.0 for k in ("slice_reduce", "slice_merge", "balltree", "erwin", "deslice_out")}
+    names = ("in_project", "slice_pass1", "slice_merge", "balltree", "erwin", "deslice_pass2", "to_out")
+    acc = {k: 0.0 for k in names}
     ev = lambda: torch.cuda.Event(enable_timing=True)
-    for it in range(iters + 1):
-        e = [ev() for _ in range(6)]
-        e[0].record()
+
+    def slice_reduce(mask):
+        _lib.check(l.haet_set_stage_mask(mask))
         _lib.check(l.haet_slice_reduce(psh, x.data_ptr(), wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(),
                                        wt.data_ptr(), bt, spill.data_ptr(), part.data_ptr(), work.data_ptr(), st))
-        e[1].record()
-        _lib.check(l.haet_slice_merge(psh, part.data_ptr(), 1, eid.data_ptr(), lse.data_ptr(), pos.data_ptr(), st))
-        e[2].record()
-        tree_idx, tree_mask, rots = balltree_device(pos, B * H, G, m.erwin.strides, m.erwin.ball_sizes,
-                                                    float(m.erwin.rotate))
-        e[3].record()
-        states = erwin_device(m.erwin, eid, pos, tree_idx, tree_mask, rots)
-        e[4].record()
+
+    def deslice(mask, states):
+        _lib.check(l.haet_set_stage_mask(mask))
         _lib.check(l.haet_deslice_out(psh, spill.data_ptr(), lse.data_ptr(), states.data_ptr(), ws.data_ptr(),
                                       bs.data_ptr(), wt.data_ptr(), bt, wo.data_ptr(), bo.data_ptr(), out.data_ptr(),
                                       work.data_ptr(), st))
-        e[5].record()
-        torch.cuda.synchronize()
-        if it == 0:
-            continue   # warm-up
-        for i, k in enumerate(acc):
-            acc[k] += e[i].elapsed_time(e[i + 1]) / iters
+    try:
+        for it in range(iters + 1):
+            e = [ev() for _ in range(8)]
+            e[0].record()
+            slice_reduce(1)
+            e[1].record()
+            slice_reduce(2)
+            e[2].record()
+            _lib.check(l.haet_slice_merge(psh, part.data_ptr(), 1, eid.data_ptr(), lse.data_ptr(), pos.data_ptr(), st))
+            e[3].record()
+            tree_idx, tree_mask, rots = balltree_device(pos, B * H, G, m.erwin.strides, m.erwin.ball_sizes,
+                                                        float(m.erwin.rotate))
+            e[4].record()
+            states = erwin_device(m.erwin, eid, pos, tree_idx, tree_mask, rots)
+            e[5].record()
+            deslice(4, states)
+            e[6].record()
+            deslice(8, states)
+            e[7].record()
+            torch.cuda.synchronize()
+            if it == 0:
+                continue   # warm-up
+            for i, k in enumerate(names):
+                acc[k] += e[i].elapsed_time(e[i + 1]) / iters
+    finally:
+        _lib.check(l.haet_set_stage_mask(15))
     return acc
 
 
+def ncu_traffic():
+    """DRAM bytes per launch of each kernel from the committed ncu --set full summary (profiles/), or {}."""
+    p = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
+    if not os.path.exists(p):
+        return {}
+    d = json.load(open(p))
+    key = {"in_project": "gemm_tc_kernel<1>", "slice_pass1": "slice_tc_kernel", "deslice_pass2": "deslice_tc_kernel",
+           "to_out": "gemm_tc_kernel<0>"}
+    return {k: d[v]["traffic_bytes"] for k, v in key.items() if v in d}
+
+
 def roofline_for(stages, args, pk):
-    """Roofline of the dominant stage.  Algorithmic work per point (DESIGN.md "algorithmic work"):
-       slice_reduce: 2*D^2 (in-projection) + 2*D*G (logits) + 2*D*G (W^T x) flop; reads x (4*D B)
-       deslice_out : 2*D*G (W.S') + 2*D^2 (to_out) flop;            writes out (4*D B)
-    (the recomputed logits of pass 2 and the spill traffic are implementation cost, not counted)."""
+    """Roofline of the dominant kernel.  Algorithmic work per point and launch, each flop counted
+    once (the 3-term split products and the recomputed logits of pass 2 are implementation cost):
+       in_project   : 2 D^2 flop;            reads x 4D B, writes x_proj 4D B
+       slice_pass1  : 4 D G flop (+ H G exp2); reads x_proj 4D B
+       deslice_pass2: 4 D G flop (+ H G exp2); reads x_proj 4D B, writes o 4D B
+       to_out       : 2 D^2 flop;            reads o 4D B, writes out 4D B"""
     D, G, N = HIDDEN, args.slices, args.points
-    work = {"slice_reduce": (N * (2 * D * D + 4 * D * G), N * 4 * D),
-            "deslice_out": (N * (2 * D * D + 2 * D * G), N * 4 * D)}
-    name = max(("slice_reduce", "deslice_out"), key=lambda k: stages[k])
+    work = {"in_project": (N * 2 * D * D, N * 8 * D), "slice_pass1": (N * 4 * D * G, N * 4 * D),
+            "deslice_pass2": (N * 4 * D * G, N * 8 * D), "to_out": (N * 2 * D * D, N * 8 * D)}
+    name = max(work, key=lambda k: stages[k])
     flops, byts = work[name]
     sec = stages[name] * 1e-3
     t_tensor, t_hbm = flops / (pk["tf"] * 1e12), byts / (pk["hbm"] * 1e9)
@@ -211,7 +241,10 @@ def roofline_for(stages, args, pk):
     else:
         ach = byts / sec / 1e9
         r = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"]}
-    r.update(kernel=name, kernel_ms=stages[name], peak_source=pk["src"], traffic=None)
+    r.update(kernel=name, kernel_ms=stages[name], peak_source=pk["src"] + " (burst: kernel timed alone)",
+             traffic=ncu_traffic().get(name), algorithmic_bytes=byts, algorithmic_flops=flops)
+    if name in ("slice_pass1", "deslice_pass2"):   # what actually bounds these kernels: MUFU ex2 at 16 / clk / SM
+        r["mufu_floor_ms"] = N * HEADS * G / (16 * 148 * 1.965e9) * 1e3
     return r
 
 

@@ -66,6 +66,7 @@ SYMBOLS = {
     "haet_layer_forward": (C.c_int, [_SH, _EC, C.POINTER(LayerWeights), _P, _P, _P, _P]),
     "haet_launch_count": (C.c_int64, []),
     "haet_set_path": (C.c_int, [C.c_int]),
+    "haet_set_stage_mask": (C.c_int, [C.c_int]),
     "haet_debug_gemm": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P]),
 }
 

@@ -9,6 +9,7 @@ namespace haet {
 static thread_local char g_err[512] = "";
 int64_t g_launches = 0;
 int g_path = 0;
+int g_stage_mask = 15;
 
 void set_error(const char *fmt, ...) {
     va_list ap;
@@ -127,6 +128,11 @@ int haet_set_path(int path) {
     g_path = path;
     return HAET_OK;
 }
+int haet_set_stage_mask(int mask) {
+    if (mask < 0 || mask > 15) { set_error("stage mask must be in 0..15"); return HAET_EINVAL; }
+    g_stage_mask = mask;
+    return HAET_OK;
+}
 int haet_debug_gemm(const float *x_d, const float *w_d, const float *bias_d, float *y_d, int64_t M, int32_t K, int32_t Nn,
                     void *img_d, void *stream) {
     if (g_path == 0 && gemm_tc_supported(K, Nn)) return launch_gemm_tc(x_d, w_d, bias_d, y_d, M, K, Nn, img_d, (cudaStream_t)stream);
@@ -148,7 +154,9 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
     void *img = (char *)workspace_d + slice_parts_bytes(s);
     const int inner = s->heads * s->dim_head;
     const bool tc = g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s);
-    if (tc && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner)) {
+    if (!(g_stage_mask & 1)) {
+        rc = HAET_OK;   // bench hook: the spill of an earlier call is reused
+    } else if (tc && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner)) {
         // Linear front-end: the GEMM epilogue writes the operand image directly
         rc = launch_inproj_tc(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st);
     } else {
@@ -159,6 +167,7 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
         if (!rc && tc) rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st);
     }
     if (rc) return rc;
+    if (!(g_stage_mask & 2)) return HAET_OK;
     if (tc) {
         if ((rc = launch_slice_tc(s, sv.img, sv.scale, ws_d, bs_d, parts, st))) return rc;
         return launch_slice_merge(s, parts, slice_tc_chunks(s), partial_d, nullptr, nullptr, st);
@@ -187,11 +196,14 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
     cudaStream_t st = (cudaStream_t)stream;
     float *o = (float *)workspace_d;
     const SpillView sv = spill_view(s, const_cast<void *>(spill_d));
-    if (g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s))
+    if (!(g_stage_mask & 4))
+        rc = HAET_OK;
+    else if (g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s))
         rc = launch_deslice_tc(s, sv.img, sv.scale, lse2_d, states_d, ws_d, bs_d, o, st);
     else
         rc = launch_deslice(s, sv.xp, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
     if (rc) return rc;
+    if (!(g_stage_mask & 8)) return HAET_OK;
     const int inner = s->heads * s->dim_head;
     if (g_path == 0 && gemm_tc_supported(inner, s->dim))
         return launch_gemm_tc(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, (char *)workspace_d + deslice_o_bytes(s), st);

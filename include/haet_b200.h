@@ -165,6 +165,10 @@ int haet_layer_forward(const haet_layer_shape *s, const haet_erwin_cfg *c, const
  * haet_debug_gemm: Y[M,Nn] = X[M,K].W[Nn,K]^T + bias through the path selected above;
  * img_d: scratch of 4*Nn*K bytes. */
 int haet_set_path(int path);
+/* bench hook: which kernels haet_slice_reduce / haet_deslice_out launch (default 15 = all), so that each can be timed
+ * alone through the real entry points on buffers a full call has filled:
+ * bit 0 in-projection (+ image pack), bit 1 pass-1 slice kernel + chunk merge, bit 2 pass-2 deslice kernel, bit 3 to_out */
+int haet_set_stage_mask(int mask);
 int haet_debug_gemm(const float *x_d, const float *w_d, const float *bias_d, float *y_d, int64_t M, int32_t K,
                     int32_t Nn, void *img_d, void *stream);
 
