@@ -260,6 +260,7 @@ def run_gpu_arm(args):
     import torch.distributed as dist
     from haet_b200 import _lib
     from haet_b200.distributed import init_from_env
+    os.environ["NCCL_DEBUG"] = os.environ.get("HAET_NCCL_DEBUG", "WARN")   # keep stdout to the one JSON line
     rank, local, world = init_from_env("nccl")
     if world != args.gpus:
         if rank == 0:

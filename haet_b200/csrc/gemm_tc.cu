@@ -15,23 +15,12 @@
 // Epilogues: EPI_F32 stores fp32 rows (to_out); EPI_IMG is the in-projection of the tensor-core path: per head it
 // adds the bias, evaluates Ada-Temp (s_n = log2 e / tau_n) and writes the spill's fp16 hi/lo operand image
 // (common.cuh) instead of fp32 rows, so that passes 1 and 2 bulk-copy their MMA operands.
-#include <cuda_fp16.h>
+#include <stdlib.h>
 
-#include "common.cuh"
-#include "tc.cuh"
+#include "gemm_tc.cuh"
 
 namespace haet {
 using namespace tc;
-
-constexpr int GT_M = 128;          // rows per tile (UMMA M)
-constexpr int GT_N = 128;          // output columns per CTA (UMMA N)
-constexpr int GT_KP = 64;          // k per panel: 64 bf16 = one 128-byte swizzle row
-constexpr int GT_STAGES = 3;
-constexpr int GT_PANEL_BYTES = GT_M * 128;   // 16 KB: 128 rows x 128 B
-constexpr int GT_PROD = 256;       // producer threads (warps 0-7)
-constexpr int GT_THREADS = GT_PROD + 32 + 128;   // + MMA warp (8) + epilogue warps (9-12)
-constexpr int GT_LD = GT_M * GT_KP / 4 / GT_PROD;   // float4 per producer thread per panel (8)
-enum { EPI_F32 = 0, EPI_IMG = 1 };
 
 // W [Nn, K] fp32 -> image [Nn/128 halves][K/64 panels][hi, lo][128 rows x 128 B swizzled]
 __global__ void gemm_tc_pack_kernel(const float *__restrict__ w, int Nn, int K, uint8_t *__restrict__ img) {
@@ -60,22 +49,6 @@ __global__ void xpi_pad_kernel(uint8_t *__restrict__ img, float *__restrict__ sc
     *reinterpret_cast<uint4 *>(img + row * XPI_ROW_BYTES + ((t & 7) << 4)) = make_uint4(0, 0, 0, 0);
     if ((t & 7) == 0) scale[row] = 0.f;
 }
-
-struct GemmEpi {   // EPI_IMG arguments
-    uint8_t *img;
-    float *scale;
-    const float *wt;
-    float bt, base_temp;
-    int64_t N, npad;   // rows m = b * N + n
-    int H;
-};
-
-struct GemmSmem {   // control block placed after the tiles
-    uint64_t w_full;
-    uint64_t a_full[GT_STAGES], a_empty[GT_STAGES];
-    uint64_t t_full[2], t_empty[2];
-    uint32_t tmem_base;
-};
 
 template <int EPI>
 __global__ void __launch_bounds__(GT_THREADS, 1)
@@ -110,62 +83,10 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
 
     if (warp < 8) {
         // ---------------- producers: X tile panel -> bf16 hi/lo, SWIZZLE_128B K-major ----------------
-        const int tid = threadIdx.x;
-        const int64_t total = my_tiles * panels;   // (tile, panel) items of this CTA, in order
-        auto load = [&](int64_t it, float4 (&v)[GT_LD]) {
-            if (it >= total) return;
-            const int64_t tile = worker + (it / panels) * n_workers;
-            const int p = (int)(it % panels);
-#pragma unroll
-            for (int i = 0; i < GT_LD / 2; ++i) {   // 8 consecutive k (32 B) per item: one 16-B bf16 chunk of the row
-                const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
-                const int64_t m = tile * GT_M + row;
-                if (m < M) {
-                    const float4 *src = reinterpret_cast<const float4 *>(X + m * K + p * GT_KP + c8 * 8);
-                    v[2 * i] = __ldg(src);
-                    v[2 * i + 1] = __ldg(src + 1);
-                } else {
-                    v[2 * i] = v[2 * i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-            }
-        };
-        int stage = 0, phase = 0;
-        auto store = [&](const float4 (&v)[GT_LD]) {
-            mbar_wait(&cb->a_empty[stage], phase ^ 1);
-            uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
-#pragma unroll
-            for (int i = 0; i < GT_LD / 2; ++i) {
-                const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
-                uint32_t hi[4], lo[4];
-#pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    const float4 f = v[2 * i + j];
-                    const __nv_bfloat162 ha = __floats2bfloat162_rn(f.x, f.y), hb = __floats2bfloat162_rn(f.z, f.w);
-                    const uint32_t ua = *reinterpret_cast<const uint32_t *>(&ha), ub = *reinterpret_cast<const uint32_t *>(&hb);
-                    const __nv_bfloat162 la = __floats2bfloat162_rn(f.x - __uint_as_float(ua << 16), f.y - __uint_as_float(ua & 0xffff0000u));
-                    const __nv_bfloat162 lb = __floats2bfloat162_rn(f.z - __uint_as_float(ub << 16), f.w - __uint_as_float(ub & 0xffff0000u));
-                    hi[2 * j] = ua; hi[2 * j + 1] = ub;
-                    lo[2 * j] = *reinterpret_cast<const uint32_t *>(&la); lo[2 * j + 1] = *reinterpret_cast<const uint32_t *>(&lb);
-                }
-                const uint32_t off = sw128_off(row, c8);
-                *reinterpret_cast<uint4 *>(hi_base + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4 *>(hi_base + GT_PANEL_BYTES + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-            }
-            fence_proxy_async();
-            mbar_arrive(&cb->a_full[stage]);
-            if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
-        };
-        float4 va[GT_LD], vb[GT_LD];
-        load(0, va);
-        load(1, vb);
-        for (int64_t it = 0; it < total; it += 2) {
-            store(va);
-            load(it + 2, va);
-            if (it + 1 < total) {
-                store(vb);
-                load(it + 3, vb);
-            }
-        }
+        gemm_produce(X, M, K, panels, my_tiles, sA,
+                     [&](int64_t ti) { return (worker + ti * n_workers) * (int64_t)GT_M; },
+                     [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
+                     [&](int st) { mbar_arrive(&cb->a_full[st]); });
     } else if (warp == 8) {
         // ---------------- MMA issuer ----------------
         if (lane == 0 && my_tiles > 0) {
@@ -207,70 +128,20 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     } else {
         // ---------------- epilogue: TMEM -> registers -> + bias -> global ----------------
         const int q = warp & 3;   // TMEM lane quarter this warp may access (warps 9..12 -> 1, 2, 3, 0)
-        float wtr[32];
-        if (EPI == EPI_IMG) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) wtr[i] = __ldg(ep.wt + i);
-        }
         for (int64_t it = 0; it < my_tiles; ++it) {
             const int64_t tile = worker + it * n_workers;
             const int buf = (int)(it & 1);
             mbar_wait(&cb->t_full[buf], (uint32_t)((it >> 1) & 1));
             tc_fence_after();
-            const int64_t m = tile * GT_M + q * 32 + lane;
-            int64_t bi = 0, n = 0;
-            if (EPI == EPI_IMG) { bi = m / ep.N; n = m - bi * ep.N; }
+            const int64_t m0 = tile * GT_M + q * 32 + (lane & ~3);   // first of this lane's 4 rows after the transpose
+            int64_t bi0 = 0, n0 = 0;
+            if (EPI == EPI_IMG) { bi0 = m0 / ep.N; n0 = m0 - bi0 * ep.N; }
 #pragma unroll 1
             for (int c0 = 0; c0 < GT_N; c0 += 32) {
                 uint32_t r[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * GT_N + c0), r);
                 tmem_wait_ld();
-                if (m < M) {
-                    const float4 *b4 = reinterpret_cast<const float4 *>(bias + half * GT_N + c0);
-                    if (EPI == EPI_F32) {
-                        float *yrow = Y + m * Nn + half * GT_N;
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            const float4 bb = __ldg(b4 + (j >> 2));
-                            float4 o;
-                            o.x = __uint_as_float(r[j]) + bb.x;
-                            o.y = __uint_as_float(r[j + 1]) + bb.y;
-                            o.z = __uint_as_float(r[j + 2]) + bb.z;
-                            o.w = __uint_as_float(r[j + 3]) + bb.w;
-                            *reinterpret_cast<float4 *>(yrow + c0 + j) = o;
-                        }
-                    } else {
-                        // one head: + bias, Ada-Temp, fp16 hi/lo image row (chunk j -> position j ^ (n & 7))
-                        const int h = (half * GT_N + c0) >> 5;
-                        const int64_t row = (bi * ep.H + h) * ep.npad + n;
-                        uint8_t *dst = ep.img + row * XPI_ROW_BYTES;
-                        const int sw = (int)(n & 7);
-                        float d = ep.bt;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float4 ba = __ldg(b4 + 2 * j), bb = __ldg(b4 + 2 * j + 1);
-                            const float v[8] = {__uint_as_float(r[8 * j]) + ba.x,     __uint_as_float(r[8 * j + 1]) + ba.y,
-                                                __uint_as_float(r[8 * j + 2]) + ba.z, __uint_as_float(r[8 * j + 3]) + ba.w,
-                                                __uint_as_float(r[8 * j + 4]) + bb.x, __uint_as_float(r[8 * j + 5]) + bb.y,
-                                                __uint_as_float(r[8 * j + 6]) + bb.z, __uint_as_float(r[8 * j + 7]) + bb.w};
-                            uint32_t hi[4], lo[4];
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                d = fmaf(v[2 * i], wtr[8 * j + 2 * i], d);
-                                d = fmaf(v[2 * i + 1], wtr[8 * j + 2 * i + 1], d);
-                                const __half2 hh = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-                                const float2 hf = __half22float2(hh);
-                                const __half2 ll = __floats2half2_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
-                                hi[i] = *reinterpret_cast<const uint32_t *>(&hh);
-                                lo[i] = *reinterpret_cast<const uint32_t *>(&ll);
-                            }
-                            *reinterpret_cast<uint4 *>(dst + ((j ^ sw) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                            *reinterpret_cast<uint4 *>(dst + (((4 + j) ^ sw) << 4)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                        }
-                        const float tau = ep.base_temp + fminf(fmaxf(d, -0.4f), 0.4f);   // Ada-Temp (IrregularMesh.py:168)
-                        ep.scale[row] = kLog2e / tau;
-                    }
-                }
+                gemm_epilogue_chunk<EPI>(r, lane, m0, bi0, n0, M, bias + half * GT_N + c0, ep.wt, Y, Nn, half * GT_N + c0, ep);
             }
             tc_fence_before();
             mbar_arrive(&cb->t_empty[buf]);
@@ -308,6 +179,8 @@ static int launch_gemm_impl(const float *x, const float *w, const float *bias, f
     const int chunks = Nn * (K / 8);
     gemm_tc_pack_kernel<<<(chunks + 255) / 256, 256, 0, st>>>(w, Nn, K, (uint8_t *)img);
     HAET_LAUNCHED();
+    if (gemm2_tc_supported(K, Nn) && !getenv("HAET_GEMM_1CTA"))
+        return launch_gemm2_tc(EPI, x, (const uint8_t *)img, bias, y, M, K, Nn, ep, st);
     const int panels = K / GT_KP, n_halves = Nn / GT_N;
     const size_t smem = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + sizeof(GemmSmem);
     static size_t smem_set = 0;

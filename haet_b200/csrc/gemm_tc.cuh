@@ -1,0 +1,209 @@
+// Shared declarations of the tcgen05 GEMM kernels (gemm_tc.cu: one CTA per tile half; gemm2_tc.cu: CTA pairs).
+#pragma once
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace haet {
+
+constexpr int GT_M = 128;          // rows per CTA tile (UMMA M per CTA)
+constexpr int GT_N = 128;          // W rows (output columns) held by one CTA
+constexpr int GT_KP = 64;          // k per panel: 64 bf16 = one 128-byte swizzle row
+constexpr int GT_STAGES = 3;
+constexpr int GT_PANEL_BYTES = GT_M * 128;   // 16 KB: 128 rows x 128 B
+constexpr int GT_PROD = 256;       // producer threads (warps 0-7)
+constexpr int GT_THREADS = GT_PROD + 32 + 128;   // + MMA warp (8) + epilogue warps (9-12)
+constexpr int GT_LD = GT_M * GT_KP / 4 / GT_PROD;   // float4 per producer thread per panel (8)
+enum { EPI_F32 = 0, EPI_IMG = 1 };
+
+struct GemmEpi {   // EPI_IMG arguments
+    uint8_t *img;
+    float *scale;
+    const float *wt;
+    float bt, base_temp;
+    int64_t N, npad;   // rows m = b * N + n
+    int H;
+    int dbg;   // development switches (HAET_GEMM_DBG): 1 = no epilogue stores, 2 = no global loads
+};
+
+struct GemmSmem {   // control block placed after the tiles
+    uint64_t w_full;
+    uint64_t a_full[GT_STAGES], a_empty[GT_STAGES];
+    uint64_t t_full[2], t_empty[2];
+    uint32_t tmem_base;
+};
+
+
+// Producer side shared by both GEMM kernels: this CTA's 128 rows of each of its tiles, k panel by k panel, fp32 from
+// global -> bf16 hi/lo -> SWIZZLE_128B K-major operand stage, two panels ahead in registers.
+// (A quarter-panel software pipeline with 8 loads in flight was tried and was 2x slower: a warp has 6 scoreboard
+// slots, so independent loads cannot be retired independently.)
+//   row0(i)        first global row of this CTA's i-th tile
+//   wait_empty(s, parity) / arrive_full(s): the stage hand-shake with the MMA issuer
+constexpr int GT_L2_AHEAD = 3;   // tiles
+template <class Row0, class WaitEmpty, class ArriveFull>
+__device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_t M, int K, int panels, int64_t my_tiles,
+                                             uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0) {
+    using namespace tc;
+    const int tid = threadIdx.x;
+    const int64_t total = my_tiles * panels;   // (tile, panel) items of this CTA, in order
+    // the rows of a tile are contiguous in X: one thread asks L2 for the tile GT_L2_AHEAD tiles ahead, so that the
+    // register loads below see L2 latency instead of HBM latency
+    auto prefetch_tile = [&](int64_t ti) {
+        if (tid != 0 || ti >= my_tiles) return;
+        const int64_t m0 = row0(ti);
+        if (m0 >= M) return;
+        const int64_t rows = M - m0 < GT_M ? M - m0 : GT_M;
+        bulk_prefetch_l2(X + m0 * K, (uint32_t)(rows * K * sizeof(float)));
+    };
+    for (int i = 0; i < GT_L2_AHEAD; ++i) prefetch_tile(i);
+    auto load = [&](int64_t it, float4 (&v)[GT_LD]) {
+        if (it >= total) return;
+        const int64_t ti = it / panels;
+        const int p = (int)(it - ti * panels);
+        if (p == 0) prefetch_tile(ti + GT_L2_AHEAD);
+        const int64_t m0 = row0(ti);
+#pragma unroll
+        for (int i = 0; i < GT_LD / 2; ++i) {   // 8 consecutive k (32 B) per item: one 16-B bf16 chunk of the row
+            const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
+            const int64_t m = m0 + row;
+            if (m < M && !(dbg & 2)) {
+                const float4 *src = reinterpret_cast<const float4 *>(X + m * K + p * GT_KP + c8 * 8);
+                v[2 * i] = __ldg(src);
+                v[2 * i + 1] = __ldg(src + 1);
+            } else {
+                v[2 * i] = v[2 * i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    };
+    int stage = 0, phase = 0;
+    auto store = [&](const float4 (&v)[GT_LD]) {
+        wait_empty(stage, phase ^ 1);
+        uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
+#pragma unroll
+        for (int i = 0; i < GT_LD / 2; ++i) {
+            const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const float4 f = v[2 * i + j];
+                const __nv_bfloat162 ha = __floats2bfloat162_rn(f.x, f.y), hb = __floats2bfloat162_rn(f.z, f.w);
+                const uint32_t ua = *reinterpret_cast<const uint32_t *>(&ha), ub = *reinterpret_cast<const uint32_t *>(&hb);
+                const __nv_bfloat162 la = __floats2bfloat162_rn(f.x - __uint_as_float(ua << 16), f.y - __uint_as_float(ua & 0xffff0000u));
+                const __nv_bfloat162 lb = __floats2bfloat162_rn(f.z - __uint_as_float(ub << 16), f.w - __uint_as_float(ub & 0xffff0000u));
+                hi[2 * j] = ua; hi[2 * j + 1] = ub;
+                lo[2 * j] = *reinterpret_cast<const uint32_t *>(&la); lo[2 * j + 1] = *reinterpret_cast<const uint32_t *>(&lb);
+            }
+            const uint32_t off = sw128_off(row, c8);
+            *reinterpret_cast<uint4 *>(hi_base + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4 *>(hi_base + GT_PANEL_BYTES + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+        fence_proxy_async();
+        arrive_full(stage);
+        if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+    };
+    float4 va[GT_LD], vb[GT_LD];
+    load(0, va);
+    load(1, vb);
+    for (int64_t it = 0; it < total; it += 2) {
+        store(va);
+        load(it + 2, va);
+        if (it + 1 < total) {
+            store(vb);
+            load(it + 3, vb);
+        }
+    }
+}
+
+// Exchange lane bit LB with register-index bit RB of a 32-register fragment (one butterfly stage of an in-warp
+// transpose): afterwards register bit RB selects the row bit LB and lane bit LB selects the column bit RB.
+template <int LB, int RB>
+__device__ __forceinline__ void xpose_stage(uint32_t (&r)[32], int lane) {
+    const bool up = (lane >> LB) & 1;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        if (j & (1 << RB)) continue;
+        const uint32_t a = r[j], b = r[j | (1 << RB)];
+        const uint32_t got = __shfl_xor_sync(0xffffffffu, up ? a : b, 1 << LB);
+        r[j] = up ? got : a;
+        r[j | (1 << RB)] = up ? b : got;
+    }
+}
+
+// Epilogue of one 32-row x 32-column accumulator chunk as tcgen05.ld.32x32b delivers it (r[j] = row `lane`, column j).
+// Written row-per-lane, every store instruction would touch 32 different rows with 16 bytes each: measured, those
+// stores bounded the GEMM at ~2 TB/s.  Two butterfly stages regroup the chunk so that 4 adjacent lanes hold 4 rows and
+// write 64 contiguous bytes of one row per instruction (whole 32-byte sectors, 8 rows per instruction).
+//   m0 / bi0 / n0: global row (and its batch / point index, EPI_IMG) of this lane's FIRST row = warp row + (lane & ~3)
+//   bias32 / wt32: the chunk's 32 bias values / the Ada-Temp weights (EPI_IMG); col0: first global column of the chunk
+template <int EPI>
+__device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane, int64_t m0, int64_t bi0, int64_t n0, int64_t M,
+                                                    const float *bias32, const float *wt32, float *Y, int ldy, int col0,
+                                                    const GemmEpi &ep) {
+    const int l4 = lane & 3;
+    if (EPI == EPI_F32) {
+        xpose_stage<0, 2>(r, lane);
+        xpose_stage<1, 3>(r, lane);
+        // register 4 i + 16 h + c = row m0 + i, column 16 h + 4 l4 + c
+        const float4 b0 = *reinterpret_cast<const float4 *>(bias32 + 4 * l4), b1 = *reinterpret_cast<const float4 *>(bias32 + 16 + 4 * l4);
+        if (ep.dbg & 1) return;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (m0 + i >= M) break;
+            float *y = Y + (m0 + i) * ldy + col0 + 4 * l4;
+            *reinterpret_cast<float4 *>(y) = make_float4(__uint_as_float(r[4 * i]) + b0.x, __uint_as_float(r[4 * i + 1]) + b0.y,
+                                                         __uint_as_float(r[4 * i + 2]) + b0.z, __uint_as_float(r[4 * i + 3]) + b0.w);
+            *reinterpret_cast<float4 *>(y + 16) = make_float4(__uint_as_float(r[4 * i + 16]) + b1.x, __uint_as_float(r[4 * i + 17]) + b1.y,
+                                                              __uint_as_float(r[4 * i + 18]) + b1.z, __uint_as_float(r[4 * i + 19]) + b1.w);
+        }
+    } else {
+        xpose_stage<0, 3>(r, lane);
+        xpose_stage<1, 4>(r, lane);
+        // register 8 i + c = row m0 + i, column 8 l4 + c: lane l4 owns 16-byte chunk l4 (hi) and 4 + l4 (lo) of the image row
+        const float4 ba = *reinterpret_cast<const float4 *>(bias32 + 8 * l4), bb = *reinterpret_cast<const float4 *>(bias32 + 8 * l4 + 4);
+        const float4 wa = *reinterpret_cast<const float4 *>(wt32 + 8 * l4), wb = *reinterpret_cast<const float4 *>(wt32 + 8 * l4 + 4);
+        const float bs[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+        const float ws[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+        const int h = col0 >> 5;
+        int64_t bi = bi0, n = n0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float d = 0.f;
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float v0 = __uint_as_float(r[8 * i + 2 * c]) + bs[2 * c], v1 = __uint_as_float(r[8 * i + 2 * c + 1]) + bs[2 * c + 1];
+                d = fmaf(v0, ws[2 * c], d);
+                d = fmaf(v1, ws[2 * c + 1], d);
+                const __half2 hh = __floats2half2_rn(v0, v1);
+                const float2 hf = __half22float2(hh);
+                const __half2 ll = __floats2half2_rn(v0 - hf.x, v1 - hf.y);
+                hi[c] = *reinterpret_cast<const uint32_t *>(&hh);
+                lo[c] = *reinterpret_cast<const uint32_t *>(&ll);
+            }
+            d += __shfl_xor_sync(0xffffffffu, d, 1);
+            d += __shfl_xor_sync(0xffffffffu, d, 2);
+            if (m0 + i < M && !(ep.dbg & 1)) {
+                // one head: Ada-Temp, fp16 hi/lo image row (chunk j -> position j ^ (n & 7))
+                const int64_t row = (bi * ep.H + h) * ep.npad + n;
+                uint8_t *dst = ep.img + row * XPI_ROW_BYTES;
+                const int sw = (int)(n & 7);
+                *reinterpret_cast<uint4 *>(dst + ((l4 ^ sw) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4 *>(dst + (((4 + l4) ^ sw) << 4)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                if (l4 == 0) {
+                    const float tau = ep.base_temp + fminf(fmaxf(d + ep.bt, -0.4f), 0.4f);   // Ada-Temp (IrregularMesh.py:168)
+                    ep.scale[row] = kLog2e / tau;
+                }
+            }
+            if (++n >= ep.N) { n = 0; ++bi; }
+        }
+    }
+}
+
+// CTA-pair variant (Nn == 256): every x tile is loaded and split once; the pair shares W through cta_group::2 MMAs
+bool gemm2_tc_supported(int K, int Nn);
+int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *bias, float *y, int64_t M, int K, int Nn,
+                    const GemmEpi &ep, cudaStream_t st);
+
+}  // namespace haet
