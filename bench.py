@@ -300,28 +300,43 @@ def run_gpu_arm(args):
         ms = float(t)
     value = N * world / (ms * 1e-3)
 
-    # ---- end to end through the public module API with HOST buffers (pinned): H2D + forward + D2H per step ----
+    # ---- end to end through the public host API (haet_b200.HostStream) with HOST buffers (pinned): every step uploads
+    # its 1M points, runs the layer and downloads the result; consecutive steps overlap on three streams (upload of
+    # step i + 1 | kernels of step i | download of step i - 1).  single_call_ms is one un-overlapped request.
+    from haet_b200 import HostStream
     xh = x.cpu().pin_memory()
-    oh = torch.empty_like(xh).pin_memory()
+    ohs = [torch.empty_like(xh).pin_memory() for _ in range(3)]
     def e2e_step():
         xd = xh.to(dev, non_blocking=True)
-        oh.copy_(m(xd), non_blocking=True)
+        ohs[0].copy_(m(xd), non_blocking=True)
     for _ in range(2):
         e2e_step()
     barrier()
-    k2 = max(2, min(args.steps, 5))
     e0.record()
-    for _ in range(k2):
-        e2e_step()
+    e2e_step()
+    e1.record()
+    barrier()
+    single_ms = e0.elapsed_time(e1)
+    hs = HostStream(m, depth=3)
+    for i in range(3):
+        hs.submit(xh, ohs[i % 3])
+    hs.drain()
+    barrier()
+    k2 = max(6, min(args.steps, 12))
+    e0.record()
+    for i in range(k2):
+        hs.submit(xh, ohs[i % 3])
+    hs.drain()
     e1.record()
     barrier()
     ms2 = e0.elapsed_time(e1) / k2
     if world > 1:
-        t = torch.tensor([ms2], device=dev)
+        t = torch.tensor([ms2, single_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms2 = float(t)
-    e2e = {"value": N * world / (ms2 * 1e-3), "unit": UNIT, "ms_per_step": ms2,
-           "h2d_bytes_per_step": xh.numel() * 4, "d2h_bytes_per_step": oh.numel() * 4}
+        ms2, single_ms = float(t[0]), float(t[1])
+    e2e = {"value": N * world / (ms2 * 1e-3), "unit": UNIT, "ms_per_step": ms2, "steps": k2,
+           "h2d_bytes_per_step": xh.numel() * 4, "d2h_bytes_per_step": ohs[0].numel() * 4,
+           "api": "haet_b200.HostStream(depth=3).submit(pinned x, pinned out)", "single_call_ms": single_ms}
 
     if rank != 0:
         if world > 1:

@@ -2,15 +2,16 @@
 
 Public surface (mirrors the reference's ``models.PhysicsAttention`` and ``balltree`` modules):
     Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D, Physics_Attention_Structured_Mesh_3D
-    ErwinTransformer, build_balltree_with_rotations, build_balltree, patch_model
+    ErwinTransformer, build_balltree_with_rotations, build_balltree, patch_model, HostStream (host-resident meshes)
 All arithmetic runs in libhaet_b200.so (hand-written CUDA behind the C-ABI of include/haet_b200.h).
 """
 from ._lib import HaetError, lib  # noqa: F401
 from .balltree import build_balltree, build_balltree_with_rotations  # noqa: F401
 from .erwin import ErwinTransformer  # noqa: F401
+from .host_stream import HostStream  # noqa: F401
 from .physics_attention import (Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D,  # noqa: F401
                                 Physics_Attention_Structured_Mesh_3D, from_reference, patch_model)
 
 __all__ = ["Physics_Attention_Irregular_Mesh", "Physics_Attention_Structured_Mesh_2D",
            "Physics_Attention_Structured_Mesh_3D", "ErwinTransformer", "build_balltree_with_rotations",
-           "build_balltree", "patch_model", "from_reference", "HaetError", "lib"]
+           "build_balltree", "patch_model", "from_reference", "HostStream", "HaetError", "lib"]

@@ -249,6 +249,29 @@ def test_c_abi_host_call_equals_module(name):
     assert torch.equal(got, want)
 
 
+def test_host_stream_pipelined_equals_module():
+    """HostStream overlaps consecutive host requests on two streams; every result equals the plain module call."""
+    import haet_b200 as hb
+    cfg, sd, x, out, m = _module("layer_irregular_small")
+    m.keep_taps = False
+    g = torch.Generator().manual_seed(5)
+    xs = [(x + 0.1 * k * torch.randn(x.shape, generator=g)).contiguous().pin_memory() for k in range(5)]
+    outs = [torch.empty_like(v).pin_memory() for v in xs]
+    want = [m(v.cuda()).cpu() for v in xs]
+    hs = hb.HostStream(m, depth=2)
+    for v, o in zip(xs, outs):
+        hs.submit(v, o)
+    hs.drain()
+    for o, w in zip(outs, want):
+        assert torch.equal(o, w)
+    with pytest.raises(ValueError):
+        hs.submit(xs[0].cuda(), outs[0])
+    with pytest.raises(ValueError):
+        hs.submit(torch.empty_like(xs[0]), outs[0])    # not pinned
+    with pytest.raises(ValueError):
+        hs.submit(xs[0], outs[0][:, :-1].contiguous().pin_memory())
+
+
 def test_point_sharded_equals_single(monkeypatch):
     """R rank-partials merged in rank order == one rank over all points (emulated on one GPU: the ranks'
     slice_reduce calls run back to back and their packed partials are concatenated rank-major, exactly what
