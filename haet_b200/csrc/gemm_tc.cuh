@@ -37,32 +37,21 @@ struct GemmSmem {   // control block placed after the tiles
 
 // Producer side shared by both GEMM kernels: this CTA's 128 rows of each of its tiles, k panel by k panel, fp32 from
 // global -> bf16 hi/lo -> SWIZZLE_128B K-major operand stage, two panels ahead in registers.
-// (A quarter-panel software pipeline with 8 loads in flight was tried and was 2x slower: a warp has 6 scoreboard
-// slots, so independent loads cannot be retired independently.)
+// (Tried and dropped: a quarter-panel software pipeline with 8 loads in flight -- 2x slower, a warp has 6 scoreboard
+// slots so independent loads cannot be retired independently; cp.async.bulk.prefetch.L2 of the tiles ahead -- ncu
+// showed the x tiles then crossing HBM twice, 0.50 ms instead of 0.43 ms.)
 //   row0(i)        first global row of this CTA's i-th tile
 //   wait_empty(s, parity) / arrive_full(s): the stage hand-shake with the MMA issuer
-constexpr int GT_L2_AHEAD = 3;   // tiles
 template <class Row0, class WaitEmpty, class ArriveFull>
 __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_t M, int K, int panels, int64_t my_tiles,
                                              uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0) {
     using namespace tc;
     const int tid = threadIdx.x;
     const int64_t total = my_tiles * panels;   // (tile, panel) items of this CTA, in order
-    // the rows of a tile are contiguous in X: one thread asks L2 for the tile GT_L2_AHEAD tiles ahead, so that the
-    // register loads below see L2 latency instead of HBM latency
-    auto prefetch_tile = [&](int64_t ti) {
-        if (tid != 0 || ti >= my_tiles) return;
-        const int64_t m0 = row0(ti);
-        if (m0 >= M) return;
-        const int64_t rows = M - m0 < GT_M ? M - m0 : GT_M;
-        bulk_prefetch_l2(X + m0 * K, (uint32_t)(rows * K * sizeof(float)));
-    };
-    for (int i = 0; i < GT_L2_AHEAD; ++i) prefetch_tile(i);
     auto load = [&](int64_t it, float4 (&v)[GT_LD]) {
         if (it >= total) return;
         const int64_t ti = it / panels;
         const int p = (int)(it - ti * panels);
-        if (p == 0) prefetch_tile(ti + GT_L2_AHEAD);
         const int64_t m0 = row0(ti);
 #pragma unroll
         for (int i = 0; i < GT_LD / 2; ++i) {   // 8 consecutive k (32 B) per item: one 16-B bf16 chunk of the row
