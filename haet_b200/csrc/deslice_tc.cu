@@ -120,13 +120,21 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
             tc_fence_before();
             mbar_arrive(&ctl->o_empty[ob]);
-            const int64_t n = n_begin + (int64_t)te * DT_TILE + r;
-            if (n < n_end) {
-                float4 *p = reinterpret_cast<float4 *>(dst + n * inner);
+            // in-warp transpose (tc.cuh): 4 adjacent lanes hold 4 rows and write 64 contiguous bytes of one row per
+            // store (8 rows per instruction) instead of 32 lanes writing 16 bytes of 32 different rows
+            xpose_stage<0, 2>(v, lane);
+            xpose_stage<1, 3>(v, lane);
+            const int64_t n0 = n_begin + (int64_t)te * DT_TILE + (r & ~3);
+            const int l4 = lane & 3;
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    p[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
-                                       __uint_as_float(v[4 * i + 3]));
+            for (int i = 0; i < 4; ++i) {
+                if (n0 + i < n_end) {
+                    float *p = dst + (n0 + i) * inner + 4 * l4;
+                    *reinterpret_cast<float4 *>(p) = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                                                 __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                    *reinterpret_cast<float4 *>(p + 16) = make_float4(__uint_as_float(v[4 * i + 16]), __uint_as_float(v[4 * i + 17]),
+                                                                      __uint_as_float(v[4 * i + 18]), __uint_as_float(v[4 * i + 19]));
+                }
             }
         }
     } else if (warp == 21) {

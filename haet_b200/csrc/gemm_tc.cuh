@@ -105,21 +105,6 @@ __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_
     }
 }
 
-// Exchange lane bit LB with register-index bit RB of a 32-register fragment (one butterfly stage of an in-warp
-// transpose): afterwards register bit RB selects the row bit LB and lane bit LB selects the column bit RB.
-template <int LB, int RB>
-__device__ __forceinline__ void xpose_stage(uint32_t (&r)[32], int lane) {
-    const bool up = (lane >> LB) & 1;
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-        if (j & (1 << RB)) continue;
-        const uint32_t a = r[j], b = r[j | (1 << RB)];
-        const uint32_t got = __shfl_xor_sync(0xffffffffu, up ? a : b, 1 << LB);
-        r[j] = up ? got : a;
-        r[j | (1 << RB)] = up ? b : got;
-    }
-}
-
 // Epilogue of one 32-row x 32-column accumulator chunk as tcgen05.ld.32x32b delivers it (r[j] = row `lane`, column j).
 // Written row-per-lane, every store instruction would touch 32 different rows with 16 bytes each: measured, those
 // stores bounded the GEMM at ~2 TB/s.  Two butterfly stages regroup the chunk so that 4 adjacent lanes hold 4 rows and

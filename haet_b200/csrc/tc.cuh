@@ -285,4 +285,20 @@ __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16 &hi, __nv_bflo
 }
 
 }  // namespace tc
+// Exchange lane bit LB with register-index bit RB of a 32-register fragment (one butterfly stage of an in-warp
+// transpose): afterwards register bit RB selects the row bit LB and lane bit LB selects the column bit RB.
+template <int LB, int RB>
+__device__ __forceinline__ void xpose_stage(uint32_t (&r)[32], int lane) {
+    const bool up = (lane >> LB) & 1;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        if (j & (1 << RB)) continue;
+        const uint32_t a = r[j], b = r[j | (1 << RB)];
+        const uint32_t got = __shfl_xor_sync(0xffffffffu, up ? a : b, 1 << LB);
+        r[j] = up ? got : a;
+        r[j | (1 << RB)] = up ? b : got;
+    }
+}
+
+
 }  // namespace haet
