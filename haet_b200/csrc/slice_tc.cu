@@ -198,15 +198,25 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 uint32_t r[32];
                 tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
-                float tmax = -INFINITY;
+                // t, the half's max AND P = 2^t in one loop: P is computed speculatively at the current running max so
+                // that the MUFU / FMA / conversion instructions of a warp interleave (a separate "max, then exp" phase
+                // left the MUFU pipe idle whenever the scheduler's warps were in the same phase); the rare raise
+                // below recomputes P from the kept t.
+                float tmax = -INFINITY, l0 = 0.f, l1 = 0.f;
+                uint32_t pk[16];   // P as packed fp16: word c = points (2c, 2c+1) of this half
 #pragma unroll
                 for (int c = 0; c < 32; c += 4) {
                     const float4 sa = s4[hh * 8 + (c >> 2)];
-                    float v;
-                    v = fmaf(__uint_as_float(r[c]) + bcj, sa.x, -m_run); r[c] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r[c + 1]) + bcj, sa.y, -m_run); r[c + 1] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r[c + 2]) + bcj, sa.z, -m_run); r[c + 2] = __float_as_uint(v); tmax = fmaxf(tmax, v);
-                    v = fmaf(__uint_as_float(r[c + 3]) + bcj, sa.w, -m_run); r[c + 3] = __float_as_uint(v); tmax = fmaxf(tmax, v);
+                    const float v0 = fmaf(__uint_as_float(r[c]) + bcj, sa.x, -m_run), v1 = fmaf(__uint_as_float(r[c + 1]) + bcj, sa.y, -m_run);
+                    const float v2 = fmaf(__uint_as_float(r[c + 2]) + bcj, sa.z, -m_run), v3 = fmaf(__uint_as_float(r[c + 3]) + bcj, sa.w, -m_run);
+                    r[c] = __float_as_uint(v0); r[c + 1] = __float_as_uint(v1); r[c + 2] = __float_as_uint(v2); r[c + 3] = __float_as_uint(v3);
+                    tmax = fmaxf(fmaxf(tmax, v0), v1);   // FMNMX3
+                    tmax = fmaxf(fmaxf(tmax, v2), v3);
+                    const float p0 = fast_ex2(v0), p1 = fast_ex2(v1), p2 = fast_ex2(v2), p3 = fast_ex2(v3);
+                    l0 += p0; l1 += p1; l0 += p2; l1 += p3;
+                    const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                    pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
                 }
                 if (ragged) {   // columns past the chunk's last point: weight 0 (their image rows are zero)
                     tmax = -INFINITY;
@@ -219,13 +229,19 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 // lazy running max: the very first half fixes it, later ones raise it only past 2^raise_thr
                 const bool first = (i == 0 && hh == 0);
                 const bool need = first || tmax > raise_thr;
-                if (__any_sync(0xffffffffu, need)) {
+                if (ragged || __any_sync(0xffffffffu, need)) {   // warp-uniform (ragged is per tile)
                     const float delta = need ? tmax : 0.f;   // m_new = m_run + delta
                     const float sc = first ? 0.f : fast_ex2(-delta);
                     m_run += delta;
                     l_run *= sc;
+                    l0 = 0.f; l1 = 0.f;
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) r[c] = __float_as_uint(__uint_as_float(r[c]) - delta);
+                    for (int c = 0; c < 32; c += 2) {   // P again, at the raised max (and with the ragged columns masked)
+                        const float p0 = fast_ex2(__uint_as_float(r[c]) - delta), p1 = fast_ex2(__uint_as_float(r[c + 1]) - delta);
+                        l0 += p0; l1 += p1;
+                        const __half2 h2 = __floats2half2_rn(p0, p1);
+                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&h2);
+                    }
                     if (i > 0) {   // rescale this warpgroup's TMEM accumulator (its earlier MMA2s are done)
                         mbar_wait(&ctl->mma2_done[w][sub], (uint32_t)((i - 1) & 1));
                         tc_fence_after();
@@ -249,16 +265,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                         tmem_st16(dcol, ph);
                     }
                 }
-                float l = l_run;
-                uint32_t pk[16];   // P as packed fp16: word c = points (2c, 2c+1) of this half
-#pragma unroll
-                for (int c = 0; c < 32; c += 2) {
-                    const float p0 = fast_ex2(__uint_as_float(r[c])), p1 = fast_ex2(__uint_as_float(r[c + 1]));
-                    l += p0; l += p1;
-                    const __half2 h2 = __floats2half2_rn(p0, p1);
-                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&h2);
-                }
-                l_run = l;
+                l_run += l0 + l1;
                 tmem_st16(dcol + hh * 16, pk);
             }
             tmem_wait_st();
