@@ -8,7 +8,7 @@
 // shared-memory tile feeds both MMAs:
 //   MMA1 (kind::f16, 3-term fp16 split = fp32-class logits; precision_study.py), tile read K-major:
 //        D[g, n] = Ws[g,:] . x_proj[n,:]          M = 128 slices, N = 64 points, K' = 96
-//   softmax warps (thread = slice row g): t = (D + bc_g) * s_n - m_run, P = 2^t, l += P, P -> TMEM as packed fp16.
+//   softmax warps (thread = slice row g): t = D * s_n - m_run (the bias bc_g enters D through one extra K step), P = 2^t, l += P, P -> TMEM as packed fp16.
 //        m_run is a LAZY running max: it is only raised when a tile exceeds it by 2^8 (P stays inside fp16),
 //        so the TMEM accumulator rescale is off the common path.
 //   MMA2 (kind::f16, A = P from TMEM, B = the hi half of the tile read MN-major: 32 columns):
@@ -26,7 +26,7 @@ using namespace tc;
 
 constexpr int ST_C = 32;            // dim_head handled by this kernel
 constexpr int ST_TILE = 64;         // points per tile
-constexpr int ST_STAGES = 6;
+constexpr int ST_STAGES = 10;
 constexpr int ST_THREADS = 608;     // 16 softmax warps + loader warp + 2 MMA-issuing warps
 constexpr int ST_GB = 128;          // slices per block (UMMA M)
 constexpr int ST_MAX_GB = 4;        // up to 512 slices
@@ -54,7 +54,8 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int n_gb = (G + ST_GB - 1) / ST_GB;
     uint8_t *sW = smem;                                              // [n_gb][2][16 KB]: [hi|hi] rows, [lo|0] rows
-    uint8_t *sB = sW + (size_t)n_gb * 2 * (ST_GB * 128);             // [stages][8 KB] point tiles
+    uint8_t *sOne = sW + (size_t)n_gb * 2 * (ST_GB * 128);           // [64 points][128 B]: k = 0, 1 are 1.0 (bias operand)
+    uint8_t *sB = sOne + ST_TILE_BYTES;                              // [stages][8 KB] point tiles
     float *sS = reinterpret_cast<float *>(sB + (size_t)ST_STAGES * ST_TILE_BYTES);   // [stages][64] s_n
     SliceCtl *ctl = reinterpret_cast<SliceCtl *>(sS + ST_STAGES * ST_TILE);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
@@ -92,7 +93,19 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         *reinterpret_cast<uint4 *>(w1 + sw128_off(r, ck)) = *reinterpret_cast<const uint4 *>(hi);
         *reinterpret_cast<uint4 *>(w1 + sw128_off(r, ck + 4)) = *reinterpret_cast<const uint4 *>(hi);
         *reinterpret_cast<uint4 *>(w2 + sw128_off(r, ck)) = *reinterpret_cast<const uint4 *>(lo);
-        *reinterpret_cast<uint4 *>(w2 + sw128_off(r, ck + 4)) = make_uint4(0, 0, 0, 0);
+        // k = 32, 33 of the lo rows carry the logit bias bc = bs_g - log(-log eps) as fp16 hi + lo: one more K step of
+        // MMA1 against the constant tile sOne adds it to D, so the softmax warps do not spend an FADD per element on it
+        uint4 bias4 = make_uint4(0, 0, 0, 0);
+        if (ck == 0 && g < G) {
+            const float bc = bs[g] - shift;
+            const __half bh = __float2half_rn(bc), bl = __float2half_rn(bc - __half2float(bh));
+            bias4.x = (uint32_t)__half_as_ushort(bh) | ((uint32_t)__half_as_ushort(bl) << 16);
+        }
+        *reinterpret_cast<uint4 *>(w2 + sw128_off(r, ck + 4)) = bias4;
+    }
+    for (int idx = threadIdx.x; idx < ST_TILE * 8; idx += ST_THREADS) {
+        const int n = idx >> 3, c = idx & 7;
+        *reinterpret_cast<uint4 *>(sOne + sw128_off(n, c)) = make_uint4(c == 0 ? 0x3c003c00u : 0u, 0, 0, 0);   // fp16 1.0, 1.0
     }
     fence_proxy_async();
     tc_fence_before();
@@ -125,7 +138,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         const int Qw = n_tiles * pw;
         const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
         const uint32_t id2 = instr_desc(FMT_F16, ST_GB, ST_SCOLS, false, true);
-        const uint32_t sW_a = smem_u32(sW) >> 4, sB_a = smem_u32(sB) >> 4;
+        const uint32_t sW_a = smem_u32(sW) >> 4, sB_a = smem_u32(sB) >> 4, one_a = smem_u32(sOne) >> 4;
         int t1 = 0, jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;   // MMA1 cursor: tile, block within the stream, stage (+phase), D buffer
         int jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;           // MMA2 cursor
         for (int q = 0; q < Qw + ST_NBUF; ++q) {
@@ -158,6 +171,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks)
                         mma_bf16_ss(d, desc_sw128_u(a2 + ks * 2, 16, 1024), desc_sw128_u(b1 + ks * 2, 16, 1024), id1, true);
+                    mma_bf16_ss(d, desc_sw128_u(a2 + 4, 16, 1024), desc_sw128_u(one_a, 16, 1024), id1, true);   // + bc_g (k = 32..47 of the lo rows)
                     tc_commit(&ctl->d_full[w][buf1]);
                 }
                 __syncwarp();
@@ -181,7 +195,6 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         const uint32_t scol = tmem_base + lane_base + (uint32_t)(w * 2 + sub) * ST_SCOLS;
         int buf = sub, bph = 0;   // D / P buffer k % 3 of the current item and its phase (k / 3) & 1
         float m_run = 0.f, l_run = 0.f;
-        const float bcj = (pw > 0 && g < G) ? bs[g] - shift : 0.f;
         const int last_valid = (int)(n_end - n_begin) - (n_tiles - 1) * ST_TILE;   // points in the last tile
         int t = 0, jj = sub, i = 0;   // item k = t * pw + jj of the stream; i = items this warpgroup has done
         while (pw > 0 && jj >= pw) { jj -= pw; ++t; }
@@ -207,8 +220,8 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
 #pragma unroll
                 for (int c = 0; c < 32; c += 4) {
                     const float4 sa = s4[hh * 8 + (c >> 2)];
-                    const float v0 = fmaf(__uint_as_float(r[c]) + bcj, sa.x, -m_run), v1 = fmaf(__uint_as_float(r[c + 1]) + bcj, sa.y, -m_run);
-                    const float v2 = fmaf(__uint_as_float(r[c + 2]) + bcj, sa.z, -m_run), v3 = fmaf(__uint_as_float(r[c + 3]) + bcj, sa.w, -m_run);
+                    const float v0 = fmaf(__uint_as_float(r[c]), sa.x, -m_run), v1 = fmaf(__uint_as_float(r[c + 1]), sa.y, -m_run);
+                    const float v2 = fmaf(__uint_as_float(r[c + 2]), sa.z, -m_run), v3 = fmaf(__uint_as_float(r[c + 3]), sa.w, -m_run);
                     r[c] = __float_as_uint(v0); r[c + 1] = __float_as_uint(v1); r[c + 2] = __float_as_uint(v2); r[c + 3] = __float_as_uint(v3);
                     tmax = fmaxf(fmaxf(tmax, v0), v1);   // FMNMX3
                     tmax = fmaxf(fmaxf(tmax, v2), v3);
@@ -330,7 +343,7 @@ int64_t slice_tc_chunks(const haet_layer_shape *s) { return s->N > 0 ? 2 * cdiv(
 int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,
                     const float *bs, float *chunk_parts, cudaStream_t st) {
     const int n_gb = (s->slice_num + ST_GB - 1) / ST_GB;
-    const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)ST_STAGES * ST_TILE_BYTES +
+    const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
     static size_t smem_set = 0;
     if (smem > smem_set) {
