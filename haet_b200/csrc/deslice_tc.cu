@@ -46,8 +46,12 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     uint8_t *sW = smem;                                     // [g_pad rows][hi(32 fp16) | lo(32 fp16)]  K-major SW128
     uint8_t *sV = sW + (size_t)g_pad * 128;                 // [g_pad rows][32 fp32]  S'_h, MN-major SW128_BASE32B
     uint8_t *sA = sV + (size_t)g_pad * 128;                 // [stages][128 rows][hi | lo]
-    float2 *sC = reinterpret_cast<float2 *>(sA + (size_t)DT_STAGES * DT_TILE_BYTES);   // [g_pad] {bc_g, -lse2_g}
-    float *sS = reinterpret_cast<float *>(sC + g_pad);                                 // [stages][128] s_n
+    // bias operands of MMA1's extra K step (no swizzle: 8-row x 16-B core matrices, K halves 128 B apart, 8-row groups 256 B
+    // apart): sBb row g = {bc_g hi, bc_g lo, 0 ..} with bc = bs_g - log(-log eps), sOne row n = {1, 1, 0 ..}
+    uint8_t *sBb = sA + (size_t)DT_STAGES * DT_TILE_BYTES;  // [g_pad / 8][256 B]
+    uint8_t *sOne = sBb + (size_t)g_pad * 32;               // [128 / 8][256 B]
+    float *sL = reinterpret_cast<float *>(sOne + DT_TILE * 32);                        // [g_pad] -lse2_g
+    float *sS = sL + g_pad;                                                            // [stages][128] s_n
     DesliceCtl *ctl = reinterpret_cast<DesliceCtl *>(sS + DT_STAGES * DT_TILE);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
     const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
@@ -90,8 +94,23 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         *reinterpret_cast<uint4 *>(sV + mn32_off(g, ck)) = reinterpret_cast<const uint4 *>(sv)[0];
         *reinterpret_cast<uint4 *>(sV + mn32_off(g, ck) + 16) = reinterpret_cast<const uint4 *>(sv)[1];
     }
-    for (int g = threadIdx.x; g < g_pad; g += DT_THREADS)
-        sC[g] = g < G ? make_float2(bs[g] - shift, -lse2[(size_t)bh * G + g]) : make_float2(0.f, -INFINITY);
+    for (int g = threadIdx.x; g < g_pad; g += DT_THREADS) {
+        sL[g] = g < G ? -lse2[(size_t)bh * G + g] : -INFINITY;
+        uint32_t b2 = 0;
+        if (g < G) {
+            const float bc = bs[g] - shift;
+            const __half bhi = __float2half_rn(bc), blo = __float2half_rn(bc - __half2float(bhi));
+            b2 = (uint32_t)__half_as_ushort(bhi) | ((uint32_t)__half_as_ushort(blo) << 16);
+        }
+        uint8_t *dstb = sBb + (g >> 3) * 256 + (g & 7) * 16;
+        *reinterpret_cast<uint4 *>(dstb) = make_uint4(b2, 0, 0, 0);
+        *reinterpret_cast<uint4 *>(dstb + 128) = make_uint4(0, 0, 0, 0);
+    }
+    for (int n = threadIdx.x; n < DT_TILE; n += DT_THREADS) {
+        uint8_t *dst1 = sOne + (n >> 3) * 256 + (n & 7) * 16;
+        *reinterpret_cast<uint4 *>(dst1) = make_uint4(0x3c003c00u, 0, 0, 0);   // fp16 1.0, 1.0
+        *reinterpret_cast<uint4 *>(dst1 + 128) = make_uint4(0, 0, 0, 0);
+    }
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
@@ -163,6 +182,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, DT_GC, false, false);
         const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
         const uint32_t wbase = smem_u32(sW) >> 4, vbase = smem_u32(sV) >> 4, abase = smem_u32(sA) >> 4;
+        const uint32_t bb_a = smem_u32(sBb) >> 4, one_a = smem_u32(sOne) >> 4;
         int jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;            // MMA1 cursor: chunk within the stream, stage (+phase), D buffer
         int t2 = 0, jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;    // MMA2 cursor
         for (int q = 0; q < Qw + DT_NBUF; ++q) {
@@ -195,6 +215,8 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                         mma_bf16_ss(d, desc_sw128_u(a + 4 + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, true);
                         mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + 4 + ks * 2, 16, 1024), id1, true);
                     }
+                    // + bc_g: ones[n, 0:16] . bias[g, 0:16]  (the softmax warps then need no per-element bias add)
+                    mma_bf16_ss(d, desc_u(one_a, 128, 256, 0), desc_u(bb_a + (uint32_t)(w + 2 * jj1) * (DT_GC * 32 >> 4), 128, 256, 0), id1, true);
                     tc_commit(&ctl->d_full[w][buf1]);
                 }
                 __syncwarp();
@@ -219,17 +241,19 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             mbar_wait(&ctl->d_full[w][buf], (uint32_t)bph);
             tc_fence_after();
             const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(w, buf);
-            const float4 *cc = reinterpret_cast<const float4 *>(sC + (w + 2 * jj) * DT_GC);
+            const float4 *ll = reinterpret_cast<const float4 *>(sL + (w + 2 * jj) * DT_GC);
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
                 uint32_t r[32];
                 tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
 #pragma unroll
-                for (int c = 0; c < 32; c += 2) {
-                    const float4 k2 = cc[hh * 16 + (c >> 1)];   // {bc, -lse} of two slices
-                    r[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c]) + k2.x, sn, k2.y)));
-                    r[c + 1] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 1]) + k2.z, sn, k2.w)));
+                for (int c = 0; c < 32; c += 4) {
+                    const float4 k4 = ll[hh * 8 + (c >> 2)];   // -lse2 of four slices
+                    r[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c]), sn, k4.x)));
+                    r[c + 1] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 1]), sn, k4.y)));
+                    r[c + 2] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 2]), sn, k4.z)));
+                    r[c + 3] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 3]), sn, k4.w)));
                 }
                 tmem_st32(dcol + hh * 32, r);
             }
@@ -256,7 +280,7 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
                       const float *states, const float *ws, const float *bs, float *o, cudaStream_t st) {
     if (s->N == 0 || s->B == 0) return HAET_OK;
     const int n_gc = (s->slice_num + DT_GC - 1) / DT_GC, g_pad = n_gc * DT_GC;
-    const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + sizeof(float2) * g_pad +
+    const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
                         sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
     static size_t smem_set = 0;
     if (smem > smem_set) {
