@@ -10,6 +10,7 @@
 // tokens are gathered through the permutation into shared memory, RMSNorm -> PE -> qkv -> attention
 // -> proj -> RMSNorm -> SwiGLU all run there, and the result is scattered back in place.
 #include "common.cuh"
+#include "tc.cuh"
 
 namespace haet {
 
@@ -30,7 +31,7 @@ __device__ void ball_linear(const float *in, int in_ld, const float *__restrict_
         const float *wr = W + (size_t)o * K;
         const float *ir = in + i * in_ld;
         float acc = b ? b[o] : 0.f;
-        for (int k = 0; k < K; ++k) acc = fmaf(ir[k], __ldg(wr + k), acc);
+        for (int k = 0; k < K; ++k) acc = fmaf(ir[k], *(wr + k), acc);
         if (ACC) out[i * out_ld + o] += acc; else out[i * out_ld + o] = acc;
     }
 }
@@ -47,25 +48,25 @@ __device__ void ball_linear4(const float *in, int in_ld, const float *__restrict
         const int i = t % rows, o = (t / rows) << 2;
         const float4 *x = reinterpret_cast<const float4 *>(in + i * in_ld);
         const float4 *w = reinterpret_cast<const float4 *>(W + (size_t)o * K);
-        const float4 bb = __ldg(reinterpret_cast<const float4 *>(b + o));
+        const float4 bb = *(reinterpret_cast<const float4 *>(b + o));
         float a0 = bb.x, a1 = bb.y, a2 = bb.z, a3 = bb.w;
         float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;
         const float4 *w2 = nullptr;
         if (GATE) {
             w2 = reinterpret_cast<const float4 *>(W2 + (size_t)o * K);
-            const float4 b2v = __ldg(reinterpret_cast<const float4 *>(b2 + o));
+            const float4 b2v = *(reinterpret_cast<const float4 *>(b2 + o));
             g0 = b2v.x; g1 = b2v.y; g2 = b2v.z; g3 = b2v.w;
         }
 #pragma unroll 4
         for (int k = 0; k < k4; ++k) {
             const float4 xv = x[k];
-            const float4 p = __ldg(w + k), q = __ldg(w + k4 + k), r = __ldg(w + 2 * k4 + k), s = __ldg(w + 3 * k4 + k);
+            const float4 p = *(w + k), q = *(w + k4 + k), r = *(w + 2 * k4 + k), s = *(w + 3 * k4 + k);
             a0 = fmaf(xv.x, p.x, a0); a0 = fmaf(xv.y, p.y, a0); a0 = fmaf(xv.z, p.z, a0); a0 = fmaf(xv.w, p.w, a0);
             a1 = fmaf(xv.x, q.x, a1); a1 = fmaf(xv.y, q.y, a1); a1 = fmaf(xv.z, q.z, a1); a1 = fmaf(xv.w, q.w, a1);
             a2 = fmaf(xv.x, r.x, a2); a2 = fmaf(xv.y, r.y, a2); a2 = fmaf(xv.z, r.z, a2); a2 = fmaf(xv.w, r.w, a2);
             a3 = fmaf(xv.x, s.x, a3); a3 = fmaf(xv.y, s.y, a3); a3 = fmaf(xv.z, s.z, a3); a3 = fmaf(xv.w, s.w, a3);
             if (GATE) {
-                const float4 p2 = __ldg(w2 + k), q2 = __ldg(w2 + k4 + k), r2 = __ldg(w2 + 2 * k4 + k), s2 = __ldg(w2 + 3 * k4 + k);
+                const float4 p2 = *(w2 + k), q2 = *(w2 + k4 + k), r2 = *(w2 + 2 * k4 + k), s2 = *(w2 + 3 * k4 + k);
                 g0 = fmaf(xv.x, p2.x, g0); g0 = fmaf(xv.y, p2.y, g0); g0 = fmaf(xv.z, p2.z, g0); g0 = fmaf(xv.w, p2.w, g0);
                 g1 = fmaf(xv.x, q2.x, g1); g1 = fmaf(xv.y, q2.y, g1); g1 = fmaf(xv.z, q2.z, g1); g1 = fmaf(xv.w, q2.w, g1);
                 g2 = fmaf(xv.x, r2.x, g2); g2 = fmaf(xv.y, r2.y, g2); g2 = fmaf(xv.z, r2.z, g2); g2 = fmaf(xv.w, r2.w, g2);
@@ -173,11 +174,26 @@ constexpr int EB_THREADS = 256;
 
 __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restrict__ x, const float *__restrict__ pos,
                                                                  const int64_t *__restrict__ perm,
-                                                                 const float *__restrict__ wts, BlockW w, int bs, int dim,
-                                                                 int heads, int hidden, int d) {
+                                                                 const float *__restrict__ wts_g, BlockW w, int bs, int dim,
+                                                                 int heads, int hidden, int d, int w_lo, int w_n) {
     extern __shared__ __align__(16) float sm[];
     const int ld = pad_dim(dim), ldq = pad_dim(3 * dim), ldh = pad_dim(hidden);
-    float *xs = sm;                    // [bs][ld]   residual stream
+    // the block's w_n packed weights (contiguous from float offset w_lo) are staged into shared memory by ONE bulk
+    // copy that overlaps the token gather: every linear layer then reads its weights at shared-memory latency (the
+    // kernel was bound by the L2 latency of those loads: 44 % long-scoreboard stalls, profiles/r1_ncu_summary.md)
+    uint64_t *wbar = reinterpret_cast<uint64_t *>(sm);   // sm[0..3]
+    float *wsm = sm + 4;                                  // [w_n]
+    const float *wts = wts_g;
+    if (w_n) {
+        if (threadIdx.x == 0) {
+            tc::mbar_init(wbar, 1);
+            tc::fence_barrier_init();
+            tc::mbar_arrive_expect_tx(wbar, (uint32_t)w_n * 4u);
+            tc::bulk_g2s(wsm, wts_g + w_lo, (uint32_t)w_n * 4u, wbar);
+        }
+        wts = wsm - w_lo;
+    }
+    float *xs = wsm + w_n;             // [bs][ld]   residual stream
     float *us = xs + bs * ld;          // [bs][ld]   normed / attention output
     float *qkv = us + bs * ld;         // [bs][ldq]
     float *hid = qkv + bs * ldq;       // [bs][ldh]  gated SwiGLU product
@@ -212,6 +228,7 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restri
         for (int i = 0; i < bs; ++i) s += rel[i * 4 + tid];
         cen[tid] = s / (float)bs;
     }
+    if (w_n) tc::mbar_wait(wbar, 0);   // initialised before the first __syncthreads above
     ball_rmsnorm(xs, ld, wts + w.norm1, us, bs, dim);
     __syncthreads();
     for (int t = tid; t < bs * d; t += blockDim.x) { const int i = t / d, j = t - i * d; rel[i * 4 + j] -= cen[j]; }
@@ -408,8 +425,13 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
                       const int64_t *rot, const float *wts, Walker &wk, cudaStream_t st) {
     const int dim = c->c_hidden[level], hidden = dim * c->mlp_ratio, bs = c->ball_sizes[level], d = c->dimensionality;
     HAET_CHECK_ARG(n % bs == 0, "level %d: %lld tokens are not a multiple of ball size %d", level, (long long)n, bs);
-    const size_t smem = block_smem(bs, dim, hidden);
-    HAET_CHECK_ARG(smem <= 200 * 1024, "ball of %d tokens x dim %d does not fit shared memory", bs, dim);
+    // weights of one block (Walker::block: contiguous, every tensor padded to 4 floats) staged in shared memory if they fit
+    int64_t w_n = 0;
+    { Walker probe; probe.block(dim, hidden, d); w_n = probe.off; }
+    const size_t smem_act = block_smem(bs, dim, hidden) + 16;
+    HAET_CHECK_ARG(smem_act <= 200 * 1024, "ball of %d tokens x dim %d does not fit shared memory", bs, dim);
+    if (smem_act + (size_t)w_n * 4 > 220 * 1024 || ((dim | hidden) & 3)) w_n = 0;
+    const size_t smem = smem_act + (size_t)w_n * 4;
     static size_t smem_set = 0;
     if (smem > 48 * 1024 && smem > smem_set) {
         HAET_CUDA(cudaFuncSetAttribute(erwin_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -421,7 +443,7 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
         const int64_t *perm = (rotate && (k & 1)) ? rot : nullptr;
         if (rotate && (k & 1)) HAET_CHECK_ARG(rot != nullptr, "tree_idx_rot must be provided for rotation");
         if (n == 0) continue;
-        erwin_block_kernel<<<(unsigned)(n / bs), EB_THREADS, smem, st>>>(x, pos, perm, wts, bw, bs, dim, heads, hidden, d);
+        erwin_block_kernel<<<(unsigned)(n / bs), EB_THREADS, smem, st>>>(x, pos, perm, wts, bw, bs, dim, heads, hidden, d, bw.norm1, (int)w_n);
         HAET_LAUNCHED();
     }
     return HAET_OK;
