@@ -245,7 +245,7 @@ __device__ void warp_nth_element(const KeyCtx &c, int *idx, int first, int nth, 
     __syncwarp();
 }
 
-constexpr int BT_WARP_NODE = 24;   // nodes of at least this many points are split by a whole warp
+constexpr int BT_WARP_NODE = 12;   // nodes of at least this many points are split by a whole warp
 
 // Split every node of levels [0, n_levels) of the implicit median tree over idx[0, n).
 // stop_small: partition_ball_tree stops at <= 1 point (balltree.h:219); build_tree always splits.
