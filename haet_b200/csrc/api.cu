@@ -46,8 +46,12 @@ static int64_t image_bytes(const haet_layer_shape *s) {   // packed-weight scrat
     const int inner = s->heads * s->dim_head;
     return align_up(4 * (int64_t)(inner > s->dim ? inner : s->dim) * (inner > s->dim ? inner : s->dim), 256);
 }
-static int64_t deslice_o_bytes(const haet_layer_shape *s) {
-    return align_up(s->B * s->N * (int64_t)s->heads * s->dim_head * (int64_t)sizeof(float), 256);
+static int64_t deslice_o_bytes(const haet_layer_shape *s) {   // fp32 o, or its operand image (rows padded to 256)
+    return align_up(opi_bytes(s->B * s->N, s->heads * s->dim_head), 256);
+}
+// pass 2 writes o as the to_out GEMM's operand image when both run on the tensor-core path
+static bool out_opi(const haet_layer_shape *s) {
+    return g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && gemm_opi_supported(s->heads * s->dim_head, s->dim);
 }
 static int64_t deslice_ws_bytes(const haet_layer_shape *s) { return deslice_o_bytes(s) + image_bytes(s); }
 static int64_t slice_parts_bytes(const haet_layer_shape *s) {
@@ -199,12 +203,15 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
     if (!(g_stage_mask & 4))
         rc = HAET_OK;
     else if (g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s))
-        rc = launch_deslice_tc(s, sv.img, sv.scale, lse2_d, states_d, ws_d, bs_d, o, st);
+        rc = launch_deslice_tc(s, sv.img, sv.scale, lse2_d, states_d, ws_d, bs_d, o, out_opi(s) ? 1 : 0, st);
     else
         rc = launch_deslice(s, sv.xp, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
     if (rc) return rc;
     if (!(g_stage_mask & 8)) return HAET_OK;
     const int inner = s->heads * s->dim_head;
+    if (out_opi(s))
+        return launch_gemm_tc_opi((const uint8_t *)o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim,
+                                  (char *)workspace_d + deslice_o_bytes(s), st);
     if (g_path == 0 && gemm_tc_supported(inner, s->dim))
         return launch_gemm_tc(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, (char *)workspace_d + deslice_o_bytes(s), st);
     return launch_linear(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, st);

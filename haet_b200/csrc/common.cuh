@@ -72,6 +72,13 @@ int launch_linear(const float *a, const float *w, const float *bias, float *out,
                   int Nn, cudaStream_t st);
 bool gemm_tc_supported(int K, int Nn);
 int64_t gemm_tc_image_bytes(int K, int Nn);
+// OPI: the to_out GEMM's A operand as pass 2 writes it when both tensor-core kernels run: rows m = b * N + n in tiles of 128,
+// [tile][k panel of 64][hi | lo][128 rows x 128 B]: 16-byte chunk c (8 bf16) of row r at r * 128 + ((c ^ (r & 7)) << 4), i.e.
+// every (tile, panel) is one 32 KB SWIZZLE_128B K-major stage of the GEMM, loaded by one bulk copy (no conversion warps).
+bool gemm_opi_supported(int K, int Nn);
+inline int64_t opi_bytes(int64_t M, int K) { return (M + 255) / 256 * 256 * (int64_t)K * 4; }
+int launch_gemm_tc_opi(const uint8_t *a_img, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
+                       cudaStream_t st);
 int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
                    cudaStream_t st);
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
@@ -82,7 +89,7 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
                     const float *bs, float *chunk_parts, cudaStream_t st);
 bool deslice_tc_supported(const haet_layer_shape *s);
 int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
-                      const float *states, const float *ws, const float *bs, float *o, cudaStream_t st);
+                      const float *states, const float *ws, const float *bs, float *o, int o_image, cudaStream_t st);
 extern int g_path;   // 0: tensor-core kernels where supported; 1: fp32 SIMT kernels everywhere
 int64_t slice_chunks(const haet_layer_shape *s);
 int launch_slice_partial(const haet_layer_shape *s, const float *xp, const float *ws, const float *bs,

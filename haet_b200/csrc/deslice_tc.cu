@@ -10,6 +10,8 @@
 // head slice streams through a 4-stage ring of bulk copies; O is double-buffered in TMEM and stored by 4 epilogue warps.
 #include <cuda_fp16.h>
 
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -38,7 +40,7 @@ __device__ __forceinline__ uint32_t dt_dbuf_col(int w, int buf) { return 128u + 
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
-                  int64_t N, int64_t npad, int H, int G, int64_t chunk_pts, float *__restrict__ o) {
+                  int64_t N, int64_t npad, int H, int G, int64_t chunk_pts, float *__restrict__ o, int o_image) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int n_gc = (G + DT_GC - 1) / DT_GC;
@@ -139,6 +141,36 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
             tc_fence_before();
             mbar_arrive(&ctl->o_empty[ob]);
+            if (o_image) {
+                // the to_out GEMM's operand image (common.cuh: OPI): lane l4 of a 4-lane group holds channels 8 l4 .. 8 l4 + 7
+                // of 4 rows and writes them as one 16-byte bf16 hi chunk and one lo chunk of the (tile, panel) block
+                xpose_stage<0, 3>(v, lane);
+                xpose_stage<1, 4>(v, lane);
+                const int64_t n0 = n_begin + (int64_t)te * DT_TILE + (r & ~3);
+                const int l4 = lane & 3, cc = (h & 1) * 4 + l4, panels = inner >> 6;
+                uint8_t *oimg = reinterpret_cast<uint8_t *>(o);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const float f0 = __uint_as_float(v[8 * i + 2 * c]), f1 = __uint_as_float(v[8 * i + 2 * c + 1]);
+                        const __nv_bfloat162 hb = __floats2bfloat162_rn(f0, f1);
+                        const uint32_t ub = *reinterpret_cast<const uint32_t *>(&hb);
+                        const __nv_bfloat162 lb = __floats2bfloat162_rn(f0 - __uint_as_float(ub << 16), f1 - __uint_as_float(ub & 0xffff0000u));
+                        hi[c] = ub;
+                        lo[c] = *reinterpret_cast<const uint32_t *>(&lb);
+                    }
+                    if (n0 + i < n_end) {
+                        const int64_t m = (int64_t)b * N + n0 + i;
+                        const int rr = (int)(m & 127);
+                        uint8_t *blk = oimg + (((m >> 7) * panels + (h >> 1)) * 2) * (int64_t)(128 * 128) + sw128_off(rr, cc);
+                        *reinterpret_cast<uint4 *>(blk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                        *reinterpret_cast<uint4 *>(blk + 128 * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    }
+                }
+                continue;
+            }
             // in-warp transpose (tc.cuh): 4 adjacent lanes hold 4 rows and write 64 contiguous bytes of one row per
             // store (8 rows per instruction) instead of 32 lanes writing 16 bytes of 32 different rows
             xpose_stage<0, 2>(v, lane);
@@ -277,7 +309,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
 bool deslice_tc_supported(const haet_layer_shape *s) { return s->dim_head == DT_C && s->slice_num <= DT_MAX_G; }
 
 int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
-                      const float *states, const float *ws, const float *bs, float *o, cudaStream_t st) {
+                      const float *states, const float *ws, const float *bs, float *o, int o_image, cudaStream_t st) {
     if (s->N == 0 || s->B == 0) return HAET_OK;
     const int n_gc = (s->slice_num + DT_GC - 1) / DT_GC, g_pad = n_gc * DT_GC;
     const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
@@ -298,7 +330,7 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
     deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                       xpi_npad(s->N), s->heads, s->slice_num, chunk_pts, o);
+                                                       xpi_npad(s->N), s->heads, s->slice_num, chunk_pts, o, o_image);
     HAET_LAUNCHED();
     return HAET_OK;
 }

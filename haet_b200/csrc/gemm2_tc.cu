@@ -21,7 +21,7 @@ using namespace tc;
 constexpr int G2_N = 256;
 constexpr int G2_EPI = 256;                          // epilogue threads: 2 warpgroups, alternating 32-column chunks
 constexpr int G2_THREADS = GT_PROD + 32 + G2_EPI;    // producers (warps 0-7), MMA warp (8), epilogue warps (9-16)
-constexpr int G2_CB_BYTES = 96;                      // GemmSmem rounded up to 16 bytes; bias[256] and wt[32] follow
+constexpr int G2_CB_BYTES = 128;                     // GemmSmem rounded up to 16 bytes; bias[256] and wt[32] follow
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G2_THREADS, 1)
@@ -45,7 +45,11 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
     if (warp == 8) {
         if (lane == 0) {
             mbar_init(&cb->w_full, 1);
-            for (int s = 0; s < GT_STAGES; ++s) { mbar_init(&cb->a_full[s], 2 * GT_PROD); mbar_init(&cb->a_empty[s], 1); }
+            for (int s = 0; s < GT_STAGES; ++s) {
+                mbar_init(&cb->a_full[s], ep.a_img ? 2 : 2 * GT_PROD);
+                mbar_init(&cb->a_empty[s], 1);
+                mbar_init(&cb->a_land[s], 1);
+            }
             for (int b = 0; b < 2; ++b) { mbar_init(&cb->t_full[b], 1); mbar_init(&cb->t_empty[b], 2 * G2_EPI); }
             fence_barrier_init();
         }
@@ -72,6 +76,36 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
     if (warp < 8) {
         // ---------------- producers: this CTA's 128 rows of the pair tile -> bf16 hi/lo, SWIZZLE_128B K-major ----------------
         const uint32_t full0 = mapa_u32(&cb->a_full[0], 0);   // the LEADER's a_full barriers (8 bytes apart)
+        if (ep.a_img) {
+            // A arrives as the ready-made operand image (pass 2 wrote [tile128][panel][hi | lo][128 rows x 128 B, swizzled]):
+            // warp 0 bulk-copies one 32 KB stage per (tile, panel), warp 1 relays "landed here" to the leader's a_full.
+            const uint8_t *Aimg = reinterpret_cast<const uint8_t *>(X);
+            const int64_t total = my_tiles * panels;
+            int stage = 0, phase = 0;
+            if (warp == 0) {
+                if (lane == 0) {
+                    for (int64_t it = 0; it < total; ++it) {
+                        const int64_t ti = it / panels;
+                        const int p = (int)(it - ti * panels);
+                        const int64_t t128 = (pair + ti * n_pairs) * 2 + rank;
+                        mbar_wait(&cb->a_empty[stage], (uint32_t)(phase ^ 1));
+                        mbar_arrive_expect_tx(&cb->a_land[stage], 2 * GT_PANEL_BYTES);
+                        bulk_g2s(sA + (size_t)stage * 2 * GT_PANEL_BYTES, Aimg + (size_t)(t128 * panels + p) * 2 * GT_PANEL_BYTES,
+                                 2 * GT_PANEL_BYTES, &cb->a_land[stage]);
+                        if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+                    }
+                }
+                __syncwarp();
+            } else if (warp == 1) {
+                for (int64_t it = 0; it < total; ++it) {
+                    mbar_wait(&cb->a_land[stage], (uint32_t)phase);
+                    fence_proxy_async();
+                    if (lane == 0) mbar_arrive_remote(full0 + 8u * stage);
+                    __syncwarp();
+                    if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        } else
         gemm_produce(X, M, K, panels, my_tiles, sA,
                      [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; },
                      [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },

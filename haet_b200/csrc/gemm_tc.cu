@@ -203,6 +203,16 @@ int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, 
     return launch_gemm_impl<EPI_F32>(x, w, bias, y, M, K, Nn, img, ep, st);
 }
 
+// to_out with A given as the operand image pass 2 wrote (common.cuh: OPI); only the CTA-pair kernel reads it
+bool gemm_opi_supported(int K, int Nn) { return gemm2_tc_supported(K, Nn) && !getenv("HAET_GEMM_1CTA") && !getenv("HAET_NO_OPI"); }
+int launch_gemm_tc_opi(const uint8_t *a_img, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
+                       cudaStream_t st) {
+    HAET_CHECK_ARG(gemm_opi_supported(K, Nn), "gemm_tc_opi: unsupported K=%d Nn=%d", K, Nn);
+    GemmEpi ep{};
+    ep.a_img = 1;
+    return launch_gemm_impl<EPI_F32>(reinterpret_cast<const float *>(a_img), w, bias, y, M, K, Nn, img, ep, st);
+}
+
 // in_project_x of the tensor-core path: X [B*N, dim] -> the spill's operand image + scales (no fp32 x_proj)
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
                      uint8_t *xpi, float *scale, void *img, cudaStream_t st) {

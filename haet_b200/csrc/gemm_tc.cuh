@@ -25,12 +25,14 @@ struct GemmEpi {   // EPI_IMG arguments
     int64_t N, npad;   // rows m = b * N + n
     int H;
     int dbg;   // development switches (HAET_GEMM_DBG): 1 = no epilogue stores, 2 = no global loads
+    int a_img; // X is the bf16 hi/lo operand image written by pass 2 (common.cuh: OPI), bulk-copied instead of converted
 };
 
 struct GemmSmem {   // control block placed after the tiles
     uint64_t w_full;
     uint64_t a_full[GT_STAGES], a_empty[GT_STAGES];
     uint64_t t_full[2], t_empty[2];
+    uint64_t a_land[GT_STAGES];   // pair kernel, operand-image A: this CTA's bulk copy of a stage has landed
     uint32_t tmem_base;
 };
 

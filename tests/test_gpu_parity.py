@@ -171,6 +171,7 @@ def test_layer_deterministic_and_noncontiguous_input():
 @pytest.mark.parametrize("variant,B,N,kw", [
     ("Physics_Attention_Irregular_Mesh", 1, 4099, dict(dim=256, heads=8, dim_head=32, slice_num=32, rotate=45, mlp_ratio=2)),
     ("Physics_Attention_Irregular_Mesh", 2, 1500, dict(dim=128, heads=8, dim_head=16, slice_num=100, rotate=45, mlp_ratio=2)),
+    ("Physics_Attention_Irregular_Mesh", 3, 1111, dict(dim=256, heads=8, dim_head=32, slice_num=64, rotate=45, mlp_ratio=2)),   # batches cross the 128-row GEMM tiles of the operand images
     ("Physics_Attention_Irregular_Mesh", 1, 3000, dict(dim=256, heads=8, dim_head=32, slice_num=512, rotate=45, mlp_ratio=1)),
     ("Physics_Attention_Irregular_Mesh", 1, 777, dict(dim=128, heads=2, dim_head=64, slice_num=64, rotate=0, mlp_ratio=4)),
     ("Physics_Attention_Structured_Mesh_2D", 4, 85 * 85, dict(dim=128, heads=8, dim_head=16, slice_num=64, H=85, W=85, rotate=45, mlp_ratio=1)),
