@@ -138,45 +138,62 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         const int Qw = n_tiles * pw;
         const uint32_t id1 = instr_desc(FMT_F16, ST_GB, ST_TILE, false, false);
         const uint32_t id2 = instr_desc(FMT_F16, ST_GB, ST_SCOLS, false, true);
-        const uint32_t sW_a = smem_u32(sW) >> 4, sB_a = smem_u32(sB) >> 4, one_a = smem_u32(sOne) >> 4;
-        int t1 = 0, jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;   // MMA1 cursor: tile, block within the stream, stage (+phase), D buffer
+        // Low descriptor words (tc.cuh: desc_join): the issuing warp was ~70 % busy per item rebuilding and masking
+        // descriptors, so they are kept as running sums -- one add per MMA.
+        constexpr uint32_t HI = DESC_HI_SW128_SBO1024;
+        constexpr uint32_t STG = ST_TILE_BYTES >> 4;                        // one stage, in 16-byte units
+        const uint32_t sB_a = smem_u32(sB) >> 4;
+        const uint32_t b1_lo0 = sB_a | (1u << 16);                          // point tile, K-major (LBO 16 B)
+        const uint32_t b2_lo0 = sB_a | (64u << 16);                         // the same tile MN-major (LBO 1024 B)
+        const uint32_t one_lo = (smem_u32(sOne) >> 4) | (1u << 16);
+        const uint32_t a_lo0 = ((smem_u32(sW) >> 4) + (uint32_t)w * (2 * ST_GB * 128 >> 4)) | (1u << 16);   // block j = w + 2 jj
+        constexpr uint32_t A_JJ = 2 * (2 * ST_GB * 128 >> 4), A_LO = ST_GB * 128 >> 4;   // next block of the stream; the [lo | bias] rows
+        int jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;           // MMA1 cursor: block within the stream, stage (+phase), D buffer
         int jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;           // MMA2 cursor
+        uint32_t b1_lo = b1_lo0, b2_lo = b2_lo0;           // running stage descriptors of the two cursors
         for (int q = 0; q < Qw + ST_NBUF; ++q) {
             if (q >= ST_NBUF) {   // ---- MMA2 of this stream's item k = q - 3: S_wg += P . hi   (wg = k & 1)
                 const int k = q - ST_NBUF;
                 mbar_wait(&ctl->p_full[w][buf2], (uint32_t)ph2);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint32_t b2 = sB_a + (uint32_t)st2 * (ST_TILE_BYTES >> 4);
                     const uint32_t pa = tmem_base + st_dbuf_col(w, buf2), sd = tmem_base + (uint32_t)(w * 2 + (k & 1)) * ST_SCOLS;
-#pragma unroll
-                    for (int ks = 0; ks < ST_TILE / 16; ++ks)   // K = 16 points = two 8-row swizzle atoms
-                        mma_f16_ts(sd, pa + ks * 8, desc_sw128_u(b2 + ks * 128, 1024, 1024), id2, ((k >> 1) | ks) != 0);
+                    mma_f16_ts(sd, pa, desc_join(b2_lo, HI), id2, k > 1);   // K = 16 points = two 8-row swizzle atoms per step
+                    mma_f16_ts(sd, pa + 8, desc_join(b2_lo + 128, HI), id2, true);
+                    mma_f16_ts(sd, pa + 16, desc_join(b2_lo + 256, HI), id2, true);
+                    mma_f16_ts(sd, pa + 24, desc_join(b2_lo + 384, HI), id2, true);
                     tc_commit(&ctl->mma2_done[w][k & 1]);
                     if (jj2 == pw - 1) tc_commit(&ctl->b_empty[st2]);
                 }
                 __syncwarp();
                 if (++buf2 == ST_NBUF) { buf2 = 0; ph2 ^= 1; }
-                if (++jj2 == pw) { jj2 = 0; if (++st2 == ST_STAGES) st2 = 0; }
+                if (++jj2 == pw) {
+                    jj2 = 0;
+                    b2_lo += STG;
+                    if (++st2 == ST_STAGES) { st2 = 0; b2_lo = b2_lo0; }
+                }
             }
-            if (q < Qw) {    // ---- MMA1 of item q: D = Ws_j . x_proj^T (hi.hi + hi.lo + lo.hi)
+            if (q < Qw) {    // ---- MMA1 of item q: D = Ws_j . x_proj^T (hi.hi + hi.lo + lo.hi) + bc_j
                 if (jj1 == 0) { mbar_wait(&ctl->b_full[st1], (uint32_t)ph1); tc_fence_after(); }
                 if (elect_one()) {
-                    const uint32_t b1 = sB_a + (uint32_t)st1 * (ST_TILE_BYTES >> 4);
-                    const uint32_t a1 = sW_a + (uint32_t)(w + 2 * jj1) * (2 * ST_GB * 128 >> 4), a2 = a1 + (ST_GB * 128 >> 4);
+                    const uint32_t al = a_lo0 + (uint32_t)jj1 * A_JJ;
                     const uint32_t d = tmem_base + st_dbuf_col(w, buf1);
-#pragma unroll
-                    for (int ks = 0; ks < 4; ++ks)
-                        mma_bf16_ss(d, desc_sw128_u(a1 + ks * 2, 16, 1024), desc_sw128_u(b1 + ks * 2, 16, 1024), id1, ks != 0);
-#pragma unroll
-                    for (int ks = 0; ks < 2; ++ks)
-                        mma_bf16_ss(d, desc_sw128_u(a2 + ks * 2, 16, 1024), desc_sw128_u(b1 + ks * 2, 16, 1024), id1, true);
-                    mma_bf16_ss(d, desc_sw128_u(a2 + 4, 16, 1024), desc_sw128_u(one_a, 16, 1024), id1, true);   // + bc_g (k = 32..47 of the lo rows)
+                    mma_bf16_ss(d, desc_join(al, HI), desc_join(b1_lo, HI), id1, false);          // [hi | hi] . [x hi | x lo], k 0..63
+                    mma_bf16_ss(d, desc_join(al + 2, HI), desc_join(b1_lo + 2, HI), id1, true);
+                    mma_bf16_ss(d, desc_join(al + 4, HI), desc_join(b1_lo + 4, HI), id1, true);
+                    mma_bf16_ss(d, desc_join(al + 6, HI), desc_join(b1_lo + 6, HI), id1, true);
+                    mma_bf16_ss(d, desc_join(al + A_LO, HI), desc_join(b1_lo, HI), id1, true);     // lo . x hi, k 0..31
+                    mma_bf16_ss(d, desc_join(al + A_LO + 2, HI), desc_join(b1_lo + 2, HI), id1, true);
+                    mma_bf16_ss(d, desc_join(al + A_LO + 4, HI), desc_join(one_lo, HI), id1, true);   // + bc_g (k = 32..47 of the lo rows)
                     tc_commit(&ctl->d_full[w][buf1]);
                 }
                 __syncwarp();
                 if (++buf1 == ST_NBUF) buf1 = 0;
-                if (++jj1 == pw) { jj1 = 0; ++t1; if (++st1 == ST_STAGES) { st1 = 0; ph1 ^= 1; } }
+                if (++jj1 == pw) {
+                    jj1 = 0;
+                    b1_lo += STG;
+                    if (++st1 == ST_STAGES) { st1 = 0; ph1 ^= 1; b1_lo = b1_lo0; }
+                }
             }
         }
         if (elect_one()) tc_commit(&ctl->all_done[w]);   // every MMA of this stream has completed when this phase flips

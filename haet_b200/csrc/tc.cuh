@@ -143,6 +143,15 @@ __device__ __forceinline__ uint64_t desc_u(uint32_t saddr16, uint32_t lbo_bytes,
     const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) | (layout << 29);
     return ((uint64_t)hi << 32) | lo;
 }
+// The same descriptors for hot issue loops: the high word of a SWIZZLE_128B descriptor with SBO = 1024 B is a constant and
+// the low word is (start address >> 4) | (LBO >> 4) << 16, so a loop keeps ONE running low word per operand and adds the
+// stage / k-step offsets to it (shared-memory addresses are < 2^18: the sum never leaves the 14 address bits).
+constexpr uint32_t DESC_HI_SW128_SBO1024 = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint64_t desc_join(uint32_t lo, uint32_t hi) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
+}
 __device__ __forceinline__ uint64_t desc_sw128_u(uint32_t saddr16, uint32_t lbo_bytes, uint32_t sbo_bytes) {
     return desc_u(saddr16, lbo_bytes, sbo_bytes, 2);
 }
