@@ -2,7 +2,9 @@
 // (IrregularMesh.py:221-232; the N x G weight matrix is recomputed tile by tile, never materialised).
 //
 // Points on the TMEM lanes (thread = point, so s_n = log2e / tau_n is a register):
-//   MMA1 (kind::f16, 3-term fp16 split): D[n, g] = x_proj[n,:] . Ws[g,:]      M = 128 points, N = 64 slices, K' = 96
+//   MMA1 (kind::f16, 3-term fp16 split): D[n, g] = x_proj[n,:] . Ws[g,:]      M = 128 points, N = 128 slices (64 when G <= 64), K' = 96 (+ 16: bias)
+//        (N = 128: with N = 64 / 32 every tcgen05.mma costs ~50 cycles of tensor-pipe time whatever its size -- the pipe was
+//        the bound of the kernel at one item per ~750 cycles -- so each instruction is made to carry twice the logits)
 //        (A = a 128-point tile of the spill's operand image, common.cuh, brought in by one bulk copy)
 //   softmax warps: P = 2^((D + bc_g) * s_n - lse2_g) -> TMEM in place (per-column constants from shared memory)
 //   MMA2 (kind::tf32, A = P from TMEM, B = S'_h as MN-major fp32): O[n, c] += sum_g P[n, g] S'[g, c]
@@ -20,22 +22,24 @@ using namespace tc;
 
 constexpr int DT_C = 32;
 constexpr int DT_TILE = 128;        // points per tile (UMMA M)
-constexpr int DT_GC = 64;           // slices per item (UMMA N of MMA1, K of MMA2)
+constexpr int DT_GCMAX = 128;       // slices per item (UMMA N of MMA1, K of MMA2): 128, or 64 when G <= 64
 constexpr int DT_STAGES = 4;
-constexpr int DT_THREADS = 736;     // 16 softmax warps + 4 epilogue warps + MMA warp 0 + loader warp + MMA warp 1
+constexpr int DT_THREADS = 576;     // 12 softmax warps (3 warpgroups) + 4 epilogue warps + MMA warp + loader warp
 constexpr int DT_MAX_G = 512;
-constexpr int DT_NBUF = 3;          // D / P buffers per issue stream
+constexpr int DT_NBUF = 3;          // D / P buffers (128 TMEM columns each)
 constexpr int DT_TILE_BYTES = DT_TILE * 128;
 
 struct DesliceCtl {
     uint64_t a_full[DT_STAGES], a_empty[DT_STAGES];
-    uint64_t d_full[2][DT_NBUF], p_full[2][DT_NBUF];
+    uint64_t d_full[DT_NBUF], p_full[DT_NBUF];
     uint64_t o_full[2], o_empty[2];
     uint32_t tmem_base;
 };
 
 // TMEM columns: O accumulators [issuer][buffer] x 32 at 0..127, D / P buffers [stream][3] x 64 at 128..511
-__device__ __forceinline__ uint32_t dt_dbuf_col(int w, int buf) { return 128u + (uint32_t)(w * DT_NBUF + buf) * DT_GC; }
+// TMEM columns: O accumulators (double-buffered) at 0..63, D / P buffers at 128 + 128 buf
+__device__ __forceinline__ uint32_t dt_dbuf_col(int buf) { return 128u + (uint32_t)buf * DT_GCMAX; }
+__host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (G + 127) / 128 * 128; }
 
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
@@ -43,8 +47,8 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                   int64_t N, int64_t npad, int H, int G, int64_t chunk_pts, float *__restrict__ o, int o_image) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
-    const int n_gc = (G + DT_GC - 1) / DT_GC;
-    const int g_pad = n_gc * DT_GC;
+    const int g_pad = dt_gpad(G), cw = g_pad < DT_GCMAX ? g_pad : DT_GCMAX;   // chunk width: slices per item
+    const int n_gc = g_pad / cw;
     uint8_t *sW = smem;                                     // [g_pad rows][hi(32 fp16) | lo(32 fp16)]  K-major SW128
     uint8_t *sV = sW + (size_t)g_pad * 128;                 // [g_pad rows][32 fp32]  S'_h, MN-major SW128_BASE32B
     uint8_t *sA = sV + (size_t)g_pad * 128;                 // [stages][128 rows][hi | lo]
@@ -62,15 +66,11 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     const int64_t n_end = min(N, n_begin + chunk_pts);
     const int n_tiles = (int)((n_end - n_begin + DT_TILE - 1) / DT_TILE);
 
-    if (warp == 20) {
+    if (warp == 16) {
         if (lane == 0) {
-            const uint32_t n_issuers = n_gc > 1 ? 2 : 1;
-            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], n_issuers); }
-            for (int w = 0; w < 2; ++w) {
-                for (int k = 0; k < DT_NBUF; ++k) { mbar_init(&ctl->d_full[w][k], 1); mbar_init(&ctl->p_full[w][k], 128); }
-                mbar_init(&ctl->o_full[w], n_issuers);
-                mbar_init(&ctl->o_empty[w], 128);
-            }
+            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 1); }
+            for (int k = 0; k < DT_NBUF; ++k) { mbar_init(&ctl->d_full[k], 1); mbar_init(&ctl->p_full[k], 128); }
+            for (int k = 0; k < 2; ++k) { mbar_init(&ctl->o_full[k], 1); mbar_init(&ctl->o_empty[k], 128); }
             fence_barrier_init();
         }
         __syncwarp();
@@ -119,9 +119,9 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
 
-    if (warp >= 16 && warp < 20) {
+    if (warp >= 12 && warp < 16) {
         // =========================== O epilogue: TMEM -> global ===========================
-        const int r = threadIdx.x - 512;   // row of the tile == TMEM lane
+        const int r = threadIdx.x - 384;   // row of the tile == TMEM lane
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
         float *dst = o + ((int64_t)b * N) * inner + h * DT_C;
         for (int te = 0; te < n_tiles; ++te) {
@@ -130,15 +130,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             tc_fence_after();
             uint32_t v[32];
             tmem_ld32(tmem_base + lane_base + (uint32_t)ob * DT_C, v);
-            if (n_gc > 1) {   // the second issue stream's share of the slices
-                uint32_t v1[32];
-                tmem_ld32(tmem_base + lane_base + (uint32_t)(2 + ob) * DT_C, v1);
-                tmem_wait_ld();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v1[i]));
-            } else {
-                tmem_wait_ld();
-            }
+            tmem_wait_ld();
             tc_fence_before();
             mbar_arrive(&ctl->o_empty[ob]);
             if (o_image) {
@@ -188,7 +180,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 }
             }
         }
-    } else if (warp == 21) {
+    } else if (warp == 17) {
         // =========================== loader: one bulk copy per 128-point tile (+ its s_n) ===========================
         if (lane == 0) {
             const uint8_t *src = img + ((int64_t)bh * npad + n_begin) * XPI_ROW_BYTES;
@@ -203,44 +195,43 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
         }
         __syncwarp();
-    } else if (warp == 20 || warp == 22) {
-        // =========================== MMA issuers ===========================
-        // warp 20 issues the slice chunks j = 0, 2, .. (softmax warpgroups 0 and 2), warp 22 j = 1, 3, .. (warpgroups 1, 3); each
-        // stream accumulates its chunks into its own O buffers (summed by the epilogue).  The whole warp runs the
-        // warp-uniform loop and one elected lane issues (see slice_tc.cu).
-        const int w = warp == 20 ? 0 : 1;
-        const int pw = (n_gc + 1 - w) >> 1;
-        const int Qw = n_tiles * pw;
-        const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, DT_GC, false, false);
+    } else if (warp == 16) {
+        // =========================== MMA issuer ===========================
+        // Items q = (tile t, slice chunk jc) in order; item q uses D / P buffer q % 3 = softmax warpgroup q % 3; MMA1 runs
+        // three items ahead of MMA2.  The whole warp runs the warp-uniform loop and one elected lane issues (slice_tc.cu).
+        const int Q = n_tiles * n_gc;
+        const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, cw, false, false);
         const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
         const uint32_t wbase = smem_u32(sW) >> 4, vbase = smem_u32(sV) >> 4, abase = smem_u32(sA) >> 4;
         const uint32_t bb_a = smem_u32(sBb) >> 4, one_a = smem_u32(sOne) >> 4;
-        int jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;            // MMA1 cursor: chunk within the stream, stage (+phase), D buffer
-        int t2 = 0, jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;    // MMA2 cursor
-        for (int q = 0; q < Qw + DT_NBUF; ++q) {
-            if (q >= DT_NBUF) {   // ---- MMA2 of this stream's item q-3: O_w += P . S'_h[g-chunk]
+        const uint32_t w_step = (uint32_t)cw * 128 >> 4, b_step = (uint32_t)cw * 32 >> 4;   // one chunk of Ws / S' rows, of bias rows
+        const int ksteps2 = cw / 8;
+        int jc1 = 0, st1 = 0, ph1 = 0, buf1 = 0;            // MMA1 cursor: chunk, stage (+phase), D buffer
+        int t2 = 0, jc2 = 0, st2 = 0, buf2 = 0, ph2 = 0;    // MMA2 cursor
+        for (int q = 0; q < Q + DT_NBUF; ++q) {
+            if (q >= DT_NBUF) {   // ---- MMA2 of item q-3: O += P . S'_h[chunk]
                 const int ob = t2 & 1;
-                if (jj2 == 0) mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t2 >> 1) & 1) ^ 1));
-                mbar_wait(&ctl->p_full[w][buf2], (uint32_t)ph2);
+                if (jc2 == 0) mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t2 >> 1) & 1) ^ 1));
+                mbar_wait(&ctl->p_full[buf2], (uint32_t)ph2);
                 tc_fence_after();
                 if (elect_one()) {
-                    const uint32_t pa = tmem_base + dt_dbuf_col(w, buf2), od = tmem_base + (uint32_t)(w * 2 + ob) * DT_C;
-                    const uint32_t vb = vbase + (uint32_t)(w + 2 * jj2) * (DT_GC * 128 >> 4);
-#pragma unroll
-                    for (int ks = 0; ks < DT_GC / 8; ++ks)
-                        mma_tf32_ts(od, pa + ks * 8, desc_u(vb + ks * 64, 512, 512, 1), id2, (jj2 | ks) != 0);
-                    if (jj2 == pw - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
+                    const uint32_t pa = tmem_base + dt_dbuf_col(buf2), od = tmem_base + (uint32_t)ob * DT_C;
+                    const uint32_t vb = vbase + (uint32_t)jc2 * w_step;
+#pragma unroll 8
+                    for (int ks = 0; ks < ksteps2; ++ks)
+                        mma_tf32_ts(od, pa + ks * 8, desc_u(vb + ks * 64, 512, 512, 1), id2, (jc2 | ks) != 0);
+                    if (jc2 == n_gc - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
                 }
                 __syncwarp();
                 if (++buf2 == DT_NBUF) { buf2 = 0; ph2 ^= 1; }
-                if (++jj2 == pw) { jj2 = 0; ++t2; if (++st2 == DT_STAGES) st2 = 0; }
+                if (++jc2 == n_gc) { jc2 = 0; ++t2; if (++st2 == DT_STAGES) st2 = 0; }
             }
-            if (q < Qw) {    // ---- MMA1 of item q: D = x_proj . Ws[g-chunk]^T  (hi.hi + lo.hi + hi.lo)
-                if (jj1 == 0) { mbar_wait(&ctl->a_full[st1], (uint32_t)ph1); tc_fence_after(); }
+            if (q < Q) {    // ---- MMA1 of item q: D = x_proj . Ws[chunk]^T  (hi.hi + lo.hi + hi.lo) + bc
+                if (jc1 == 0) { mbar_wait(&ctl->a_full[st1], (uint32_t)ph1); tc_fence_after(); }
                 if (elect_one()) {
                     const uint32_t a = abase + (uint32_t)st1 * (DT_TILE_BYTES >> 4);
-                    const uint32_t wb = wbase + (uint32_t)(w + 2 * jj1) * (DT_GC * 128 >> 4);
-                    const uint32_t d = tmem_base + dt_dbuf_col(w, buf1);
+                    const uint32_t wb = wbase + (uint32_t)jc1 * w_step;
+                    const uint32_t d = tmem_base + dt_dbuf_col(buf1);
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks) {
                         mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, ks != 0);
@@ -248,34 +239,32 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                         mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + 4 + ks * 2, 16, 1024), id1, true);
                     }
                     // + bc_g: ones[n, 0:16] . bias[g, 0:16]  (the softmax warps then need no per-element bias add)
-                    mma_bf16_ss(d, desc_u(one_a, 128, 256, 0), desc_u(bb_a + (uint32_t)(w + 2 * jj1) * (DT_GC * 32 >> 4), 128, 256, 0), id1, true);
-                    tc_commit(&ctl->d_full[w][buf1]);
+                    mma_bf16_ss(d, desc_u(one_a, 128, 256, 0), desc_u(bb_a + (uint32_t)jc1 * b_step, 128, 256, 0), id1, true);
+                    tc_commit(&ctl->d_full[buf1]);
                 }
                 __syncwarp();
                 if (++buf1 == DT_NBUF) buf1 = 0;
-                if (++jj1 == pw) { jj1 = 0; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
+                if (++jc1 == n_gc) { jc1 = 0; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
             }
         }
-    } else {
+    } else if (warp < 12) {
         // =========================== softmax warpgroups ===========================
-        // 4 warpgroups: wg & 1 = the issue stream it serves; it takes every other item of the stream (items cycle through
-        // the stream's 3 D / P buffers), so each scheduler has 4 softmax warps and MMA1 runs 3 items ahead.
-        const int wg = warp >> 2, w = wg & 1, sub = wg >> 1, q4 = warp & 3, row = q4 * 32 + lane;
+        // 3 warpgroups, warpgroup i owns D / P buffer i and takes the items q = i, i + 3, ..: it sees EVERY phase of its two
+        // barriers (a warpgroup that skipped phases could alias the mbarrier parity when it runs two uses ahead).
+        const int wg = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;
         const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
-        const int pw = (n_gc + 1 - w) >> 1, Qw = n_tiles * pw;
-        int t = 0, jj = sub;   // item k = t * pw + jj of the stream
-        int buf = sub, bph = 0;   // D / P buffer k % 3 of the current item and its phase (k / 3) & 1
-        while (jj >= pw && pw > 0) { jj -= pw; ++t; }
-        for (int k = sub; k < Qw; k += 2) {
-            const int stage = t % DT_STAGES;
+        const int Q = n_tiles * n_gc, halves = cw / 32;
+        for (int q = wg; q < Q; q += DT_NBUF) {
+            const int t = q / n_gc, jc = q - t * n_gc;
+            const int stage = t % DT_STAGES, buf = wg;
             mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1));
             const float sn = sS[stage * DT_TILE + row];
-            mbar_wait(&ctl->d_full[w][buf], (uint32_t)bph);
+            mbar_wait(&ctl->d_full[buf], (uint32_t)((q / DT_NBUF) & 1));
             tc_fence_after();
-            const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(w, buf);
-            const float4 *ll = reinterpret_cast<const float4 *>(sL + (w + 2 * jj) * DT_GC);
-#pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
+            const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(buf);
+            const float4 *ll = reinterpret_cast<const float4 *>(sL + jc * cw);
+#pragma unroll 1
+            for (int hh = 0; hh < halves; ++hh) {
                 uint32_t r[32];
                 tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
@@ -291,16 +280,12 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
             tmem_wait_st();
             tc_fence_before();
-            mbar_arrive(&ctl->p_full[w][buf]);
-            buf += 2;
-            if (buf >= DT_NBUF) { buf -= DT_NBUF; bph ^= 1; }
-            jj += 2;
-            while (jj >= pw) { jj -= pw; ++t; }
+            mbar_arrive(&ctl->p_full[buf]);
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 20) {
+    if (warp == 16) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }
@@ -311,7 +296,7 @@ bool deslice_tc_supported(const haet_layer_shape *s) { return s->dim_head == DT_
 int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
                       const float *states, const float *ws, const float *bs, float *o, int o_image, cudaStream_t st) {
     if (s->N == 0 || s->B == 0) return HAET_OK;
-    const int n_gc = (s->slice_num + DT_GC - 1) / DT_GC, g_pad = n_gc * DT_GC;
+    const int g_pad = dt_gpad(s->slice_num);
     const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
                         sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
     static size_t smem_set = 0;
