@@ -24,20 +24,20 @@ constexpr int DT_C = 32;
 constexpr int DT_TILE = 128;        // points per tile (UMMA M)
 constexpr int DT_GCMAX = 128;       // slices per item (UMMA N of MMA1, K of MMA2): 128, or 64 when G <= 64
 constexpr int DT_STAGES = 4;
-constexpr int DT_THREADS = 576;     // 12 softmax warps (3 warpgroups) + 4 epilogue warps + MMA warp + loader warp
+constexpr int DT_THREADS = 640;     // 12 softmax warps (3 warpgroups) + 4 epilogue warps + MMA1 warp + loader warp + 2 MMA2 warps
 constexpr int DT_MAX_G = 512;
 constexpr int DT_NBUF = 3;          // D / P buffers (128 TMEM columns each)
 constexpr int DT_TILE_BYTES = DT_TILE * 128;
 
 struct DesliceCtl {
     uint64_t a_full[DT_STAGES], a_empty[DT_STAGES];
-    uint64_t d_full[DT_NBUF], p_full[DT_NBUF];
+    uint64_t d_full[DT_NBUF], p_full[DT_NBUF], p_free[DT_NBUF];
     uint64_t o_full[2], o_empty[2];
     uint32_t tmem_base;
 };
 
 // TMEM columns: O accumulators [issuer][buffer] x 32 at 0..127, D / P buffers [stream][3] x 64 at 128..511
-// TMEM columns: O accumulators (double-buffered) at 0..63, D / P buffers at 128 + 128 buf
+// TMEM columns: O accumulators [MMA2 warp][double buffer] x 32 at 0..127, D / P buffers at 128 + 128 buf
 __device__ __forceinline__ uint32_t dt_dbuf_col(int buf) { return 128u + (uint32_t)buf * DT_GCMAX; }
 __host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (G + 127) / 128 * 128; }
 
@@ -68,9 +68,9 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
 
     if (warp == 16) {
         if (lane == 0) {
-            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 1); }
-            for (int k = 0; k < DT_NBUF; ++k) { mbar_init(&ctl->d_full[k], 1); mbar_init(&ctl->p_full[k], 128); }
-            for (int k = 0; k < 2; ++k) { mbar_init(&ctl->o_full[k], 1); mbar_init(&ctl->o_empty[k], 128); }
+            for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 2); }
+            for (int k = 0; k < DT_NBUF; ++k) { mbar_init(&ctl->d_full[k], 1); mbar_init(&ctl->p_full[k], 128); mbar_init(&ctl->p_free[k], 2); }
+            for (int k = 0; k < 2; ++k) { mbar_init(&ctl->o_full[k], 2); mbar_init(&ctl->o_empty[k], 128); }
             fence_barrier_init();
         }
         __syncwarp();
@@ -130,7 +130,13 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             tc_fence_after();
             uint32_t v[32];
             tmem_ld32(tmem_base + lane_base + (uint32_t)ob * DT_C, v);
-            tmem_wait_ld();
+            {   // the second MMA2 warp's half of every chunk's K steps
+                uint32_t v1[32];
+                tmem_ld32(tmem_base + lane_base + (uint32_t)(2 + ob) * DT_C, v1);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v1[i]));
+            }
             tc_fence_before();
             mbar_arrive(&ctl->o_empty[ob]);
             if (o_image) {
@@ -196,56 +202,66 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         }
         __syncwarp();
     } else if (warp == 16) {
-        // =========================== MMA issuer ===========================
-        // Items q = (tile t, slice chunk jc) in order; item q uses D / P buffer q % 3 = softmax warpgroup q % 3; MMA1 runs
-        // three items ahead of MMA2.  The whole warp runs the warp-uniform loop and one elected lane issues (slice_tc.cu).
+        // =========================== MMA1 issuer ===========================
+        // Items q = (tile t, slice chunk jc) in order; item q uses D / P buffer q % 3 = softmax warpgroup q % 3.  One warp can
+        // issue a tcgen05.mma only every ~75 cycles whatever its size (clock64 trace: 7 + 8 small MMAs = 1300 cycles per item was
+        // the bound of the kernel while the tensor pipe sat at 40 %), so the instruction streams are spread over THREE
+        // warps: this one issues the logits MMAs, warps 18 / 19 each half of the K steps of P . S'.  The whole warp runs the
+        // warp-uniform loop and one elected lane issues (slice_tc.cu).
         const int Q = n_tiles * n_gc;
         const uint32_t id1 = instr_desc(FMT_F16, DT_TILE, cw, false, false);
-        const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
-        const uint32_t wbase = smem_u32(sW) >> 4, vbase = smem_u32(sV) >> 4, abase = smem_u32(sA) >> 4;
+        const uint32_t wbase = smem_u32(sW) >> 4, abase = smem_u32(sA) >> 4;
         const uint32_t bb_a = smem_u32(sBb) >> 4, one_a = smem_u32(sOne) >> 4;
-        const uint32_t w_step = (uint32_t)cw * 128 >> 4, b_step = (uint32_t)cw * 32 >> 4;   // one chunk of Ws / S' rows, of bias rows
-        const int ksteps2 = cw / 8;
-        int jc1 = 0, st1 = 0, ph1 = 0, buf1 = 0;            // MMA1 cursor: chunk, stage (+phase), D buffer
-        int t2 = 0, jc2 = 0, st2 = 0, buf2 = 0, ph2 = 0;    // MMA2 cursor
-        for (int q = 0; q < Q + DT_NBUF; ++q) {
-            if (q >= DT_NBUF) {   // ---- MMA2 of item q-3: O += P . S'_h[chunk]
-                const int ob = t2 & 1;
-                if (jc2 == 0) mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t2 >> 1) & 1) ^ 1));
-                mbar_wait(&ctl->p_full[buf2], (uint32_t)ph2);
-                tc_fence_after();
-                if (elect_one()) {
-                    const uint32_t pa = tmem_base + dt_dbuf_col(buf2), od = tmem_base + (uint32_t)ob * DT_C;
-                    const uint32_t vb = vbase + (uint32_t)jc2 * w_step;
-#pragma unroll 8
-                    for (int ks = 0; ks < ksteps2; ++ks)
-                        mma_tf32_ts(od, pa + ks * 8, desc_u(vb + ks * 64, 512, 512, 1), id2, (jc2 | ks) != 0);
-                    if (jc2 == n_gc - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
-                }
-                __syncwarp();
-                if (++buf2 == DT_NBUF) { buf2 = 0; ph2 ^= 1; }
-                if (++jc2 == n_gc) { jc2 = 0; ++t2; if (++st2 == DT_STAGES) st2 = 0; }
-            }
-            if (q < Q) {    // ---- MMA1 of item q: D = x_proj . Ws[chunk]^T  (hi.hi + lo.hi + hi.lo) + bc
-                if (jc1 == 0) { mbar_wait(&ctl->a_full[st1], (uint32_t)ph1); tc_fence_after(); }
-                if (elect_one()) {
-                    const uint32_t a = abase + (uint32_t)st1 * (DT_TILE_BYTES >> 4);
-                    const uint32_t wb = wbase + (uint32_t)jc1 * w_step;
-                    const uint32_t d = tmem_base + dt_dbuf_col(buf1);
+        const uint32_t w_step = (uint32_t)cw * 128 >> 4, b_step = (uint32_t)cw * 32 >> 4;   // one chunk of Ws rows, of bias rows
+        int jc1 = 0, st1 = 0, ph1 = 0, buf1 = 0, fph = 0;   // chunk, stage (+phase), D buffer, phase of p_free
+        for (int q = 0; q < Q; ++q) {    // D = x_proj . Ws[chunk]^T  (hi.hi + lo.hi + hi.lo) + bc
+            if (q >= DT_NBUF) mbar_wait(&ctl->p_free[buf1], (uint32_t)fph);   // both halves of P . S' of item q - 3 have completed
+            if (jc1 == 0) mbar_wait(&ctl->a_full[st1], (uint32_t)ph1);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t a = abase + (uint32_t)st1 * (DT_TILE_BYTES >> 4);
+                const uint32_t wb = wbase + (uint32_t)jc1 * w_step;
+                const uint32_t d = tmem_base + dt_dbuf_col(buf1);
 #pragma unroll
-                    for (int ks = 0; ks < 2; ++ks) {
-                        mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, ks != 0);
-                        mma_bf16_ss(d, desc_sw128_u(a + 4 + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, true);
-                        mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + 4 + ks * 2, 16, 1024), id1, true);
-                    }
-                    // + bc_g: ones[n, 0:16] . bias[g, 0:16]  (the softmax warps then need no per-element bias add)
-                    mma_bf16_ss(d, desc_u(one_a, 128, 256, 0), desc_u(bb_a + (uint32_t)jc1 * b_step, 128, 256, 0), id1, true);
-                    tc_commit(&ctl->d_full[buf1]);
+                for (int ks = 0; ks < 2; ++ks) {
+                    mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, ks != 0);
+                    mma_bf16_ss(d, desc_sw128_u(a + 4 + ks * 2, 16, 1024), desc_sw128_u(wb + ks * 2, 16, 1024), id1, true);
+                    mma_bf16_ss(d, desc_sw128_u(a + ks * 2, 16, 1024), desc_sw128_u(wb + 4 + ks * 2, 16, 1024), id1, true);
                 }
-                __syncwarp();
-                if (++buf1 == DT_NBUF) buf1 = 0;
-                if (++jc1 == n_gc) { jc1 = 0; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
+                // + bc_g: ones[n, 0:16] . bias[g, 0:16]  (the softmax warps then need no per-element bias add)
+                mma_bf16_ss(d, desc_u(one_a, 128, 256, 0), desc_u(bb_a + (uint32_t)jc1 * b_step, 128, 256, 0), id1, true);
+                tc_commit(&ctl->d_full[buf1]);
             }
+            __syncwarp();
+            if (++buf1 == DT_NBUF) { buf1 = 0; if (q >= DT_NBUF) fph ^= 1; }
+            if (++jc1 == n_gc) { jc1 = 0; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
+        }
+    } else if (warp >= 18) {
+        // =========================== MMA2 issuers: O_u += P . S'_h[chunk], K steps [u, u + 1) * cw / 16 ===========================
+        const int u = warp - 18;
+        const int Q = n_tiles * n_gc;
+        const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
+        const uint32_t vbase = smem_u32(sV) >> 4;
+        const uint32_t w_step = (uint32_t)cw * 128 >> 4;
+        const int kh = cw / 16;   // K steps (of 8 slices) per warp
+        int t2 = 0, jc2 = 0, st2 = 0, buf2 = 0, ph2 = 0;
+        for (int k = 0; k < Q; ++k) {
+            const int ob = t2 & 1;
+            if (jc2 == 0) mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t2 >> 1) & 1) ^ 1));
+            mbar_wait(&ctl->p_full[buf2], (uint32_t)ph2);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t pa = tmem_base + dt_dbuf_col(buf2) + (uint32_t)(u * kh) * 8, od = tmem_base + (uint32_t)(u * 2 + ob) * DT_C;
+                const uint32_t vb = vbase + (uint32_t)jc2 * w_step + (uint32_t)(u * kh) * 64;
+#pragma unroll 8
+                for (int ks = 0; ks < kh; ++ks)
+                    mma_tf32_ts(od, pa + ks * 8, desc_u(vb + ks * 64, 512, 512, 1), id2, (jc2 | ks) != 0);
+                tc_commit(&ctl->p_free[buf2]);
+                if (jc2 == n_gc - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
+            }
+            __syncwarp();
+            if (++buf2 == DT_NBUF) { buf2 = 0; ph2 ^= 1; }
+            if (++jc2 == n_gc) { jc2 = 0; ++t2; if (++st2 == DT_STAGES) st2 = 0; }
         }
     } else if (warp < 12) {
         // =========================== softmax warpgroups ===========================
