@@ -6,8 +6,9 @@
 //        (N = 128: with N = 64 / 32 every tcgen05.mma costs ~50 cycles of tensor-pipe time whatever its size -- the pipe was
 //        the bound of the kernel at one item per ~750 cycles -- so each instruction is made to carry twice the logits)
 //        (A = a 128-point tile of the spill's operand image, common.cuh, brought in by one bulk copy)
-//   softmax warps: P = 2^((D + bc_g) * s_n - lse2_g) -> TMEM in place (per-column constants from shared memory)
-//   MMA2 (kind::tf32, A = P from TMEM, B = S'_h as MN-major fp32): O[n, c] += sum_g P[n, g] S'[g, c]
+//   softmax warps: P = 2^(D * s_n - lse2_g + 14) -> TMEM as packed fp16 (the bias bc_g rides in MMA1 as an extra K step; W <= 1, so
+//        2^14 W keeps 11 bits down to W = 2^-28 -- same mantissa as tf32 -- and the epilogue multiplies by 2^-14)
+//   MMA2 (kind::f16, A = P from TMEM, B = S'_h as MN-major fp16 rows): O[n, c] += sum_g P[n, g] S'[g, c]
 // CTA = (b, h, chunk of points): the Ws and S'_h operand images are built once and stay resident; the x_proj
 // head slice streams through a 4-stage ring of bulk copies; O is double-buffered in TMEM and stored by 4 epilogue warps.
 #include <cuda_fp16.h>
@@ -26,6 +27,7 @@ constexpr int DT_GCMAX = 128;       // slices per item (UMMA N of MMA1, K of MMA
 constexpr int DT_STAGES = 4;
 constexpr int DT_THREADS = 640;     // 12 softmax warps (3 warpgroups) + 4 epilogue warps + MMA1 warp + loader warp + 2 MMA2 warps
 constexpr int DT_MAX_G = 512;
+constexpr float DT_PSHIFT = 14.f;   // P is handed to MMA2 as fp16 2^14 W (W <= 1): full precision down to W = 2^-28, flush below 2^-38
 constexpr int DT_NBUF = 3;          // D / P buffers (128 TMEM columns each)
 constexpr int DT_TILE_BYTES = DT_TILE * 128;
 
@@ -76,28 +78,26 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         __syncwarp();
         tmem_alloc<512>(&ctl->tmem_base);
     }
-    // resident operand images: Ws rows [hi | lo] and S'_h rows (tf32-rounded), per-column constants
+    // resident operand images: Ws rows [hi | lo] and S'_h rows (fp16), per-column constants
     for (int idx = threadIdx.x; idx < g_pad * 4; idx += DT_THREADS) {
         const int g = idx >> 2, ck = idx & 3;
         __align__(16) __half hi[8], lo[8];
-        __align__(16) float sv[8];
+        __align__(16) __half sv[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const float v = g < G ? ws[(size_t)g * DT_C + ck * 8 + i] : 0.f;
             hi[i] = __float2half_rn(v);
             lo[i] = __float2half_rn(v - __half2float(hi[i]));
             const float s = g < G ? states[((size_t)bh * G + g) * DT_C + ck * 8 + i] : 0.f;
-            uint32_t u;
-            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(s));
-            sv[i] = __uint_as_float(u);
+            sv[i] = __float2half_rn(s);
         }
         *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(hi);
         *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck + 4)) = *reinterpret_cast<const uint4 *>(lo);
-        *reinterpret_cast<uint4 *>(sV + mn32_off(g, ck)) = reinterpret_cast<const uint4 *>(sv)[0];
-        *reinterpret_cast<uint4 *>(sV + mn32_off(g, ck) + 16) = reinterpret_cast<const uint4 *>(sv)[1];
+        *reinterpret_cast<uint4 *>(sV + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(sv);   // MN-major operand: row g = 32 fp16 channels
+        *reinterpret_cast<uint4 *>(sV + sw128_off(g, ck + 4)) = make_uint4(0, 0, 0, 0);
     }
     for (int g = threadIdx.x; g < g_pad; g += DT_THREADS) {
-        sL[g] = g < G ? -lse2[(size_t)bh * G + g] : -INFINITY;
+        sL[g] = g < G ? DT_PSHIFT - lse2[(size_t)bh * G + g] : -INFINITY;
         uint32_t b2 = 0;
         if (g < G) {
             const float bc = bs[g] - shift;
@@ -135,7 +135,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 tmem_ld32(tmem_base + lane_base + (uint32_t)(2 + ob) * DT_C, v1);
                 tmem_wait_ld();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(v1[i]));
+                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint((__uint_as_float(v[i]) + __uint_as_float(v1[i])) * 6.103515625e-05f);   // 2^-DT_PSHIFT
             }
             tc_fence_before();
             mbar_arrive(&ctl->o_empty[ob]);
@@ -240,10 +240,10 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         // =========================== MMA2 issuers: O_u += P . S'_h[chunk], K steps [u, u + 1) * cw / 16 ===========================
         const int u = warp - 18;
         const int Q = n_tiles * n_gc;
-        const uint32_t id2 = instr_desc(FMT_TF32, DT_TILE, DT_C, false, true);
+        const uint32_t id2 = instr_desc(FMT_F16, DT_TILE, DT_C, false, true);
         const uint32_t vbase = smem_u32(sV) >> 4;
         const uint32_t w_step = (uint32_t)cw * 128 >> 4;
-        const int kh = cw / 16;   // K steps (of 8 slices) per warp
+        const int kh = cw / 32;   // K steps (of 16 slices) per warp
         int t2 = 0, jc2 = 0, st2 = 0, buf2 = 0, ph2 = 0;
         for (int k = 0; k < Q; ++k) {
             const int ob = t2 & 1;
@@ -252,10 +252,10 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             tc_fence_after();
             if (elect_one()) {
                 const uint32_t pa = tmem_base + dt_dbuf_col(buf2) + (uint32_t)(u * kh) * 8, od = tmem_base + (uint32_t)(u * 2 + ob) * DT_C;
-                const uint32_t vb = vbase + (uint32_t)jc2 * w_step + (uint32_t)(u * kh) * 64;
-#pragma unroll 8
-                for (int ks = 0; ks < kh; ++ks)
-                    mma_tf32_ts(od, pa + ks * 8, desc_u(vb + ks * 64, 512, 512, 1), id2, (jc2 | ks) != 0);
+                const uint32_t vb = vbase + (uint32_t)jc2 * w_step + (uint32_t)(u * kh) * 128;
+#pragma unroll 4
+                for (int ks = 0; ks < kh; ++ks)   // K = 16 slices = 8 packed TMEM columns of P, two 8-row swizzle atoms of S'
+                    mma_f16_ts(od, pa + ks * 8, desc_sw128_u(vb + ks * 128, 1024, 1024), id2, (jc2 | ks) != 0);
                 tc_commit(&ctl->p_free[buf2]);
                 if (jc2 == n_gc - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
             }
@@ -281,18 +281,19 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             const float4 *ll = reinterpret_cast<const float4 *>(sL + jc * cw);
 #pragma unroll 1
             for (int hh = 0; hh < halves; ++hh) {
-                uint32_t r[32];
+                uint32_t r[32], pk[16];
                 tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
 #pragma unroll
                 for (int c = 0; c < 32; c += 4) {
-                    const float4 k4 = ll[hh * 8 + (c >> 2)];   // -lse2 of four slices
-                    r[c] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c]), sn, k4.x)));
-                    r[c + 1] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 1]), sn, k4.y)));
-                    r[c + 2] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 2]), sn, k4.z)));
-                    r[c + 3] = __float_as_uint(fast_ex2(fmaf(__uint_as_float(r[c + 3]), sn, k4.w)));
+                    const float4 k4 = ll[hh * 8 + (c >> 2)];   // 14 - lse2 of four slices
+                    const float p0 = fast_ex2(fmaf(__uint_as_float(r[c]), sn, k4.x)), p1 = fast_ex2(fmaf(__uint_as_float(r[c + 1]), sn, k4.y));
+                    const float p2 = fast_ex2(fmaf(__uint_as_float(r[c + 2]), sn, k4.z)), p3 = fast_ex2(fmaf(__uint_as_float(r[c + 3]), sn, k4.w));
+                    const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                    pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
                 }
-                tmem_st32(dcol + hh * 32, r);
+                tmem_st16(dcol + hh * 16, pk);   // packed P trails the logits it replaces (columns already read)
             }
             tmem_wait_st();
             tc_fence_before();
