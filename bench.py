@@ -67,7 +67,9 @@ class ClockSampler:
         self.rows.append([str(sm), str(mx), flag(0x8), flag(0x40), flag(0x20), flag(0x4)])
 
     def _run(self):
-        while not self._stop.is_set():
+        first = True
+        while first or not self._stop.is_set():
+            first = False
             try:
                 if self._nvml is not None:
                     self._sample_nvml()
@@ -81,11 +83,17 @@ class ClockSampler:
             self._stop.wait(0.02 if self._nvml is not None else 0.1)
 
     def __enter__(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
         return self
 
+    def start(self):
+        """Begin sampling: called once the timed steps are ENQUEUED, so the queries (which take the driver lock for
+        milliseconds) run while the GPU executes the timed region and cannot stall its launches."""
+        if self._t is None:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
     def __exit__(self, *a):
+        self.start()
         self._stop.set()
         self._t.join(timeout=6)
 
@@ -310,7 +318,7 @@ def run_gpu_arm(args):
     # captured once into a CUDA graph and replayed ("graph-replayed iterations"): the clock queries the contract
     # asks for inside the timed region take the driver lock for milliseconds and would otherwise stall the launches.
     step, per_step, launch_mode = (lambda: m(x)), None, "eager"
-    if not args.no_graph:
+    if not args.no_graph and world == 1:   # N > 1: the NCCL all-gather of the slice state is launched eagerly
         try:
             side = torch.cuda.Stream(dev)
             side.wait_stream(torch.cuda.current_stream(dev))
@@ -339,6 +347,7 @@ def run_gpu_arm(args):
         for _ in range(args.steps):
             step()
         e1.record()
+        clk.start()
         barrier()
     ms = e0.elapsed_time(e1) / args.steps
     launches = per_step * args.steps if per_step is not None else lib.haet_launch_count() - n0
