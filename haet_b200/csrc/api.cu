@@ -44,7 +44,9 @@ struct Carver {
 
 static int64_t image_bytes(const haet_layer_shape *s) {   // packed-weight scratch of the tcgen05 GEMM
     const int inner = s->heads * s->dim_head;
-    return align_up(4 * (int64_t)(inner > s->dim ? inner : s->dim) * (inner > s->dim ? inner : s->dim), 256);
+    int64_t b = 4 * (int64_t)(inner > s->dim ? inner : s->dim) * (inner > s->dim ? inner : s->dim);
+    if (s->conv_nd != 0 && conv_tc_supported(s) && conv_tc_image_bytes(s) > b) b = conv_tc_image_bytes(s);
+    return align_up(b, 256);
 }
 static int64_t deslice_o_bytes(const haet_layer_shape *s) {   // fp32 o, or its operand image (rows padded to 256)
     return align_up(opi_bytes(s->B * s->N, s->heads * s->dim_head), 256);
@@ -166,6 +168,8 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
     } else {
         if (g_path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
             rc = launch_gemm_tc(x_d, wx_d, bx_d, xp, s->B * s->N, s->dim, inner, img, st);
+        else if (g_path == 0 && s->conv_nd != 0 && conv_tc_supported(s) && !getenv("HAET_CONV_SIMT"))
+            rc = launch_conv_tc(s, x_d, wx_d, bx_d, xp, img, st);   // Conv2d / Conv3d front-end: implicit GEMM on tcgen05
         else
             rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
         if (!rc && tc) rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st);

@@ -83,6 +83,11 @@ int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, 
                    cudaStream_t st);
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
                      uint8_t *xpi, float *scale, void *img, cudaStream_t st);
+// Conv2d / Conv3d front-end as an implicit GEMM on tcgen05 (conv_tc.cu); wx tap-major [inner, taps, dim]
+bool conv_tc_supported(const haet_layer_shape *s);
+int64_t conv_tc_image_bytes(const haet_layer_shape *s);
+int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, float *xp, void *img,
+                   cudaStream_t st);
 bool slice_tc_supported(const haet_layer_shape *s);
 int64_t slice_tc_chunks(const haet_layer_shape *s);
 int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,

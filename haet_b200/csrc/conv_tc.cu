@@ -1,0 +1,215 @@
+// Conv2d / Conv3d front-end (kernel k, padding k/2; StructuredMesh2D.py:109,173-189, StructuredMesh3D.py:113,177-193) as
+// an implicit GEMM on tcgen05:
+//   xp[m, o] = b[o] + sum_tap sum_ci x[nbr(m, tap), ci] W[o, tap, ci]        M = B * N grid points, K = taps * dim
+// with the 3-term bf16 split of gemm_tc.cu (fp32-class accuracy, fp32 accumulation in TMEM).  Same roles as the dense
+// GEMM -- 8 producer warps gather and split the A rows (the neighbour's channels, zeros outside the grid), one MMA warp,
+// 4 epilogue warps -- except that W (taps * dim * 4 bytes per output row: 7 MB at 64^3 x 256) cannot stay in shared
+// memory: a loader warp streams it, one pre-swizzled 32 KB [hi | lo] panel per (tap, 64 channels), through the same
+// 3-stage ring as A.  One CTA = one 128-column half of 128-row tiles; persistent grid.
+#include "gemm_tc.cuh"
+
+namespace haet {
+using namespace tc;
+
+constexpr int CT_THREADS = GT_PROD + 32 + 128 + 32;   // producers (0-7), MMA warp (8), epilogue warps (9-12), W loader (13)
+
+struct ConvSmem {
+    uint64_t a_full[GT_STAGES], w_full[GT_STAGES], empty[GT_STAGES];
+    uint64_t t_full[2], t_empty[2];
+    uint32_t tmem_base;
+};
+
+struct ConvGeom {
+    int64_t N;            // grid points per batch element
+    int g0, g1, g2;       // grid extents (g2 = 1 for 2D), point n = (i * g1 + j) * g2 + k
+    int ks, nd, din;      // kernel size, 2 or 3, input channels
+};
+
+template <int DUMMY>
+__global__ void __launch_bounds__(CT_THREADS, 1)
+conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
+               float *__restrict__ Y, int64_t M, int Nn, int n_workers, ConvGeom geo) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int kp = geo.din / GT_KP;                       // 64-channel panels per tap
+    const int taps = geo.nd == 3 ? geo.ks * geo.ks * geo.ks : geo.ks * geo.ks;
+    const int panels = taps * kp;
+    const int n_halves = Nn / GT_N;
+    uint8_t *sA = smem;                                          // [stages][hi|lo][16 KB]: gathered x rows
+    uint8_t *sWs = sA + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES;  // [stages][hi|lo][16 KB]: W panel of this column half
+    ConvSmem *cb = reinterpret_cast<ConvSmem *>(sWs + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int half = blockIdx.x % n_halves, worker = blockIdx.x / n_halves;
+    const int64_t n_tiles = (M + GT_M - 1) / GT_M;
+    const int64_t my_tiles = worker < n_tiles ? (n_tiles - worker + n_workers - 1) / n_workers : 0;
+
+    if (warp == 8) {
+        if (lane == 0) {
+            for (int s = 0; s < GT_STAGES; ++s) { mbar_init(&cb->a_full[s], GT_PROD); mbar_init(&cb->w_full[s], 1); mbar_init(&cb->empty[s], 1); }
+            for (int b = 0; b < 2; ++b) { mbar_init(&cb->t_full[b], 1); mbar_init(&cb->t_empty[b], 128); }
+            fence_barrier_init();
+        }
+        __syncwarp();
+        tmem_alloc<256>(&cb->tmem_base);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = cb->tmem_base;
+
+    if (warp < 8) {
+        // ---------------- producers: implicit im2col.  Each thread owns 4 (row, chunk) items of the tile; the grid coordinates
+        // of its rows are recomputed when the tile changes, the tap offset per panel. ----------------
+        int64_t cur_ti = -1;
+        int ci_[GT_LD / 2], cj_[GT_LD / 2], ck_[GT_LD / 2];
+        int64_t base_[GT_LD / 2];   // (b * N + n) of the row, -1 past M
+        const int pad = geo.ks / 2;
+        auto src = [&](int64_t ti, int p, int i, int row, int c8) -> const float * {
+            if (ti != cur_ti) {   // first item of a new tile: (this lambda is called with i = 0..3 in order)
+                if (i == GT_LD / 2 - 1) cur_ti = ti;
+                const int64_t m = (worker + ti * n_workers) * (int64_t)GT_M + row;
+                if (m < M) {
+                    const int64_t b = m / geo.N, n = m - b * geo.N;
+                    const int64_t ij = n / geo.g2;
+                    ck_[i] = (int)(n - ij * geo.g2);
+                    ci_[i] = (int)(ij / geo.g1);
+                    cj_[i] = (int)(ij - (int64_t)ci_[i] * geo.g1);
+                    base_[i] = m;
+                } else {
+                    base_[i] = -1;
+                }
+            }
+            if (base_[i] < 0) return nullptr;
+            const int tap = p / kp, c0 = (p - tap * kp) * GT_KP;
+            int di, dj, dk = 0;
+            if (geo.nd == 3) { di = tap / (geo.ks * geo.ks) - pad; dj = (tap / geo.ks) % geo.ks - pad; dk = tap % geo.ks - pad; }
+            else { di = tap / geo.ks - pad; dj = tap % geo.ks - pad; }
+            const int ii = ci_[i] + di, jj = cj_[i] + dj, kk = ck_[i] + dk;
+            if (ii < 0 || ii >= geo.g0 || jj < 0 || jj >= geo.g1 || kk < 0 || kk >= geo.g2) return nullptr;   // zero padding
+            const int64_t nbr = base_[i] + ((int64_t)di * geo.g1 + dj) * geo.g2 + dk;
+            return X + nbr * geo.din + c0 + c8 * 8;
+        };
+        gemm_produce_g(panels, my_tiles, sA, src,
+                       [&](int st, int parity) { mbar_wait(&cb->empty[st], (uint32_t)parity); },
+                       [&](int st) { mbar_arrive(&cb->a_full[st]); });
+    } else if (warp == 13) {
+        // ---------------- W loader: one 32 KB panel [hi | lo] of this column half per stage ----------------
+        if (lane == 0) {
+            const uint8_t *src = Wimg + (size_t)half * panels * (2 * GT_PANEL_BYTES);
+            int stage = 0, phase = 0;
+            for (int64_t it = 0; it < my_tiles; ++it)
+                for (int p = 0; p < panels; ++p) {
+                    mbar_wait(&cb->empty[stage], (uint32_t)(phase ^ 1));
+                    mbar_arrive_expect_tx(&cb->w_full[stage], 2 * GT_PANEL_BYTES);
+                    bulk_g2s(sWs + (size_t)stage * 2 * GT_PANEL_BYTES, src + (size_t)p * 2 * GT_PANEL_BYTES, 2 * GT_PANEL_BYTES, &cb->w_full[stage]);
+                    if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+                }
+        }
+        __syncwarp();
+    } else if (warp == 8) {
+        // ---------------- MMA issuer ----------------
+        if (lane == 0 && my_tiles > 0) {
+            const uint32_t idesc = instr_desc(FMT_BF16, GT_M, GT_N, false, false);
+            int stage = 0, phase = 0;
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const int buf = (int)(it & 1);
+                mbar_wait(&cb->t_empty[buf], (uint32_t)(((it >> 1) & 1) ^ 1));
+                tc_fence_after();
+                const uint32_t d = tmem_base + (uint32_t)buf * GT_N;
+                for (int p = 0; p < panels; ++p) {
+                    mbar_wait(&cb->a_full[stage], phase);
+                    mbar_wait(&cb->w_full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_hi = smem_u32(sA + (size_t)stage * 2 * GT_PANEL_BYTES), a_lo = a_hi + GT_PANEL_BYTES;
+                    const uint32_t b_hi = smem_u32(sWs + (size_t)stage * 2 * GT_PANEL_BYTES), b_lo = b_hi + GT_PANEL_BYTES;
+#pragma unroll
+                    for (int ks = 0; ks < GT_KP / 16; ++ks) {
+                        const uint64_t dah = smem_desc_sw128(a_hi + ks * 32, 16, 1024);
+                        const uint64_t dal = smem_desc_sw128(a_lo + ks * 32, 16, 1024);
+                        const uint64_t dbh = smem_desc_sw128(b_hi + ks * 32, 16, 1024);
+                        const uint64_t dbl = smem_desc_sw128(b_lo + ks * 32, 16, 1024);
+                        mma_bf16_ss(d, dah, dbh, idesc, (p | ks) != 0);
+                        mma_bf16_ss(d, dal, dbh, idesc, true);
+                        mma_bf16_ss(d, dah, dbl, idesc, true);
+                    }
+                    tc_commit(&cb->empty[stage]);   // frees the A and the W half of the stage
+                    if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+                }
+                tc_commit(&cb->t_full[buf]);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------- epilogue: TMEM -> registers -> + bias -> xp [M, Nn] ----------------
+        const int q = warp & 3;
+        GemmEpi ep{};
+        for (int64_t it = 0; it < my_tiles; ++it) {
+            const int64_t tile = worker + it * n_workers;
+            const int buf = (int)(it & 1);
+            mbar_wait(&cb->t_full[buf], (uint32_t)((it >> 1) & 1));
+            tc_fence_after();
+            const int64_t m0 = tile * GT_M + q * 32 + (lane & ~3);
+#pragma unroll 1
+            for (int c0 = 0; c0 < GT_N; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * GT_N + c0), r);
+                tmem_wait_ld();
+                gemm_epilogue_chunk<EPI_F32>(r, lane, m0, 0, 0, M, bias + half * GT_N + c0, nullptr, Y, Nn, half * GT_N + c0, ep);
+            }
+            tc_fence_before();
+            mbar_arrive(&cb->t_empty[buf]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) {
+        tc_fence_after();
+        tmem_dealloc<256>(tmem_base);
+    }
+}
+
+bool conv_tc_supported(const haet_layer_shape *s) {
+    const int inner = s->heads * s->dim_head;
+    return (s->conv_nd == 2 || s->conv_nd == 3) && s->dim % GT_KP == 0 && inner % GT_N == 0 && (s->kernel & 1) == 1 && s->kernel <= 7;
+}
+
+int64_t conv_tc_image_bytes(const haet_layer_shape *s) {
+    const int taps = s->conv_nd == 3 ? s->kernel * s->kernel * s->kernel : s->kernel * s->kernel;
+    return (int64_t)s->heads * s->dim_head * taps * s->dim * 4;
+}
+
+// wx: [inner, taps, dim] (tap-major, as the SIMT path reads it); img: scratch of conv_tc_image_bytes(s)
+int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, float *xp, void *img,
+                   cudaStream_t st) {
+    HAET_CHECK_ARG(conv_tc_supported(s), "conv_tc: unsupported shape");
+    const int inner = s->heads * s->dim_head;
+    ConvGeom geo;
+    geo.N = s->N; geo.g0 = s->grid[0]; geo.g1 = s->grid[1]; geo.g2 = s->conv_nd == 3 ? s->grid[2] : 1;
+    geo.ks = s->kernel; geo.nd = s->conv_nd; geo.din = s->dim;
+    HAET_CHECK_ARG((int64_t)geo.g0 * geo.g1 * geo.g2 == s->N, "grid %dx%dx%d does not match N=%lld", geo.g0, geo.g1, geo.g2,
+                   (long long)s->N);
+    const int taps = geo.nd == 3 ? geo.ks * geo.ks * geo.ks : geo.ks * geo.ks;
+    const int K = taps * s->dim;
+    const int64_t M = s->B * s->N;
+    if (M == 0) return HAET_OK;
+    if (int rc = launch_gemm_tc_pack(wx, inner, K, (uint8_t *)img, st)) return rc;
+    const size_t smem = 1024 + (size_t)GT_STAGES * 4 * GT_PANEL_BYTES + sizeof(ConvSmem);
+    static bool attr = false;
+    if (!attr) {
+        HAET_CUDA(cudaFuncSetAttribute(conv_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = true;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int n_halves = inner / GT_N;
+    const int64_t n_tiles = (M + GT_M - 1) / GT_M;
+    int n_workers = sms / n_halves;
+    if (n_workers < 1) n_workers = 1;
+    if (n_workers > n_tiles) n_workers = (int)n_tiles;
+    conv_tc_kernel<0><<<n_workers * n_halves, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
+    HAET_LAUNCHED();
+    return HAET_OK;
+}
+
+}  // namespace haet

@@ -39,6 +39,13 @@ __global__ void gemm_tc_pack_kernel(const float *__restrict__ w, int Nn, int K, 
     *reinterpret_cast<uint4 *>(base + GT_PANEL_BYTES) = *reinterpret_cast<const uint4 *>(lo);
 }
 
+int launch_gemm_tc_pack(const float *w, int Nn, int K, uint8_t *img, cudaStream_t st) {
+    const int chunks = Nn * (K / 8);
+    gemm_tc_pack_kernel<<<(chunks + 255) / 256, 256, 0, st>>>(w, Nn, K, img);
+    HAET_LAUNCHED();
+    return HAET_OK;
+}
+
 // zero the pad rows [N, npad) of every (b, h) of the spill image and their scales
 __global__ void xpi_pad_kernel(uint8_t *__restrict__ img, float *__restrict__ scale, int64_t N, int64_t npad, int64_t bh_count) {
     const int64_t pad = npad - N;

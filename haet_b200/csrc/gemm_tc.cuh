@@ -44,9 +44,11 @@ struct GemmSmem {   // control block placed after the tiles
 // showed the x tiles then crossing HBM twice, 0.50 ms instead of 0.43 ms.)
 //   row0(i)        first global row of this CTA's i-th tile
 //   wait_empty(s, parity) / arrive_full(s): the stage hand-shake with the MMA issuer
-template <class Row0, class WaitEmpty, class ArriveFull>
-__device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_t M, int K, int panels, int64_t my_tiles,
-                                             uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0) {
+//   srcf(ti, p, i, row, c8) address of the 8 consecutive fp32 (32 B) of tile ti, k panel p, tile row `row`, 16-byte bf16
+//                  chunk c8 (i = which of the thread's 4 items), or nullptr for zeros (rows past M, conv padding)
+template <class SrcFn, class WaitEmpty, class ArriveFull>
+__device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uint8_t *sA, SrcFn srcf, WaitEmpty wait_empty,
+                                               ArriveFull arrive_full) {
     using namespace tc;
     const int tid = threadIdx.x;
     const int64_t total = my_tiles * panels;   // (tile, panel) items of this CTA, in order
@@ -54,13 +56,11 @@ __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_
         if (it >= total) return;
         const int64_t ti = it / panels;
         const int p = (int)(it - ti * panels);
-        const int64_t m0 = row0(ti);
 #pragma unroll
         for (int i = 0; i < GT_LD / 2; ++i) {   // 8 consecutive k (32 B) per item: one 16-B bf16 chunk of the row
             const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
-            const int64_t m = m0 + row;
-            if (m < M && !(dbg & 2)) {
-                const float4 *src = reinterpret_cast<const float4 *>(X + m * K + p * GT_KP + c8 * 8);
+            const float4 *src = reinterpret_cast<const float4 *>(srcf(ti, p, i, row, c8));
+            if (src) {
                 v[2 * i] = __ldg(src);
                 v[2 * i + 1] = __ldg(src + 1);
             } else {
@@ -105,6 +105,18 @@ __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_
             load(it + 3, vb);
         }
     }
+}
+
+// dense A: row m of X [M, K]
+template <class Row0, class WaitEmpty, class ArriveFull>
+__device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_t M, int K, int panels, int64_t my_tiles,
+                                             uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0) {
+    gemm_produce_g(panels, my_tiles, sA,
+                   [&](int64_t ti, int p, int, int row, int c8) -> const float * {
+                       const int64_t m = row0(ti) + row;
+                       return (m < M && !(dbg & 2)) ? X + m * K + p * GT_KP + c8 * 8 : nullptr;
+                   },
+                   wait_empty, arrive_full);
 }
 
 // Epilogue of one 32-row x 32-column accumulator chunk as tcgen05.ld.32x32b delivers it (r[j] = row `lane`, column j).
@@ -178,6 +190,7 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
 }
 
 // CTA-pair variant (Nn == 256): every x tile is loaded and split once; the pair shares W through cta_group::2 MMAs
+int launch_gemm_tc_pack(const float *w, int Nn, int K, uint8_t *img, cudaStream_t st);   // W [Nn, K] -> [half][panel][hi | lo] image
 bool gemm2_tc_supported(int K, int Nn);
 int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *bias, float *y, int64_t M, int K, int Nn,
                     const GemmEpi &ep, cudaStream_t st);
