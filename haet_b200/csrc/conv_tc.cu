@@ -5,7 +5,9 @@
 // GEMM -- 8 producer warps gather and split the A rows (the neighbour's channels, zeros outside the grid), one MMA warp,
 // 4 epilogue warps -- except that W (taps * dim * 4 bytes per output row: 7 MB at 64^3 x 256) cannot stay in shared
 // memory: a loader warp streams it, one pre-swizzled 32 KB [hi | lo] panel per (tap, 64 channels), through the same
-// 3-stage ring as A.  One CTA = one 128-column half of 128-row tiles; persistent grid.
+// 3-stage ring as A.  One CTA = NH 128-column halves of 128-row tiles (NH = 2 when the output has a multiple of 256
+// columns: the A rows are then gathered and converted once for 256 columns, UMMA N = 256, W through a 2-stage ring);
+// persistent grid.
 #include "gemm_tc.cuh"
 
 namespace haet {
@@ -14,7 +16,7 @@ using namespace tc;
 constexpr int CT_THREADS = GT_PROD + 32 + 128 + 32;   // producers (0-7), MMA warp (8), epilogue warps (9-12), W loader (13)
 
 struct ConvSmem {
-    uint64_t a_full[GT_STAGES], w_full[GT_STAGES], empty[GT_STAGES];
+    uint64_t a_full[GT_STAGES], a_empty[GT_STAGES], w_full[GT_STAGES], w_empty[GT_STAGES];
     uint64_t t_full[2], t_empty[2];
     uint32_t tmem_base;
 };
@@ -25,7 +27,7 @@ struct ConvGeom {
     int ks, nd, din;      // kernel size, 2 or 3, input channels
 };
 
-template <int DUMMY>
+template <int NH>
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
                float *__restrict__ Y, int64_t M, int Nn, int n_workers, ConvGeom geo) {
@@ -34,23 +36,29 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     const int kp = geo.din / GT_KP;                       // 64-channel panels per tap
     const int taps = geo.nd == 3 ? geo.ks * geo.ks * geo.ks : geo.ks * geo.ks;
     const int panels = taps * kp;
-    const int n_halves = Nn / GT_N;
+    constexpr int CN = NH * GT_N;                         // columns per CTA
+    constexpr int WST = NH == 2 ? 2 : GT_STAGES;          // W ring depth (NH = 2: 64 KB panels)
+    constexpr size_t WSTAGE = (size_t)NH * 2 * GT_PANEL_BYTES;
+    const int n_groups = Nn / CN;
     uint8_t *sA = smem;                                          // [stages][hi|lo][16 KB]: gathered x rows
     uint8_t *sWs = sA + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES;  // [stages][hi|lo][16 KB]: W panel of this column half
-    ConvSmem *cb = reinterpret_cast<ConvSmem *>(sWs + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES);
+    ConvSmem *cb = reinterpret_cast<ConvSmem *>(sWs + (size_t)WST * WSTAGE);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int half = blockIdx.x % n_halves, worker = blockIdx.x / n_halves;
+    const int group = blockIdx.x % n_groups, worker = blockIdx.x / n_groups;
     const int64_t n_tiles = (M + GT_M - 1) / GT_M;
     const int64_t my_tiles = worker < n_tiles ? (n_tiles - worker + n_workers - 1) / n_workers : 0;
 
     if (warp == 8) {
         if (lane == 0) {
-            for (int s = 0; s < GT_STAGES; ++s) { mbar_init(&cb->a_full[s], GT_PROD); mbar_init(&cb->w_full[s], 1); mbar_init(&cb->empty[s], 1); }
+            for (int s = 0; s < GT_STAGES; ++s) {
+                mbar_init(&cb->a_full[s], GT_PROD); mbar_init(&cb->a_empty[s], 1);
+                mbar_init(&cb->w_full[s], 1); mbar_init(&cb->w_empty[s], 1);
+            }
             for (int b = 0; b < 2; ++b) { mbar_init(&cb->t_full[b], 1); mbar_init(&cb->t_empty[b], 128); }
             fence_barrier_init();
         }
         __syncwarp();
-        tmem_alloc<256>(&cb->tmem_base);
+        tmem_alloc<2 * CN>(&cb->tmem_base);
     }
     tc_fence_before();
     __syncthreads();
@@ -90,38 +98,43 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
             return X + nbr * geo.din + c0 + c8 * 8;
         };
         gemm_produce_g(panels, my_tiles, sA, src,
-                       [&](int st, int parity) { mbar_wait(&cb->empty[st], (uint32_t)parity); },
+                       [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
                        [&](int st) { mbar_arrive(&cb->a_full[st]); });
     } else if (warp == 13) {
         // ---------------- W loader: one 32 KB panel [hi | lo] of this column half per stage ----------------
         if (lane == 0) {
-            const uint8_t *src = Wimg + (size_t)half * panels * (2 * GT_PANEL_BYTES);
             int stage = 0, phase = 0;
             for (int64_t it = 0; it < my_tiles; ++it)
                 for (int p = 0; p < panels; ++p) {
-                    mbar_wait(&cb->empty[stage], (uint32_t)(phase ^ 1));
-                    mbar_arrive_expect_tx(&cb->w_full[stage], 2 * GT_PANEL_BYTES);
-                    bulk_g2s(sWs + (size_t)stage * 2 * GT_PANEL_BYTES, src + (size_t)p * 2 * GT_PANEL_BYTES, 2 * GT_PANEL_BYTES, &cb->w_full[stage]);
-                    if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+                    mbar_wait(&cb->w_empty[stage], (uint32_t)(phase ^ 1));
+                    mbar_arrive_expect_tx(&cb->w_full[stage], (uint32_t)WSTAGE);
+                    uint8_t *dst = sWs + (size_t)stage * WSTAGE;   // [hi: NH x 16 KB][lo: NH x 16 KB] = 128 NH rows, contiguous per half
+#pragma unroll
+                    for (int h = 0; h < NH; ++h) {
+                        const uint8_t *src = Wimg + ((size_t)(group * NH + h) * panels + p) * (2 * GT_PANEL_BYTES);
+                        bulk_g2s(dst + (size_t)h * GT_PANEL_BYTES, src, GT_PANEL_BYTES, &cb->w_full[stage]);
+                        bulk_g2s(dst + (size_t)(NH + h) * GT_PANEL_BYTES, src + GT_PANEL_BYTES, GT_PANEL_BYTES, &cb->w_full[stage]);
+                    }
+                    if (++stage == WST) { stage = 0; phase ^= 1; }
                 }
         }
         __syncwarp();
     } else if (warp == 8) {
         // ---------------- MMA issuer ----------------
         if (lane == 0 && my_tiles > 0) {
-            const uint32_t idesc = instr_desc(FMT_BF16, GT_M, GT_N, false, false);
-            int stage = 0, phase = 0;
+            const uint32_t idesc = instr_desc(FMT_BF16, GT_M, CN, false, false);
+            int stage = 0, phase = 0, wst = 0, wph = 0;
             for (int64_t it = 0; it < my_tiles; ++it) {
                 const int buf = (int)(it & 1);
                 mbar_wait(&cb->t_empty[buf], (uint32_t)(((it >> 1) & 1) ^ 1));
                 tc_fence_after();
-                const uint32_t d = tmem_base + (uint32_t)buf * GT_N;
+                const uint32_t d = tmem_base + (uint32_t)buf * CN;
                 for (int p = 0; p < panels; ++p) {
                     mbar_wait(&cb->a_full[stage], phase);
-                    mbar_wait(&cb->w_full[stage], phase);
+                    mbar_wait(&cb->w_full[wst], wph);
                     tc_fence_after();
                     const uint32_t a_hi = smem_u32(sA + (size_t)stage * 2 * GT_PANEL_BYTES), a_lo = a_hi + GT_PANEL_BYTES;
-                    const uint32_t b_hi = smem_u32(sWs + (size_t)stage * 2 * GT_PANEL_BYTES), b_lo = b_hi + GT_PANEL_BYTES;
+                    const uint32_t b_hi = smem_u32(sWs + (size_t)wst * WSTAGE), b_lo = b_hi + NH * GT_PANEL_BYTES;
 #pragma unroll
                     for (int ks = 0; ks < GT_KP / 16; ++ks) {
                         const uint64_t dah = smem_desc_sw128(a_hi + ks * 32, 16, 1024);
@@ -132,8 +145,10 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
                         mma_bf16_ss(d, dal, dbh, idesc, true);
                         mma_bf16_ss(d, dah, dbl, idesc, true);
                     }
-                    tc_commit(&cb->empty[stage]);   // frees the A and the W half of the stage
+                    tc_commit(&cb->a_empty[stage]);
+                    tc_commit(&cb->w_empty[wst]);
                     if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+                    if (++wst == WST) { wst = 0; wph ^= 1; }
                 }
                 tc_commit(&cb->t_full[buf]);
             }
@@ -150,11 +165,11 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
             tc_fence_after();
             const int64_t m0 = tile * GT_M + q * 32 + (lane & ~3);
 #pragma unroll 1
-            for (int c0 = 0; c0 < GT_N; c0 += 32) {
+            for (int c0 = 0; c0 < CN; c0 += 32) {
                 uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * GT_N + c0), r);
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * CN + c0), r);
                 tmem_wait_ld();
-                gemm_epilogue_chunk<EPI_F32>(r, lane, m0, 0, 0, M, bias + half * GT_N + c0, nullptr, Y, Nn, half * GT_N + c0, ep);
+                gemm_epilogue_chunk<EPI_F32>(r, lane, m0, 0, 0, M, bias + group * CN + c0, nullptr, Y, Nn, group * CN + c0, ep);
             }
             tc_fence_before();
             mbar_arrive(&cb->t_empty[buf]);
@@ -164,7 +179,7 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     __syncthreads();
     if (warp == 8) {
         tc_fence_after();
-        tmem_dealloc<256>(tmem_base);
+        tmem_dealloc<2 * CN>(tmem_base);
     }
 }
 
@@ -193,21 +208,24 @@ int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, c
     const int64_t M = s->B * s->N;
     if (M == 0) return HAET_OK;
     if (int rc = launch_gemm_tc_pack(wx, inner, K, (uint8_t *)img, st)) return rc;
-    const size_t smem = 1024 + (size_t)GT_STAGES * 4 * GT_PANEL_BYTES + sizeof(ConvSmem);
-    static bool attr = false;
-    if (!attr) {
-        HAET_CUDA(cudaFuncSetAttribute(conv_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
+    const int nh = (inner % (2 * GT_N) == 0 && !getenv("HAET_CONV_NH1")) ? 2 : 1;
+    const size_t smem = 1024 + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES + (size_t)(nh == 2 ? 2 : GT_STAGES) * nh * 2 * GT_PANEL_BYTES + sizeof(ConvSmem);
+    static bool attr[3] = {false, false, false};
+    if (!attr[nh]) {
+        if (nh == 2) HAET_CUDA(cudaFuncSetAttribute(conv_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        else HAET_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr[nh] = true;
     }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int n_halves = inner / GT_N;
+    const int n_groups = inner / (nh * GT_N);
     const int64_t n_tiles = (M + GT_M - 1) / GT_M;
-    int n_workers = sms / n_halves;
+    int n_workers = sms / n_groups;
     if (n_workers < 1) n_workers = 1;
     if (n_workers > n_tiles) n_workers = (int)n_tiles;
-    conv_tc_kernel<0><<<n_workers * n_halves, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
+    if (nh == 2) conv_tc_kernel<2><<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
+    else conv_tc_kernel<1><<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
     HAET_LAUNCHED();
     return HAET_OK;
 }
