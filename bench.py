@@ -318,7 +318,8 @@ def run_gpu_arm(args):
     # captured once into a CUDA graph and replayed ("graph-replayed iterations"): the clock queries the contract
     # asks for inside the timed region take the driver lock for milliseconds and would otherwise stall the launches.
     step, per_step, launch_mode = (lambda: m(x)), None, "eager"
-    if not args.no_graph and world == 1:   # N > 1: the NCCL all-gather of the slice state is launched eagerly
+    # N > 1: capturable when the slice state is exchanged by the peer-memory kernel (a captured NCCL all-gather hung on replay)
+    if not args.no_graph and (world == 1 or getattr(m, "_px", None) is not None):
         try:
             side = torch.cuda.Stream(dev)
             side.wait_stream(torch.cuda.current_stream(dev))

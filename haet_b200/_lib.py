@@ -55,6 +55,8 @@ SYMBOLS = {
     "haet_balltree_slots": (C.c_int64, [C.c_int64, C.c_int64]),
     "haet_slice_reduce": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P]),
     "haet_slice_merge": (C.c_int, [_SH, _P, C.c_int32, _P, _P, _P, _P]),
+    "haet_peer_buffer_bytes": (C.c_int64, [_SH]),
+    "haet_peer_exchange": (C.c_int, [_SH, C.POINTER(C.c_void_p), C.c_int32, C.c_int32, _P, _P, _P, _P]),
     "haet_balltree_build": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_int32, C.POINTER(C.c_int32),
                                       C.POINTER(C.c_int32), C.c_int32, C.c_double, _P, _P,
                                       C.POINTER(C.c_void_p), _P]),

@@ -56,6 +56,7 @@ class _PhysicsAttentionBase(nn.Module):
         self.to_out = nn.Sequential(nn.Linear(inner_dim, dim), nn.Dropout(dropout))
         # point-sharded multi-GPU: set to a torch.distributed group whose ranks hold disjoint point ranges
         self.point_group = None
+        self._px_key, self._px = None, None   # peer-memory exchange of the slice state (distributed.PeerExchange)
         self._wx_cache = None
         self.last_taps = None   # filled when keep_taps is set (tests)
         self.keep_taps = False
@@ -116,8 +117,7 @@ class _PhysicsAttentionBase(nn.Module):
                                        wt.data_ptr(), bt, spill.data_ptr(), partial.data_ptr(), work.data_ptr(), st))
         parts, n_ranks = partial, 1
         if self.point_group is not None:
-            from .distributed import gather_partials
-            parts, n_ranks = gather_partials(partial, self.point_group)
+            parts, n_ranks = self._exchange(sh, partial)
         eidetic = torch.empty(T, Cc, **f32)
         lse2 = torch.empty(T, **f32)
         pos = torch.empty(T, self.dimensionality, **f32)
@@ -138,6 +138,20 @@ class _PhysicsAttentionBase(nn.Module):
                                   tree_mask=tree_mask, rot_idx=rots, S_out=states)
         out = self.to_out[1](out)   # nn.Dropout: identity in eval / p == 0 (IrregularMesh.py:139,235)
         return out if in_dtype == torch.float32 else out.to(in_dtype)
+
+    def _exchange(self, sh, partial):
+        """Every rank's packed slice state, rank-major: one kernel over NVLink peer memory when it can be set up (and
+        HAET_NCCL_EXCHANGE is not set), else an NCCL (or gloo) all-gather."""
+        import os
+        from .distributed import PeerExchange, gather_partials
+        key = (id(self.point_group), sh.B, sh.slice_num, sh.heads, sh.dim_head, str(partial.device))
+        if self._px_key != key:
+            self._px_key, self._px = key, None
+            if partial.is_cuda and not os.environ.get("HAET_NCCL_EXCHANGE"):
+                self._px = PeerExchange.create(sh, self.point_group, partial.device)
+        if self._px is not None:
+            return self._px(sh, partial)
+        return gather_partials(partial, self.point_group)
 
     def _bt(self) -> float:
         """ada_temp_linear.bias as a host scalar, cached per parameter version (one sync when it changes)."""

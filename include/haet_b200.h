@@ -117,6 +117,17 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
 int haet_slice_merge(const haet_layer_shape *s, const float *partials_d, int32_t n_ranks,
                      float *eidetic_d, float *lse2_d, float *pos_d, void *stream);
 
+/* ---- cross-GPU exchange of the packed slice state over peer memory (new) ----
+ * Replaces the all-gather between the two merge levels by a kernel working on NVLink peer memory (csrc/peer_exchange.cu).
+ * peer_bufs: HOST array of `world` device pointers, entry r = rank r's symmetric buffer of haet_peer_buffer_bytes() bytes as
+ * mapped in this process (zero-initialised once; e.g. torch.distributed._symmetric_memory); partial_d: this rank's packed
+ * state from haet_slice_reduce; gathered_d [world * haet_partial_floats()] is what haet_slice_merge(n_ranks = world) reads;
+ * state_d: 4 zero-initialised uint32 in local memory (device-side epoch, tickets, error word).  No host-side counter:
+ * graph capturable.  Every rank must make the same sequence of calls. */
+int64_t haet_peer_buffer_bytes(const haet_layer_shape *s);
+int haet_peer_exchange(const haet_layer_shape *s, void *const *peer_bufs, int32_t rank, int32_t world,
+                       const float *partial_d, float *gathered_d, void *state_d, void *stream);
+
 /* ---- ball tree (balltree.pyx:598-662) ----------------------------------------------
  * pos_d [n_trees*pts, d] fp32; every tree has `pts` >= 2 consecutive rows (batch_idx = row / pts).
  * tree_idx_d int64[slots], tree_mask_d uint8[slots]; rot_idx_d[i] int64[slots / prod(strides[:i])]

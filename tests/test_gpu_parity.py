@@ -315,6 +315,35 @@ def test_point_sharded_equals_single(monkeypatch):
         assert float((lse - full["lse2"].reshape(-1)).abs().max()) < 1e-4
 
 
+def test_peer_exchange_single_rank_epochs():
+    """haet_peer_exchange with one rank (its own buffer as the only peer): the gathered state is the partial, the two
+    slots alternate and the device-side epoch advances per launch -- the 2-rank exchange over NVLink is covered by
+    scripts/check_multigpu.py under torchrun (a second rank on the same GPU would be two kernels waiting on each other)."""
+    from haet_b200 import _lib
+    cfg, sd, x, out, m = _module("layer_irregular_small")
+    l = _lib.lib()
+    sh = m._shape(x.shape[0], x.shape[1])
+    n = int(l.haet_partial_floats(C.byref(sh)))
+    nb = int(l.haet_peer_buffer_bytes(C.byref(sh)))
+    assert nb == (2 * n + 4) * 4
+    buf = torch.zeros(nb // 4, device="cuda")
+    state = torch.zeros(4, dtype=torch.int32, device="cuda")
+    peers = (C.c_void_p * 1)(buf.data_ptr())
+    st = torch.cuda.current_stream().cuda_stream
+    for it in range(1, 4):
+        part = torch.randn(n, device="cuda")
+        got = torch.full((n,), float("nan"), device="cuda")
+        _lib.check(l.haet_peer_exchange(C.byref(sh), peers, 0, 1, part.data_ptr(), got.data_ptr(), state.data_ptr(), st))
+        torch.cuda.synchronize()
+        assert torch.equal(got, part)
+        assert torch.equal(buf[(it & 1) * n:(it & 1) * n + n], part)          # slot = epoch & 1
+        assert state.tolist() == [it, 0, 0, 0]                                # epoch advanced, tickets reset, no error
+        assert buf[2 * n:2 * n + 1].view(torch.int32).item() == it            # the published flag
+    with pytest.raises(_lib.HaetError):
+        l_rc = l.haet_peer_exchange(C.byref(sh), peers, 1, 1, part.data_ptr(), got.data_ptr(), state.data_ptr(), st)
+        _lib.check(l_rc)
+
+
 @pytest.mark.parametrize("N,G", [(1_000_000, 256)])
 def test_full_size_properties(N, G):
     """BASELINE config 4 shape (1M points, 256 hidden, 8 heads, 256 slices): size-independent properties.
