@@ -54,6 +54,8 @@ SYMBOLS = {
     "haet_erwin_workspace_bytes": (C.c_int64, [_EC, C.c_int64]),
     "haet_balltree_slots": (C.c_int64, [C.c_int64, C.c_int64]),
     "haet_slice_reduce": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P]),
+    "haet_slice_ln_workspace_bytes": (C.c_int64, [_SH]),
+    "haet_slice_reduce_ln": (C.c_int, [_SH, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P]),
     "haet_slice_merge": (C.c_int, [_SH, _P, C.c_int32, _P, _P, _P, _P]),
     "haet_peer_buffer_bytes": (C.c_int64, [_SH]),
     "haet_peer_exchange": (C.c_int, [_SH, C.POINTER(C.c_void_p), C.c_int32, C.c_int32, _P, _P, _P, _P]),
@@ -63,6 +65,7 @@ SYMBOLS = {
     "haet_erwin_forward": (C.c_int, [_EC, _P, _P, C.c_int64, _P, _P, C.c_int64, C.POINTER(C.c_void_p), _P, _P,
                                      _P, _P]),
     "haet_deslice_out": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P]),
+    "haet_deslice_out_res": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P, _P]),
     "haet_layer_scratch_bytes": (C.c_int64, [_SH, _EC]),
     "haet_layer_forward_host": (C.c_int, [_SH, _EC, C.POINTER(LayerWeights), _P, _P, _P, _P]),
     "haet_layer_forward": (C.c_int, [_SH, _EC, C.POINTER(LayerWeights), _P, _P, _P, _P]),

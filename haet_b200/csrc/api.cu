@@ -146,9 +146,39 @@ int haet_debug_gemm(const float *x_d, const float *w_d, const float *bias_d, flo
 }
 int64_t haet_deslice_workspace_bytes(const haet_layer_shape *s) { return deslice_ws_bytes(s); }
 
+// ln_1 scratch behind the regular slice workspace: folded weights + row statistics when the in-projection fuses it, else normalised x
+static bool ln_fuse_ok(const haet_layer_shape *s) {
+    return g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && s->conv_nd == 0 &&
+           gemm_tc_supported(s->dim, s->heads * s->dim_head) && ln_fused_supported(s);
+}
+int64_t haet_slice_ln_workspace_bytes(const haet_layer_shape *s) {
+    const int64_t extra = ln_fuse_ok(s) ? ln_fused_scratch_bytes(s) : align_up(s->B * s->N * (int64_t)s->dim * 4, 256);
+    return align_up(haet_slice_workspace_bytes(s), 256) + extra;
+}
+
+static int slice_reduce_impl(const haet_layer_shape *s, const float *x_d, const float *wx_d, const float *bx_d,
+                             const float *ws_d, const float *bs_d, const float *wt_d, float bt, void *spill_d,
+                             float *partial_d, void *workspace_d, void *stream, const float *ln_g_d, const float *ln_b_d,
+                             float ln_eps);
+
 int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *wx_d, const float *bx_d,
                       const float *ws_d, const float *bs_d, const float *wt_d, float bt, void *spill_d,
                       float *partial_d, void *workspace_d, void *stream) {
+    return slice_reduce_impl(s, x_d, wx_d, bx_d, ws_d, bs_d, wt_d, bt, spill_d, partial_d, workspace_d, stream, nullptr, nullptr, 0.f);
+}
+
+int haet_slice_reduce_ln(const haet_layer_shape *s, const float *x_d, const float *ln_g_d, const float *ln_b_d, float ln_eps,
+                         const float *wx_d, const float *bx_d, const float *ws_d, const float *bs_d, const float *wt_d,
+                         float bt, void *spill_d, float *partial_d, void *workspace_d, void *stream) {
+    HAET_CHECK_ARG(ln_g_d != nullptr && ln_b_d != nullptr, "haet_slice_reduce_ln: LayerNorm weight and bias are required");
+    HAET_CHECK_ARG(ln_eps > 0.f, "haet_slice_reduce_ln: eps must be positive");
+    return slice_reduce_impl(s, x_d, wx_d, bx_d, ws_d, bs_d, wt_d, bt, spill_d, partial_d, workspace_d, stream, ln_g_d, ln_b_d, ln_eps);
+}
+
+static int slice_reduce_impl(const haet_layer_shape *s, const float *x_d, const float *wx_d, const float *bx_d,
+                             const float *ws_d, const float *bs_d, const float *wt_d, float bt, void *spill_d,
+                             float *partial_d, void *workspace_d, void *stream, const float *ln_g_d, const float *ln_b_d,
+                             float ln_eps) {
     int rc = check_shape(s);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
@@ -160,11 +190,19 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
     void *img = (char *)workspace_d + slice_parts_bytes(s);
     const int inner = s->heads * s->dim_head;
     const bool tc = g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s);
+    LnArgs ln{ln_g_d, ln_b_d, ln_eps, (char *)workspace_d + align_up(haet_slice_workspace_bytes(s), 256)};
+    const bool ln_fused = ln_g_d != nullptr && ln_fuse_ok(s);
+    if (ln_g_d != nullptr && !ln_fused && (g_stage_mask & 1)) {
+        // shapes / paths without the fused kernel: normalise into the scratch, then the regular route
+        float *xn = (float *)ln.scratch;
+        if ((rc = launch_layernorm_rows(x_d, ln_g_d, ln_b_d, ln_eps, xn, s->B * s->N, s->dim, st))) return rc;
+        x_d = xn;
+    }
     if (!(g_stage_mask & 1)) {
         rc = HAET_OK;   // bench hook: the spill of an earlier call is reused
     } else if (tc && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner)) {
         // Linear front-end: the GEMM epilogue writes the operand image directly
-        rc = launch_inproj_tc(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st);
+        rc = launch_inproj_tc(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st, ln_fused ? &ln : nullptr);
     } else {
         if (g_path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
             rc = launch_gemm_tc(x_d, wx_d, bx_d, xp, s->B * s->N, s->dim, inner, img, st);
@@ -198,6 +236,12 @@ int haet_slice_merge(const haet_layer_shape *s, const float *partials_d, int32_t
 int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float *lse2_d, const float *states_d,
                      const float *ws_d, const float *bs_d, const float *wt_d, float bt, const float *wo_d,
                      const float *bo_d, float *out_d, void *workspace_d, void *stream) {
+    return haet_deslice_out_res(s, spill_d, lse2_d, states_d, ws_d, bs_d, wt_d, bt, wo_d, bo_d, nullptr, out_d, workspace_d, stream);
+}
+
+int haet_deslice_out_res(const haet_layer_shape *s, const void *spill_d, const float *lse2_d, const float *states_d,
+                         const float *ws_d, const float *bs_d, const float *wt_d, float bt, const float *wo_d,
+                         const float *bo_d, const float *resid_d, float *out_d, void *workspace_d, void *stream) {
     int rc = check_shape(s);
     if (rc) return rc;
     if (s->B == 0 || s->N == 0) return HAET_OK;
@@ -213,12 +257,14 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
     if (rc) return rc;
     if (!(g_stage_mask & 8)) return HAET_OK;
     const int inner = s->heads * s->dim_head;
+    HAET_CHECK_ARG(resid_d != out_d || resid_d == nullptr, "the residual must not alias the output");
     if (out_opi(s))
         return launch_gemm_tc_opi((const uint8_t *)o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim,
-                                  (char *)workspace_d + deslice_o_bytes(s), st);
+                                  (char *)workspace_d + deslice_o_bytes(s), st, resid_d);
     if (g_path == 0 && gemm_tc_supported(inner, s->dim))
-        return launch_gemm_tc(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, (char *)workspace_d + deslice_o_bytes(s), st);
-    return launch_linear(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, st);
+        return launch_gemm_tc(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, (char *)workspace_d + deslice_o_bytes(s), st, resid_d);
+    if ((rc = launch_linear(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, st))) return rc;
+    return resid_d ? launch_add_rows(out_d, resid_d, s->B * s->N * (int64_t)s->dim, st) : HAET_OK;
 }
 
 int64_t haet_layer_scratch_bytes(const haet_layer_shape *s, const haet_erwin_cfg *c) {

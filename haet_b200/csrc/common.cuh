@@ -77,12 +77,25 @@ int64_t gemm_tc_image_bytes(int K, int Nn);
 // every (tile, panel) is one 32 KB SWIZZLE_128B K-major stage of the GEMM, loaded by one bulk copy (no conversion warps).
 bool gemm_opi_supported(int K, int Nn);
 inline int64_t opi_bytes(int64_t M, int K) { return (M + 255) / 256 * 256 * (int64_t)K * 4; }
+// resid (nullable) [M, Nn]: added to the output rows in the epilogue (block fusion)
 int launch_gemm_tc_opi(const uint8_t *a_img, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
-                       cudaStream_t st);
+                       cudaStream_t st, const float *resid = nullptr);
 int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
-                   cudaStream_t st);
+                   cudaStream_t st, const float *resid = nullptr);
+// ln_1 in front of the layer (HAETransolver_Irregular_Mesh.py:125), fused into the CTA-pair in-projection when ln != nullptr:
+// scratch = ln_fused_scratch_bytes() bytes (folded weights, wsum, per-row statistics)
+struct LnArgs {
+    const float *gamma, *beta;
+    float eps;
+    void *scratch;
+};
+bool ln_fused_supported(const haet_layer_shape *s);
+int64_t ln_fused_scratch_bytes(const haet_layer_shape *s);
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
-                     uint8_t *xpi, float *scale, void *img, cudaStream_t st);
+                     uint8_t *xpi, float *scale, void *img, cudaStream_t st, const LnArgs *ln = nullptr);
+// unfused helpers for the shapes / paths the fused kernels do not cover
+int launch_layernorm_rows(const float *x, const float *gamma, const float *beta, float eps, float *y, int64_t M, int K, cudaStream_t st);
+int launch_add_rows(float *y, const float *resid, int64_t n, cudaStream_t st);
 // Conv2d / Conv3d front-end as an implicit GEMM on tcgen05 (conv_tc.cu); wx tap-major [inner, taps, dim]
 bool conv_tc_supported(const haet_layer_shape *s);
 int64_t conv_tc_image_bytes(const haet_layer_shape *s);

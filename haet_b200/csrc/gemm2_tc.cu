@@ -23,7 +23,7 @@ constexpr int G2_EPI = 256;                          // epilogue threads: 2 warp
 constexpr int G2_THREADS = GT_PROD + 32 + G2_EPI;    // producers (warps 0-7), MMA warp (8), epilogue warps (9-16)
 constexpr int G2_CB_BYTES = 128;                     // GemmSmem rounded up to 16 bytes; bias[256] and wt[32] follow
 
-template <int EPI>
+template <int EPI, bool LN, bool RES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G2_THREADS, 1)
 gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
                 float *__restrict__ Y, int64_t M, int K, int n_pairs, GemmEpi ep) {
@@ -104,7 +104,35 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
                     __syncwarp();
                     if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
                 }
+            } else if (RES && warp == 2) {
+                // the residual rows of the NEXT tile are pulled into L2 while this tile is in the epilogue, so that the
+                // epilogue's loads are L2 hits (read from HBM they serialised the epilogue: 0.34 -> 0.81 ms)
+                auto pf = [&](int64_t ti) {
+                    const int64_t r0 = ((pair + ti * n_pairs) * 2 + rank) * (int64_t)GT_M;
+                    if (ti >= my_tiles || r0 >= M) return;
+                    const int64_t rows = M - r0 < GT_M ? M - r0 : GT_M;
+                    const char *src = reinterpret_cast<const char *>(ep.resid + r0 * G2_N);
+                    for (int64_t off = 0; off < rows * G2_N * 4; off += 32768)
+                        bulk_prefetch_l2(src + off, (uint32_t)(rows * G2_N * 4 - off < 32768 ? rows * G2_N * 4 - off : 32768));
+                };
+                if (lane == 0) {
+                    pf(0);
+                    for (int64_t it = 0; it < my_tiles; ++it) {
+                        mbar_wait(&cb->t_full[it & 1], (uint32_t)((it >> 1) & 1));
+                        pf(it + 1);
+                    }
+                }
+                __syncwarp();
             }
+        } else if (LN) {
+            // fused ln_1: the producers see every element of their rows anyway; they leave (mean, rstd) per row for the epilogue
+            auto row0 = [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; };
+            LnStatsHook ln;
+            ln.stats = ep.ln_stats; ln.M = M; ln.K = K; ln.panels = panels; ln.eps = ep.ln_eps;
+            gemm_produce(X, M, K, panels, my_tiles, sA, row0,
+                         [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
+                         [&](int st) { mbar_arrive_remote(full0 + 8u * st); }, ep.dbg,
+                         [&](const float4 (&v)[GT_LD], int64_t ti, int p) { ln.run(v, ti, p, row0); });
         } else
         gemm_produce(X, M, K, panels, my_tiles, sA,
                      [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; },
@@ -156,12 +184,20 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
             const int64_t m0 = ptile * (2 * GT_M) + rank * GT_M + q * 32 + (lane & ~3);   // first of this lane's 4 rows
             int64_t bi0 = 0, n0 = 0;
             if (EPI == EPI_IMG) { bi0 = m0 / ep.N; n0 = m0 - bi0 * ep.N; }
+            float2 rs[4];   // LN: (rstd, -mean rstd) of this lane's 4 rows, written by this CTA's producers (L2 read: not L1-cached)
+            if (LN) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float2 mr = m0 + i < M ? __ldcg(ep.ln_stats + m0 + i) : make_float2(0.f, 0.f);
+                    rs[i] = make_float2(mr.y, -mr.x * mr.y);
+                }
+            }
 #pragma unroll 1
             for (int c0 = eg * 32; c0 < G2_N; c0 += 64) {
                 uint32_t r[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * G2_N + c0), r);
                 tmem_wait_ld();
-                gemm_epilogue_chunk<EPI>(r, lane, m0, bi0, n0, M, sBias + c0, sWt, Y, G2_N, c0, ep);
+                gemm_epilogue_chunk<EPI, LN, RES>(r, lane, m0, bi0, n0, M, sBias + c0, sWt, Y, G2_N, c0, ep, rs);
             }
             tc_fence_before();
             mbar_arrive_remote(empty0 + 8u * buf);
@@ -183,13 +219,20 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     HAET_CHECK_ARG(gemm2_tc_supported(K, Nn), "gemm2_tc: unsupported K=%d Nn=%d", K, Nn);
     const int panels = K / GT_KP;
     const size_t smem = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + G2_CB_BYTES + sizeof(float) * (G2_N + 32);
-    static size_t smem_set[2] = {0, 0};
-    if (smem > smem_set[epi]) {
-        if (epi == EPI_IMG)
-            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_IMG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const bool ln = epi == EPI_IMG && ep.ln_stats != nullptr;
+    const bool res = epi == EPI_F32 && ep.resid != nullptr;
+    const int variant = ln ? 2 : res ? 3 : epi;
+    static size_t smem_set[4] = {0, 0, 0, 0};
+    if (smem > smem_set[variant]) {
+        if (ln)
+            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_IMG, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        else if (res)
+            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_F32, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        else if (epi == EPI_IMG)
+            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_IMG, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         else
-            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set[epi] = smem;
+            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_F32, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set[variant] = smem;
     }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -200,10 +243,15 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     if (n_pairs < 1) n_pairs = 1;
     GemmEpi epd = ep;
     if (const char *e = getenv("HAET_GEMM_DBG")) epd.dbg = atoi(e);
-    if (epi == EPI_IMG)
-        gemm2_tc_kernel<EPI_IMG><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);
+    if (ln) {
+        HAET_CHECK_ARG(ep.wsum != nullptr, "fused LayerNorm needs wsum");
+        gemm2_tc_kernel<EPI_IMG, true, false><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);
+    } else if (res)
+        gemm2_tc_kernel<EPI_F32, false, true><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);
+    else if (epi == EPI_IMG)
+        gemm2_tc_kernel<EPI_IMG, false, false><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);
     else
-        gemm2_tc_kernel<EPI_F32><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);
+        gemm2_tc_kernel<EPI_F32, false, false><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);
     HAET_LAUNCHED();
     return HAET_OK;
 }

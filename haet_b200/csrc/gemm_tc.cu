@@ -201,30 +201,121 @@ static int launch_gemm_impl(const float *x, const float *w, const float *bias, f
     if (n_workers > n_tiles) n_workers = (int)n_tiles;
     gemm_tc_kernel<EPI><<<n_workers * n_halves, GT_THREADS, smem, st>>>(x, (const uint8_t *)img, bias, y, M, K, Nn, n_workers, ep);
     HAET_LAUNCHED();
+    if (EPI == EPI_F32 && ep.resid) return launch_add_rows(y, ep.resid, M * Nn, st);   // only the pair kernel fuses the residual
     return HAET_OK;
 }
 
 int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
-                   cudaStream_t st) {
+                   cudaStream_t st, const float *resid) {
     GemmEpi ep{};
+    ep.resid = resid;
     return launch_gemm_impl<EPI_F32>(x, w, bias, y, M, K, Nn, img, ep, st);
 }
 
 // to_out with A given as the operand image pass 2 wrote (common.cuh: OPI); only the CTA-pair kernel reads it
 bool gemm_opi_supported(int K, int Nn) { return gemm2_tc_supported(K, Nn) && !getenv("HAET_GEMM_1CTA") && !getenv("HAET_NO_OPI"); }
 int launch_gemm_tc_opi(const uint8_t *a_img, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
-                       cudaStream_t st) {
+                       cudaStream_t st, const float *resid) {
     HAET_CHECK_ARG(gemm_opi_supported(K, Nn), "gemm_tc_opi: unsupported K=%d Nn=%d", K, Nn);
     GemmEpi ep{};
     ep.a_img = 1;
+    ep.resid = resid;
     return launch_gemm_impl<EPI_F32>(reinterpret_cast<const float *>(a_img), w, bias, y, M, K, Nn, img, ep, st);
+}
+
+// ---- block fusion helpers ------------------------------------------------------------------------------
+// ln_1 folded into the in-projection (one block per output row o, K <= 256 threads each own one k):
+//   Wf[o, k] = W[o, k] gamma[k],  bf[o] = b[o] + sum_k W[o, k] beta[k],
+//   wsum[o] = sum_k (hi + lo)(Wf[o, k])  -- of the bf16 pair the MMA actually multiplies, so that the mean term cancels exactly
+__global__ void ln_fold_kernel(const float *__restrict__ w, const float *__restrict__ b, const float *__restrict__ gamma,
+                               const float *__restrict__ beta, int K, float *__restrict__ wf, float *__restrict__ bf,
+                               float *__restrict__ wsum) {
+    __shared__ float sa[256], sb[256];
+    const int o = blockIdx.x, k = threadIdx.x;
+    float a = 0.f, c = 0.f;
+    if (k < K) {
+        const float wv = w[(size_t)o * K + k], f = wv * gamma[k];
+        wf[(size_t)o * K + k] = f;
+        __nv_bfloat16 hi, lo;
+        split_bf16(f, hi, lo);
+        a = __bfloat162float(hi) + __bfloat162float(lo);
+        c = wv * beta[k];
+    }
+    sa[k] = a; sb[k] = c;
+    __syncthreads();
+    for (int o2 = 128; o2; o2 >>= 1) {   // fixed-order tree: bit-reproducible
+        if (k < o2) { sa[k] += sa[k + o2]; sb[k] += sb[k + o2]; }
+        __syncthreads();
+    }
+    if (k == 0) { wsum[o] = sa[0]; bf[o] = b[o] + sb[0]; }
+}
+
+bool ln_fused_supported(const haet_layer_shape *s) {
+    const int inner = s->heads * s->dim_head;
+    return g_path == 0 && s->conv_nd == 0 && s->dim_head == 32 && gemm2_tc_supported(s->dim, inner) && !getenv("HAET_GEMM_1CTA") &&
+           !getenv("HAET_NO_LN_FUSE");
+}
+static int64_t ln_fold_floats(const haet_layer_shape *s) {
+    const int64_t inner = s->heads * s->dim_head;
+    return align_up(inner * s->dim, 64) + 2 * align_up(inner, 64);
+}
+int64_t ln_fused_scratch_bytes(const haet_layer_shape *s) {
+    return align_up(ln_fold_floats(s) * 4 + s->B * s->N * (int64_t)sizeof(float2), 256);
+}
+
+// nn.LayerNorm over the last dimension, one warp per row (the unfused route: conv front-ends, SIMT path, other shapes)
+__global__ void layernorm_rows_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta,
+                                      float eps, float *__restrict__ y, int64_t M, int K) {
+    const int64_t m = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (m >= M) return;
+    const float *xr = x + m * K;
+    float s1 = 0.f;
+    for (int k = lane; k < K; k += 32) s1 += xr[k];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    const float mean = s1 / (float)K;
+    float s2 = 0.f;
+    for (int k = lane; k < K; k += 32) { const float d = xr[k] - mean; s2 = fmaf(d, d, s2); }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    const float rstd = rsqrtf(s2 / (float)K + eps);
+    for (int k = lane; k < K; k += 32) y[m * K + k] = (xr[k] - mean) * rstd * gamma[k] + beta[k];
+}
+int launch_layernorm_rows(const float *x, const float *gamma, const float *beta, float eps, float *y, int64_t M, int K, cudaStream_t st) {
+    if (M == 0) return HAET_OK;
+    layernorm_rows_kernel<<<(unsigned)cdiv(M, 8), 256, 0, st>>>(x, gamma, beta, eps, y, M, K);
+    HAET_LAUNCHED();
+    return HAET_OK;
+}
+__global__ void add_rows_kernel(float *__restrict__ y, const float *__restrict__ r, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) y[i] += r[i];
+}
+int launch_add_rows(float *y, const float *resid, int64_t n, cudaStream_t st) {
+    if (n == 0) return HAET_OK;
+    add_rows_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(y, resid, n);
+    HAET_LAUNCHED();
+    return HAET_OK;
 }
 
 // in_project_x of the tensor-core path: X [B*N, dim] -> the spill's operand image + scales (no fp32 x_proj)
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
-                     uint8_t *xpi, float *scale, void *img, cudaStream_t st) {
+                     uint8_t *xpi, float *scale, void *img, cudaStream_t st, const LnArgs *ln) {
     HAET_CHECK_ARG(s->dim_head == 32, "the operand image needs dim_head == 32");
     GemmEpi ep{};
+    if (ln) {
+        HAET_CHECK_ARG(ln_fused_supported(s), "fused LayerNorm: unsupported shape");
+        const int inner = s->heads * s->dim_head;
+        float *wf = (float *)ln->scratch, *bf = wf + align_up((int64_t)inner * s->dim, 64), *wsum = bf + align_up(inner, 64);
+        ln_fold_kernel<<<inner, 256, 0, st>>>(wx, bx, ln->gamma, ln->beta, s->dim, wf, bf, wsum);
+        HAET_LAUNCHED();
+        ep.wsum = wsum;
+        ep.ln_stats = reinterpret_cast<float2 *>(wsum + align_up(inner, 64));
+        ep.ln_eps = ln->eps;
+        wx = wf;
+        bx = bf;
+    }
     ep.img = xpi; ep.scale = scale; ep.wt = wt; ep.bt = bt; ep.base_temp = s->base_temp;
     ep.N = s->N; ep.npad = xpi_npad(s->N); ep.H = s->heads;
     const int64_t pad = ep.npad - ep.N, bh = s->B * s->heads;

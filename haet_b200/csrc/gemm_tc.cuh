@@ -26,6 +26,15 @@ struct GemmEpi {   // EPI_IMG arguments
     int H;
     int dbg;   // development switches (HAET_GEMM_DBG): 1 = no epilogue stores, 2 = no global loads
     int a_img; // X is the bf16 hi/lo operand image written by pass 2 (common.cuh: OPI), bulk-copied instead of converted
+    // Block fusion (HAETransolver_Irregular_Mesh.py:125  fx = Attn(ln_1(fx)) + fx):
+    //   EPI_F32: resid [M, ldy] is added to the output rows (nullptr: none)
+    //   pair kernel, LN = true: X is the RAW residual stream; W / bias arrive folded (W.gamma, b + W.beta), the producers
+    //   leave (mean_m, rstd_m) of every row in ln_stats [M] and the epilogue applies
+    //   xp[m, o] = rstd_m (acc[m, o] - mean_m wsum[o]) + bias'[o],  wsum[o] = sum_k W'[o, k]
+    const float *resid;
+    const float *wsum;
+    float2 *ln_stats;
+    float ln_eps;
 };
 
 struct GemmSmem {   // control block placed after the tiles
@@ -46,9 +55,13 @@ struct GemmSmem {   // control block placed after the tiles
 //   wait_empty(s, parity) / arrive_full(s): the stage hand-shake with the MMA issuer
 //   srcf(ti, p, i, row, c8) address of the 8 consecutive fp32 (32 B) of tile ti, k panel p, tile row `row`, 16-byte bf16
 //                  chunk c8 (i = which of the thread's 4 items), or nullptr for zeros (rows past M, conv padding)
-template <class SrcFn, class WaitEmpty, class ArriveFull>
+struct NoPanelHook {
+    __device__ __forceinline__ void operator()(const float4 (&)[8], int64_t, int) const {}
+};
+//   hook(v, ti, p): sees the fp32 registers of (tile ti, panel p) right before they are split and stored (LayerNorm statistics)
+template <class SrcFn, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
 __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uint8_t *sA, SrcFn srcf, WaitEmpty wait_empty,
-                                               ArriveFull arrive_full) {
+                                               ArriveFull arrive_full, PanelHook hook = PanelHook()) {
     using namespace tc;
     const int tid = threadIdx.x;
     const int64_t total = my_tiles * panels;   // (tile, panel) items of this CTA, in order
@@ -69,7 +82,11 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
         }
     };
     int stage = 0, phase = 0;
+    int64_t s_ti = 0;   // (tile, panel) of the item being stored
+    int s_p = 0;
     auto store = [&](const float4 (&v)[GT_LD]) {
+        hook(v, s_ti, s_p);
+        if (++s_p == panels) { s_p = 0; ++s_ti; }
         wait_empty(stage, phase ^ 1);
         uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
 #pragma unroll
@@ -108,16 +125,54 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
 }
 
 // dense A: row m of X [M, K]
-template <class Row0, class WaitEmpty, class ArriveFull>
+template <class Row0, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
 __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_t M, int K, int panels, int64_t my_tiles,
-                                             uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0) {
+                                             uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0,
+                                             PanelHook hook = PanelHook()) {
     gemm_produce_g(panels, my_tiles, sA,
                    [&](int64_t ti, int p, int, int row, int c8) -> const float * {
                        const int64_t m = row0(ti) + row;
                        return (m < M && !(dbg & 2)) ? X + m * K + p * GT_KP + c8 * 8 : nullptr;
                    },
-                   wait_empty, arrive_full);
+                   wait_empty, arrive_full, hook);
 }
+
+// LayerNorm statistics of the rows a producer thread touches (pair kernel, LN = true).  Thread tid holds, per panel, the 8
+// floats (row i * 32 + tid / 8, chunk tid & 7) for i < 4: the 8 threads of a row reduce with 3 shuffles after the last
+// panel and lane (tid & 7) == 0 writes (mean, rstd) -- nn.LayerNorm: biased variance, eps inside the root.
+struct LnStatsHook {
+    float2 *stats;
+    int64_t M;
+    int K, panels;
+    float eps;
+    float s1[4], s2[4];
+    template <class Row0>
+    __device__ __forceinline__ void run(const float4 (&v)[8], int64_t ti, int p, Row0 row0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (p == 0) { s1[i] = 0.f; s2[i] = 0.f; }
+            const float4 a = v[2 * i], b = v[2 * i + 1];
+            s1[i] += (a.x + a.y) + (a.z + a.w) + (b.x + b.y) + (b.z + b.w);
+            s2[i] = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, s2[i]))));
+            s2[i] = fmaf(b.x, b.x, fmaf(b.y, b.y, fmaf(b.z, b.z, fmaf(b.w, b.w, s2[i]))));
+        }
+        if (p != panels - 1) return;
+        const int tid = threadIdx.x;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float a = s1[i], b = s2[i];
+#pragma unroll
+            for (int o = 1; o < 8; o <<= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+            const int64_t m = row0(ti) + i * 32 + (tid >> 3);
+            if ((tid & 7) == 0 && m < M) {
+                const float mean = a / (float)K;
+                const float var = fmaxf(b / (float)K - mean * mean, 0.f);
+                stats[m] = make_float2(mean, rsqrtf(var + eps));
+            }
+        }
+        __threadfence_block();   // ordered before this thread's arrive on the stage barrier (the epilogue reads after t_full)
+    }
+};
 
 // Epilogue of one 32-row x 32-column accumulator chunk as tcgen05.ld.32x32b delivers it (r[j] = row `lane`, column j).
 // Written row-per-lane, every store instruction would touch 32 different rows with 16 bytes each: measured, those
@@ -125,12 +180,28 @@ __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_
 // write 64 contiguous bytes of one row per instruction (whole 32-byte sectors, 8 rows per instruction).
 //   m0 / bi0 / n0: global row (and its batch / point index, EPI_IMG) of this lane's FIRST row = warp row + (lane & ~3)
 //   bias32 / wt32: the chunk's 32 bias values / the Ada-Temp weights (EPI_IMG); col0: first global column of the chunk
-template <int EPI>
+//   LN (EPI_IMG only): rs[i] = (rstd, -mean * rstd) of row m0 + i; ep.wsum as documented in GemmEpi
+//   RES (EPI_F32 only): ep.resid rows are added; their loads are issued BEFORE the transposes so that the L2 latency
+//   (the pair kernel prefetches the tile into L2 one tile ahead) overlaps the shuffles
+template <int EPI, bool LN = false, bool RES = false>
 __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane, int64_t m0, int64_t bi0, int64_t n0, int64_t M,
                                                     const float *bias32, const float *wt32, float *Y, int ldy, int col0,
-                                                    const GemmEpi &ep) {
+                                                    const GemmEpi &ep, const float2 *rs = nullptr) {
     const int l4 = lane & 3;
     if (EPI == EPI_F32) {
+        float4 q0[4], q1[4];
+        if (RES) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (m0 + i < M) {
+                    const float *rp = ep.resid + (m0 + i) * ldy + col0 + 4 * l4;
+                    q0[i] = __ldg(reinterpret_cast<const float4 *>(rp));
+                    q1[i] = __ldg(reinterpret_cast<const float4 *>(rp + 16));
+                } else {
+                    q0[i] = q1[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+        }
         xpose_stage<0, 2>(r, lane);
         xpose_stage<1, 3>(r, lane);
         // register 4 i + 16 h + c = row m0 + i, column 16 h + 4 l4 + c
@@ -140,10 +211,16 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
         for (int i = 0; i < 4; ++i) {
             if (m0 + i >= M) break;
             float *y = Y + (m0 + i) * ldy + col0 + 4 * l4;
-            *reinterpret_cast<float4 *>(y) = make_float4(__uint_as_float(r[4 * i]) + b0.x, __uint_as_float(r[4 * i + 1]) + b0.y,
-                                                         __uint_as_float(r[4 * i + 2]) + b0.z, __uint_as_float(r[4 * i + 3]) + b0.w);
-            *reinterpret_cast<float4 *>(y + 16) = make_float4(__uint_as_float(r[4 * i + 16]) + b1.x, __uint_as_float(r[4 * i + 17]) + b1.y,
-                                                              __uint_as_float(r[4 * i + 18]) + b1.z, __uint_as_float(r[4 * i + 19]) + b1.w);
+            float4 o0 = make_float4(__uint_as_float(r[4 * i]) + b0.x, __uint_as_float(r[4 * i + 1]) + b0.y,
+                                    __uint_as_float(r[4 * i + 2]) + b0.z, __uint_as_float(r[4 * i + 3]) + b0.w);
+            float4 o1 = make_float4(__uint_as_float(r[4 * i + 16]) + b1.x, __uint_as_float(r[4 * i + 17]) + b1.y,
+                                    __uint_as_float(r[4 * i + 18]) + b1.z, __uint_as_float(r[4 * i + 19]) + b1.w);
+            if (RES) {   // + fx (the block's residual connection), read with the same full-sector pattern as the store
+                o0.x += q0[i].x; o0.y += q0[i].y; o0.z += q0[i].z; o0.w += q0[i].w;
+                o1.x += q1[i].x; o1.y += q1[i].y; o1.z += q1[i].z; o1.w += q1[i].w;
+            }
+            *reinterpret_cast<float4 *>(y) = o0;
+            *reinterpret_cast<float4 *>(y + 16) = o1;
         }
     } else {
         xpose_stage<0, 3>(r, lane);
@@ -153,6 +230,12 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
         const float4 wa = *reinterpret_cast<const float4 *>(wt32 + 8 * l4), wb = *reinterpret_cast<const float4 *>(wt32 + 8 * l4 + 4);
         const float bs[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
         const float ws[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+        float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (LN) {
+            const float4 sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
+            const float4 sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
+            su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
+        }
         const int h = col0 >> 5;
         int64_t bi = bi0, n = n0;
 #pragma unroll
@@ -161,7 +244,14 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
             uint32_t hi[4], lo[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                const float v0 = __uint_as_float(r[8 * i + 2 * c]) + bs[2 * c], v1 = __uint_as_float(r[8 * i + 2 * c + 1]) + bs[2 * c + 1];
+                float v0, v1;
+                if (LN) {
+                    v0 = fmaf(__uint_as_float(r[8 * i + 2 * c]), rs[i].x, fmaf(rs[i].y, su[2 * c], bs[2 * c]));
+                    v1 = fmaf(__uint_as_float(r[8 * i + 2 * c + 1]), rs[i].x, fmaf(rs[i].y, su[2 * c + 1], bs[2 * c + 1]));
+                } else {
+                    v0 = __uint_as_float(r[8 * i + 2 * c]) + bs[2 * c];
+                    v1 = __uint_as_float(r[8 * i + 2 * c + 1]) + bs[2 * c + 1];
+                }
                 d = fmaf(v0, ws[2 * c], d);
                 d = fmaf(v1, ws[2 * c + 1], d);
                 const __half2 hh = __floats2half2_rn(v0, v1);

@@ -85,6 +85,18 @@ class _PhysicsAttentionBase(nn.Module):
 
     @torch.no_grad()
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self._forward(x, None, False)
+
+    @torch.no_grad()
+    def forward_block(self, fx: torch.Tensor, ln_1: nn.LayerNorm) -> torch.Tensor:
+        """``self(ln_1(fx)) + fx`` -- the attention half of TransolverErwinBlock.forward
+        (models/HAETransolver_Irregular_Mesh.py:125) with the LayerNorm fused into the in-projection kernel and the
+        residual add into the to_out epilogue (haet_slice_reduce_ln / haet_deslice_out_res)."""
+        if tuple(ln_1.normalized_shape) != (self.dim,) or ln_1.weight is None or ln_1.bias is None:
+            raise ValueError("forward_block expects an affine nn.LayerNorm over the hidden dimension")
+        return self._forward(fx, ln_1, True)
+
+    def _forward(self, x: torch.Tensor, ln_1: Optional[nn.LayerNorm], residual: bool) -> torch.Tensor:
         if not x.is_cuda:
             raise _lib.HaetError("haet_b200 PhysicsAttention runs on CUDA tensors only (no CPU fallback)")
         if x.dim() != 3 or x.shape[2] != self.dim:
@@ -110,11 +122,20 @@ class _PhysicsAttentionBase(nn.Module):
         H, G, Cc = self.heads, self.slice_num, self.dim_head
         T = B * H * G
         spill = torch.empty(max(l.haet_spill_bytes(psh), 4), dtype=torch.uint8, device=dev)
-        wsz = max(l.haet_slice_workspace_bytes(psh), l.haet_deslice_workspace_bytes(psh), 4)
+        slice_ws = l.haet_slice_ln_workspace_bytes(psh) if ln_1 is not None else l.haet_slice_workspace_bytes(psh)
+        wsz = max(slice_ws, l.haet_deslice_workspace_bytes(psh), 4)
         work = torch.empty(wsz, dtype=torch.uint8, device=dev)
         partial = torch.empty(l.haet_partial_floats(psh), **f32)
-        _lib.check(l.haet_slice_reduce(psh, x.data_ptr(), wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(),
-                                       wt.data_ptr(), bt, spill.data_ptr(), partial.data_ptr(), work.data_ptr(), st))
+        if ln_1 is not None:
+            lg = ln_1.weight.detach().float().contiguous()
+            lb = ln_1.bias.detach().float().contiguous()
+            _lib.check(l.haet_slice_reduce_ln(psh, x.data_ptr(), lg.data_ptr(), lb.data_ptr(), float(ln_1.eps),
+                                              wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(), wt.data_ptr(),
+                                              bt, spill.data_ptr(), partial.data_ptr(), work.data_ptr(), st))
+        else:
+            _lib.check(l.haet_slice_reduce(psh, x.data_ptr(), wx.data_ptr(), bx.data_ptr(), ws.data_ptr(),
+                                           bs.data_ptr(), wt.data_ptr(), bt, spill.data_ptr(), partial.data_ptr(),
+                                           work.data_ptr(), st))
         parts, n_ranks = partial, 1
         if self.point_group is not None:
             parts, n_ranks = self._exchange(sh, partial)
@@ -130,9 +151,11 @@ class _PhysicsAttentionBase(nn.Module):
                                                     float(self.erwin.rotate))
         states = erwin_device(self.erwin, eidetic, pos, tree_idx, tree_mask, rots)
         out = torch.empty(B, N, self.dim, **f32)
-        _lib.check(l.haet_deslice_out(psh, spill.data_ptr(), lse2.data_ptr(), states.data_ptr(), ws.data_ptr(),
-                                      bs.data_ptr(), wt.data_ptr(), bt, wo.data_ptr(), bo.data_ptr(), out.data_ptr(),
-                                      work.data_ptr(), st))
+        if residual and self.to_out[1].p > 0 and self.to_out[1].training:
+            raise NotImplementedError("forward_block is eval-mode only (dropout sits between to_out and the residual)")
+        _lib.check(l.haet_deslice_out_res(psh, spill.data_ptr(), lse2.data_ptr(), states.data_ptr(), ws.data_ptr(),
+                                          bs.data_ptr(), wt.data_ptr(), bt, wo.data_ptr(), bo.data_ptr(),
+                                          x.data_ptr() if residual else None, out.data_ptr(), work.data_ptr(), st))
         if self.keep_taps:
             self.last_taps = dict(S=eidetic.view(B, H, G, Cc), lse2=lse2.view(B, H, G), pos=pos, tree_idx=tree_idx,
                                   tree_mask=tree_mask, rot_idx=rots, S_out=states)
@@ -209,9 +232,22 @@ class Physics_Attention_Structured_Mesh_3D(_PhysicsAttentionBase):
                     enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed)
 
 
-def patch_model(model: nn.Module) -> nn.Module:
+def _fused_block_forward(self, fx):
+    """TransolverErwinBlock.forward (models/HAETransolver_Irregular_Mesh.py:112-135) with ``Attn(ln_1(fx)) + fx`` as
+    one fused call; the MLP half is the block's own modules, unchanged."""
+    fx = self.Attn.forward_block(fx, self.ln_1)
+    fx = self.mlp(self.ln_2(fx)) + fx
+    if self.last_layer:
+        return self.mlp2(self.ln_3(fx))
+    return fx
+
+
+def patch_model(model: nn.Module, fuse_blocks: bool = False) -> nn.Module:
     """Swap every reference ``Physics_Attention_*`` inside ``model`` (a reference-constructed HAETransolver_*)
-    for the haet_b200 module of the same name, carrying the state_dict over (strict)."""
+    for the haet_b200 module of the same name, carrying the state_dict over (strict).  With ``fuse_blocks`` every
+    block that holds one (attributes ``ln_1, Attn, ln_2, mlp, last_layer`` as in TransolverErwinBlock) also gets the
+    fused forward above (eval / inference only)."""
+    import types
     mapping = {c.__name__: c for c in (Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D,
                                        Physics_Attention_Structured_Mesh_3D)}
     for parent in list(model.modules()):
@@ -221,6 +257,11 @@ def patch_model(model: nn.Module) -> nn.Module:
                 continue
             new = from_reference(child, cls)
             setattr(parent, name, new)
+    if fuse_blocks:
+        for blk in model.modules():
+            if isinstance(getattr(blk, "Attn", None), _PhysicsAttentionBase) and \
+                    all(hasattr(blk, a) for a in ("ln_1", "ln_2", "mlp", "last_layer")):
+                blk.forward = types.MethodType(_fused_block_forward, blk)
     return model
 
 

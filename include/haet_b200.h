@@ -24,6 +24,9 @@
  *   haet_erwin_forward     models/components/erwinflash/erwin_flash.py:138-195
  *                          (+ components/{layers,attention,mlp,pooling}.py)
  *   haet_deslice_out       IrregularMesh.py:221-235 (deslice W.S' + to_out)
+ *   haet_slice_reduce_ln / haet_deslice_out_res
+ *                          the same with the caller's ln_1 and residual add fused in
+ *                          (models/HAETransolver_Irregular_Mesh.py:125)
  *   haet_layer_forward_host  the whole Physics_Attention_*.forward
  *                          (IrregularMesh.py:141-235) on HOST buffers
  */
@@ -109,6 +112,16 @@ int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *
                       const float *ws_d, const float *bs_d, const float *wt_d, float bt,
                       void *spill_d, float *partial_d, void *workspace_d, void *stream);
 
+/* Block fusion, SURVEY 8f rank 1 (models/HAETransolver_Irregular_Mesh.py:125  fx = self.Attn(self.ln_1(fx)) + fx):
+ * haet_slice_reduce_ln == haet_slice_reduce(LayerNorm(x; ln_g_d, ln_b_d, ln_eps)) with x_d the RAW residual stream.  On the
+ * tensor-core Linear front-end (heads*dim_head == 256) the in-projection kernel computes the row statistics while it
+ * converts x and applies them in its epilogue (weights folded on the device: no normalised copy of x ever exists); other
+ * shapes normalise into the workspace first.  workspace_d must hold haet_slice_ln_workspace_bytes() bytes. */
+int64_t haet_slice_ln_workspace_bytes(const haet_layer_shape *s);
+int haet_slice_reduce_ln(const haet_layer_shape *s, const float *x_d, const float *ln_g_d, const float *ln_b_d, float ln_eps,
+                         const float *wx_d, const float *bx_d, const float *ws_d, const float *bs_d, const float *wt_d,
+                         float bt, void *spill_d, float *partial_d, void *workspace_d, void *stream);
+
 /* Merge R packed rank-partials (rank-major, fixed order => bit-reproducible on every rank) into
  *   eidetic_d [B*heads*G, C]  = (S/l)/(1+1e-5)          (IrregularMesh.py:181-188; sum_n W == 1)
  *   lse2_d    [B*heads*G]     = m2 + log2(l)            (global softmax normaliser, base 2)
@@ -154,6 +167,12 @@ int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float
                      const float *states_d, const float *ws_d, const float *bs_d, const float *wt_d,
                      float bt, const float *wo_d, const float *bo_d, float *out_d,
                      void *workspace_d, void *stream);
+
+/* Same with the block's residual connection fused into the to_out epilogue: out = deslice_out(...) + resid_d
+ * (resid_d [B, N, dim], may be NULL, must not alias out_d). */
+int haet_deslice_out_res(const haet_layer_shape *s, const void *spill_d, const float *lse2_d, const float *states_d,
+                         const float *ws_d, const float *bs_d, const float *wt_d, float bt, const float *wo_d,
+                         const float *bo_d, const float *resid_d, float *out_d, void *workspace_d, void *stream);
 
 /* ---- whole layer on HOST buffers (copies inside) ------------------------------------
  * The call a non-torch host (C, C++, ctypes) makes: x_h / out_h are host pointers (pinned for

@@ -206,6 +206,87 @@ def test_layer_matches_oracle_trained_like(variant, B, N, kw):
     assert rel_l2(got, want) < TOL
 
 
+# ------------------------------------------------------------------------------------------------
+# block fusion: fx = Attn(ln_1(fx)) + fx  (HAETransolver_Irregular_Mesh.py:125)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("variant,B,N,kw,shift", [
+    # fused route: CTA-pair in-projection computes the LayerNorm statistics, to_out adds the residual
+    ("Physics_Attention_Irregular_Mesh", 1, 4099, dict(dim=256, heads=8, dim_head=32, slice_num=32, rotate=45, mlp_ratio=2), 0.0),
+    ("Physics_Attention_Irregular_Mesh", 3, 1111, dict(dim=256, heads=8, dim_head=32, slice_num=64, rotate=45, mlp_ratio=2), 1.5),
+    ("Physics_Attention_Irregular_Mesh", 1, 130, dict(dim=256, heads=8, dim_head=32, slice_num=256, rotate=45, mlp_ratio=2), -0.7),
+    # unfused routes behind the same entry points: single-CTA GEMM shapes, SIMT shapes, conv front-ends
+    ("Physics_Attention_Irregular_Mesh", 2, 1500, dict(dim=128, heads=8, dim_head=16, slice_num=100, rotate=45, mlp_ratio=2), 0.5),
+    ("Physics_Attention_Irregular_Mesh", 1, 777, dict(dim=128, heads=4, dim_head=32, slice_num=64, rotate=0, mlp_ratio=4), 0.5),
+    ("Physics_Attention_Structured_Mesh_2D", 1, 21 * 13, dict(dim=256, heads=8, dim_head=32, slice_num=64, H=21, W=13, rotate=45, mlp_ratio=2), 0.5),
+])
+def test_block_fusion_matches_oracle(variant, B, N, kw, shift):
+    """forward_block(fx, ln_1) against the oracle run on the reference's own composition LayerNorm -> layer -> + fx,
+    with a raw residual stream (row means / scales far from normalised) and a non-trivial LayerNorm affine."""
+    import haet_b200 as hb
+    torch.manual_seed(N + 7)
+    m = getattr(hb, variant)(**kw).eval()
+    trained_like_(m, N + 1)
+    D = kw["dim"]
+    ln = torch.nn.LayerNorm(D)
+    with torch.no_grad():
+        ln.weight.copy_(1 + 0.3 * torch.randn(D))
+        ln.bias.copy_(0.2 * torch.randn(D))
+    fx = torch.randn(B, N, D) * (0.5 + 2 * torch.rand(B, N, 1)) + shift + 0.3 * torch.randn(1, 1, D)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    import copy
+    m = m.cuda()
+    ln_c = copy.deepcopy(ln).cuda()
+    m.keep_taps = True
+    got = m.forward_block(fx.cuda(), ln_c)
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    okw = dict(heads=kw["heads"], dim_head=kw["dim_head"], slice_num=kw["slice_num"], rotate=kw["rotate"],
+               mlp_ratio=kw["mlp_ratio"], dimensionality=2 if variant.endswith("2D") else 3)
+    if variant.endswith("2D"):
+        okw["grid"] = (kw["H"], kw["W"])
+    taps = {}
+    with torch.no_grad():
+        xn = ln(fx)
+    attn = O.physics_attention_forward(sd, xn, tree=tree, pos_override=t["pos"].cpu(), taps=taps, **okw)
+    assert rel_l2(t["S"], taps["S"]) < TOL
+    assert rel_l2(got.cpu() - fx, attn) < TOL          # the attention term alone (the residual would mask errors)
+    assert rel_l2(got, attn + fx) < TOL
+    # and against this library's own unfused composition (same kernels, only the fusion differs): the slice state always,
+    # the output when both runs built the same tree (a near-tie median may flip on a 1e-6 change of pos, DESIGN section 6)
+    S_fused, tree_fused = t["S"].clone(), t["tree_idx"].clone()
+    unf = m(ln_c(fx.cuda())) + fx.cuda()
+    assert rel_l2(m.last_taps["S"], S_fused) < 3e-4
+    if torch.equal(m.last_taps["tree_idx"], tree_fused):
+        assert rel_l2(got - fx.cuda(), unf - fx.cuda()) < 5e-4
+
+
+def test_patch_model_fused_blocks():
+    """patch_model(fuse_blocks=True) on a block with the reference's attribute names == the unfused block."""
+    import haet_b200 as hb
+
+    class Block(torch.nn.Module):   # attribute names of TransolverErwinBlock (HAETransolver_Irregular_Mesh.py:79-110)
+        def __init__(self):
+            super().__init__()
+            self.last_layer = False
+            self.ln_1 = torch.nn.LayerNorm(256)
+            self.Attn = hb.Physics_Attention_Irregular_Mesh(256, heads=8, dim_head=32, slice_num=32, mlp_ratio=2)
+            self.ln_2 = torch.nn.LayerNorm(256)
+            self.mlp = torch.nn.Sequential(torch.nn.Linear(256, 256), torch.nn.GELU(), torch.nn.Linear(256, 256))
+
+        def forward(self, fx):
+            fx = self.Attn(self.ln_1(fx)) + fx
+            return self.mlp(self.ln_2(fx)) + fx
+
+    torch.manual_seed(3)
+    blk = Block().cuda().eval()
+    fx = torch.randn(2, 900, 256, device="cuda")
+    with torch.no_grad():
+        want = blk(fx)
+        hb.patch_model(blk, fuse_blocks=True)
+        got = blk(fx)
+    assert rel_l2(got, want) < 2e-4
+
+
 def test_errors_are_loud():
     import haet_b200 as hb
     m = hb.Physics_Attention_Irregular_Mesh(64, heads=4, dim_head=16, slice_num=32, rotate=45)
