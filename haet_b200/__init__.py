@@ -2,7 +2,8 @@
 
 Public surface (mirrors the reference's ``models.PhysicsAttention`` and ``balltree`` modules):
     Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D, Physics_Attention_Structured_Mesh_3D
-    ErwinTransformer, build_balltree_with_rotations, build_balltree, patch_model, HostStream (host-resident meshes)
+    ErwinTransformer, build_balltree_with_rotations, build_balltree, patch_model, HostStream (host-resident meshes),
+    block_mlp / Physics_Attention_*.forward_block (the two halves of TransolverErwinBlock.forward, fused)
 All arithmetic runs in libhaet_b200.so (hand-written CUDA behind the C-ABI of include/haet_b200.h).
 """
 from ._lib import HaetError, lib  # noqa: F401
@@ -10,8 +11,8 @@ from .balltree import build_balltree, build_balltree_with_rotations  # noqa: F40
 from .erwin import ErwinTransformer  # noqa: F401
 from .host_stream import HostStream  # noqa: F401
 from .physics_attention import (Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D,  # noqa: F401
-                                Physics_Attention_Structured_Mesh_3D, from_reference, patch_model)
+                                Physics_Attention_Structured_Mesh_3D, block_mlp, from_reference, patch_model)
 
 __all__ = ["Physics_Attention_Irregular_Mesh", "Physics_Attention_Structured_Mesh_2D",
            "Physics_Attention_Structured_Mesh_3D", "ErwinTransformer", "build_balltree_with_rotations",
-           "build_balltree", "patch_model", "from_reference", "HostStream", "HaetError", "lib"]
+           "build_balltree", "patch_model", "block_mlp", "from_reference", "HostStream", "HaetError", "lib"]

@@ -267,6 +267,27 @@ int haet_deslice_out_res(const haet_layer_shape *s, const void *spill_d, const f
     return resid_d ? launch_add_rows(out_d, resid_d, s->B * s->N * (int64_t)s->dim, st) : HAET_OK;
 }
 
+int64_t haet_block_mlp_workspace_bytes(int64_t M, int32_t dim, int32_t hidden) {
+    if (M < 0 || !mlp_tc_supported(dim, hidden)) {
+        set_error("haet_block_mlp: unsupported dim=%d hidden=%d (dim 256, hidden a multiple of 256, tensor-core path)", dim, hidden);
+        return HAET_ENOSUP;
+    }
+    return mlp_tc_workspace_bytes(M, dim, hidden);
+}
+
+int haet_block_mlp(const float *x_d, int64_t M, int32_t dim, int32_t hidden, const float *ln_g_d, const float *ln_b_d,
+                   float ln_eps, const float *w1_d, const float *b1_d, const float *w2_d, const float *b2_d, float *out_d,
+                   void *workspace_d, void *stream) {
+    HAET_CHECK_ARG(M >= 0 && x_d && ln_g_d && ln_b_d && w1_d && b1_d && w2_d && b2_d && out_d && workspace_d, "haet_block_mlp: null argument");
+    HAET_CHECK_ARG(ln_eps > 0.f, "haet_block_mlp: eps must be positive");
+    HAET_CHECK_ARG(x_d != out_d, "haet_block_mlp: the output must not alias the input");
+    if (!mlp_tc_supported(dim, hidden)) {
+        set_error("haet_block_mlp: unsupported dim=%d hidden=%d (dim 256, hidden a multiple of 256, tensor-core path)", dim, hidden);
+        return HAET_ENOSUP;
+    }
+    return launch_mlp_tc(x_d, M, dim, hidden, ln_g_d, ln_b_d, ln_eps, w1_d, b1_d, w2_d, b2_d, out_d, workspace_d, (cudaStream_t)stream);
+}
+
 int64_t haet_layer_scratch_bytes(const haet_layer_shape *s, const haet_erwin_cfg *c) {
     LayerBuf b;
     if (check_shape(s) || carve_layer(s, c, nullptr, true, b)) return -1;

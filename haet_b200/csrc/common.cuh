@@ -93,6 +93,11 @@ bool ln_fused_supported(const haet_layer_shape *s);
 int64_t ln_fused_scratch_bytes(const haet_layer_shape *s);
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
                      uint8_t *xpi, float *scale, void *img, cudaStream_t st, const LnArgs *ln = nullptr);
+// block MLP on the CTA-pair kernel (gemm_tc.cu)
+bool mlp_tc_supported(int dim, int hidden);
+int64_t mlp_tc_workspace_bytes(int64_t M, int dim, int hidden);
+int launch_mlp_tc(const float *x, int64_t M, int dim, int hidden, const float *ln_g, const float *ln_b, float ln_eps,
+                  const float *w1, const float *b1, const float *w2, const float *b2, float *out, void *workspace, cudaStream_t st);
 // unfused helpers for the shapes / paths the fused kernels do not cover
 int launch_layernorm_rows(const float *x, const float *gamma, const float *beta, float eps, float *y, int64_t M, int K, cudaStream_t st);
 int launch_add_rows(float *y, const float *resid, int64_t n, cudaStream_t st);

@@ -65,7 +65,7 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
         }
         mbar_wait(&cb->w_full, 0);
     }
-    for (int i = threadIdx.x; i < G2_N; i += G2_THREADS) sBias[i] = bias[i];
+    for (int i = threadIdx.x; i < G2_N; i += G2_THREADS) sBias[i] = bias ? bias[i] : 0.f;
     if (EPI == EPI_IMG && threadIdx.x < 32) sWt[threadIdx.x] = ep.wt[threadIdx.x];
     // barriers initialised, TMEM allocated and W resident in BOTH CTAs before any remote arrive / pair MMA
     tc_fence_before();
@@ -81,6 +81,7 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
             // warp 0 bulk-copies one 32 KB stage per (tile, panel), warp 1 relays "landed here" to the leader's a_full.
             const uint8_t *Aimg = reinterpret_cast<const uint8_t *>(X);
             const int64_t total = my_tiles * panels;
+            const int a_panels = ep.a_panels ? ep.a_panels : panels;   // panels per tile of the image / first one this GEMM reads
             int stage = 0, phase = 0;
             if (warp == 0) {
                 if (lane == 0) {
@@ -90,7 +91,7 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
                         const int64_t t128 = (pair + ti * n_pairs) * 2 + rank;
                         mbar_wait(&cb->a_empty[stage], (uint32_t)(phase ^ 1));
                         mbar_arrive_expect_tx(&cb->a_land[stage], 2 * GT_PANEL_BYTES);
-                        bulk_g2s(sA + (size_t)stage * 2 * GT_PANEL_BYTES, Aimg + (size_t)(t128 * panels + p) * 2 * GT_PANEL_BYTES,
+                        bulk_g2s(sA + (size_t)stage * 2 * GT_PANEL_BYTES, Aimg + (size_t)(t128 * a_panels + ep.a_panel0 + p) * 2 * GT_PANEL_BYTES,
                                  2 * GT_PANEL_BYTES, &cb->a_land[stage]);
                         if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
                     }
@@ -219,6 +220,24 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     HAET_CHECK_ARG(gemm2_tc_supported(K, Nn), "gemm2_tc: unsupported K=%d Nn=%d", K, Nn);
     const int panels = K / GT_KP;
     const size_t smem = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + G2_CB_BYTES + sizeof(float) * (G2_N + 32);
+    if (epi == EPI_OPI) {   // block MLP fc1: ln_2 + GELU + operand image
+        HAET_CHECK_ARG(ep.ln_stats != nullptr && ep.wsum != nullptr && ep.opi != nullptr, "EPI_OPI needs the LayerNorm scratch and an image");
+        static bool set = false;
+        if (!set) {
+            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_OPI, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            set = true;
+        }
+        int dev0 = 0, sms0 = 148;
+        cudaGetDevice(&dev0);
+        cudaDeviceGetAttribute(&sms0, cudaDevAttrMultiProcessorCount, dev0);
+        const int64_t tiles = (M + 2 * GT_M - 1) / (2 * GT_M);
+        int np = sms0 / 2;
+        if (np > tiles) np = (int)tiles;
+        if (np < 1) np = 1;
+        gemm2_tc_kernel<EPI_OPI, true, false><<<2 * np, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, np, ep);
+        HAET_LAUNCHED();
+        return HAET_OK;
+    }
     const bool ln = epi == EPI_IMG && ep.ln_stats != nullptr;
     const bool res = epi == EPI_F32 && ep.resid != nullptr;
     const int variant = ln ? 2 : res ? 3 : epi;

@@ -23,7 +23,7 @@ namespace haet {
 using namespace tc;
 
 // W [Nn, K] fp32 -> image [Nn/128 halves][K/64 panels][hi, lo][128 rows x 128 B swizzled]
-__global__ void gemm_tc_pack_kernel(const float *__restrict__ w, int Nn, int K, uint8_t *__restrict__ img) {
+__global__ void gemm_tc_pack_kernel(const float *__restrict__ w, int Nn, int K, uint8_t *__restrict__ img, int ldw) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // one thread per 8 consecutive k (one 16-B chunk)
     const int chunks_per_row = K / 8;
     if (idx >= Nn * chunks_per_row) return;
@@ -33,15 +33,15 @@ __global__ void gemm_tc_pack_kernel(const float *__restrict__ w, int Nn, int K, 
     const int panels = K / GT_KP;
     __align__(16) __nv_bfloat16 hi[8], lo[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) split_bf16(w[(size_t)n * K + k0 + i], hi[i], lo[i]);
+    for (int i = 0; i < 8; ++i) split_bf16(w[(size_t)n * ldw + k0 + i], hi[i], lo[i]);
     uint8_t *base = img + ((size_t)half * panels + panel) * (2 * GT_PANEL_BYTES) + sw128_off(row, chunk);
     *reinterpret_cast<uint4 *>(base) = *reinterpret_cast<const uint4 *>(hi);
     *reinterpret_cast<uint4 *>(base + GT_PANEL_BYTES) = *reinterpret_cast<const uint4 *>(lo);
 }
 
-int launch_gemm_tc_pack(const float *w, int Nn, int K, uint8_t *img, cudaStream_t st) {
+int launch_gemm_tc_pack(const float *w, int Nn, int K, uint8_t *img, cudaStream_t st, int ldw) {
     const int chunks = Nn * (K / 8);
-    gemm_tc_pack_kernel<<<(chunks + 255) / 256, 256, 0, st>>>(w, Nn, K, img);
+    gemm_tc_pack_kernel<<<(chunks + 255) / 256, 256, 0, st>>>(w, Nn, K, img, ldw ? ldw : K);
     HAET_LAUNCHED();
     return HAET_OK;
 }
@@ -184,7 +184,7 @@ static int launch_gemm_impl(const float *x, const float *w, const float *bias, f
     if (M == 0) return HAET_OK;
     HAET_CHECK_ARG(gemm_tc_supported(K, Nn), "gemm_tc: unsupported K=%d Nn=%d", K, Nn);
     const int chunks = Nn * (K / 8);
-    gemm_tc_pack_kernel<<<(chunks + 255) / 256, 256, 0, st>>>(w, Nn, K, (uint8_t *)img);
+    gemm_tc_pack_kernel<<<(chunks + 255) / 256, 256, 0, st>>>(w, Nn, K, (uint8_t *)img, K);
     HAET_LAUNCHED();
     if (gemm2_tc_supported(K, Nn) && !getenv("HAET_GEMM_1CTA"))
         return launch_gemm2_tc(EPI, x, (const uint8_t *)img, bias, y, M, K, Nn, ep, st);
@@ -324,6 +324,48 @@ int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx,
         HAET_LAUNCHED();
     }
     return launch_gemm_impl<EPI_IMG>(x, wx, bx, nullptr, s->B * s->N, s->dim, s->heads * s->dim_head, img, ep, st);
+}
+
+// ---- block MLP: out = W2 . gelu(W1 . LayerNorm(x) + b1) + b2 + x  (HAETransolver_Irregular_Mesh.py:128,
+// models/components/mlp.py:67-96 with n_layers = 0), on the CTA-pair kernel, 256 hidden columns per launch:
+//   fc1 block j: ln_2 fused as in the in-projection, epilogue = GELU -> panels [4 j, 4 j + 4) of the operand image h
+//   fc2 block j: A = those panels (bulk-copied), out (+)= h_j . W2[:, 256 j : 256 j + 256]^T (+ b2 + x for j = 0, + out after)
+bool mlp_tc_supported(int dim, int hidden) {
+    return g_path == 0 && dim == 256 && hidden >= 256 && hidden % 256 == 0 && hidden <= 2048 && !getenv("HAET_GEMM_1CTA");
+}
+int64_t mlp_tc_workspace_bytes(int64_t M, int dim, int hidden) {
+    return align_up(opi_bytes(M, hidden), 256) + align_up(gemm_tc_image_bytes(dim, 256), 256) +
+           align_up((int64_t)(256 * dim + 2 * 256) * 4, 256) + align_up(M * (int64_t)sizeof(float2), 256);
+}
+int launch_mlp_tc(const float *x, int64_t M, int dim, int hidden, const float *ln_g, const float *ln_b, float ln_eps,
+                  const float *w1, const float *b1, const float *w2, const float *b2, float *out, void *workspace, cudaStream_t st) {
+    HAET_CHECK_ARG(mlp_tc_supported(dim, hidden), "block MLP: unsupported dim=%d hidden=%d (dim 256, hidden a multiple of 256)", dim, hidden);
+    if (M == 0) return HAET_OK;
+    char *p = (char *)workspace;
+    uint8_t *h = (uint8_t *)p;      p += align_up(opi_bytes(M, hidden), 256);
+    uint8_t *img = (uint8_t *)p;    p += align_up(gemm_tc_image_bytes(dim, 256), 256);
+    float *wf = (float *)p;         p += align_up((int64_t)(256 * dim + 2 * 256) * 4, 256);
+    float *bf = wf + 256 * dim, *wsum = bf + 256;
+    float2 *stats = (float2 *)p;
+    const int blocks = hidden / 256;
+    int rc;
+    for (int j = 0; j < blocks; ++j) {
+        ln_fold_kernel<<<256, 256, 0, st>>>(w1 + (size_t)j * 256 * dim, b1 + j * 256, ln_g, ln_b, dim, wf, bf, wsum);
+        HAET_LAUNCHED();
+        if ((rc = launch_gemm_tc_pack(wf, 256, dim, img, st))) return rc;
+        GemmEpi ep{};
+        ep.wsum = wsum; ep.ln_stats = stats; ep.ln_eps = ln_eps;
+        ep.opi = h; ep.opi_panels = hidden / 64; ep.opi_panel0 = 4 * j;
+        if ((rc = launch_gemm2_tc(EPI_OPI, x, img, bf, nullptr, M, dim, 256, ep, st))) return rc;
+    }
+    for (int j = 0; j < blocks; ++j) {
+        if ((rc = launch_gemm_tc_pack(w2 + j * 256, dim, 256, img, st, hidden))) return rc;
+        GemmEpi ep{};
+        ep.a_img = 1; ep.a_panels = hidden / 64; ep.a_panel0 = 4 * j;
+        ep.resid = j == 0 ? x : out;   // in place after the first block: every element is read, then written, by the same thread
+        if ((rc = launch_gemm2_tc(EPI_F32, reinterpret_cast<const float *>(h), img, j == 0 ? b2 : nullptr, out, M, 256, dim, ep, st))) return rc;
+    }
+    return HAET_OK;
 }
 
 }  // namespace haet

@@ -15,7 +15,7 @@ constexpr int GT_PANEL_BYTES = GT_M * 128;   // 16 KB: 128 rows x 128 B
 constexpr int GT_PROD = 256;       // producer threads (warps 0-7)
 constexpr int GT_THREADS = GT_PROD + 32 + 128;   // + MMA warp (8) + epilogue warps (9-12)
 constexpr int GT_LD = GT_M * GT_KP / 4 / GT_PROD;   // float4 per producer thread per panel (8)
-enum { EPI_F32 = 0, EPI_IMG = 1 };
+enum { EPI_F32 = 0, EPI_IMG = 1, EPI_OPI = 2 };   // EPI_OPI: GELU, then the NEXT GEMM's bf16 hi/lo operand image (block MLP)
 
 struct GemmEpi {   // EPI_IMG arguments
     uint8_t *img;
@@ -35,6 +35,12 @@ struct GemmEpi {   // EPI_IMG arguments
     const float *wsum;
     float2 *ln_stats;
     float ln_eps;
+    // block MLP (mlp.py:67-96): EPI_OPI writes gelu(y) as panels [opi_panel0, opi_panel0 + Nn / 64) of an operand image with
+    // opi_panels panels per 128-row tile; an a_img GEMM reads panels [a_panel0, a_panel0 + K / 64) of an image with a_panels
+    // (0: K / 64) panels per tile -- a hidden layer wider than 256 is produced / consumed 256 columns per launch
+    uint8_t *opi;
+    int opi_panels, opi_panel0;
+    int a_panels, a_panel0;
 };
 
 struct GemmSmem {   // control block placed after the tiles
@@ -222,6 +228,45 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
             *reinterpret_cast<float4 *>(y) = o0;
             *reinterpret_cast<float4 *>(y + 16) = o1;
         }
+    } else if (EPI == EPI_OPI) {
+        xpose_stage<0, 3>(r, lane);
+        xpose_stage<1, 4>(r, lane);
+        // register 8 i + c = row m0 + i, column col0 + 8 l4 + c: one 16-byte bf16 chunk (hi) + one (lo) of the next GEMM's A row
+        const float4 ba = *reinterpret_cast<const float4 *>(bias32 + 8 * l4), bb = *reinterpret_cast<const float4 *>(bias32 + 8 * l4 + 4);
+        const float bs[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+        float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (LN) {
+            const float4 sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
+            const float4 sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
+            su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
+        }
+        const int panel = ep.opi_panel0 + (col0 >> 6), cc = ((col0 & 63) >> 3) + l4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                float v[2];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const float a = __uint_as_float(r[8 * i + 2 * c + e]);
+                    const float y = LN ? fmaf(a, rs[i].x, fmaf(rs[i].y, su[2 * c + e], bs[2 * c + e])) : a + bs[2 * c + e];
+                    v[e] = 0.5f * y * (1.f + erff(y * 0.70710678118654752f));   // nn.GELU() (exact, mlp.py:8)
+                }
+                const __nv_bfloat162 hb = __floats2bfloat162_rn(v[0], v[1]);
+                const uint32_t ub = *reinterpret_cast<const uint32_t *>(&hb);
+                const __nv_bfloat162 lb = __floats2bfloat162_rn(v[0] - __uint_as_float(ub << 16), v[1] - __uint_as_float(ub & 0xffff0000u));
+                hi[c] = ub;
+                lo[c] = *reinterpret_cast<const uint32_t *>(&lb);
+            }
+            const int64_t m = m0 + i;
+            if (m < M) {
+                const int rr = (int)(m & 127);
+                uint8_t *blk = ep.opi + (((m >> 7) * ep.opi_panels + panel) * 2) * (int64_t)GT_PANEL_BYTES + tc::sw128_off(rr, cc);
+                *reinterpret_cast<uint4 *>(blk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4 *>(blk + GT_PANEL_BYTES) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+        }
     } else {
         xpose_stage<0, 3>(r, lane);
         xpose_stage<1, 4>(r, lane);
@@ -280,7 +325,7 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
 }
 
 // CTA-pair variant (Nn == 256): every x tile is loaded and split once; the pair shares W through cta_group::2 MMAs
-int launch_gemm_tc_pack(const float *w, int Nn, int K, uint8_t *img, cudaStream_t st);   // W [Nn, K] -> [half][panel][hi | lo] image
+int launch_gemm_tc_pack(const float *w, int Nn, int K, uint8_t *img, cudaStream_t st, int ldw = 0);   // W [Nn, K] (row stride ldw) -> [half][panel][hi | lo] image
 bool gemm2_tc_supported(int K, int Nn);
 int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *bias, float *y, int64_t M, int K, int Nn,
                     const GemmEpi &ep, cudaStream_t st);

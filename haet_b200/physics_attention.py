@@ -232,11 +232,42 @@ class Physics_Attention_Structured_Mesh_3D(_PhysicsAttentionBase):
                     enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed)
 
 
+@torch.no_grad()
+def block_mlp(fx: torch.Tensor, ln_2: nn.LayerNorm, mlp: nn.Module) -> torch.Tensor:
+    """``mlp(ln_2(fx)) + fx`` (models/HAETransolver_Irregular_Mesh.py:128) through haet_block_mlp when ``mlp`` is the
+    reference's ``MLP(n_layers=0, act='gelu')`` (models/components/mlp.py:67-96: ``linear_pre = Sequential(Linear, GELU)``,
+    ``linear_post = Linear``) of a supported shape (dim 256, hidden a multiple of 256); any other MLP runs as the
+    block's own torch modules on the GPU."""
+    pre, post = getattr(mlp, "linear_pre", None), getattr(mlp, "linear_post", None)
+    ok = (fx.is_cuda and isinstance(pre, nn.Sequential) and len(pre) == 2 and isinstance(pre[0], nn.Linear)
+          and isinstance(pre[1], nn.GELU) and getattr(pre[1], "approximate", "none") == "none"
+          and isinstance(post, nn.Linear) and len(getattr(mlp, "linears", ())) == 0
+          and ln_2.weight is not None and ln_2.bias is not None and pre[0].bias is not None and post.bias is not None)
+    if ok:
+        l = _lib.lib()
+        dim, hidden = pre[0].in_features, pre[0].out_features
+        M = fx.numel() // fx.shape[-1]
+        wsz = l.haet_block_mlp_workspace_bytes(M, dim, hidden) if fx.shape[-1] == dim == post.out_features else -1
+        if wsz >= 0:
+            in_dtype = fx.dtype
+            x = fx.contiguous().float()
+            f = lambda t: t.detach().float().contiguous()
+            w1, b1, w2, b2, g, b = f(pre[0].weight), f(pre[0].bias), f(post.weight), f(post.bias), f(ln_2.weight), f(ln_2.bias)
+            work = torch.empty(max(wsz, 4), dtype=torch.uint8, device=x.device)
+            out = torch.empty_like(x)
+            st = torch.cuda.current_stream(x.device).cuda_stream
+            _lib.check(l.haet_block_mlp(x.data_ptr(), M, dim, hidden, g.data_ptr(), b.data_ptr(), float(ln_2.eps),
+                                        w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(), out.data_ptr(),
+                                        work.data_ptr(), st))
+            return out if in_dtype == torch.float32 else out.to(in_dtype)
+    return mlp(ln_2(fx)) + fx
+
+
 def _fused_block_forward(self, fx):
-    """TransolverErwinBlock.forward (models/HAETransolver_Irregular_Mesh.py:112-135) with ``Attn(ln_1(fx)) + fx`` as
-    one fused call; the MLP half is the block's own modules, unchanged."""
+    """TransolverErwinBlock.forward (models/HAETransolver_Irregular_Mesh.py:112-135): ``Attn(ln_1(fx)) + fx`` as one
+    fused call, ``mlp(ln_2(fx)) + fx`` as the fused GEMM pair (block_mlp)."""
     fx = self.Attn.forward_block(fx, self.ln_1)
-    fx = self.mlp(self.ln_2(fx)) + fx
+    fx = block_mlp(fx, self.ln_2, self.mlp)
     if self.last_layer:
         return self.mlp2(self.ln_3(fx))
     return fx

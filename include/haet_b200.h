@@ -174,6 +174,19 @@ int haet_deslice_out_res(const haet_layer_shape *s, const void *spill_d, const f
                          const float *ws_d, const float *bs_d, const float *wt_d, float bt, const float *wo_d,
                          const float *bo_d, const float *resid_d, float *out_d, void *workspace_d, void *stream);
 
+/* ---- the MLP half of the block (new) ------------------------------------------
+ * out = W2 . gelu(W1 . LayerNorm(x) + b1) + b2 + x
+ * replaces  fx = self.mlp(self.ln_2(fx)) + fx  (models/HAETransolver_Irregular_Mesh.py:128) with
+ * MLP(n_layers=0, act=gelu) = Linear(dim, hidden) -> nn.GELU() -> Linear(hidden, dim)  (models/components/mlp.py:67-96).
+ * x_d / out_d [M, dim] fp32 (must not alias), w1_d [hidden, dim], w2_d [dim, hidden].  Two tensor-core GEMM passes: ln_2 is
+ * fused into the first (row statistics in its producers), GELU into its epilogue, which writes the hidden activations as
+ * the second GEMM's bf16 hi/lo operand image; bias and residual ride in the second epilogue.  Supported: dim == 256 and
+ * hidden a multiple of 256 (else HAET_ENOSUP; haet_block_mlp_workspace_bytes returns HAET_ENOSUP as well). */
+int64_t haet_block_mlp_workspace_bytes(int64_t M, int32_t dim, int32_t hidden);
+int haet_block_mlp(const float *x_d, int64_t M, int32_t dim, int32_t hidden, const float *ln_g_d, const float *ln_b_d,
+                   float ln_eps, const float *w1_d, const float *b1_d, const float *w2_d, const float *b2_d, float *out_d,
+                   void *workspace_d, void *stream);
+
 /* ---- whole layer on HOST buffers (copies inside) ------------------------------------
  * The call a non-torch host (C, C++, ctypes) makes: x_h / out_h are host pointers (pinned for
  * full speed); weights are device pointers prepared once.  Allocates nothing: scratch_d must

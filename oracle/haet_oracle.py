@@ -316,3 +316,19 @@ def physics_attention_forward(sd: Dict[str, torch.Tensor], x: torch.Tensor, *, h
         if N * G * B * heads <= (1 << 26):
             taps["W"] = W
     return out
+
+
+# ---- the rest of TransolverErwinBlock around the layer ------------------------------------------------
+def block_attention_half(sd, fx, ln_w, ln_b, ln_eps=1e-5, **layer_kw):
+    """models/HAETransolver_Irregular_Mesh.py:125  fx = self.Attn(self.ln_1(fx)) + fx"""
+    xn = F.layer_norm(fx.float(), (fx.shape[-1],), ln_w.float(), ln_b.float(), ln_eps)
+    return physics_attention_forward(sd, xn, **layer_kw) + fx.float()
+
+
+def block_mlp_half(fx, ln_w, ln_b, w1, b1, w2, b2, ln_eps=1e-5, dtype=torch.float64):
+    """models/HAETransolver_Irregular_Mesh.py:128  fx = self.mlp(self.ln_2(fx)) + fx  with
+    models/components/mlp.py:67-96 (n_layers = 0, res = False): linear_pre = Linear + nn.GELU() (exact erf), linear_post."""
+    x = fx.to(dtype)
+    xn = F.layer_norm(x, (x.shape[-1],), ln_w.to(dtype), ln_b.to(dtype), ln_eps)
+    h = F.gelu(F.linear(xn, w1.to(dtype), b1.to(dtype)))
+    return (F.linear(h, w2.to(dtype), b2.to(dtype)) + x).float()

@@ -260,6 +260,55 @@ def test_block_fusion_matches_oracle(variant, B, N, kw, shift):
         assert rel_l2(got - fx.cuda(), unf - fx.cuda()) < 5e-4
 
 
+class _RefMLP(torch.nn.Module):
+    """Attribute layout of the reference MLP (models/components/mlp.py:67-74) with n_layers = 0."""
+
+    def __init__(self, dim, hidden):
+        super().__init__()
+        self.linear_pre = torch.nn.Sequential(torch.nn.Linear(dim, hidden), torch.nn.GELU())
+        self.linear_post = torch.nn.Linear(hidden, dim)
+        self.linears = torch.nn.ModuleList()
+
+    def forward(self, x):
+        return self.linear_post(self.linear_pre(x))
+
+
+@pytest.mark.parametrize("B,N,hidden,shift", [(1, 4099, 256, 0.0), (3, 1111, 512, 1.5), (1, 130, 1024, -0.7), (2, 256, 256, 0.3)])
+def test_block_mlp_matches_oracle(B, N, hidden, shift):
+    """haet_block_mlp (ln_2 + Linear + GELU + Linear + residual as two tensor-core GEMM passes) against the fp64 oracle."""
+    import haet_b200 as hb
+    torch.manual_seed(N + hidden)
+    D = 256
+    ln = torch.nn.LayerNorm(D)
+    mlp = _RefMLP(D, hidden)
+    with torch.no_grad():
+        ln.weight.copy_(1 + 0.3 * torch.randn(D))
+        ln.bias.copy_(0.2 * torch.randn(D))
+        for p in mlp.parameters():
+            p.mul_(2.0)
+    fx = torch.randn(B, N, D) * (0.5 + 2 * torch.rand(B, N, 1)) + shift + 0.3 * torch.randn(1, 1, D)
+    want = O.block_mlp_half(fx, ln.weight, ln.bias, mlp.linear_pre[0].weight, mlp.linear_pre[0].bias,
+                            mlp.linear_post.weight, mlp.linear_post.bias, ln.eps)
+    n0 = hb.lib().haet_launch_count()
+    got = hb.block_mlp(fx.cuda(), ln.cuda(), mlp.cuda())
+    assert hb.lib().haet_launch_count() > n0, "the fused kernels did not run"
+    assert got.shape == fx.shape
+    assert rel_l2(got.cpu() - fx, want - fx) < 1e-4     # the MLP term alone: 3-term bf16 products, ~2^-17
+    assert rel_l2(got, want) < 1e-4
+
+
+def test_block_mlp_other_shapes_use_the_modules():
+    """Shapes the GEMM pair does not cover run as the block's own modules (still on the GPU) and say so via ENOSUP."""
+    import haet_b200 as hb
+    assert hb.lib().haet_block_mlp_workspace_bytes(1000, 128, 256) < 0
+    assert hb.lib().haet_block_mlp_workspace_bytes(1000, 256, 384) < 0
+    torch.manual_seed(0)
+    ln, mlp = torch.nn.LayerNorm(128).cuda(), _RefMLP(128, 256).cuda()
+    fx = torch.randn(2, 300, 128, device="cuda")
+    with torch.no_grad():
+        assert torch.equal(hb.block_mlp(fx, ln, mlp), mlp(ln(fx)) + fx)
+
+
 def test_patch_model_fused_blocks():
     """patch_model(fuse_blocks=True) on a block with the reference's attribute names == the unfused block."""
     import haet_b200 as hb
@@ -271,7 +320,7 @@ def test_patch_model_fused_blocks():
             self.ln_1 = torch.nn.LayerNorm(256)
             self.Attn = hb.Physics_Attention_Irregular_Mesh(256, heads=8, dim_head=32, slice_num=32, mlp_ratio=2)
             self.ln_2 = torch.nn.LayerNorm(256)
-            self.mlp = torch.nn.Sequential(torch.nn.Linear(256, 256), torch.nn.GELU(), torch.nn.Linear(256, 256))
+            self.mlp = _RefMLP(256, 512)
 
         def forward(self, fx):
             fx = self.Attn(self.ln_1(fx)) + fx
