@@ -240,6 +240,47 @@ def stage_times(m, x, iters=5):
     return acc
 
 
+def block_times(m, x, mlp_ratio, iters=10):
+    """The whole TransolverErwinBlock around the layer (HAETransolver_Irregular_Mesh.py:125-128), fused:
+    fx = Attn(ln_1(fx)) + fx via forward_block, fx = mlp(ln_2(fx)) + fx via haet_block_mlp.  Reported next to the layer line."""
+    import haet_b200 as hb
+    dev = x.device
+    D = x.shape[-1]
+
+    class RefMLP(torch.nn.Module):   # attribute layout of models/components/mlp.py:67-74 (n_layers = 0)
+        def __init__(self):
+            super().__init__()
+            self.linear_pre = torch.nn.Sequential(torch.nn.Linear(D, D * mlp_ratio), torch.nn.GELU())
+            self.linear_post = torch.nn.Linear(D * mlp_ratio, D)
+            self.linears = torch.nn.ModuleList()
+
+        def forward(self, v):
+            return self.linear_post(self.linear_pre(v))
+
+    torch.manual_seed(1)
+    ln1, ln2, mlp = torch.nn.LayerNorm(D).to(dev), torch.nn.LayerNorm(D).to(dev), RefMLP().to(dev)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    with torch.no_grad():
+        t_attn = timed(lambda: m.forward_block(x, ln1))
+        t_mlp = timed(lambda: hb.block_mlp(x, ln2, mlp))
+        t_block = timed(lambda: hb.block_mlp(m.forward_block(x, ln1), ln2, mlp))
+    return {"what": "TransolverErwinBlock forward, fused (ln_1 + layer + residual; ln_2 + MLP + residual), eager launches",
+            "mlp_ratio": mlp_ratio, "attention_half_ms": t_attn, "mlp_half_ms": t_mlp, "block_ms": t_block,
+            "points_per_s": x.shape[0] * x.shape[1] / (t_block * 1e-3)}
+
+
 def ncu_traffic():
     """DRAM bytes per launch of each kernel from the committed ncu --set full summary (profiles/), or {}."""
     p = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
@@ -411,6 +452,8 @@ def run_gpu_arm(args):
             "gpu_launches": int(launches), "roofline": roof,
             "layer_roofline": {"t_roof_ms": t_roof, "frac": t_roof / ms, "peak_source": pk["src"]},
             "stages_ms": stages}
+    if world == 1:
+        line["block"] = block_times(m, x, MLP_RATIO)
     if world == 1 and not args.no_cpu:
         sec, cores = cpu_layer_time(args.slices, args.cpu_points, 2, 1)
         line["cpu_baseline"] = {"value": args.cpu_points / sec, "unit": UNIT, "cores": cores, "kind": "port",

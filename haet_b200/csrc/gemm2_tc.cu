@@ -105,26 +105,10 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
                     __syncwarp();
                     if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
                 }
-            } else if (RES && warp == 2) {
-                // the residual rows of the NEXT tile are pulled into L2 while this tile is in the epilogue, so that the
-                // epilogue's loads are L2 hits (read from HBM they serialised the epilogue: 0.34 -> 0.81 ms)
-                auto pf = [&](int64_t ti) {
-                    const int64_t r0 = ((pair + ti * n_pairs) * 2 + rank) * (int64_t)GT_M;
-                    if (ti >= my_tiles || r0 >= M) return;
-                    const int64_t rows = M - r0 < GT_M ? M - r0 : GT_M;
-                    const char *src = reinterpret_cast<const char *>(ep.resid + r0 * G2_N);
-                    for (int64_t off = 0; off < rows * G2_N * 4; off += 32768)
-                        bulk_prefetch_l2(src + off, (uint32_t)(rows * G2_N * 4 - off < 32768 ? rows * G2_N * 4 - off : 32768));
-                };
-                if (lane == 0) {
-                    pf(0);
-                    for (int64_t it = 0; it < my_tiles; ++it) {
-                        mbar_wait(&cb->t_full[it & 1], (uint32_t)((it >> 1) & 1));
-                        pf(it + 1);
-                    }
-                }
-                __syncwarp();
             }
+            // (RES: pulling the next tile's residual rows into L2 from the idle warps -- bulk or per-line prefetch -- made them
+            // cross HBM 1.75 times, ncu dram__bytes_read 2.78 GB against 2.05 GB, and was slower than no prefetch: 0.58 against
+            // 0.50 ms.  What fixed the naive 0.81 ms was issuing the epilogue's residual loads before its transposes.)
         } else if (LN) {
             // fused ln_1: the producers see every element of their rows anyway; they leave (mean, rstd) per row for the epilogue
             auto row0 = [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; };

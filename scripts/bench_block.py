@@ -49,7 +49,33 @@ with torch.no_grad():
         stages[name + "_plain"] = timed(lambda: m(xn))
         stages[name + "_fused"] = timed(lambda: m.forward_block(fx, ln))
     l.haet_set_stage_mask(15)
+
+    # the MLP half: fx = mlp(ln_2(fx)) + fx with the reference's MLP layout (mlp.py:67-74), hidden = mlp_ratio * 256
+    class RefMLP(torch.nn.Module):
+        def __init__(self, dim, hidden):
+            super().__init__()
+            self.linear_pre = torch.nn.Sequential(torch.nn.Linear(dim, hidden), torch.nn.GELU())
+            self.linear_post = torch.nn.Linear(hidden, dim)
+            self.linears = torch.nn.ModuleList()
+
+        def forward(self, x):
+            return self.linear_post(self.linear_pre(x))
+
+    mlp_res = {}
+    for ratio in (1, 2):
+        mlp = RefMLP(256, 256 * ratio).cuda()
+        ln2 = torch.nn.LayerNorm(256).cuda()
+        t_torch = timed(lambda: mlp(ln2(fx)) + fx, n=5, warm=2)
+        t_ours = timed(lambda: hb.block_mlp(fx, ln2, mlp))
+        ra, rb = mlp(ln2(fx)), hb.block_mlp(fx, ln2, mlp) - fx
+        mlp_res[f"mlp_ratio_{ratio}"] = {"ms_torch_fp32": t_torch, "ms_fused": t_ours,
+                                         "rel_l2_mlp_term_vs_torch_fp32": float((rb - ra).double().norm() / ra.double().norm())}
+        t_block_torch = timed(lambda: (lambda y: mlp(ln2(y)) + y)(m(ln(fx)) + fx), n=5, warm=2)
+        t_block = timed(lambda: hb.block_mlp(m.forward_block(fx, ln), ln2, mlp))
+        mlp_res[f"mlp_ratio_{ratio}"].update({"ms_whole_block_unfused": t_block_torch, "ms_whole_block_fused": t_block,
+                                              "block_points_per_s_fused": N / (t_block * 1e-3)})
 print(json.dumps({"config": f"block attention half, N={N}, G={G}", "ms_layernorm_torch": t_ln, "ms_layer": t_layer,
                   "ms_residual_add_torch": t_add, "ms_unfused_total": t_unfused, "ms_fused_total": t_fused,
                   "points_per_s_unfused": N / (t_unfused * 1e-3), "points_per_s_fused": N / (t_fused * 1e-3),
-                  "rel_l2_attention_term_fused_vs_unfused": err, "stages_ms_incl_small_kernels": stages}))
+                  "rel_l2_attention_term_fused_vs_unfused": err, "stages_ms_incl_small_kernels": stages, "mlp_half": mlp_res,
+                  "torch_matmul_tf32": torch.backends.cuda.matmul.allow_tf32}))
