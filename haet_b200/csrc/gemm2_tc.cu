@@ -113,11 +113,10 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
             // fused ln_1: the producers see every element of their rows anyway; they leave (mean, rstd) per row for the epilogue
             auto row0 = [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; };
             LnStatsHook ln;
-            ln.stats = ep.ln_stats; ln.M = M; ln.K = K; ln.panels = panels; ln.eps = ep.ln_eps;
             gemm_produce(X, M, K, panels, my_tiles, sA, row0,
                          [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
                          [&](int st) { mbar_arrive_remote(full0 + 8u * st); }, ep.dbg,
-                         [&](const float4 (&v)[GT_LD], int64_t ti, int p) { ln.run(v, ti, p, row0); });
+                         [&](const float4 (&v)[GT_LD], int64_t item) { ln.run(v, item, panels, row0, ep, M, K); });
         } else
         gemm_produce(X, M, K, panels, my_tiles, sA,
                      [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; },
@@ -245,7 +244,7 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     if (n_pairs > n_ptiles) n_pairs = (int)n_ptiles;
     if (n_pairs < 1) n_pairs = 1;
     GemmEpi epd = ep;
-    if (const char *e = getenv("HAET_GEMM_DBG")) epd.dbg = atoi(e);
+    if (const char *e = getenv("HAET_GEMM_DBG")) epd.dbg |= atoi(e);
     if (ln) {
         HAET_CHECK_ARG(ep.wsum != nullptr, "fused LayerNorm needs wsum");
         gemm2_tc_kernel<EPI_IMG, true, false><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);

@@ -62,9 +62,9 @@ struct GemmSmem {   // control block placed after the tiles
 //   srcf(ti, p, i, row, c8) address of the 8 consecutive fp32 (32 B) of tile ti, k panel p, tile row `row`, 16-byte bf16
 //                  chunk c8 (i = which of the thread's 4 items), or nullptr for zeros (rows past M, conv padding)
 struct NoPanelHook {
-    __device__ __forceinline__ void operator()(const float4 (&)[8], int64_t, int) const {}
+    __device__ __forceinline__ void operator()(const float4 (&)[8], int64_t) const {}
 };
-//   hook(v, ti, p): sees the fp32 registers of (tile ti, panel p) right before they are split and stored (LayerNorm statistics)
+//   hook(v, it): sees the fp32 registers of item it = tile * panels + panel right before they are split and stored (LayerNorm statistics)
 template <class SrcFn, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
 __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uint8_t *sA, SrcFn srcf, WaitEmpty wait_empty,
                                                ArriveFull arrive_full, PanelHook hook = PanelHook()) {
@@ -88,11 +88,8 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
         }
     };
     int stage = 0, phase = 0;
-    int64_t s_ti = 0;   // (tile, panel) of the item being stored
-    int s_p = 0;
-    auto store = [&](const float4 (&v)[GT_LD]) {
-        hook(v, s_ti, s_p);
-        if (++s_p == panels) { s_p = 0; ++s_ti; }
+    auto store = [&](const float4 (&v)[GT_LD], int64_t item) {
+        hook(v, item);
         wait_empty(stage, phase ^ 1);
         uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
 #pragma unroll
@@ -121,10 +118,10 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
     load(0, va);
     load(1, vb);
     for (int64_t it = 0; it < total; it += 2) {
-        store(va);
+        store(va, it);
         load(it + 2, va);
         if (it + 1 < total) {
-            store(vb);
+            store(vb, it + 1);
             load(it + 3, vb);
         }
     }
@@ -147,13 +144,12 @@ __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_
 // floats (row i * 32 + tid / 8, chunk tid & 7) for i < 4: the 8 threads of a row reduce with 3 shuffles after the last
 // panel and lane (tid & 7) == 0 writes (mean, rstd) -- nn.LayerNorm: biased variance, eps inside the root.
 struct LnStatsHook {
-    float2 *stats;
-    int64_t M;
-    int K, panels;
-    float eps;
     float s1[4], s2[4];
+    // everything else comes from the kernel parameters (constant bank): no registers held across the load / store pipeline
     template <class Row0>
-    __device__ __forceinline__ void run(const float4 (&v)[8], int64_t ti, int p, Row0 row0) {
+    __device__ __forceinline__ void run(const float4 (&v)[8], int64_t item, int panels, Row0 row0, const GemmEpi &ep, int64_t M, int K) {
+        if (ep.dbg & 16) return;   // the statistics were written by ln_stats_kernel (launch_ln_stats)
+        const int p = (int)(item % panels);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             if (p == 0) { s1[i] = 0.f; s2[i] = 0.f; }
@@ -164,16 +160,18 @@ struct LnStatsHook {
         }
         if (p != panels - 1) return;
         const int tid = threadIdx.x;
+        const int64_t mrow = row0(item / panels) + (tid >> 3);
+        const float invK = 1.f / (float)K;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             float a = s1[i], b = s2[i];
 #pragma unroll
             for (int o = 1; o < 8; o <<= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
-            const int64_t m = row0(ti) + i * 32 + (tid >> 3);
+            const int64_t m = mrow + i * 32;
             if ((tid & 7) == 0 && m < M) {
-                const float mean = a / (float)K;
-                const float var = fmaxf(b / (float)K - mean * mean, 0.f);
-                stats[m] = make_float2(mean, rsqrtf(var + eps));
+                const float mean = a * invK;
+                const float var = fmaxf(fmaf(b, invK, -mean * mean), 0.f);
+                ep.ln_stats[m] = make_float2(mean, rsqrtf(var + ep.ln_eps));
             }
         }
         __threadfence_block();   // ordered before this thread's arrive on the stage barrier (the epilogue reads after t_full)
@@ -194,6 +192,14 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
                                                     const float *bias32, const float *wt32, float *Y, int ldy, int col0,
                                                     const GemmEpi &ep, const float2 *rs = nullptr) {
     const int l4 = lane & 3;
+    // LN: the chunk's wsum values come from global memory (L1 / L2): issued before the transposes so that their latency
+    // overlaps the shuffles (the same fix as the residual loads below)
+    float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (LN && EPI != EPI_F32) {
+        const float4 sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
+        const float4 sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
+        su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
+    }
     if (EPI == EPI_F32) {
         float4 q0[4], q1[4];
         if (RES) {
@@ -234,12 +240,6 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
         // register 8 i + c = row m0 + i, column col0 + 8 l4 + c: one 16-byte bf16 chunk (hi) + one (lo) of the next GEMM's A row
         const float4 ba = *reinterpret_cast<const float4 *>(bias32 + 8 * l4), bb = *reinterpret_cast<const float4 *>(bias32 + 8 * l4 + 4);
         const float bs[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-        float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (LN) {
-            const float4 sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
-            const float4 sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
-            su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
-        }
         const int panel = ep.opi_panel0 + (col0 >> 6), cc = ((col0 & 63) >> 3) + l4;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -275,12 +275,6 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
         const float4 wa = *reinterpret_cast<const float4 *>(wt32 + 8 * l4), wb = *reinterpret_cast<const float4 *>(wt32 + 8 * l4 + 4);
         const float bs[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
         const float ws[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
-        float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (LN) {
-            const float4 sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
-            const float4 sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
-            su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
-        }
         const int h = col0 >> 5;
         int64_t bi = bi0, n = n0;
 #pragma unroll

@@ -50,5 +50,34 @@ print(f"rank {rank}/{world}: exchange = {mode}, bit-equal to NCCL path = {bit_eq
 assert bit_equal and stream_equal
 print(f"rank {rank}/{world}: exchange = {mode}, rel_l2(sharded, single) = {err:.3e}, peer timeout = {px_err}", flush=True)
 assert err < 2e-4 and not px_err   # Erwin + deslice amplify the 1e-6 merge-order differences (north_star bar: 1e-3)
+# the fused block point-sharded: LayerNorm, residual and the MLP are row-local, so each rank runs
+# forward_block + block_mlp on its shard with the same single exchange; against the single-GPU fused block
+import haet_b200 as hb
+
+
+class RefMLP(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.linear_pre = torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.GELU())
+        self.linear_post = torch.nn.Linear(512, 256)
+        self.linears = torch.nn.ModuleList()
+
+    def forward(self, v):
+        return self.linear_post(self.linear_pre(v))
+
+
+torch.manual_seed(5)
+ln1, ln2, mlp = torch.nn.LayerNorm(256).to(dev), torch.nn.LayerNorm(256).to(dev), RefMLP().to(dev)
+fx = (torch.randn(1, N, 256, generator=g) * 1.5 + 0.3).to(dev)
+m.point_group = None
+with torch.no_grad():
+    full_b = hb.block_mlp(m.forward_block(fx, ln1), ln2, mlp)
+    m.point_group = dist.group.WORLD
+    m._px_key = None
+    out_b = hb.block_mlp(m.forward_block(fx[:, lo:hi].contiguous(), ln1), ln2, mlp)
+torch.cuda.synchronize()
+err_b = float((out_b - full_b[:, lo:hi]).norm() / full_b[:, lo:hi].norm())
+print(f"rank {rank}/{world}: fused block sharded vs single rel_l2 = {err_b:.3e}", flush=True)
+assert err_b < 2e-4
 dist.barrier()
 dist.destroy_process_group()
