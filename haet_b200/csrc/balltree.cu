@@ -13,6 +13,8 @@
 // Keys are the fp32 positions: the reference promotes them to fp64 before comparing
 // (balltree.pyx:542), which is exact and monotonic, so fp32 compares give the same order; the
 // max-spread test (balltree.h:52-62) subtracts in fp64 and is done in fp64 here.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace haet {
@@ -300,6 +302,10 @@ __global__ void __launch_bounds__(256) balltree_kernel(BallTreeArgs a) {
     const int tid = threadIdx.x;
     const int64_t tree = blockIdx.x;
     const int64_t row0 = tree * a.pts;
+    // blockIdx.y = role: the rotated partitions of the levels are independent of each other (each starts from the pooled
+    // rotated leaves, not from the previous level's permutation), so CTA (tree, r) rebuilds the (deterministic) main tree
+    // and then partitions only the levels lvl % gridDim.y == r; role 0 also writes the main tree.  0.111 -> see DESIGN
+    const int role = blockIdx.y, roles = gridDim.y;
 
     for (int i = tid; i < n * d; i += blockDim.x) P[i] = a.pos[row0 * d + i];
     for (int i = tid; i < n; i += blockDim.x) idx[i] = i;
@@ -313,9 +319,11 @@ __global__ void __launch_bounds__(256) balltree_kernel(BallTreeArgs a) {
         const bool pair = (e - s) >= 2;
         const int i0 = idx[s], i1 = pair ? idx[s + 1] : idx[s];
         leaf[2 * j] = i0; leaf[2 * j + 1] = i1;
-        const int64_t o = tree * a.slots + 2 * j;
-        a.tree_idx[o] = row0 + i0; a.tree_idx[o + 1] = row0 + i1;
-        a.tree_mask[o] = 1; a.tree_mask[o + 1] = pair ? 1 : 0;
+        if (role == 0) {
+            const int64_t o = tree * a.slots + 2 * j;
+            a.tree_idx[o] = row0 + i0; a.tree_idx[o + 1] = row0 + i1;
+            a.tree_mask[o] = 1; a.tree_mask[o + 1] = pair ? 1 : 0;
+        }
     }
     __syncthreads();
     if (!a.rotate) return;
@@ -332,15 +340,21 @@ __global__ void __launch_bounds__(256) balltree_kernel(BallTreeArgs a) {
     __syncthreads();
     int cur = slots;
     for (int lvl = 0; lvl < a.n_levels; ++lvl) {
-        for (int i = tid; i < cur; i += blockDim.x) idx[i] = i;
-        __syncthreads();
-        // number of levels that can still split anything: ranges shrink to <= 1 after ceil(log2 cur)
-        int lv = a.targets[lvl];
-        int maxlv = cur > 1 ? 32 - __clz(cur - 1) : 0;
-        if (lv > maxlv) lv = maxlv;
-        split_levels(rotA, idx, cur, d, lv, Apos, Bpos);
-        int64_t *out = a.rot_idx[lvl] + tree * cur;
-        for (int i = tid; i < cur; i += blockDim.x) out[i] = tree * cur + idx[i];
+        if (lvl % roles == role) {   // CTA-uniform
+            for (int i = tid; i < cur; i += blockDim.x) idx[i] = i;
+            __syncthreads();
+            // number of levels that can still split anything: ranges shrink to <= 1 after ceil(log2 cur)
+            int lv = a.targets[lvl];
+            int maxlv = cur > 1 ? 32 - __clz(cur - 1) : 0;
+            if (lv > maxlv) lv = maxlv;
+            split_levels(rotA, idx, cur, d, lv, Apos, Bpos);
+            int64_t *out = a.rot_idx[lvl] + tree * cur;
+            for (int i = tid; i < cur; i += blockDim.x) out[i] = tree * cur + idx[i];
+        }
+        if (lvl + 1 >= a.n_levels) break;
+        bool later = false;   // does this CTA still own a level after lvl?
+        for (int l2 = lvl + 1; l2 < a.n_levels; ++l2) later |= (l2 % roles == role);
+        if (!later) break;
         if (lvl < a.n_levels - 1) {
             const int s = a.strides[lvl];
             const int nn = cur / s;
@@ -416,7 +430,10 @@ extern "C" int haet_balltree_build(const float *pos_d, int64_t n_trees, int64_t 
         HAET_CUDA(cudaFuncSetAttribute(balltree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set = smem;
     }
-    balltree_kernel<<<(unsigned)n_trees, 256, smem, (cudaStream_t)stream>>>(a);
+    int roles = a.rotate ? n_levels : 1;   // one CTA per (tree, rotated level)
+    if (roles > 4) roles = 4;
+    if (getenv("HAET_TREE_ROLES")) { roles = atoi(getenv("HAET_TREE_ROLES")); if (roles < 1 || roles > n_levels) roles = 1; }
+    balltree_kernel<<<dim3((unsigned)n_trees, (unsigned)roles), 256, smem, (cudaStream_t)stream>>>(a);
     HAET_LAUNCHED();
     return HAET_OK;
 }
