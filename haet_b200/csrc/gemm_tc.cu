@@ -354,7 +354,7 @@ int launch_mlp_tc(const float *x, int64_t M, int dim, int hidden, const float *l
         HAET_LAUNCHED();
         if ((rc = launch_gemm_tc_pack(wf, 256, dim, img, st))) return rc;
         GemmEpi ep{};
-        ep.wsum = wsum; ep.ln_stats = stats; ep.ln_eps = ln_eps;
+        ep.wsum = wsum; ep.ln_stats = stats; ep.ln_eps = ln_eps; ep.ln_reuse = j > 0;
         ep.opi = h; ep.opi_panels = hidden / 64; ep.opi_panel0 = 4 * j;
         if ((rc = launch_gemm2_tc(EPI_OPI, x, img, bf, nullptr, M, dim, 256, ep, st))) return rc;
     }

@@ -35,6 +35,7 @@ struct GemmEpi {   // EPI_IMG arguments
     const float *wsum;
     float2 *ln_stats;
     float ln_eps;
+    int ln_reuse;   // ln_stats was filled by an earlier launch over the same X (later column blocks of the block MLP's fc1)
     // block MLP (mlp.py:67-96): EPI_OPI writes gelu(y) as panels [opi_panel0, opi_panel0 + Nn / 64) of an operand image with
     // opi_panels panels per 128-row tile; an a_img GEMM reads panels [a_panel0, a_panel0 + K / 64) of an image with a_panels
     // (0: K / 64) panels per tile -- a hidden layer wider than 256 is produced / consumed 256 columns per launch
@@ -148,7 +149,7 @@ struct LnStatsHook {
     // everything else comes from the kernel parameters (constant bank): no registers held across the load / store pipeline
     template <class Row0>
     __device__ __forceinline__ void run(const float4 (&v)[8], int64_t item, int panels, Row0 row0, const GemmEpi &ep, int64_t M, int K) {
-        if (ep.dbg & 16) return;   // the statistics were written by ln_stats_kernel (launch_ln_stats)
+        if ((ep.dbg & 16) || ep.ln_reuse) return;   // timing ablation / ln_stats already holds these rows' statistics
         const int p = (int)(item % panels);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
