@@ -113,10 +113,10 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
             // fused ln_1: the producers see every element of their rows anyway; they leave (mean, rstd) per row for the epilogue
             auto row0 = [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; };
             LnStatsHook ln;
-            gemm_produce(X, M, K, panels, my_tiles, sA, row0,
+            gemm_produce<int>(X, M, K, panels, my_tiles, sA, row0,
                          [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
                          [&](int st) { mbar_arrive_remote(full0 + 8u * st); }, ep.dbg,
-                         [&](const float4 (&v)[GT_LD], int64_t item) { ln.run(v, item, panels, row0, ep, M, K); });
+                         [&](const float4 (&v)[GT_LD], int item) { ln.run(v, item, panels, row0, ep, M, K); });
         } else
         gemm_produce(X, M, K, panels, my_tiles, sA,
                      [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; },
@@ -172,7 +172,7 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
             if (LN) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const float2 mr = m0 + i < M ? __ldcg(ep.ln_stats + m0 + i) : make_float2(0.f, 0.f);
+                    const float2 mr = (m0 + i < M && !(ep.dbg & 32)) ? __ldcg(ep.ln_stats + m0 + i) : make_float2(0.f, 1.f);
                     rs[i] = make_float2(mr.y, -mr.x * mr.y);
                 }
             }

@@ -66,15 +66,17 @@ struct NoPanelHook {
     __device__ __forceinline__ void operator()(const float4 (&)[8], int64_t) const {}
 };
 //   hook(v, it): sees the fp32 registers of item it = tile * panels + panel right before they are split and stored (LayerNorm statistics)
-template <class SrcFn, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
+//   Idx: type of the item counter.  int64_t is what the tuned plain kernels were measured with; the LN variants use int
+//   (a 64-bit division is a subroutine call and the extra live registers pushed them into 100-230 B of spills: 0.72 -> 0.60 ms)
+template <class Idx = int64_t, class SrcFn, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
 __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uint8_t *sA, SrcFn srcf, WaitEmpty wait_empty,
                                                ArriveFull arrive_full, PanelHook hook = PanelHook()) {
     using namespace tc;
     const int tid = threadIdx.x;
-    const int64_t total = my_tiles * panels;   // (tile, panel) items of this CTA, in order
-    auto load = [&](int64_t it, float4 (&v)[GT_LD]) {
+    const Idx total = (Idx)(my_tiles * panels);   // (tile, panel) items of this CTA, in order
+    auto load = [&](Idx it, float4 (&v)[GT_LD]) {
         if (it >= total) return;
-        const int64_t ti = it / panels;
+        const Idx ti = it / (Idx)panels;
         const int p = (int)(it - ti * panels);
 #pragma unroll
         for (int i = 0; i < GT_LD / 2; ++i) {   // 8 consecutive k (32 B) per item: one 16-B bf16 chunk of the row
@@ -89,7 +91,7 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
         }
     };
     int stage = 0, phase = 0;
-    auto store = [&](const float4 (&v)[GT_LD], int64_t item) {
+    auto store = [&](const float4 (&v)[GT_LD], Idx item) {
         hook(v, item);
         wait_empty(stage, phase ^ 1);
         uint8_t *hi_base = sA + (size_t)stage * 2 * GT_PANEL_BYTES;
@@ -118,7 +120,7 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
     float4 va[GT_LD], vb[GT_LD];
     load(0, va);
     load(1, vb);
-    for (int64_t it = 0; it < total; it += 2) {
+    for (Idx it = 0; it < total; it += 2) {
         store(va, it);
         load(it + 2, va);
         if (it + 1 < total) {
@@ -129,11 +131,11 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
 }
 
 // dense A: row m of X [M, K]
-template <class Row0, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
+template <class Idx = int64_t, class Row0, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
 __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_t M, int K, int panels, int64_t my_tiles,
                                              uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0,
                                              PanelHook hook = PanelHook()) {
-    gemm_produce_g(panels, my_tiles, sA,
+    gemm_produce_g<Idx>(panels, my_tiles, sA,
                    [&](int64_t ti, int p, int, int row, int c8) -> const float * {
                        const int64_t m = row0(ti) + row;
                        return (m < M && !(dbg & 2)) ? X + m * K + p * GT_KP + c8 * 8 : nullptr;
@@ -150,7 +152,8 @@ struct LnStatsHook {
     template <class Row0>
     __device__ __forceinline__ void run(const float4 (&v)[8], int64_t item, int panels, Row0 row0, const GemmEpi &ep, int64_t M, int K) {
         if ((ep.dbg & 16) || ep.ln_reuse) return;   // timing ablation / ln_stats already holds these rows' statistics
-        const int p = (int)(item % panels);
+        const unsigned it32 = (unsigned)item, ti32 = it32 / (unsigned)panels;   // 32-bit: a 64-bit division is a subroutine call
+        const int p = (int)(it32 - ti32 * (unsigned)panels);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             if (p == 0) { s1[i] = 0.f; s2[i] = 0.f; }
@@ -161,7 +164,7 @@ struct LnStatsHook {
         }
         if (p != panels - 1) return;
         const int tid = threadIdx.x;
-        const int64_t mrow = row0(item / panels) + (tid >> 3);
+        const int64_t mrow = row0((int64_t)ti32) + (tid >> 3);
         const float invK = 1.f / (float)K;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -196,7 +199,7 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
     // LN: the chunk's wsum values come from global memory (L1 / L2): issued before the transposes so that their latency
     // overlaps the shuffles (the same fix as the residual loads below)
     float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (LN && EPI != EPI_F32) {
+    if (LN && EPI != EPI_F32 && !(ep.dbg & 64)) {
         const float4 sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
         const float4 sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
         su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
