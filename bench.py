@@ -287,8 +287,8 @@ def ncu_traffic():
     if not os.path.exists(p):
         return {}
     d = json.load(open(p))
-    key = {"in_project": "gemm_tc_kernel<1>", "slice_pass1": "slice_tc_kernel", "deslice_pass2": "deslice_tc_kernel",
-           "to_out": "gemm_tc_kernel<0>"}
+    key = {"in_project": "gemm2_tc_kernel<1, 0, 0>", "slice_pass1": "slice_tc_kernel", "deslice_pass2": "deslice_tc_kernel",
+           "to_out": "gemm2_tc_kernel<0, 0, 0>"}
     return {k: d[v]["traffic_bytes"] for k, v in key.items() if v in d}
 
 

@@ -74,8 +74,25 @@ with torch.no_grad():
         t_block = timed(lambda: hb.block_mlp(m.forward_block(fx, ln), ln2, mlp))
         mlp_res[f"mlp_ratio_{ratio}"].update({"ms_whole_block_unfused": t_block_torch, "ms_whole_block_fused": t_block,
                                               "block_points_per_s_fused": N / (t_block * 1e-3)})
+    # an 8-block stack (BASELINE config 4 "full model": n_layers 8; without the model's preprocess MLP and output head,
+    # HAETransolver_Irregular_Mesh.py:297-336), every block with its own weights, fused path, mlp_ratio 2
+    blocks = []
+    for i in range(8):
+        torch.manual_seed(100 + i)
+        blocks.append((hb.Physics_Attention_Irregular_Mesh(256, heads=8, dim_head=32, slice_num=G, mlp_ratio=2).cuda().eval(),
+                       torch.nn.LayerNorm(256).cuda(), torch.nn.LayerNorm(256).cuda(), RefMLP(256, 512).cuda()))
+
+    def stack():
+        y = fx
+        for attn, l1, l2, mm in blocks:
+            y = hb.block_mlp(attn.forward_block(y, l1), l2, mm)
+        return y
+
+    t_stack = timed(stack, n=5, warm=2)
+    stack_res = {"blocks": 8, "ms": t_stack, "points_per_s": N / (t_stack * 1e-3), "finite": bool(torch.isfinite(stack()).all())}
+
 print(json.dumps({"config": f"block attention half, N={N}, G={G}", "ms_layernorm_torch": t_ln, "ms_layer": t_layer,
                   "ms_residual_add_torch": t_add, "ms_unfused_total": t_unfused, "ms_fused_total": t_fused,
                   "points_per_s_unfused": N / (t_unfused * 1e-3), "points_per_s_fused": N / (t_fused * 1e-3),
-                  "rel_l2_attention_term_fused_vs_unfused": err, "stages_ms_incl_small_kernels": stages, "mlp_half": mlp_res,
+                  "rel_l2_attention_term_fused_vs_unfused": err, "stages_ms_incl_small_kernels": stages, "mlp_half": mlp_res, "stack_of_8_blocks_fused": stack_res,
                   "torch_matmul_tf32": torch.backends.cuda.matmul.allow_tf32}))

@@ -309,6 +309,32 @@ def test_block_mlp_other_shapes_use_the_modules():
         assert torch.equal(hb.block_mlp(fx, ln, mlp), mlp(ln(fx)) + fx)
 
 
+def test_block_entry_points_fail_loudly():
+    """Bad arguments to the fused-block entry points are errors, never silent fallbacks."""
+    import haet_b200 as hb
+    from haet_b200 import _lib
+    l = hb.lib()
+    m = hb.Physics_Attention_Irregular_Mesh(256, heads=8, dim_head=32, slice_num=32, mlp_ratio=2).cuda().eval()
+    fx = torch.randn(1, 300, 256, device="cuda")
+    with pytest.raises(ValueError):
+        m.forward_block(fx, torch.nn.LayerNorm(128).cuda())                      # LayerNorm over another width
+    with pytest.raises(ValueError):
+        m.forward_block(fx, torch.nn.LayerNorm(256, elementwise_affine=False).cuda())
+    with pytest.raises(_lib.HaetError):
+        m.forward_block(fx.cpu(), torch.nn.LayerNorm(256))                       # no CPU path
+    x = torch.randn(256, 256, device="cuda")
+    w = torch.randn(256, 256, device="cuda")
+    v = torch.randn(256, device="cuda")
+    work = torch.empty(l.haet_block_mlp_workspace_bytes(256, 256, 256), dtype=torch.uint8, device="cuda")
+    args = lambda out, eps: (x.data_ptr(), 256, 256, 256, v.data_ptr(), v.data_ptr(), eps, w.data_ptr(), v.data_ptr(),
+                             w.data_ptr(), v.data_ptr(), out, work.data_ptr(), None)
+    assert l.haet_block_mlp(*args(x.data_ptr(), 1e-5)) == _lib.HAET_EINVAL        # output aliases the input
+    assert b"alias" in l.haet_last_error()
+    assert l.haet_block_mlp(*args(torch.empty_like(x).data_ptr(), 0.0)) == _lib.HAET_EINVAL   # eps <= 0
+    assert l.haet_block_mlp(x.data_ptr(), 256, 128, 256, v.data_ptr(), v.data_ptr(), 1e-5, w.data_ptr(), v.data_ptr(),
+                            w.data_ptr(), v.data_ptr(), torch.empty_like(x).data_ptr(), work.data_ptr(), None) == _lib.HAET_ENOSUP
+
+
 def test_patch_model_fused_blocks():
     """patch_model(fuse_blocks=True) on a block with the reference's attribute names == the unfused block."""
     import haet_b200 as hb
