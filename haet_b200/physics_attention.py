@@ -238,8 +238,10 @@ def block_mlp(fx: torch.Tensor, ln_2: nn.LayerNorm, mlp: nn.Module) -> torch.Ten
     reference's ``MLP(n_layers=0, act='gelu')`` (models/components/mlp.py:67-96: ``linear_pre = Sequential(Linear, GELU)``,
     ``linear_post = Linear``) of a supported shape (dim 256, hidden a multiple of 256); any other MLP runs as the
     block's own torch modules on the GPU."""
+    if not fx.is_cuda:
+        raise _lib.HaetError("haet_b200.block_mlp runs on CUDA tensors only (no CPU fallback)")
     pre, post = getattr(mlp, "linear_pre", None), getattr(mlp, "linear_post", None)
-    ok = (fx.is_cuda and isinstance(pre, nn.Sequential) and len(pre) == 2 and isinstance(pre[0], nn.Linear)
+    ok = (isinstance(pre, nn.Sequential) and len(pre) == 2 and isinstance(pre[0], nn.Linear)
           and isinstance(pre[1], nn.GELU) and getattr(pre[1], "approximate", "none") == "none"
           and isinstance(post, nn.Linear) and len(getattr(mlp, "linears", ())) == 0
           and ln_2.weight is not None and ln_2.bias is not None and pre[0].bias is not None and post.bias is not None)

@@ -322,6 +322,8 @@ def test_block_entry_points_fail_loudly():
         m.forward_block(fx, torch.nn.LayerNorm(256, elementwise_affine=False).cuda())
     with pytest.raises(_lib.HaetError):
         m.forward_block(fx.cpu(), torch.nn.LayerNorm(256))                       # no CPU path
+    with pytest.raises(_lib.HaetError):
+        hb.block_mlp(fx.cpu(), torch.nn.LayerNorm(256), _RefMLP(256, 256))           # no CPU path
     x = torch.randn(256, 256, device="cuda")
     w = torch.randn(256, 256, device="cuda")
     v = torch.randn(256, device="cuda")
