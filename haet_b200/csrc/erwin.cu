@@ -9,6 +9,8 @@
 // the -- possibly rotated -- sequence), so a block is ONE kernel with one CTA per ball: the ball's
 // tokens are gathered through the permutation into shared memory, RMSNorm -> PE -> qkv -> attention
 // -> proj -> RMSNorm -> SwiGLU all run there, and the result is scattered back in place.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -184,15 +186,20 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restri
     uint64_t *wbar = reinterpret_cast<uint64_t *>(sm);   // sm[0..3]
     float *wsm = sm + 4;                                  // [w_n]
     const float *wts = wts_g;
+    // programmatic dependent launch (run_blocks sets the attribute): the NEXT kernel of the stream may start now -- its CTAs
+    // land on the idle SMs (64 balls on 148 SMs) and stage their weights while this one computes
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (w_n) {
         if (threadIdx.x == 0) {
             tc::mbar_init(wbar, 1);
             tc::fence_barrier_init();
             tc::mbar_arrive_expect_tx(wbar, (uint32_t)w_n * 4u);
-            tc::bulk_g2s(wsm, wts_g + w_lo, (uint32_t)w_n * 4u, wbar);
+            tc::bulk_g2s(wsm, wts_g + w_lo, (uint32_t)w_n * 4u, wbar);   // weights are constants: no dependency on the previous kernel
         }
         wts = wsm - w_lo;
     }
+    // everything below reads what the previous kernel of the stream wrote (tokens, positions, permutations)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     float *xs = wsm + w_n;             // [bs][ld]   residual stream
     float *us = xs + bs * ld;          // [bs][ld]   normed / attention output
     float *qkv = us + bs * ld;         // [bs][ldq]
@@ -351,6 +358,28 @@ __global__ void erwin_unpool_kernel(const float *__restrict__ xp, const float *_
     xc[t] = fmaf(xc[t] + acc, wts[w.scale + c], wts[w.shift + c]);
 }
 
+// Launch with the programmatic-stream-serialization attribute: the kernel may be scheduled while its predecessor in the
+// stream is still running; it executes griddepcontrol.wait before it reads anything the predecessor wrote, which blocks
+// until the predecessor has completed and flushed its writes.  Used for the block kernels only, whose prologue (staging
+// 42-166 KB of weights) is independent of the predecessor: Erwin 0.168 -> 0.155 ms.  On the small gather / pool / unpool /
+// scatter kernels (nothing to do before the wait) it was slower (layer 2.41 -> 2.44 ms) and was dropped.
+// Works under CUDA-graph capture (programmatic dependency edges).  HAET_NO_PDL=1 turns the attribute off.
+template <class... KArgs, class... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    static const int off = getenv("HAET_NO_PDL") ? 1 : 0;
+    at[0].val.programmaticStreamSerializationAllowed = off ? 0 : 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---- host walker: the packed-weight order (mirrored by haet_b200/erwin_pack.py) ------------
 struct Walker {
     int64_t off = 0;
@@ -443,7 +472,8 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
         const int64_t *perm = (rotate && (k & 1)) ? rot : nullptr;
         if (rotate && (k & 1)) HAET_CHECK_ARG(rot != nullptr, "tree_idx_rot must be provided for rotation");
         if (n == 0) continue;
-        erwin_block_kernel<<<(unsigned)(n / bs), EB_THREADS, smem, st>>>(x, pos, perm, wts, bw, bs, dim, heads, hidden, d, bw.norm1, (int)w_n);
+        HAET_CUDA(launch_pdl(erwin_block_kernel, dim3((unsigned)(n / bs)), dim3(EB_THREADS), smem, st, x, pos, perm, wts, bw, bs, dim, heads,
+                             hidden, d, (int)bw.norm1, (int)w_n));
         HAET_LAUNCHED();
     }
     return HAET_OK;
