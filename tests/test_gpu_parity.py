@@ -309,6 +309,36 @@ def test_block_mlp_other_shapes_use_the_modules():
         assert torch.equal(hb.block_mlp(fx, ln, mlp), mlp(ln(fx)) + fx)
 
 
+@pytest.mark.parametrize("M,hidden", [(130, 256), (3333, 512), (257, 1024)])
+def test_block_mlp_stays_inside_its_buffers(M, hidden):
+    """Canaries around the output and the workspace of haet_block_mlp (ragged M: last 128-row tile and last pair tile partly
+    empty) -- compute-sanitizer is not available on the GPU pool, so the bounds are checked this way."""
+    import haet_b200 as hb
+    l = hb.lib()
+    torch.manual_seed(M)
+    dev = "cuda"
+    D, PAD = 256, 1 << 16
+    x = torch.randn(M, D, device=dev)
+    g, b = torch.rand(D, device=dev) + 0.5, torch.randn(D, device=dev) * 0.1
+    w1, b1 = torch.randn(hidden, D, device=dev) / 16, torch.randn(hidden, device=dev) * 0.1
+    w2, b2 = torch.randn(D, hidden, device=dev) / 16, torch.randn(D, device=dev) * 0.1
+    wsz = l.haet_block_mlp_workspace_bytes(M, D, hidden)
+    assert wsz > 0
+    big_out = torch.full((M * D + 2 * PAD,), 12345.0, device=dev)
+    big_work = torch.full((wsz + 2 * PAD,), 0x5A, dtype=torch.uint8, device=dev)
+    out, work = big_out[PAD:PAD + M * D], big_work[PAD:PAD + wsz]
+    x_before = x.clone()
+    from haet_b200 import _lib
+    _lib.check(l.haet_block_mlp(x.data_ptr(), M, D, hidden, g.data_ptr(), b.data_ptr(), 1e-5, w1.data_ptr(), b1.data_ptr(),
+                                w2.data_ptr(), b2.data_ptr(), out.data_ptr(), work.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert bool((big_out[:PAD] == 12345.0).all()) and bool((big_out[PAD + M * D:] == 12345.0).all())
+    assert bool((big_work[:PAD] == 0x5A).all()) and bool((big_work[PAD + wsz:] == 0x5A).all())
+    assert torch.equal(x, x_before)                                              # inputs are never written
+    want = O.block_mlp_half(x.cpu(), g.cpu(), b.cpu(), w1.cpu(), b1.cpu(), w2.cpu(), b2.cpu(), 1e-5)
+    assert rel_l2(out.view(M, D), want) < 1e-4
+
+
 def test_block_entry_points_fail_loudly():
     """Bad arguments to the fused-block entry points are errors, never silent fallbacks."""
     import haet_b200 as hb
