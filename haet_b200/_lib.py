@@ -74,6 +74,7 @@ SYMBOLS = {
     "haet_launch_count": (C.c_int64, []),
     "haet_set_path": (C.c_int, [C.c_int]),
     "haet_set_stage_mask": (C.c_int, [C.c_int]),
+    "haet_set_raise_threshold": (C.c_int, [C.c_float]),
     "haet_debug_gemm": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P]),
 }
 

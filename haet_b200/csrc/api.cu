@@ -1,5 +1,6 @@
 // extern "C" entry points of libhaet_b200.so (see include/haet_b200.h).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -7,9 +8,34 @@
 namespace haet {
 
 static thread_local char g_err[512] = "";
-int64_t g_launches = 0;
-int g_path = 0;
-int g_stage_mask = 15;
+std::atomic<int64_t> g_launches{0};
+
+static bool env_on(const char *name) {
+    const char *e = getenv(name);
+    return e != nullptr && e[0] != '\0' && !(e[0] == '0' && e[1] == '\0');
+}
+const Options &options() {   // function-local static: initialised once, thread-safe
+    static const Options o = [] {
+        Options v{};
+        v.gemm_1cta = env_on("HAET_GEMM_1CTA");
+        v.no_opi = env_on("HAET_NO_OPI");
+        v.no_ln_fuse = env_on("HAET_NO_LN_FUSE");
+        v.conv_simt = env_on("HAET_CONV_SIMT");
+        v.conv_nh1 = env_on("HAET_CONV_NH1");
+        v.no_pdl = env_on("HAET_NO_PDL");
+        const char *e = getenv("HAET_TREE_ROLES");
+        v.tree_roles = e ? atoi(e) : 0;
+        e = getenv("HAET_PEER_TIMEOUT_S");
+        v.peer_timeout_s = e ? atof(e) : 60.0;
+        if (!(v.peer_timeout_s > 0.0)) v.peer_timeout_s = 60.0;
+        return v;
+    }();
+    return o;
+}
+Hooks &hooks() {
+    static thread_local Hooks h;
+    return h;
+}
 
 void set_error(const char *fmt, ...) {
     va_list ap;
@@ -53,7 +79,7 @@ static int64_t deslice_o_bytes(const haet_layer_shape *s) {   // fp32 o, or its 
 }
 // pass 2 writes o as the to_out GEMM's operand image when both run on the tensor-core path
 static bool out_opi(const haet_layer_shape *s) {
-    return g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && gemm_opi_supported(s->heads * s->dim_head, s->dim);
+    return hooks().path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && gemm_opi_supported(s->heads * s->dim_head, s->dim);
 }
 static int64_t deslice_ws_bytes(const haet_layer_shape *s) { return deslice_o_bytes(s) + image_bytes(s); }
 static int64_t slice_parts_bytes(const haet_layer_shape *s) {
@@ -103,7 +129,7 @@ extern "C" {
 
 int haet_version(void) { return 1; }
 const char *haet_last_error(void) { return g_err; }
-int64_t haet_launch_count(void) { return g_launches; }
+int64_t haet_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 int haet_device_check(void) {
     int dev = 0;
@@ -131,24 +157,29 @@ int64_t haet_partial_floats(const haet_layer_shape *s) {
 int64_t haet_slice_workspace_bytes(const haet_layer_shape *s) { return slice_parts_bytes(s) + image_bytes(s); }
 int haet_set_path(int path) {
     if (path != 0 && path != 1) { set_error("path must be 0 (tensor core) or 1 (fp32 SIMT)"); return HAET_EINVAL; }
-    g_path = path;
+    hooks().path = path;
     return HAET_OK;
 }
 int haet_set_stage_mask(int mask) {
     if (mask < 0 || mask > 15) { set_error("stage mask must be in 0..15"); return HAET_EINVAL; }
-    g_stage_mask = mask;
+    hooks().stage_mask = mask;
+    return HAET_OK;
+}
+int haet_set_raise_threshold(float log2_units) {
+    if (!(log2_units >= 0.f) || log2_units > 15.f) { set_error("raise threshold must be in [0, 15] log2 units (0 = default)"); return HAET_EINVAL; }
+    hooks().st_raise = log2_units;
     return HAET_OK;
 }
 int haet_debug_gemm(const float *x_d, const float *w_d, const float *bias_d, float *y_d, int64_t M, int32_t K, int32_t Nn,
                     void *img_d, void *stream) {
-    if (g_path == 0 && gemm_tc_supported(K, Nn)) return launch_gemm_tc(x_d, w_d, bias_d, y_d, M, K, Nn, img_d, (cudaStream_t)stream);
+    if (hooks().path == 0 && gemm_tc_supported(K, Nn)) return launch_gemm_tc(x_d, w_d, bias_d, y_d, M, K, Nn, img_d, (cudaStream_t)stream);
     return launch_linear(x_d, w_d, bias_d, y_d, M, K, Nn, (cudaStream_t)stream);
 }
 int64_t haet_deslice_workspace_bytes(const haet_layer_shape *s) { return deslice_ws_bytes(s); }
 
 // ln_1 scratch behind the regular slice workspace: folded weights + row statistics when the in-projection fuses it, else normalised x
 static bool ln_fuse_ok(const haet_layer_shape *s) {
-    return g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && s->conv_nd == 0 &&
+    return hooks().path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && s->conv_nd == 0 &&
            gemm_tc_supported(s->dim, s->heads * s->dim_head) && ln_fused_supported(s);
 }
 int64_t haet_slice_ln_workspace_bytes(const haet_layer_shape *s) {
@@ -189,31 +220,31 @@ static int slice_reduce_impl(const haet_layer_shape *s, const float *x_d, const 
     float *parts = (float *)workspace_d;
     void *img = (char *)workspace_d + slice_parts_bytes(s);
     const int inner = s->heads * s->dim_head;
-    const bool tc = g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s);
+    const bool tc = hooks().path == 0 && slice_tc_supported(s) && deslice_tc_supported(s);
     LnArgs ln{ln_g_d, ln_b_d, ln_eps, (char *)workspace_d + align_up(haet_slice_workspace_bytes(s), 256)};
     const bool ln_fused = ln_g_d != nullptr && ln_fuse_ok(s);
-    if (ln_g_d != nullptr && !ln_fused && (g_stage_mask & 1)) {
+    if (ln_g_d != nullptr && !ln_fused && (hooks().stage_mask & 1)) {
         // shapes / paths without the fused kernel: normalise into the scratch, then the regular route
         float *xn = (float *)ln.scratch;
         if ((rc = launch_layernorm_rows(x_d, ln_g_d, ln_b_d, ln_eps, xn, s->B * s->N, s->dim, st))) return rc;
         x_d = xn;
     }
-    if (!(g_stage_mask & 1)) {
+    if (!(hooks().stage_mask & 1)) {
         rc = HAET_OK;   // bench hook: the spill of an earlier call is reused
     } else if (tc && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner)) {
         // Linear front-end: the GEMM epilogue writes the operand image directly
         rc = launch_inproj_tc(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st, ln_fused ? &ln : nullptr);
     } else {
-        if (g_path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
+        if (hooks().path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
             rc = launch_gemm_tc(x_d, wx_d, bx_d, xp, s->B * s->N, s->dim, inner, img, st);
-        else if (g_path == 0 && s->conv_nd != 0 && conv_tc_supported(s) && !getenv("HAET_CONV_SIMT"))
+        else if (hooks().path == 0 && s->conv_nd != 0 && conv_tc_supported(s) && !options().conv_simt)
             rc = launch_conv_tc(s, x_d, wx_d, bx_d, xp, img, st);   // Conv2d / Conv3d front-end: implicit GEMM on tcgen05
         else
             rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
         if (!rc && tc) rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st);
     }
     if (rc) return rc;
-    if (!(g_stage_mask & 2)) return HAET_OK;
+    if (!(hooks().stage_mask & 2)) return HAET_OK;
     if (tc) {
         if ((rc = launch_slice_tc(s, sv.img, sv.scale, ws_d, bs_d, parts, st))) return rc;
         return launch_slice_merge(s, parts, slice_tc_chunks(s), partial_d, nullptr, nullptr, st);
@@ -248,20 +279,20 @@ int haet_deslice_out_res(const haet_layer_shape *s, const void *spill_d, const f
     cudaStream_t st = (cudaStream_t)stream;
     float *o = (float *)workspace_d;
     const SpillView sv = spill_view(s, const_cast<void *>(spill_d));
-    if (!(g_stage_mask & 4))
+    if (!(hooks().stage_mask & 4))
         rc = HAET_OK;
-    else if (g_path == 0 && slice_tc_supported(s) && deslice_tc_supported(s))
+    else if (hooks().path == 0 && slice_tc_supported(s) && deslice_tc_supported(s))
         rc = launch_deslice_tc(s, sv.img, sv.scale, lse2_d, states_d, ws_d, bs_d, o, out_opi(s) ? 1 : 0, st);
     else
         rc = launch_deslice(s, sv.xp, lse2_d, states_d, ws_d, bs_d, wt_d, bt, o, st);
     if (rc) return rc;
-    if (!(g_stage_mask & 8)) return HAET_OK;
+    if (!(hooks().stage_mask & 8)) return HAET_OK;
     const int inner = s->heads * s->dim_head;
     HAET_CHECK_ARG(resid_d != out_d || resid_d == nullptr, "the residual must not alias the output");
     if (out_opi(s))
         return launch_gemm_tc_opi((const uint8_t *)o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim,
                                   (char *)workspace_d + deslice_o_bytes(s), st, resid_d);
-    if (g_path == 0 && gemm_tc_supported(inner, s->dim))
+    if (hooks().path == 0 && gemm_tc_supported(inner, s->dim))
         return launch_gemm_tc(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, (char *)workspace_d + deslice_o_bytes(s), st, resid_d);
     if ((rc = launch_linear(o, wo_d, bo_d, out_d, s->B * s->N, inner, s->dim, st))) return rc;
     return resid_d ? launch_add_rows(out_d, resid_d, s->B * s->N * (int64_t)s->dim, st) : HAET_OK;

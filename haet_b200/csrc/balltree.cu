@@ -425,14 +425,10 @@ extern "C" int haet_balltree_build(const float *pos_d, int64_t n_trees, int64_t 
         a.R[6] = (float)(-s); a.R[7] = (float)(s * c); a.R[8] = (float)(c * c);
     }
     const size_t smem = (size_t)a.slots * d * 3 * sizeof(float) + (size_t)a.slots * 4 * sizeof(int);
-    static size_t smem_set = 0;
-    if (smem > 48 * 1024 && smem > smem_set) {
-        HAET_CUDA(cudaFuncSetAttribute(balltree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
-    }
+    if (smem > 48 * 1024) HAET_DYN_SMEM(balltree_kernel, smem);
     int roles = a.rotate ? n_levels : 1;   // one CTA per (tree, rotated level)
     if (roles > 4) roles = 4;
-    if (getenv("HAET_TREE_ROLES")) { roles = atoi(getenv("HAET_TREE_ROLES")); if (roles < 1 || roles > n_levels) roles = 1; }
+    if (options().tree_roles > 0) { roles = options().tree_roles; if (roles > n_levels) roles = 1; }
     balltree_kernel<<<dim3((unsigned)n_trees, (unsigned)roles), 256, smem, (cudaStream_t)stream>>>(a);
     HAET_LAUNCHED();
     return HAET_OK;

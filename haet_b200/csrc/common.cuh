@@ -5,12 +5,44 @@
 #include <stdio.h>
 #include <math.h>
 
+#include <atomic>
+
 #include "../../include/haet_b200.h"
 
 namespace haet {
 
 void set_error(const char *fmt, ...);
-extern int64_t g_launches;
+extern std::atomic<int64_t> g_launches;   // haet_launch_count()
+
+// Ablation switches ("environment switches"): read from the environment ONCE, when the library is first used,
+// and immutable afterwards, so that a *_bytes() query and the launch that follows always agree.
+struct Options {
+    bool gemm_1cta, no_opi, no_ln_fuse, conv_simt, conv_nh1, no_pdl;
+    int tree_roles;          // 0: one CTA per rotated level
+    double peer_timeout_s;
+};
+const Options &options();
+// Test / bench hooks (haet_set_path, haet_set_stage_mask, haet_set_raise_threshold): THREAD-LOCAL, so a caller that never
+// touches them is never affected by another thread that does -- the entry points themselves keep no mutable state.
+struct Hooks {
+    int path = 0;            // 0: tensor-core kernels where supported; 1: fp32 SIMT kernels everywhere
+    int stage_mask = 15;
+    float st_raise = 0.f;    // 0: default lazy-max threshold of pass 1
+};
+Hooks &hooks();
+
+// Opt a kernel in to `bytes` of dynamic shared memory.  The attribute is per device, so the cache is too (a second GPU in the
+// same process gets its own opt-in); a race between two threads only repeats the (idempotent) call.
+#define HAET_DYN_SMEM(kernel, bytes)                                                                          \
+    do {                                                                                                      \
+        static std::atomic<size_t> done_[64];                                                                 \
+        int dev_ = 0;                                                                                         \
+        HAET_CUDA(cudaGetDevice(&dev_));                                                                      \
+        if ((size_t)(bytes) > done_[dev_ & 63].load(std::memory_order_relaxed)) {                             \
+            HAET_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            done_[dev_ & 63].store((size_t)(bytes), std::memory_order_relaxed);                               \
+        }                                                                                                     \
+    } while (0)
 
 #define HAET_CHECK_ARG(cond, ...)            \
     do {                                     \
@@ -32,7 +64,7 @@ extern int64_t g_launches;
 // after a kernel launch: count it and surface launch-configuration errors
 #define HAET_LAUNCHED()                      \
     do {                                     \
-        ++haet::g_launches;                  \
+        haet::g_launches.fetch_add(1, std::memory_order_relaxed); \
         HAET_CUDA(cudaGetLastError());       \
     } while (0)
 
@@ -113,7 +145,6 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
 bool deslice_tc_supported(const haet_layer_shape *s);
 int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
                       const float *states, const float *ws, const float *bs, float *o, int o_image, cudaStream_t st);
-extern int g_path;   // 0: tensor-core kernels where supported; 1: fp32 SIMT kernels everywhere
 int64_t slice_chunks(const haet_layer_shape *s);
 int launch_slice_partial(const haet_layer_shape *s, const float *xp, const float *ws, const float *bs,
                          const float *wt, float bt, float *chunk_parts, cudaStream_t st);

@@ -208,14 +208,10 @@ int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, c
     const int64_t M = s->B * s->N;
     if (M == 0) return HAET_OK;
     if (int rc = launch_gemm_tc_pack(wx, inner, K, (uint8_t *)img, st)) return rc;
-    const int nh = (inner % (2 * GT_N) == 0 && !getenv("HAET_CONV_NH1")) ? 2 : 1;
+    const int nh = (inner % (2 * GT_N) == 0 && !options().conv_nh1) ? 2 : 1;
     const size_t smem = 1024 + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES + (size_t)(nh == 2 ? 2 : GT_STAGES) * nh * 2 * GT_PANEL_BYTES + sizeof(ConvSmem);
-    static bool attr[3] = {false, false, false};
-    if (!attr[nh]) {
-        if (nh == 2) HAET_CUDA(cudaFuncSetAttribute(conv_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        else HAET_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr[nh] = true;
-    }
+    if (nh == 2) HAET_DYN_SMEM(conv_tc_kernel<2>, smem);
+    else HAET_DYN_SMEM(conv_tc_kernel<1>, smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

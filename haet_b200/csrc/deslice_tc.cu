@@ -9,6 +9,9 @@
 //   softmax warps: P = 2^(D * s_n - lse2_g + 14) -> TMEM as packed fp16 (the bias bc_g rides in MMA1 as an extra K step; W <= 1, so
 //        2^14 W keeps 11 bits down to W = 2^-28 -- same mantissa as tf32 -- and the epilogue multiplies by 2^-14)
 //   MMA2 (kind::f16, A = P from TMEM, B = S'_h as MN-major fp16 rows): O[n, c] += sum_g P[n, g] S'[g, c]
+//        (S'_h is scaled by a per-(b, h) power of two so that its largest magnitude sits in [2^13, 2^14): the single fp16 term
+//        then keeps 2^-12 relative precision whatever the range of the Erwin output -- no overflow above 65504, no flush
+//        of small rows -- and the epilogue multiplies the scale back out)
 // CTA = (b, h, chunk of points): the Ws and S'_h operand images are built once and stay resident; the x_proj
 // head slice streams through a 4-stage ring of bulk copies; O is double-buffered in TMEM and stored by 4 epilogue warps.
 #include <cuda_fp16.h>
@@ -36,6 +39,8 @@ struct DesliceCtl {
     uint64_t d_full[DT_NBUF], p_full[DT_NBUF], p_free[DT_NBUF];
     uint64_t o_full[2], o_empty[2];
     uint32_t tmem_base;
+    float red[20];       // block reduction of max |S'_h| (one slot per warp)
+    float o_scale;       // 2^-DT_PSHIFT / (the power-of-two scale applied to S'_h)
 };
 
 // TMEM columns: O accumulators [issuer][buffer] x 32 at 0..127, D / P buffers [stream][3] x 64 at 128..511
@@ -78,6 +83,27 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         __syncwarp();
         tmem_alloc<512>(&ctl->tmem_base);
     }
+    // power-of-two scale of S'_h: 2^(14 - e) with max |S'_h| in [2^(e-1), 2^e)
+    {
+        float amax = 0.f;
+        const float *sp = states + (size_t)bh * G * DT_C;
+        for (int idx = threadIdx.x; idx < G * DT_C; idx += DT_THREADS) amax = fmaxf(amax, fabsf(sp[idx]));
+#pragma unroll
+        for (int o2 = 16; o2; o2 >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o2));
+        if (lane == 0) ctl->red[threadIdx.x >> 5] = amax;
+    }
+    __syncthreads();
+    float v_scale = 1.f;
+    {
+        float amax = 0.f;
+#pragma unroll
+        for (int w2 = 0; w2 < DT_THREADS / 32; ++w2) amax = fmaxf(amax, ctl->red[w2]);
+        int e = 14;
+        if (amax > 0.f && amax <= 3.0e38f) frexpf(amax, &e);   // amax = f 2^e, f in [0.5, 1); zero / inf / NaN states: no scaling
+        e = e < -90 ? -90 : e;
+        v_scale = ldexpf(1.f, 14 - e);
+        if (threadIdx.x == 0) ctl->o_scale = ldexpf(1.f, e - 14 - (int)DT_PSHIFT);
+    }
     // resident operand images: Ws rows [hi | lo] and S'_h rows (fp16), per-column constants
     for (int idx = threadIdx.x; idx < g_pad * 4; idx += DT_THREADS) {
         const int g = idx >> 2, ck = idx & 3;
@@ -89,7 +115,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             hi[i] = __float2half_rn(v);
             lo[i] = __float2half_rn(v - __half2float(hi[i]));
             const float s = g < G ? states[((size_t)bh * G + g) * DT_C + ck * 8 + i] : 0.f;
-            sv[i] = __float2half_rn(s);
+            sv[i] = __float2half_rn(s * v_scale);
         }
         *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(hi);
         *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck + 4)) = *reinterpret_cast<const uint4 *>(lo);
@@ -122,6 +148,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     if (warp >= 12 && warp < 16) {
         // =========================== O epilogue: TMEM -> global ===========================
         const int r = threadIdx.x - 384;   // row of the tile == TMEM lane
+        const float o_scale = ctl->o_scale;
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
         float *dst = o + ((int64_t)b * N) * inner + h * DT_C;
         for (int te = 0; te < n_tiles; ++te) {
@@ -135,7 +162,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 tmem_ld32(tmem_base + lane_base + (uint32_t)(2 + ob) * DT_C, v1);
                 tmem_wait_ld();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint((__uint_as_float(v[i]) + __uint_as_float(v1[i])) * 6.103515625e-05f);   // 2^-DT_PSHIFT
+                for (int i = 0; i < 32; ++i) v[i] = __float_as_uint((__uint_as_float(v[i]) + __uint_as_float(v1[i])) * o_scale);   // 2^-DT_PSHIFT / scale of S'
             }
             tc_fence_before();
             mbar_arrive(&ctl->o_empty[ob]);
@@ -316,11 +343,7 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const int g_pad = dt_gpad(s->slice_num);
     const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
                         sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-        HAET_CUDA(cudaFuncSetAttribute(deslice_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
-    }
+    HAET_DYN_SMEM(deslice_tc_kernel, smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -373,14 +373,13 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    static const int off = getenv("HAET_NO_PDL") ? 1 : 0;
-    at[0].val.programmaticStreamSerializationAllowed = off ? 0 : 1;
+    at[0].val.programmaticStreamSerializationAllowed = options().no_pdl ? 0 : 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
-// ---- host walker: the packed-weight order (mirrored by haet_b200/erwin_pack.py) ------------
+// ---- host walker: the packed-weight order (mirrored by ErwinTransformer.packed_weights in haet_b200/erwin.py) ------------
 struct Walker {
     int64_t off = 0;
     int take(int64_t n) { int64_t o = off; off += (n + 3) / 4 * 4; return (int)o; }
@@ -461,11 +460,7 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
     HAET_CHECK_ARG(smem_act <= 200 * 1024, "ball of %d tokens x dim %d does not fit shared memory", bs, dim);
     if (smem_act + (size_t)w_n * 4 > 220 * 1024 || ((dim | hidden) & 3)) w_n = 0;
     const size_t smem = smem_act + (size_t)w_n * 4;
-    static size_t smem_set = 0;
-    if (smem > 48 * 1024 && smem > smem_set) {
-        HAET_CUDA(cudaFuncSetAttribute(erwin_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
-    }
+    if (smem > 48 * 1024) HAET_DYN_SMEM(erwin_block_kernel, smem);
     const bool rotate = c->rotate > 0 && depth > 1;   // layers.py:74-91
     for (int k = 0; k < depth; ++k) {
         BlockW bw = wk.block(dim, hidden, d);

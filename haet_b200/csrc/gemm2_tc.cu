@@ -205,11 +205,7 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     const size_t smem = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + G2_CB_BYTES + sizeof(float) * (G2_N + 32);
     if (epi == EPI_OPI) {   // block MLP fc1: ln_2 + GELU + operand image
         HAET_CHECK_ARG(ep.ln_stats != nullptr && ep.wsum != nullptr && ep.opi != nullptr, "EPI_OPI needs the LayerNorm scratch and an image");
-        static bool set = false;
-        if (!set) {
-            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_OPI, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            set = true;
-        }
+        HAET_DYN_SMEM((gemm2_tc_kernel<EPI_OPI, true, false>), smem);
         int dev0 = 0, sms0 = 148;
         cudaGetDevice(&dev0);
         cudaDeviceGetAttribute(&sms0, cudaDevAttrMultiProcessorCount, dev0);
@@ -223,19 +219,14 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     }
     const bool ln = epi == EPI_IMG && ep.ln_stats != nullptr;
     const bool res = epi == EPI_F32 && ep.resid != nullptr;
-    const int variant = ln ? 2 : res ? 3 : epi;
-    static size_t smem_set[4] = {0, 0, 0, 0};
-    if (smem > smem_set[variant]) {
-        if (ln)
-            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_IMG, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        else if (res)
-            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_F32, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        else if (epi == EPI_IMG)
-            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_IMG, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        else
-            HAET_CUDA(cudaFuncSetAttribute(gemm2_tc_kernel<EPI_F32, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set[variant] = smem;
-    }
+    if (ln)
+        HAET_DYN_SMEM((gemm2_tc_kernel<EPI_IMG, true, false>), smem);
+    else if (res)
+        HAET_DYN_SMEM((gemm2_tc_kernel<EPI_F32, false, true>), smem);
+    else if (epi == EPI_IMG)
+        HAET_DYN_SMEM((gemm2_tc_kernel<EPI_IMG, false, false>), smem);
+    else
+        HAET_DYN_SMEM((gemm2_tc_kernel<EPI_F32, false, false>), smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -244,7 +235,9 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     if (n_pairs > n_ptiles) n_pairs = (int)n_ptiles;
     if (n_pairs < 1) n_pairs = 1;
     GemmEpi epd = ep;
+#ifdef HAET_DEV_HOOKS   // timing ablations (results are garbage): never compiled into the shipped library
     if (const char *e = getenv("HAET_GEMM_DBG")) epd.dbg |= atoi(e);
+#endif
     if (ln) {
         HAET_CHECK_ARG(ep.wsum != nullptr, "fused LayerNorm needs wsum");
         gemm2_tc_kernel<EPI_IMG, true, false><<<2 * n_pairs, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, n_pairs, epd);

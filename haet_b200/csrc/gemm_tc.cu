@@ -166,15 +166,11 @@ bool gemm_tc_supported(int K, int Nn) { return K % GT_KP == 0 && K >= GT_KP && K
 
 int64_t gemm_tc_image_bytes(int K, int Nn) { return (int64_t)Nn * K * 2 * 2; }
 
-static int sm_count() {
-    static int n = 0;
-    if (!n) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
-    }
-    return n;
+static int sm_count() {   // of the CURRENT device (no process-wide cache: devices may differ)
+    int dev = 0, n = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n > 0 ? n : 148;
 }
 
 // img: scratch of gemm_tc_image_bytes(K, Nn) bytes (the packed weights; rebuilt each call, ~2 us)
@@ -186,15 +182,11 @@ static int launch_gemm_impl(const float *x, const float *w, const float *bias, f
     const int chunks = Nn * (K / 8);
     gemm_tc_pack_kernel<<<(chunks + 255) / 256, 256, 0, st>>>(w, Nn, K, (uint8_t *)img, K);
     HAET_LAUNCHED();
-    if (gemm2_tc_supported(K, Nn) && !getenv("HAET_GEMM_1CTA"))
+    if (gemm2_tc_supported(K, Nn) && !options().gemm_1cta)
         return launch_gemm2_tc(EPI, x, (const uint8_t *)img, bias, y, M, K, Nn, ep, st);
     const int panels = K / GT_KP, n_halves = Nn / GT_N;
     const size_t smem = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + sizeof(GemmSmem);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-        HAET_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
-    }
+    HAET_DYN_SMEM(gemm_tc_kernel<EPI>, smem);
     const int64_t n_tiles = (M + GT_M - 1) / GT_M;
     int n_workers = sm_count() / n_halves;
     if (n_workers < 1) n_workers = 1;
@@ -213,7 +205,7 @@ int launch_gemm_tc(const float *x, const float *w, const float *bias, float *y, 
 }
 
 // to_out with A given as the operand image pass 2 wrote (common.cuh: OPI); only the CTA-pair kernel reads it
-bool gemm_opi_supported(int K, int Nn) { return gemm2_tc_supported(K, Nn) && !getenv("HAET_GEMM_1CTA") && !getenv("HAET_NO_OPI"); }
+bool gemm_opi_supported(int K, int Nn) { return gemm2_tc_supported(K, Nn) && !options().gemm_1cta && !options().no_opi; }
 int launch_gemm_tc_opi(const uint8_t *a_img, const float *w, const float *bias, float *y, int64_t M, int K, int Nn, void *img,
                        cudaStream_t st, const float *resid) {
     HAET_CHECK_ARG(gemm_opi_supported(K, Nn), "gemm_tc_opi: unsupported K=%d Nn=%d", K, Nn);
@@ -252,8 +244,8 @@ __global__ void ln_fold_kernel(const float *__restrict__ w, const float *__restr
 
 bool ln_fused_supported(const haet_layer_shape *s) {
     const int inner = s->heads * s->dim_head;
-    return g_path == 0 && s->conv_nd == 0 && s->dim_head == 32 && gemm2_tc_supported(s->dim, inner) && !getenv("HAET_GEMM_1CTA") &&
-           !getenv("HAET_NO_LN_FUSE");
+    return hooks().path == 0 && s->conv_nd == 0 && s->dim_head == 32 && gemm2_tc_supported(s->dim, inner) && !options().gemm_1cta &&
+           !options().no_ln_fuse;
 }
 static int64_t ln_fold_floats(const haet_layer_shape *s) {
     const int64_t inner = s->heads * s->dim_head;
@@ -331,7 +323,7 @@ int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx,
 //   fc1 block j: ln_2 fused as in the in-projection, epilogue = GELU -> panels [4 j, 4 j + 4) of the operand image h
 //   fc2 block j: A = those panels (bulk-copied), out (+)= h_j . W2[:, 256 j : 256 j + 256]^T (+ b2 + x for j = 0, + out after)
 bool mlp_tc_supported(int dim, int hidden) {
-    return g_path == 0 && dim == 256 && hidden >= 256 && hidden % 256 == 0 && hidden <= 2048 && !getenv("HAET_GEMM_1CTA");
+    return hooks().path == 0 && dim == 256 && hidden >= 256 && hidden % 256 == 0 && hidden <= 2048 && !options().gemm_1cta;
 }
 int64_t mlp_tc_workspace_bytes(int64_t M, int dim, int hidden) {
     return align_up(opi_bytes(M, hidden), 256) + align_up(gemm_tc_image_bytes(dim, 256), 256) +

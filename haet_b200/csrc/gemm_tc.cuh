@@ -295,6 +295,9 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
                     v0 = __uint_as_float(r[8 * i + 2 * c]) + bs[2 * c];
                     v1 = __uint_as_float(r[8 * i + 2 * c + 1]) + bs[2 * c + 1];
                 }
+                // the image is fp16 hi + lo: saturate at the largest finite half instead of storing (inf, -inf) -> NaN logits
+                v0 = fminf(fmaxf(v0, -65504.f), 65504.f);
+                v1 = fminf(fmaxf(v1, -65504.f), 65504.f);
                 d = fmaf(v0, ws[2 * c], d);
                 d = fmaf(v1, ws[2 * c + 1], d);
                 const __half2 hh = __floats2half2_rn(v0, v1);

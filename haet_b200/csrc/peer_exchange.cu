@@ -139,11 +139,7 @@ int haet_peer_exchange(const haet_layer_shape *s, void *const *peer_bufs, int32_
     int blocks = (int)((n / 4 + PX_THREADS - 1) / PX_THREADS);
     if (blocks > 64) blocks = 64;   // all co-resident: the flag of step 1 is published by the last block to arrive
     if (blocks < 1) blocks = 1;
-    static const unsigned long long timeout_ns = [] {
-        const char *e = getenv("HAET_PEER_TIMEOUT_S");
-        const double sec = e && atof(e) > 0 ? atof(e) : 60.0;
-        return (unsigned long long)(sec * 1e9);
-    }();
+    const unsigned long long timeout_ns = (unsigned long long)(options().peer_timeout_s * 1e9);
     peer_exchange_kernel<<<blocks, PX_THREADS, 0, (cudaStream_t)stream>>>(pp, rank, world, n, partial_d, gathered_d,
                                                                           (uint32_t *)state_d, timeout_ns);
     HAET_LAUNCHED();

@@ -9,8 +9,10 @@
 //   MMA1 (kind::f16, 3-term fp16 split = fp32-class logits; precision_study.py), tile read K-major:
 //        D[g, n] = Ws[g,:] . x_proj[n,:]          M = 128 slices, N = 64 points, K' = 96
 //   softmax warps (thread = slice row g): t = D * s_n - m_run (the bias bc_g enters D through one extra K step), P = 2^t, l += P, P -> TMEM as packed fp16.
-//        m_run is a LAZY running max: it is only raised when a tile exceeds it by 2^8 (P stays inside fp16),
-//        so the TMEM accumulator rescale is off the common path.
+//        m_run is a LAZY running reference: it starts ST_HEAD = 7 log2 units BELOW the first tile's max and is only raised
+//        when a tile exceeds it by 2^15 (P stays inside fp16), so the TMEM accumulator rescale is off the common path.
+//        The 7 units of head room put the fp16 flush-to-zero point of P at 2^-31 of the largest weight seen: whatever
+//        l (fp32, unrounded p) still counts and S (fp16 P) has lost is then < N_chunk 2^-31 of the column's mass.
 //   MMA2 (kind::f16, A = P from TMEM, B = the hi half of the tile read MN-major: 32 columns):
 //        S[g, c] += sum_n P[g,n] hi[n,c]      M = 128, N = 32, K = 64   (hi carries x_proj to 2^-12: ample for S)
 // Warp roles: 4 softmax warpgroups (4 warps per scheduler hide the TMEM / MUFU latencies), 1 loader warp (bulk copies),
@@ -33,7 +35,8 @@ constexpr int ST_MAX_GB = 4;        // up to 512 slices
 constexpr int ST_TILE_BYTES = ST_TILE * 128;   // one operand tile: 64 rows x 128 B
 constexpr int ST_SCOLS = 32;        // TMEM columns of one warpgroup's accumulator (P . hi; the fp16 hi half carries x_proj to 2^-12)
 constexpr int ST_NBUF = 3;          // D / P buffers per issue stream
-constexpr float ST_RAISE = 8.0f;    // lazy-max threshold (log2 units): P <= 2^8 fits fp16
+constexpr float ST_RAISE = 15.0f;   // lazy-max threshold (log2 units): P <= 2^15 fits fp16
+constexpr float ST_HEAD = 7.0f;     // a (re)set reference sits this far below the max that caused it
 
 struct SliceCtl {
     uint64_t b_full[ST_STAGES], b_empty[ST_STAGES];
@@ -256,11 +259,11 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                         tmax = fmaxf(tmax, __uint_as_float(r[c]));
                     }
                 }
-                // lazy running max: the very first half fixes it, later ones raise it only past 2^raise_thr
+                // lazy running reference: the very first half fixes it (max - ST_HEAD), later ones raise it only past 2^raise_thr
                 const bool first = (i == 0 && hh == 0);
                 const bool need = first || tmax > raise_thr;
                 if (ragged || __any_sync(0xffffffffu, need)) {   // warp-uniform (ragged is per tile)
-                    const float delta = need ? tmax : 0.f;   // m_new = m_run + delta
+                    const float delta = need ? tmax - ST_HEAD : 0.f;   // m_new = m_run + delta: the new max maps to 2^ST_HEAD
                     const float sc = first ? 0.f : fast_ex2(-delta);
                     m_run += delta;
                     l_run *= sc;
@@ -362,14 +365,9 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
     const int n_gb = (s->slice_num + ST_GB - 1) / ST_GB;
     const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-        HAET_CUDA(cudaFuncSetAttribute(slice_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
-    }
+    HAET_DYN_SMEM(slice_tc_kernel, smem);
     const int64_t chunk_pts = slice_tc_chunk_pts(s);
-    const char *env = getenv("HAET_ST_RAISE");   // test hook: force the accumulator-rescale path
-    const float raise_thr = env ? (float)atof(env) : ST_RAISE;
+    const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : ST_RAISE;   // haet_set_raise_threshold: tests force the accumulator-rescale path
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads));
     slice_tc_kernel<<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
                                                      s->slice_num, chunk_pts, raise_thr, chunk_parts);

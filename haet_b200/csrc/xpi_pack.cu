@@ -9,7 +9,7 @@ namespace haet {
 
 bool spill_needs_xp(const haet_layer_shape *s) {
     const int inner = s->heads * s->dim_head;
-    return g_path != 0 || s->conv_nd != 0 || !slice_tc_supported(s) || !deslice_tc_supported(s) ||
+    return hooks().path != 0 || s->conv_nd != 0 || !slice_tc_supported(s) || !deslice_tc_supported(s) ||
            !gemm_tc_supported(s->dim, inner);
 }
 
@@ -44,7 +44,9 @@ __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__
 #pragma unroll
         for (int j = 0; j < 4; ++j) {   // chunk j: channels 8j .. 8j+7
             const float4 a = __ldg(src + 2 * j), c = __ldg(src + 2 * j + 1);
-            const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+            float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = fminf(fmaxf(v[i], -65504.f), 65504.f);   // fp16 hi + lo image: saturate, never (inf, -inf)
             uint32_t hi[4], lo[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {

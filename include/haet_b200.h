@@ -106,7 +106,9 @@ int64_t haet_balltree_slots(int64_t n_trees, int64_t pts);
  * ws_d     in_project_slice.weight [G, C];  bs_d [G];  wt_d ada_temp_linear.weight [C]; bt scalar
  * spill_d  haet_spill_bytes() bytes (projected points kept for the deslice pass)
  * partial_d haet_partial_floats() floats: this rank's un-normalised slice state in the
- *          base-2 log domain: m2 = max_n z*log2e, l = sum_n 2^(z2-m2), S = sum_n 2^(z2-m2) x_proj
+ *          base-2 log domain: m2 = a reference exponent (<= max_n z*log2e), l = sum_n 2^(z2-m2), S = sum_n 2^(z2-m2) x_proj
+ * Numeric range: the tensor-core path keeps x_proj as fp16 hi + lo (relative 2^-22 for |x_proj| in [2^-3, 65504]); values
+ * beyond +-65504 SATURATE (they never become inf / NaN) and values below 2^-14 keep an absolute precision of 2^-25.
  */
 int haet_slice_reduce(const haet_layer_shape *s, const float *x_d, const float *wx_d, const float *bx_d,
                       const float *ws_d, const float *bs_d, const float *wt_d, float bt,
@@ -154,7 +156,7 @@ int haet_balltree_build(const float *pos_d, int64_t n_trees, int64_t pts, int32_
 
 /* ---- Erwin over the slice tokens (erwin_flash.py:138-195, eval-mode BatchNorm) -------
  * x_d [T, c_hidden[0]], pos_d [T, d]; tree from haet_balltree_build (n_slots entries);
- * weights_d: packed fp32 parameters in the order documented in haet_b200/erwin_pack.py;
+ * weights_d: packed fp32 parameters in the order documented in haet_b200/erwin.py (pack order) / csrc/erwin.cu (Walker);
  * out_d [T, c_hidden[0]] in the original token order (erwin_flash.py:193). */
 int haet_erwin_forward(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T,
                        const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
@@ -203,6 +205,9 @@ int haet_layer_forward(const haet_layer_shape *s, const haet_erwin_cfg *c, const
                        const float *x_d, float *out_d, void *scratch_d, void *stream);
 
 /* ---- switches and test hooks -------------------------------------------------------
+ * The three setters below are THREAD-LOCAL: they change what later calls made by the SAME host thread launch and
+ * nothing else.  The library keeps no other mutable state (the ablation switches of INTEGRATION.md are read from the
+ * environment once, at first use), so the entry points are re-entrant across threads and streams.
  * haet_set_path(0): tcgen05 tensor-core kernels wherever the shape allows (default);
  * haet_set_path(1): the exact-fp32 SIMT CUDA kernels everywhere (device-side cross-check).
  * haet_debug_gemm: Y[M,Nn] = X[M,K].W[Nn,K]^T + bias through the path selected above;
@@ -212,6 +217,9 @@ int haet_set_path(int path);
  * alone through the real entry points on buffers a full call has filled:
  * bit 0 in-projection (+ image pack), bit 1 pass-1 slice kernel + chunk merge, bit 2 pass-2 deslice kernel, bit 3 to_out */
 int haet_set_stage_mask(int mask);
+/* test hook: lazy-max threshold of pass 1 in log2 units, (0, 15]; 0 restores the default (15).  A small value forces the
+ * accumulator-rescale path on ordinary inputs. */
+int haet_set_raise_threshold(float log2_units);
 int haet_debug_gemm(const float *x_d, const float *w_d, const float *bias_d, float *y_d, int64_t M, int32_t K,
                     int32_t Nn, void *img_d, void *stream);
 

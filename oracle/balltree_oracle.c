@@ -26,7 +26,7 @@
  *
  * Parity status: PINNED -- checked bit-for-bit against the reference's own
  * compiled extension (oracle/_ref/balltree*.so, built by oracle/build_ref.py)
- * in tests/test_oracle_balltree.py and against tests/golden/balltree_*.npz.
+ * in tests/test_oracle_vs_reference.py and against tests/golden/balltree_*.npz.
  */
 #include <math.h>
 #include <stdint.h>
@@ -324,7 +324,7 @@ void haet_oracle_rotation_matrix(double angle_deg, int d, float *R /* d*d row-ma
 /* leaves @ R in fp32 (pyx:646): out[i][j] = sum_k leaves[i][k]*R[k][j].  torch's CPU matmul
  * (what the reference executes here) was measured to be bit-identical to a forward FMA chain
  * acc = a0*r0; acc = fma(a_k, r_k, acc)  (4096x{2,3} random rows, 0 mismatches; the unfused and
- * the reversed orders mismatch on >50% of entries) -- see tests/test_oracle_balltree.py. */
+ * the reversed orders mismatch on >50% of entries) -- see tests/test_oracle_vs_reference.py::test_rotation_matmul_is_forward_fma_chain. */
 void haet_oracle_rotate(const float *leaves, int64_t n, int d, const float *R, float *out)
 {
     for (int64_t i = 0; i < n; ++i)

@@ -332,3 +332,80 @@ def block_mlp_half(fx, ln_w, ln_b, w1, b1, w2, b2, ln_eps=1e-5, dtype=torch.floa
     xn = F.layer_norm(x, (x.shape[-1],), ln_w.to(dtype), ln_b.to(dtype), ln_eps)
     h = F.gelu(F.linear(xn, w1.to(dtype), b1.to(dtype)))
     return (F.linear(h, w2.to(dtype), b2.to(dtype)) + x).float()
+
+
+# ---- streamed restatement for the BASELINE-size meshes (W is never materialised) -------------------------------------
+def in_project_taps(own, x, heads, dim_head, grid, dtype=torch.float64):
+    """Same map as ``in_project`` for the conv front-ends (StructuredMesh2D.py:173-189 / StructuredMesh3D.py:177-193),
+    evaluated tap by tap (sum over the k^nd taps of a shifted [N, D] x [D, inner] product) so that a 64^3 x 256 grid needs
+    no im2col buffer (F.conv3d on the CPU would allocate N x 27 D doubles).  Returns x_proj [B, N, inner]."""
+    w, b = own["in_project_x.weight"].to(dtype), own["in_project_x.bias"].to(dtype)
+    B, N, D = x.shape
+    if w.dim() == 2:
+        return F.linear(x.to(dtype), w, b)
+    k = w.shape[-1]
+    p = k // 2
+    g = tuple(grid) + (1,) * (3 - len(grid))
+    nd = len(grid)
+    xg = x.to(dtype).reshape(B, g[0], g[1], g[2], D)
+    xpad = F.pad(xg, (0, 0, p if nd == 3 else 0, p if nd == 3 else 0, p, p, p, p))   # zero padding = conv padding
+    out = b.expand(B, g[0], g[1], g[2], -1).clone()
+    for i in range(k):
+        for j in range(k):
+            for l in range(k if nd == 3 else 1):
+                wt = w[:, :, i, j, l] if nd == 3 else w[:, :, i, j]
+                out += xpad[:, i:i + g[0], j:j + g[1], l:l + g[2], :] @ wt.t()
+    return out.reshape(B, N, -1)
+
+
+def streamed_slice_state(sd, x, *, heads, dim_head, grid=None, base_temp=0.5, epsilon=1e-6, chunk=16384,
+                         dtype=torch.float64):
+    """IrregularMesh.py:157-188 on meshes of any size: the points stream through in chunks carrying the running column
+    state (m, l, sum e^{z-m} x_proj) of the softmax over the N points, exactly what a two-pass evaluation of
+    torch.softmax(dim=2) followed by the einsum computes.  Returns
+        x_proj [B, N, H*C], tau [B, N, H], S [B, H, G, C] (= W^T x / (mass + 1e-5), mass = 1 in exact arithmetic, F2),
+        lse [B, H, G] = log sum_n exp(z)  (natural log)."""
+    own, _ = split_state_dict(sd, dtype)
+    x = x.detach().cpu()
+    B, N, _ = x.shape
+    xp = in_project_taps(own, x, heads, dim_head, grid, dtype) if own["in_project_x.weight"].dim() > 2 else \
+        torch.cat([F.linear(x[:, i:i + chunk].to(dtype), own["in_project_x.weight"], own["in_project_x.bias"])
+                   for i in range(0, N, chunk)], dim=1)
+    ws, bs = own["in_project_slice.weight"], own["in_project_slice.bias"]
+    wt, bt = own["ada_temp_linear.weight"], own["ada_temp_linear.bias"]
+    c = torch.log(-torch.log(torch.tensor(epsilon, dtype=torch.float32))).to(dtype)          # :172 (fp32 scalar)
+    G, C = ws.shape
+    m = torch.full((B, heads, G), -float("inf"), dtype=dtype)
+    l = torch.zeros(B, heads, G, dtype=dtype)
+    S = torch.zeros(B, heads, G, C, dtype=dtype)
+    tau_all = torch.empty(B, N, heads, dtype=dtype)
+    for i in range(0, N, chunk):
+        xc = xp[:, i:i + chunk].reshape(B, -1, heads, C)                                        # [B, n, H, C]
+        tau = base_temp + F.linear(xc, wt, bt).clamp(-0.4, 0.4)                                 # :168  [B, n, H, 1]
+        tau_all[:, i:i + chunk] = tau[..., 0]
+        z = (F.linear(xc, ws, bs) - c) / tau                                                    # :173-174  [B, n, H, G]
+        mc = z.amax(dim=1)                                                                      # [B, H, G]
+        mn = torch.maximum(m, mc)
+        sc = torch.exp(m - mn)
+        sc[m == -float("inf")] = 0
+        e = torch.exp(z - mn[:, None])
+        l = l * sc + e.sum(1)
+        S = S * sc[..., None] + torch.einsum("bnhg,bnhc->bhgc", e, xc)
+        m = mn
+    return dict(x_proj=xp, tau=tau_all, S=S / l[..., None] / (1 + 1e-5), lse=m + torch.log(l))
+
+
+def streamed_output_rows(sd, st, S_out, rows, *, heads, dim_head, epsilon=1e-6, dtype=torch.float64):
+    """IrregularMesh.py:221-235 for the sampled point rows ``rows`` (indices into N) of every batch item:
+    W[n, g] = exp(z[n, g] - lse[g]) with the global normaliser from ``streamed_slice_state``, out = to_out(W . S')."""
+    own, _ = split_state_dict(sd, dtype)
+    xp, tau, lse = st["x_proj"], st["tau"], st["lse"]
+    B = xp.shape[0]
+    ws, bs = own["in_project_slice.weight"], own["in_project_slice.bias"]
+    G, C = ws.shape
+    c = torch.log(-torch.log(torch.tensor(epsilon, dtype=torch.float32))).to(dtype)
+    xc = xp[:, rows].reshape(B, -1, heads, C)
+    z = (F.linear(xc, ws, bs) - c) / tau[:, rows][..., None]
+    W = torch.exp(z - lse[:, None])                                                            # [B, n, H, G]
+    o = torch.einsum("bnhg,bhgc->bnhc", W, S_out.to(dtype).reshape(B, heads, G, C)).reshape(B, len(rows), heads * C)
+    return F.linear(o, own["to_out.0.weight"], own["to_out.0.bias"])

@@ -159,6 +159,97 @@ def test_layer_matches_reference_golden(name):
         assert rel_l2(got, out) < TOL
 
 
+@pytest.mark.parametrize("path", [0, 1])
+def test_both_device_paths_match_oracle(path):
+    """The tcgen05 path (0) and the exact-fp32 SIMT cross-check path (1, haet_set_path) on the tensor-core shape."""
+    import haet_b200 as hb
+    kw = dict(dim=256, heads=8, dim_head=32, slice_num=64, rotate=45, mlp_ratio=2)
+    torch.manual_seed(21)
+    m = hb.Physics_Attention_Irregular_Mesh(**kw).eval()
+    trained_like_(m, 22)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    x = torch.nn.functional.layer_norm(torch.randn(2, 1300, 256), (256,))
+    m = m.cuda()
+    m.keep_taps = True
+    assert hb.lib().haet_set_path(path) == 0
+    got = m(x.cuda())
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    taps = {}
+    want = O.physics_attention_forward(sd, x, tree=tree, pos_override=t["pos"].cpu(), taps=taps, heads=8, dim_head=32,
+                                       slice_num=64, rotate=45, mlp_ratio=2, dimensionality=3)
+    assert rel_l2(t["S"], taps["S"]) < (TOL if path == 0 else TOL_FP32)
+    assert rel_l2(got, want) < (TOL if path == 0 else 1e-4)
+
+
+def test_forced_accumulator_rescale_path():
+    """haet_set_raise_threshold(0.25): pass 1 raises its running reference (and rescales the TMEM accumulator and the P
+    already stored) on nearly every tile; the slice state must not move."""
+    import haet_b200 as hb
+    kw = dict(dim=256, heads=8, dim_head=32, slice_num=256, rotate=45, mlp_ratio=2)
+    torch.manual_seed(31)
+    m = hb.Physics_Attention_Irregular_Mesh(**kw).eval()
+    trained_like_(m, 32)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    x = torch.nn.functional.layer_norm(torch.randn(1, 20000, 256), (256,))
+    # sort the points so that the logits of slice 0 INCREASE along the mesh: the running reference keeps being overtaken
+    own, _ = O.split_state_dict(sd)
+    xp = torch.nn.functional.linear(x[0], own["in_project_x.weight"], own["in_project_x.bias"])[:, :32]
+    x = x[:, torch.argsort(xp @ own["in_project_slice.weight"][0])].contiguous()
+    m = m.cuda()
+    m.keep_taps = True
+    m(x.cuda())
+    S0, l0 = m.last_taps["S"].clone(), m.last_taps["lse2"].clone()
+    assert hb.lib().haet_set_raise_threshold(0.25) == 0
+    m(x.cuda())
+    S1, l1 = m.last_taps["S"], m.last_taps["lse2"]
+    st = O.streamed_slice_state(sd, x, heads=8, dim_head=32)
+    assert rel_l2(S0, st["S"]) < 1e-4 and rel_l2(S1, st["S"]) < 1e-4
+    assert float((l0 - l1).abs().max()) < 1e-4
+    assert hb.lib().haet_set_raise_threshold(-1.0) != 0 and hb.lib().haet_set_raise_threshold(16.0) != 0
+
+
+def test_c_abi_is_reentrant_across_threads_and_streams():
+    """Two host threads, each on its own CUDA stream, drive the layer concurrently through the C-ABI (one of them on
+    the SIMT path via the thread-local hook): each result is bitwise what the same thread configuration gives serially,
+    and the other thread's hook never leaks."""
+    import threading
+    import haet_b200 as hb
+    kw = dict(dim=256, heads=8, dim_head=32, slice_num=64, rotate=45, mlp_ratio=2)
+    torch.manual_seed(41)
+    m = hb.Physics_Attention_Irregular_Mesh(**kw).eval()
+    trained_like_(m, 42)
+    m = m.cuda()
+    xs = [torch.nn.functional.layer_norm(torch.randn(1, 3000 + 500 * i, 256, device="cuda"), (256,)) for i in range(2)]
+    l = hb.lib()
+    serial = []
+    for i, x in enumerate(xs):
+        l.haet_set_path(i)
+        serial.append(m(x).clone())
+    l.haet_set_path(0)
+    torch.cuda.synchronize()
+    out, err = [None, None], []
+
+    def work(i):
+        try:
+            l.haet_set_path(i)             # thread-local: thread 1 runs the SIMT kernels, thread 0 the tcgen05 ones
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                for _ in range(3):
+                    out[i] = m(xs[i])
+            s.synchronize()
+        except Exception as e:   # pragma: no cover
+            err.append(e)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not err, err
+    assert torch.equal(out[0], serial[0]) and torch.equal(out[1], serial[1])
+    # the main thread's hook is untouched by the workers
+    assert torch.equal(m(xs[0]), serial[0])
+
+
 def test_layer_deterministic_and_noncontiguous_input():
     cfg, sd, x, out, m = _module("layer_irregular_small")
     a = m(x.cuda())
@@ -179,6 +270,9 @@ def test_layer_deterministic_and_noncontiguous_input():
     # conv front-ends on the tcgen05 implicit-GEMM path (dim % 64 == 0, inner % 128 == 0, dim_head == 32), B > 1, odd grids
     ("Physics_Attention_Structured_Mesh_3D", 2, 9 * 6 * 5, dict(dim=128, heads=4, dim_head=32, slice_num=32, H=9, W=6, D=5, rotate=45, mlp_ratio=2)),
     ("Physics_Attention_Structured_Mesh_2D", 1, 21 * 13, dict(dim=256, heads=8, dim_head=32, slice_num=64, H=21, W=13, rotate=45, mlp_ratio=2)),
+    # Conv3d with 256 output channels: the 128 x 256-tile variant (UMMA N = 256, 27 taps) -- BASELINE config 3's route
+    ("Physics_Attention_Structured_Mesh_3D", 1, 12 * 10 * 9, dict(dim=256, heads=8, dim_head=32, slice_num=64, H=12, W=10, D=9, rotate=45, mlp_ratio=2)),
+    ("Physics_Attention_Structured_Mesh_3D", 2, 7 * 8 * 5, dict(dim=256, heads=8, dim_head=32, slice_num=32, H=7, W=8, D=5, rotate=45, mlp_ratio=2)),
 ])
 def test_layer_matches_oracle_trained_like(variant, B, N, kw):
     """Bigger / odd shapes (N not tile aligned, non power-of-two slice_num, 512 slices, rotate off, BASELINE

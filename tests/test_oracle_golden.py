@@ -34,6 +34,31 @@ def test_layer_oracle_matches_reference_golden(name):
     assert rel_l2(got, out) < 2e-6
 
 
+@pytest.mark.parametrize("name", ["layer_irregular_small", "layer_2d_small", "layer_3d_small"])
+def test_streamed_oracle_equals_materialising_oracle(name):
+    """The streamed restatement used at the BASELINE sizes (no N x G weights in memory; conv front-ends tap by tap) is the
+    same function as the golden-pinned one: fp64 against fp64, chunked so that the running-state merge is exercised."""
+    cfg, sd, x, out = load_layer_golden(name)
+    kw = oracle_kwargs(cfg)
+    taps = {}
+    want = O.physics_attention_forward(sd, x, taps=taps, dtype=torch.float64, **kw)
+    st = O.streamed_slice_state(sd, x, heads=kw["heads"], dim_head=kw["dim_head"], grid=kw.get("grid"), chunk=97)
+    assert rel_l2(st["S"], taps["S"]) < 1e-12
+    W = taps["W"]                                                    # [B, H, N, G]
+    lse = torch.logsumexp(torch.log(W) + 0, dim=2)                   # log sum_n W = 0: the normaliser is consistent
+    assert float(lse.abs().max()) < 1e-9
+    rows = torch.arange(0, x.shape[1], 5)
+    got = O.streamed_output_rows(sd, st, taps["S_out"], rows, heads=kw["heads"], dim_head=kw["dim_head"])
+    assert rel_l2(got, want[:, rows]) < 1e-12
+    # and its normaliser reproduces W itself on the sampled rows: exp(z - lse)
+    own, _ = O.split_state_dict(sd, torch.float64)
+    xc = st["x_proj"][:, rows].reshape(x.shape[0], -1, kw["heads"], kw["dim_head"])
+    c = torch.log(-torch.log(torch.tensor(1e-6, dtype=torch.float32))).double()
+    z = (torch.nn.functional.linear(xc, own["in_project_slice.weight"], own["in_project_slice.bias"]) - c) / \
+        st["tau"][:, rows][..., None]
+    assert rel_l2(torch.exp(z - st["lse"][:, None]).permute(0, 2, 1, 3), W[:, :, rows]) < 1e-12
+
+
 def test_layer_oracle_fp64_close_to_fp32():
     cfg, sd, x, out = load_layer_golden("layer_irregular_small")
     taps = {}
