@@ -30,7 +30,7 @@ class ErwinCfg(C.Structure):
                 ("dec_num_heads", C.c_int32 * MAX_LEVELS), ("dec_depths", C.c_int32 * MAX_LEVELS),
                 ("strides", C.c_int32 * MAX_LEVELS),
                 ("rotate", C.c_float), ("decode", C.c_int32), ("mlp_ratio", C.c_int32),
-                ("dimensionality", C.c_int32)]
+                ("dimensionality", C.c_int32), ("attn_bias", C.c_int32)]
 
 
 class LayerWeights(C.Structure):
@@ -124,11 +124,11 @@ def _arr(vals: Sequence[int]):
 
 
 def make_erwin_cfg(c_hidden, ball_sizes, enc_num_heads, enc_depths, dec_num_heads, dec_depths, strides, rotate,
-                   decode=True, mlp_ratio=4, dimensionality=3) -> ErwinCfg:
+                   decode=True, mlp_ratio=4, dimensionality=3, attn_bias=False) -> ErwinCfg:
     # erwin_flash.py:58-60
     assert len(enc_num_heads) == len(enc_depths) == len(ball_sizes)
     assert len(dec_num_heads) == len(dec_depths) == len(strides)
     assert len(strides) == len(ball_sizes) - 1
     return ErwinCfg(len(ball_sizes), _arr(c_hidden), _arr(ball_sizes), _arr(enc_num_heads), _arr(enc_depths),
                     _arr(dec_num_heads), _arr(dec_depths), _arr(strides), float(rotate), int(bool(decode)),
-                    int(mlp_ratio), int(dimensionality))
+                    int(mlp_ratio), int(dimensionality), int(bool(attn_bias)))

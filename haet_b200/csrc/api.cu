@@ -127,7 +127,7 @@ using namespace haet;
 
 extern "C" {
 
-int haet_version(void) { return 1; }
+int haet_version(void) { return 2; }
 const char *haet_last_error(void) { return g_err; }
 int64_t haet_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 

@@ -3,6 +3,10 @@
 // Reference: models/components/erwinflash/erwin_flash.py:138-195 (forward), components/layers.py:30-32
 // (block), :72-92 (BasicLayer, rotated odd blocks), components/attention.py:35-91 (BallMSA, flash
 // variant: no distance bias, qkv columns laid out (three, head, head_dim)), components/mlp.py:17-18
+// Optional (haet_erwin_cfg.attn_bias): the distance bias of the non-flash copy,
+// benchmarks/02-Car-Design-ShapeNetCar/models/components/erwin/components/attention.py:28-32,49-51:
+// logits += sigma_att[h] * ||p_i - p_j||_2 inside the ball (that copy's (H E K) qkv column order is
+// permuted to (three, head, head_dim) when the weights are packed, haet_b200/erwin.py).
 // (SwiGLU), components/pooling.py:25-40, 58-72 (BallPooling / BallUnpooling, BatchNorm1d eval).
 //
 // Everything inside one ErwinTransformerBlock is local to a ball (ball_size consecutive tokens of
@@ -18,6 +22,7 @@ namespace haet {
 
 struct BlockW {  // float offsets into the packed weights
     int norm1, norm2, pe_w, pe_b, qkv_w, qkv_b, proj_w, proj_b, w1, b1, w2, b2, w3, b3;
+    int sigma;   // [heads] sigma_att of the distance bias, or -1
 };
 struct PoolW { int w, b, scale, shift; };
 
@@ -98,13 +103,21 @@ __device__ void ball_rmsnorm(const float *in, int ld, const float *__restrict__ 
     }
 }
 
-// softmax(q k^T / sqrt(hd)) v inside the ball, one (query, head) per thread; HD4 = head_dim / 4 (1 or 2) fast paths
+// sigma_h ||p_i - p_j||_2 in log2 units (rel holds the ball-relative positions, 4 floats per token, unused lanes zero)
+__device__ __forceinline__ float dist_bias(const float *rel, int i, int j, float sig2) {
+    const float dx = rel[4 * i] - rel[4 * j], dy = rel[4 * i + 1] - rel[4 * j + 1], dz = rel[4 * i + 2] - rel[4 * j + 2];
+    return sig2 * sqrtf(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+}
+
+// softmax(q k^T / sqrt(hd) [+ sigma_h dist]) v inside the ball, one (query, head) per thread; HD4 = head_dim / 4 (1 or 2) fast paths
 template <int HD4>
-__device__ void ball_attention(const float *qkv, int ldq, float *us, int ld, int bs, int dim, int heads) {
+__device__ void ball_attention(const float *qkv, int ldq, float *us, int ld, int bs, int dim, int heads,
+                               const float *__restrict__ sigma, const float *rel) {
     const int hd = HD4 * 4;
     const float scale = rsqrtf((float)hd) * kLog2e;
     for (int t = threadIdx.x; t < bs * heads; t += blockDim.x) {
         const int i = t % bs, h = t / bs;
+        const float sig2 = sigma ? sigma[h] * kLog2e : 0.f;
         float4 q[HD4], o[HD4];
 #pragma unroll
         for (int c = 0; c < HD4; ++c) {
@@ -122,6 +135,7 @@ __device__ void ball_attention(const float *qkv, int ldq, float *us, int ld, int
                 const float4 kv = kr[c];
                 s = fmaf(q[c].x, kv.x, s); s = fmaf(q[c].y, kv.y, s); s = fmaf(q[c].z, kv.z, s); s = fmaf(q[c].w, kv.w, s);
             }
+            if (sigma) s += dist_bias(rel, i, j, sig2);
             const float mn = fmaxf(mx, s);
             const float corr = exp2f(mx - mn), p = exp2f(s - mn);
             mx = mn;
@@ -142,18 +156,20 @@ __device__ void ball_attention(const float *qkv, int ldq, float *us, int ld, int
 }
 
 // generic head_dim (scalar two-pass)
-__device__ void ball_attention_any(const float *qkv, int ldq, float *us, int ld, int bs, int dim, int heads) {
+__device__ void ball_attention_any(const float *qkv, int ldq, float *us, int ld, int bs, int dim, int heads,
+                                   const float *__restrict__ sigma, const float *rel) {
     const int hd = dim / heads;
     const float scale = rsqrtf((float)hd) * kLog2e;
     for (int t = threadIdx.x; t < bs * heads; t += blockDim.x) {
         const int i = t % bs, h = t / bs;
+        const float sig2 = sigma ? sigma[h] * kLog2e : 0.f;
         const float *q = qkv + i * ldq + h * hd;
         float mx = -INFINITY;
         for (int j = 0; j < bs; ++j) {
             const float *k = qkv + j * ldq + dim + h * hd;
             float s = 0.f;
             for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
-            mx = fmaxf(mx, s * scale);
+            mx = fmaxf(mx, s * scale + (sigma ? dist_bias(rel, i, j, sig2) : 0.f));
         }
         float *o = us + i * ld + h * hd;
         for (int c = 0; c < hd; ++c) o[c] = 0.f;
@@ -163,7 +179,7 @@ __device__ void ball_attention_any(const float *qkv, int ldq, float *us, int ld,
             const float *v = qkv + j * ldq + 2 * dim + h * hd;
             float s = 0.f;
             for (int c = 0; c < hd; ++c) s = fmaf(q[c], k[c], s);
-            const float p = exp2f(s * scale - mx);
+            const float p = exp2f(s * scale + (sigma ? dist_bias(rel, i, j, sig2) : 0.f) - mx);
             den += p;
             for (int c = 0; c < hd; ++c) o[c] = fmaf(p, v[c], o[c]);
         }
@@ -225,9 +241,9 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restri
             xs[i * ld + k] = x[(int64_t)tok[i] * dim + k];
         }
     }
-    for (int t = tid; t < bs * d; t += blockDim.x) {
-        const int i = t / d, j = t - i * d;
-        rel[i * 4 + j] = pos[(int64_t)tok[i] * d + j];
+    for (int t = tid; t < bs * 4; t += blockDim.x) {
+        const int i = t >> 2, j = t & 3;
+        rel[t] = j < d ? pos[(int64_t)tok[i] * d + j] : 0.f;
     }
     __syncthreads();
     if (tid < d) {  // ball centre: mean over the ball (attention.py:35-40)
@@ -247,9 +263,10 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restri
     __syncthreads();
     {
         const int hd = dim / heads;
-        if (vec && hd == 8) ball_attention<2>(qkv, ldq, us, ld, bs, dim, heads);
-        else if (vec && hd == 4) ball_attention<1>(qkv, ldq, us, ld, bs, dim, heads);
-        else ball_attention_any(qkv, ldq, us, ld, bs, dim, heads);
+        const float *sigma = w.sigma >= 0 ? wts + w.sigma : nullptr;
+        if (vec && hd == 8) ball_attention<2>(qkv, ldq, us, ld, bs, dim, heads, sigma, rel);
+        else if (vec && hd == 4) ball_attention<1>(qkv, ldq, us, ld, bs, dim, heads, sigma, rel);
+        else ball_attention_any(qkv, ldq, us, ld, bs, dim, heads, sigma, rel);
     }
     __syncthreads();
     if (vec) ball_linear4<true, false>(us, ld, wts + w.proj_w, wts + w.proj_b, nullptr, nullptr, xs, ld, bs, dim, dim);
@@ -383,7 +400,7 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 struct Walker {
     int64_t off = 0;
     int take(int64_t n) { int64_t o = off; off += (n + 3) / 4 * 4; return (int)o; }
-    BlockW block(int dim, int hidden, int d) {
+    BlockW block(int dim, int hidden, int d, int bias_heads = 0) {   // bias_heads > 0: the block carries sigma_att[heads]
         BlockW b;
         b.norm1 = take(dim); b.norm2 = take(dim);
         b.pe_w = take((int64_t)dim * d); b.pe_b = take(dim);
@@ -392,6 +409,7 @@ struct Walker {
         b.w1 = take((int64_t)hidden * dim); b.b1 = take(hidden);
         b.w2 = take((int64_t)hidden * dim); b.b2 = take(hidden);
         b.w3 = take((int64_t)dim * hidden); b.b3 = take(dim);
+        b.sigma = bias_heads > 0 ? take(bias_heads) : -1;
         return b;
     }
     PoolW pool(int64_t rows, int64_t K, int bn) {
@@ -426,15 +444,15 @@ extern "C" int64_t haet_erwin_weight_floats(const haet_erwin_cfg *c) {
     Walker wk;
     const int d = c->dimensionality, L = c->n_levels - 1;
     for (int i = 0; i < L; ++i) {
-        for (int k = 0; k < c->enc_depths[i]; ++k) wk.block(c->c_hidden[i], c->c_hidden[i] * c->mlp_ratio, d);
+        for (int k = 0; k < c->enc_depths[i]; ++k) wk.block(c->c_hidden[i], c->c_hidden[i] * c->mlp_ratio, d, c->attn_bias ? c->enc_num_heads[i] : 0);
         if (c->strides[i] != 1)  // stride 1: BallPooling is the identity (pooling.py:26-27); its params are unused
             wk.pool(c->c_hidden[i + 1], (int64_t)c->strides[i] * (c->c_hidden[i] + d), c->c_hidden[i + 1]);
     }
-    for (int k = 0; k < c->enc_depths[L]; ++k) wk.block(c->c_hidden[L], c->c_hidden[L] * c->mlp_ratio, d);
+    for (int k = 0; k < c->enc_depths[L]; ++k) wk.block(c->c_hidden[L], c->c_hidden[L] * c->mlp_ratio, d, c->attn_bias ? c->enc_num_heads[L] : 0);
     if (c->decode)
         for (int i = L - 1; i >= 0; --i) {
             wk.pool((int64_t)c->strides[i] * c->c_hidden[i], c->c_hidden[i + 1] + (int64_t)c->strides[i] * d, c->c_hidden[i]);
-            for (int k = 0; k < c->dec_depths[i]; ++k) wk.block(c->c_hidden[i], c->c_hidden[i] * c->mlp_ratio, d);
+            for (int k = 0; k < c->dec_depths[i]; ++k) wk.block(c->c_hidden[i], c->c_hidden[i] * c->mlp_ratio, d, c->attn_bias ? c->dec_num_heads[i] : 0);
         }
     return wk.off;
 }
@@ -455,7 +473,8 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
     HAET_CHECK_ARG(n % bs == 0, "level %d: %lld tokens are not a multiple of ball size %d", level, (long long)n, bs);
     // weights of one block (Walker::block: contiguous, every tensor padded to 4 floats) staged in shared memory if they fit
     int64_t w_n = 0;
-    { Walker probe; probe.block(dim, hidden, d); w_n = probe.off; }
+    const int bias_heads = c->attn_bias ? heads : 0;
+    { Walker probe; probe.block(dim, hidden, d, bias_heads); w_n = probe.off; }
     const size_t smem_act = block_smem(bs, dim, hidden) + 16;
     HAET_CHECK_ARG(smem_act <= 200 * 1024, "ball of %d tokens x dim %d does not fit shared memory", bs, dim);
     if (smem_act + (size_t)w_n * 4 > 220 * 1024 || ((dim | hidden) & 3)) w_n = 0;
@@ -463,7 +482,7 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
     if (smem > 48 * 1024) HAET_DYN_SMEM(erwin_block_kernel, smem);
     const bool rotate = c->rotate > 0 && depth > 1;   // layers.py:74-91
     for (int k = 0; k < depth; ++k) {
-        BlockW bw = wk.block(dim, hidden, d);
+        BlockW bw = wk.block(dim, hidden, d, bias_heads);
         const int64_t *perm = (rotate && (k & 1)) ? rot : nullptr;
         if (rotate && (k & 1)) HAET_CHECK_ARG(rot != nullptr, "tree_idx_rot must be provided for rotation");
         if (n == 0) continue;

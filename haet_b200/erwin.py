@@ -41,13 +41,15 @@ class BallMSA(nn.Module):
         self.qkv = nn.Linear(dim, 3 * dim)
         self.proj = nn.Linear(dim, dim)
         self.pe_proj = nn.Linear(dimensionality, dim)
-        # kept for checkpoint compatibility; the flash variant never applies the distance bias
+        # the flash variant never applies the distance bias; ErwinTransformer(variant="erwin") does
         self.sigma_att = nn.Parameter(-1 + 0.01 * torch.randn((1, num_heads, 1, 1)))
 
 
 class ErwinTransformerBlock(nn.Module):
-    def __init__(self, dim: int, num_heads: int, ball_size: int, mlp_ratio: int, dimensionality: int = 3):
+    def __init__(self, dim: int, num_heads: int, ball_size: int, mlp_ratio: int, dimensionality: int = 3,
+                 variant: str = "flash"):
         super().__init__()
+        self.variant = variant
         self.ball_size = ball_size
         self.norm1 = nn.RMSNorm(dim)
         self.norm2 = nn.RMSNorm(dim)
@@ -56,8 +58,17 @@ class ErwinTransformerBlock(nn.Module):
 
     def tensors(self):
         a, s = self.BMSA, self.swiglu
-        return [self.norm1.weight, self.norm2.weight, a.pe_proj.weight, a.pe_proj.bias, a.qkv.weight, a.qkv.bias,
-                a.proj.weight, a.proj.bias, s.w1.weight, s.w1.bias, s.w2.weight, s.w2.bias, s.w3.weight, s.w3.bias]
+        qw, qb = a.qkv.weight, a.qkv.bias
+        extra = []
+        if self.variant == "erwin":
+            # the non-flash copy lays the qkv output columns out as (H E K) (benchmarks/02-*/models/components/erwin/
+            # components/attention.py:42-48); the kernels read (three, head, head_dim): permute the ROWS of the weight
+            H, E = a.num_heads, a.head_dim
+            qw = qw.detach().reshape(H, E, 3, -1).permute(2, 0, 1, 3).reshape(3 * H * E, -1)
+            qb = qb.detach().reshape(H, E, 3).permute(2, 0, 1).reshape(-1)
+            extra = [a.sigma_att.detach().reshape(-1)]   # distance bias sigma_att[h] (attention.py:28-32)
+        return [self.norm1.weight, self.norm2.weight, a.pe_proj.weight, a.pe_proj.bias, qw, qb,
+                a.proj.weight, a.proj.bias, s.w1.weight, s.w1.bias, s.w2.weight, s.w2.bias, s.w3.weight, s.w3.bias] + extra
 
 
 class _PoolBase(nn.Module):
@@ -86,11 +97,11 @@ class BallUnpooling(_PoolBase):
 
 class BasicLayer(nn.Module):
     def __init__(self, direction, depth: int, stride, in_dim: int, out_dim: int, num_heads: int, ball_size: int,
-                 mlp_ratio: int, rotate: bool, dimensionality: int = 3):
+                 mlp_ratio: int, rotate: bool, dimensionality: int = 3, variant: str = "flash"):
         super().__init__()
         hidden_dim = in_dim if direction == "down" else out_dim
-        self.blocks = nn.ModuleList([ErwinTransformerBlock(hidden_dim, num_heads, ball_size, mlp_ratio, dimensionality)
-                                     for _ in range(depth)])
+        self.blocks = nn.ModuleList([ErwinTransformerBlock(hidden_dim, num_heads, ball_size, mlp_ratio, dimensionality,
+                                                           variant) for _ in range(depth)])
         self.rotate = [i % 2 for i in range(depth)] if rotate else [False] * depth
         self.direction = direction
         if direction == "down" and stride is not None:
@@ -101,12 +112,21 @@ class BasicLayer(nn.Module):
 
 class ErwinTransformer(nn.Module):
     """Same constructor as the reference (erwin_flash.py:42-58); ``embed`` must be False and ``mp_steps`` 0,
-    the only mode the HAET layer uses (IrregularMesh.py:61-62)."""
+    the only mode the HAET layer uses (IrregularMesh.py:61-62).
+
+    ``variant`` (extension): "flash" = models/components/erwinflash (no distance bias, qkv columns
+    (three, head, head_dim)) -- what the top-level HAET models import; "erwin" = the non-flash copy under
+    benchmarks/02-Car-Design-ShapeNetCar/models/components/erwin: ``sigma_att[h] * cdist(pos, pos)`` added to the per-ball
+    logits and qkv columns laid out (H E K).  Parameter names are the same in both, checkpoints are not interchangeable."""
 
     def __init__(self, c_in: int, c_hidden: List, ball_sizes: List, enc_num_heads: List, enc_depths: List,
                  dec_num_heads: List, dec_depths: List, strides: List, rotate: int, decode: bool = True,
-                 mlp_ratio: int = 4, dimensionality: int = 3, mp_steps: int = 3, embed: bool = True):
+                 mlp_ratio: int = 4, dimensionality: int = 3, mp_steps: int = 3, embed: bool = True,
+                 variant: str = "flash"):
         super().__init__()
+        if variant not in ("flash", "erwin"):
+            raise ValueError("variant must be 'flash' (erwinflash) or 'erwin' (distance-bias copy)")
+        self.variant = variant
         assert len(enc_num_heads) == len(enc_depths) == len(ball_sizes)
         assert len(dec_num_heads) == len(dec_depths) == len(strides)
         assert len(strides) == len(ball_sizes) - 1
@@ -122,16 +142,16 @@ class ErwinTransformer(nn.Module):
         num_layers = len(enc_depths) - 1
         self.encoder = nn.ModuleList(
             BasicLayer("down", enc_depths[i], strides[i], c_hidden[i], c_hidden[i + 1], enc_num_heads[i], ball_sizes[i],
-                       mlp_ratio, rotate > 0, dimensionality) for i in range(num_layers))
+                       mlp_ratio, rotate > 0, dimensionality, variant) for i in range(num_layers))
         self.bottleneck = BasicLayer(None, enc_depths[-1], None, c_hidden[-1], c_hidden[-1], enc_num_heads[-1],
-                                     ball_sizes[-1], mlp_ratio, rotate > 0, dimensionality)
+                                     ball_sizes[-1], mlp_ratio, rotate > 0, dimensionality, variant)
         if decode:
             self.decoder = nn.ModuleList(
                 BasicLayer("up", dec_depths[i], strides[i], c_hidden[i + 1], c_hidden[i], dec_num_heads[i], ball_sizes[i],
-                           mlp_ratio, rotate > 0, dimensionality) for i in range(num_layers - 1, -1, -1))
+                           mlp_ratio, rotate > 0, dimensionality, variant) for i in range(num_layers - 1, -1, -1))
         self.in_dim, self.out_dim = c_in, c_hidden[0]
         self.cfg = _lib.make_erwin_cfg(c_hidden, ball_sizes, enc_num_heads, enc_depths, dec_num_heads, dec_depths,
-                                       strides, rotate, decode, mlp_ratio, dimensionality)
+                                       strides, rotate, decode, mlp_ratio, dimensionality, variant == "erwin")
         self._packed: Optional[torch.Tensor] = None
         self._packed_key = None
         self.apply(self._init_weights)

@@ -25,7 +25,7 @@ class _PhysicsAttentionBase(nn.Module):
 
     def _setup(self, dim, heads, dim_head, dropout, slice_num, base_temp, epsilon, c_hidden, ball_sizes,
                enc_num_heads, enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps,
-               embed):
+               embed, erwin_variant="flash"):
         inner_dim = dim_head * heads
         self.dim_head, self.heads = dim_head, heads
         self.epsilon, self.base_temp = epsilon, base_temp
@@ -52,7 +52,7 @@ class _PhysicsAttentionBase(nn.Module):
                                       enc_num_heads=enc_num_heads, enc_depths=enc_depths, dec_num_heads=dec_num_heads,
                                       dec_depths=dec_depths, strides=strides, rotate=rotate, decode=decode,
                                       mlp_ratio=mlp_ratio, dimensionality=self.dimensionality, mp_steps=mp_steps,
-                                      embed=embed)
+                                      embed=embed, variant=erwin_variant)
         self.to_out = nn.Sequential(nn.Linear(inner_dim, dim), nn.Dropout(dropout))
         # point-sharded multi-GPU: set to a torch.distributed group whose ranks hold disjoint point ranges
         self.point_group = None
@@ -192,12 +192,14 @@ class Physics_Attention_Irregular_Mesh(_PhysicsAttentionBase):
 
     def __init__(self, dim, heads=8, dim_head=64, dropout=0.0, slice_num=64, base_temp=0.5, epsilon=1e-6,
                  c_hidden=None, ball_sizes=None, enc_num_heads=None, enc_depths=None, dec_num_heads=None,
-                 dec_depths=None, strides=None, rotate=1, decode=True, mlp_ratio=4, mp_steps=0, embed=False):
+                 dec_depths=None, strides=None, rotate=1, decode=True, mlp_ratio=4, mp_steps=0, embed=False, *,
+                 erwin_variant="flash"):
         super().__init__()
         self.dimensionality = 3
         self.in_project_x = nn.Linear(dim, dim_head * heads)
         self._setup(dim, heads, dim_head, dropout, slice_num, base_temp, epsilon, c_hidden, ball_sizes, enc_num_heads,
-                    enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed)
+                    enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed,
+                    erwin_variant)
 
 
 class Physics_Attention_Structured_Mesh_2D(_PhysicsAttentionBase):
@@ -207,13 +209,14 @@ class Physics_Attention_Structured_Mesh_2D(_PhysicsAttentionBase):
     def __init__(self, dim, heads=8, dim_head=64, dropout=0.0, slice_num=64, H=101, W=31, kernel=3, base_temp=0.5,
                  epsilon=1e-6, c_hidden=None, ball_sizes=None, enc_num_heads=None, enc_depths=None,
                  dec_num_heads=None, dec_depths=None, strides=None, rotate=1, decode=True, mlp_ratio=4, mp_steps=0,
-                 embed=False):
+                 embed=False, *, erwin_variant="flash"):
         super().__init__()
         self.H, self.W = H, W
         self.dimensionality = 2
         self.in_project_x = nn.Conv2d(dim, dim_head * heads, kernel, 1, kernel // 2)
         self._setup(dim, heads, dim_head, dropout, slice_num, base_temp, epsilon, c_hidden, ball_sizes, enc_num_heads,
-                    enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed)
+                    enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed,
+                    erwin_variant)
 
 
 class Physics_Attention_Structured_Mesh_3D(_PhysicsAttentionBase):
@@ -223,13 +226,14 @@ class Physics_Attention_Structured_Mesh_3D(_PhysicsAttentionBase):
     def __init__(self, dim, heads=8, dim_head=64, dropout=0.0, slice_num=32, H=32, W=32, D=32, kernel=3,
                  base_temp=0.5, epsilon=1e-6, c_hidden=None, ball_sizes=None, enc_num_heads=None, enc_depths=None,
                  dec_num_heads=None, dec_depths=None, strides=None, rotate=1, decode=True, mlp_ratio=4, mp_steps=0,
-                 embed=False):
+                 embed=False, *, erwin_variant="flash"):
         super().__init__()
         self.H, self.W, self.D = H, W, D
         self.dimensionality = 3
         self.in_project_x = nn.Conv3d(dim, dim_head * heads, kernel, 1, kernel // 2)
         self._setup(dim, heads, dim_head, dropout, slice_num, base_temp, epsilon, c_hidden, ball_sizes, enc_num_heads,
-                    enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed)
+                    enc_depths, dec_num_heads, dec_depths, strides, rotate, decode, mlp_ratio, mp_steps, embed,
+                    erwin_variant)
 
 
 @torch.no_grad()

@@ -78,6 +78,9 @@ typedef struct haet_erwin_cfg {
     int32_t decode;
     int32_t mlp_ratio;
     int32_t dimensionality;
+    int32_t attn_bias;                   /* 0: erwinflash BallMSA (no bias, the HAET default); 1: add the distance bias
+                                          * sigma_att[h] * ||p_i - p_j|| of the non-flash copy (benchmarks/02-.../erwin/components/
+                                          * attention.py:28-32,49-51); every block's packed weights then end with sigma_att[heads] */
 } haet_erwin_cfg;
 
 int haet_version(void);

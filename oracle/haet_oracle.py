@@ -141,8 +141,13 @@ def _bn(x, sd, pre, training):
     return (x - mean) / torch.sqrt(var + 1e-5) * w + b
 
 
-def _ball_msa(x, pos, sd, pre, num_heads, ball_size):
-    """attention.py:35-91 (flash variant: no distance bias, column layout (three, head, hd))."""
+def _ball_msa(x, pos, sd, pre, num_heads, ball_size, variant="flash"):
+    """attention.py:35-91 (flash variant: no distance bias, column layout (three, head, hd)).
+
+    variant="erwin": the non-flash copy, benchmarks/02-Car-Design-ShapeNetCar/models/components/erwin/components/
+    attention.py:40-53 -- qkv columns laid out (H E K) (:42-48) and the distance bias
+    sigma_att * cdist(pos, pos) (:28-32) passed to scaled_dot_product_attention as attn_mask (:49-51), i.e. added
+    to q k^T / sqrt(E) before the softmax."""
     T, dim = x.shape
     hd = dim // num_heads
     nb = T // ball_size
@@ -150,6 +155,13 @@ def _ball_msa(x, pos, sd, pre, num_heads, ball_size):
     rel = (p - p.mean(dim=1, keepdim=True)).view(T, -1)                      # :35-40
     x = x + F.linear(rel, sd[pre + ".pe_proj.weight"], sd[pre + ".pe_proj.bias"])  # :59-62
     qkv = F.linear(x, sd[pre + ".qkv.weight"], sd[pre + ".qkv.bias"])          # :65
+    if variant == "erwin":
+        qkv = qkv.view(nb, ball_size, num_heads, hd, 3)                        # "(n m) (H E K) -> K n H m E"
+        q, k, v = (qkv[..., i].permute(0, 2, 1, 3) for i in range(3))         # [nb, h, n, hd]
+        bias = sd[pre + ".sigma_att"].to(x.dtype) * torch.cdist(p, p, p=2).unsqueeze(1)   # [1,H,1,1] * [nb,1,m,m]
+        att = torch.softmax(q @ k.transpose(-1, -2) * (1.0 / math.sqrt(hd)) + bias, dim=-1)
+        o = (att @ v).permute(0, 2, 1, 3).reshape(T, dim)                      # "n H m E -> (n m) (H E)"
+        return F.linear(o, sd[pre + ".proj.weight"], sd[pre + ".proj.bias"])
     qkv = qkv.view(nb, ball_size, 3, num_heads, hd)                            # :68-76
     q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))            # [nb, h, n, hd]
     att = torch.softmax(q @ k.transpose(-1, -2) * (1.0 / math.sqrt(hd)), dim=-1)  # :79-84
@@ -164,20 +176,20 @@ def _swiglu(x, sd, pre):
                     sd[pre + ".w3.weight"], sd[pre + ".w3.bias"])
 
 
-def _block(x, pos, sd, pre, num_heads, ball_size):
+def _block(x, pos, sd, pre, num_heads, ball_size, variant="flash"):
     """layers.py:30-32"""
-    x = x + _ball_msa(_rmsnorm(x, sd[pre + ".norm1.weight"]), pos, sd, pre + ".BMSA", num_heads, ball_size)
+    x = x + _ball_msa(_rmsnorm(x, sd[pre + ".norm1.weight"]), pos, sd, pre + ".BMSA", num_heads, ball_size, variant)
     return x + _swiglu(_rmsnorm(x, sd[pre + ".norm2.weight"]), sd, pre + ".swiglu")
 
 
-def _blocks(x, pos, rot, sd, pre, depth, num_heads, ball_size, rotate):
+def _blocks(x, pos, rot, sd, pre, depth, num_heads, ball_size, rotate, variant="flash"):
     """layers.py:74-91: odd blocks run on the rotated permutation and are permuted back."""
     inv = torch.argsort(rot) if (rotate and depth > 1) else None
     for i in range(depth):
         if rotate and i % 2 == 1:
-            x = _block(x[rot], pos[rot], sd, f"{pre}.blocks.{i}", num_heads, ball_size)[inv]
+            x = _block(x[rot], pos[rot], sd, f"{pre}.blocks.{i}", num_heads, ball_size, variant)[inv]
         else:
-            x = _block(x, pos, sd, f"{pre}.blocks.{i}", num_heads, ball_size)
+            x = _block(x, pos, sd, f"{pre}.blocks.{i}", num_heads, ball_size, variant)
     return x
 
 
@@ -189,6 +201,7 @@ def erwin_forward(sd: Dict[str, torch.Tensor], cfg: dict, x: torch.Tensor, pos: 
     pre-built (tree_idx, tree_mask, rot_list) triple."""
     strides, balls = cfg["strides"], cfg["ball_sizes"]
     rotate = cfg["rotate"] > 0
+    var = cfg.get("variant", "flash")
     if tree is None:
         tree = balltree_build_with_rotations(pos, batch_idx, strides, balls, cfg["rotate"])
     tree_idx, tree_mask, rots = tree
@@ -200,7 +213,7 @@ def erwin_forward(sd: Dict[str, torch.Tensor], cfg: dict, x: torch.Tensor, pos: 
     x, p = x[tree_idx], pos[tree_idx]            # :176-181
     for i in range(nlev):                        # encoder :183-185
         rot = rots.pop(0)
-        x = _blocks(x, p, rot, sd, f"encoder.{i}", cfg["enc_depths"][i], cfg["enc_num_heads"][i], balls[i], rotate)
+        x = _blocks(x, p, rot, sd, f"encoder.{i}", cfg["enc_depths"][i], cfg["enc_num_heads"][i], balls[i], rotate, var)
         xs.append(x); ps.append(p); rs.append(rot)
         s = strides[i]                           # BallPooling pooling.py:25-40
         if s != 1:
@@ -212,7 +225,7 @@ def erwin_forward(sd: Dict[str, torch.Tensor], cfg: dict, x: torch.Tensor, pos: 
                     sd, f"encoder.{i}.pool.norm", bn_training)
             p = centers
     rot = rots.pop(0)                            # bottleneck :187-188
-    x = _blocks(x, p, rot, sd, "bottleneck", cfg["enc_depths"][-1], cfg["enc_num_heads"][-1], balls[-1], rotate)
+    x = _blocks(x, p, rot, sd, "bottleneck", cfg["enc_depths"][-1], cfg["enc_num_heads"][-1], balls[-1], rotate, var)
     if not cfg.get("decode", True):
         return x
     for j, i in enumerate(range(nlev - 1, -1, -1)):   # decoder :190-192
@@ -224,7 +237,7 @@ def erwin_forward(sd: Dict[str, torch.Tensor], cfg: dict, x: torch.Tensor, pos: 
                       sd[f"decoder.{j}.unpool.proj.bias"]).view(n * s, -1)
         x = _bn(cx + up, sd, f"decoder.{j}.unpool.norm", bn_training)
         p = cp
-        x = _blocks(x, p, crot, sd, f"decoder.{j}", cfg["dec_depths"][i], cfg["dec_num_heads"][i], balls[i], rotate)
+        x = _blocks(x, p, crot, sd, f"decoder.{j}", cfg["dec_depths"][i], cfg["dec_num_heads"][i], balls[i], rotate, var)
     return x[tree_mask][torch.argsort(tree_idx[tree_mask])]   # :193
 
 

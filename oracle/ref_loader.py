@@ -124,3 +124,29 @@ def load_reference():
     att.BallMSA.forward = forward_fp32
     _REF = mod
     return mod
+
+
+_REF_ERWIN = None
+NONFLASH_ROOT = os.path.join(REFERENCE_ROOT, "benchmarks", "02-Car-Design-ShapeNetCar", "models", "components", "erwin")
+
+
+def load_reference_erwin_nonflash():
+    """The reference's NON-flash Erwin copy (benchmarks/02-Car-Design-ShapeNetCar/models/components/erwin/), unmodified:
+    SDPA attention with the distance bias sigma_att * cdist (components/attention.py:28-32,49-51) and (H E K) qkv columns.
+    Runs on the CPU as shipped once ``torch_cluster`` (imported, never called with mp_steps=0) and ``balltree`` resolve."""
+    global _REF_ERWIN
+    if _REF_ERWIN is not None:
+        return _REF_ERWIN
+    if not os.path.isdir(NONFLASH_ROOT):
+        raise RuntimeError("reference sources are not present on this machine")
+    _install_stubs()
+    if load_reference_balltree() is None:
+        raise RuntimeError("reference balltree extension could not be built")
+    spec = importlib.util.spec_from_file_location(
+        "haet_reference_erwin_nonflash", os.path.join(NONFLASH_ROOT, "__init__.py"),
+        submodule_search_locations=[NONFLASH_ROOT])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["haet_reference_erwin_nonflash"] = mod
+    spec.loader.exec_module(mod)
+    _REF_ERWIN = mod
+    return mod

@@ -89,7 +89,51 @@ def save_balltree(name, d, n_trees, G, angle, mode, seed):
     np.savez_compressed(os.path.join(OUT, name + ".npz"), **blob)
 
 
+def save_erwin_bias(name, seed, T_trees=4, G=64, d=3):
+    """The NON-flash Erwin copy (distance bias, (H E K) qkv columns) on slice-token-shaped input:
+    the features fed to the encoder (after the copy's always-on input Linear, which HAET's embed=False has no
+    counterpart for), positions, the state_dict without that Linear, and the reference output."""
+    mod = ref_loader.load_reference_erwin_nonflash()
+    cfg = dict(c_in=16, c_hidden=[16, 32], ball_sizes=[32, 16], enc_num_heads=[2, 4], enc_depths=[2, 2],
+               dec_num_heads=[2], dec_depths=[2], strides=[2], rotate=45, decode=True, mlp_ratio=2, dimensionality=d,
+               mp_steps=0)
+    torch.manual_seed(seed)
+    m = mod.ErwinTransformer(**cfg).eval()
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():
+        for n, p in m.named_parameters():
+            if n.endswith(".weight") and p.dim() == 2:
+                p.copy_(torch.randn(p.shape, generator=g) * (1.0 / p.shape[1] ** 0.5))
+            elif n.endswith(".bias") and "norm" not in n:
+                p.copy_(torch.randn(p.shape, generator=g) * 0.1)
+            elif n.endswith("sigma_att"):
+                p.copy_(-1 + 0.5 * torch.randn(p.shape, generator=g))     # a bias that matters: positions span [0, 1]
+            elif "norm" in n and n.endswith(".weight"):
+                p.copy_(1 + 0.2 * torch.randn(p.shape, generator=g))
+        for n, b in m.named_buffers():
+            if n.endswith("running_mean"):
+                b.copy_(0.2 * torch.randn(b.shape, generator=g))
+            elif n.endswith("running_var"):
+                b.copy_(0.5 + torch.rand(b.shape, generator=g))
+    T = T_trees * G
+    x_in = torch.randn(T, cfg["c_in"], generator=g)
+    pos = torch.rand(T, d, generator=g)
+    bidx = torch.arange(T_trees).repeat_interleave(G)
+    with torch.no_grad():
+        x_emb = m.embed(x_in, pos, None)
+        out = m(x_in, pos, bidx)
+    cfg_o = {k: v for k, v in cfg.items() if k not in ("mp_steps", "c_in")}
+    blob = {"x": x_emb.numpy(), "pos": pos.numpy(), "out": out.numpy(), "pts": np.int64(G),
+            "cfg": np.frombuffer(json.dumps(cfg_o).encode(), dtype=np.uint8)}
+    for k, v in m.state_dict().items():
+        if not k.startswith("embed."):
+            blob["sd/" + k] = v.numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **blob)
+    print(name, "out absmax", float(out.abs().max()))
+
+
 if __name__ == "__main__":
+    save_erwin_bias("erwin_bias_small", seed=21)
     save_layer("layer_irregular_small", "Physics_Attention_Irregular_Mesh",
                dict(dim=64, heads=4, dim_head=16, slice_num=32, rotate=45, mlp_ratio=2), B=2, N=1031, seed=10)
     save_layer("layer_irregular_g64_fresh", "Physics_Attention_Irregular_Mesh",

@@ -204,7 +204,9 @@ def test_forced_accumulator_rescale_path():
     m(x.cuda())
     S1, l1 = m.last_taps["S"], m.last_taps["lse2"]
     st = O.streamed_slice_state(sd, x, heads=8, dim_head=32)
-    assert rel_l2(S0, st["S"]) < 1e-4 and rel_l2(S1, st["S"]) < 1e-4
+    # both within the tensor-core path's S floor (fp16 P and hi operand, peaky softmax: ~2e-4) and next to each other
+    assert rel_l2(S0, st["S"]) < 5e-4 and rel_l2(S1, st["S"]) < 5e-4
+    assert rel_l2(S1, S0) < 3e-4
     assert float((l0 - l1).abs().max()) < 1e-4
     assert hb.lib().haet_set_raise_threshold(-1.0) != 0 and hb.lib().haet_set_raise_threshold(16.0) != 0
 
@@ -486,6 +488,45 @@ def test_patch_model_fused_blocks():
         hb.patch_model(blk, fuse_blocks=True)
         got = blk(fx)
     assert rel_l2(got, want) < 2e-4
+
+
+def test_erwin_distance_bias_variant_matches_nonflash_reference_golden():
+    """ErwinTransformer(variant="erwin") -- sigma_att * ||p_i - p_j|| added to the per-ball logits, the
+    non-flash copy's (H E K) qkv columns -- against the output of the reference's own non-flash Erwin
+    (benchmarks/02-Car-Design-ShapeNetCar/models/components/erwin, golden erwin_bias_small.npz), tree built on the device."""
+    import haet_b200 as hb
+    from tests.test_oracle_golden import _load_erwin_bias_golden
+    cfg, sd, x, pos, pts, out = _load_erwin_bias_golden()
+    e = hb.ErwinTransformer(c_in=cfg["c_hidden"][0], mp_steps=0, embed=False, variant="erwin", **cfg)
+    e.load_state_dict(sd, strict=True)
+    e = e.cuda().eval()
+    got = e(x.cuda(), pos.cuda(), pts_per_tree=pts)
+    assert rel_l2(got, out) < 5e-5
+    # the same weights WITHOUT the bias / with the flash column order are a different function
+    f = hb.ErwinTransformer(c_in=cfg["c_hidden"][0], mp_steps=0, embed=False, variant="flash", **cfg)
+    f.load_state_dict(sd, strict=True)
+    assert rel_l2(f.cuda().eval()(x.cuda(), pos.cuda(), pts_per_tree=pts), out) > 1e-2
+    # and inside the layer: the keyword-only extension of the drop-in modules
+    torch.manual_seed(3)
+    m = hb.Physics_Attention_Irregular_Mesh(64, heads=4, dim_head=16, slice_num=64, rotate=45, mlp_ratio=2,
+                                            erwin_variant="erwin").eval()
+    trained_like_(m, 4)
+    with torch.no_grad():
+        for n, p in m.named_parameters():
+            if n.endswith("sigma_att"):
+                p.copy_(-1 + 0.5 * torch.randn(p.shape))
+    sdm = {k: v.clone() for k, v in m.state_dict().items()}
+    xx = torch.nn.functional.layer_norm(torch.randn(2, 900, 64), (64,))
+    m = m.cuda()
+    m.keep_taps = True
+    gotm = m(xx.cuda())
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    ecfg = O.default_erwin_cfg(4, 16, 64, 3, rotate=45, mlp_ratio=2)
+    ecfg["variant"] = "erwin"
+    want = O.physics_attention_forward(sdm, xx, tree=tree, pos_override=t["pos"].cpu(), heads=4, dim_head=16, slice_num=64,
+                                       dimensionality=3, erwin_cfg=ecfg)
+    assert rel_l2(gotm, want) < TOL
 
 
 def test_errors_are_loud():

@@ -66,3 +66,24 @@ def test_layer_oracle_fp64_close_to_fp32():
     tree = (taps["tree_idx"], taps["tree_mask"], taps["rot_idx"])
     got64 = O.physics_attention_forward(sd, x, dtype=torch.float64, tree=tree, **oracle_kwargs(cfg))
     assert rel_l2(got64.float(), got32) < 1e-4
+
+
+def _load_erwin_bias_golden():
+    import json
+    import os
+    from tests.helpers import GOLDEN
+    z = np.load(os.path.join(GOLDEN, "erwin_bias_small.npz"))
+    cfg = json.loads(bytes(z["cfg"]).decode())
+    sd = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd/")}
+    return cfg, sd, torch.from_numpy(z["x"]), torch.from_numpy(z["pos"]), int(z["pts"]), torch.from_numpy(z["out"])
+
+
+def test_erwin_distance_bias_oracle_matches_nonflash_reference_golden():
+    """the oracle's variant="erwin" (sigma_att * cdist bias, (H E K) qkv columns) against the output of the
+    reference's non-flash Erwin copy (golden made by tests/golden/make_golden.py::save_erwin_bias)."""
+    cfg, sd, x, pos, pts, out = _load_erwin_bias_golden()
+    bidx = torch.arange(x.shape[0] // pts).repeat_interleave(pts)
+    got = O.erwin_forward(sd, dict(cfg, variant="erwin"), x, pos, bidx)
+    assert rel_l2(got, out) < 2e-6
+    # and the bias matters: the flash arithmetic on the same weights is far away
+    assert rel_l2(O.erwin_forward(sd, dict(cfg, variant="flash"), x, pos, bidx), out) > 1e-2
