@@ -68,6 +68,11 @@ SYMBOLS = {
     "haet_deslice_out_res": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P, _P]),
     "haet_block_mlp_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     "haet_block_mlp": (C.c_int, [_P, C.c_int64, C.c_int32, C.c_int32, _P, _P, C.c_float, _P, _P, _P, _P, _P, _P, _P]),
+    "haet_model_prologue_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    "haet_model_prologue": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
+                                      _P, _P, _P, _P, _P, C.c_int32, _P, _P, _P]),
+    "haet_time_embed": (C.c_int, [_P, C.c_int64, C.c_int32, _P, _P, _P, _P, _P, _P, _P]),
+    "haet_head_ln_linear": (C.c_int, [_P, C.c_int64, C.c_int32, _P, _P, C.c_float, _P, _P, C.c_int32, _P, _P]),
     "haet_layer_scratch_bytes": (C.c_int64, [_SH, _EC]),
     "haet_layer_forward_host": (C.c_int, [_SH, _EC, C.POINTER(LayerWeights), _P, _P, _P, _P]),
     "haet_layer_forward": (C.c_int, [_SH, _EC, C.POINTER(LayerWeights), _P, _P, _P, _P]),

@@ -27,6 +27,9 @@
  *   haet_slice_reduce_ln / haet_deslice_out_res
  *                          the same with the caller's ln_1 and residual add fused in
  *                          (models/HAETransolver_Irregular_Mesh.py:125)
+ *   haet_model_prologue / haet_time_embed / haet_head_ln_linear
+ *                          Model.forward around the blocks: preprocess MLP + placeholder + time embedding
+ *                          (HAETransolver_Irregular_Mesh.py:351-370, 297-336) and the last block's mlp2(ln_3(fx)) (:131-132)
  *   haet_layer_forward_host  the whole Physics_Attention_*.forward
  *                          (IrregularMesh.py:141-235) on HOST buffers
  */
@@ -191,6 +194,31 @@ int64_t haet_block_mlp_workspace_bytes(int64_t M, int32_t dim, int32_t hidden);
 int haet_block_mlp(const float *x_d, int64_t M, int32_t dim, int32_t hidden, const float *ln_g_d, const float *ln_b_d,
                    float ln_eps, const float *w1_d, const float *b1_d, const float *w2_d, const float *b2_d, float *out_d,
                    void *workspace_d, void *stream);
+
+/* ---- model prologue / epilogue around the blocks (new) ----------------------------
+ * haet_model_prologue replaces, in Model.forward (models/HAETransolver_Irregular_Mesh.py:351-370; the structured models'
+ * HAETransolver_Structured_Mesh_2D.py:384-410 is the same computation),
+ *     fx = preprocess(cat(x, fx)) + placeholder [+ time_fc(timestep_embedding(T))]
+ * with preprocess = MLP(n_layers = 0, act = gelu) = Linear(K, hidden) -> GELU -> Linear(hidden, dim)  (components/mlp.py:67-96):
+ *     out[m, :] = W2 . gelu(W1 . [feat_a[m] | feat_f[m]] + b1) + b2 + add
+ * feat_a_d [B*N, Ka] (the coordinates, or precomputed position features) and feat_f_d [B*N, Kf] (the function values) are
+ * concatenated on the fly; either may be NULL with its width 0.  ref > 0 (unified_pos of the irregular model, get_grid,
+ * :297-336): feat_a_d holds 2-D coordinates (Ka == 2) and the features are their ref*ref distances to the reference grid.
+ * add_d: NULL, or [dim] (placeholder; add_per_batch = 0), or [B, dim] (placeholder + time embedding from haet_time_embed;
+ * add_per_batch = 1).  Supported: dim == 256, hidden a multiple of 256 (<= 2048), Ka(ref^2) + Kf <= 128; otherwise HAET_ENOSUP
+ * (the caller then runs its own modules).  The hidden activations only exist as the second GEMM's operand image. */
+int64_t haet_model_prologue_workspace_bytes(int64_t M, int32_t Ka, int32_t Kf, int32_t ref, int32_t hidden, int32_t dim);
+int haet_model_prologue(const float *feat_a_d, int32_t Ka, const float *feat_f_d, int32_t Kf, int32_t ref, int64_t B, int64_t N,
+                        int32_t hidden, int32_t dim, const float *w1_d, const float *b1_d, const float *w2_d, const float *b2_d,
+                        const float *add_d, int32_t add_per_batch, float *out_d, void *workspace_d, void *stream);
+/* add_d[b, :] = base_d[:] (may be NULL) + W2 . silu(W1 . timestep_embedding(t_d[b], dim) + b1) + b2
+ * (models/components/embedding.py:72-99; time_fc of HAETransolver_Irregular_Mesh.py:220-223, :367-370) */
+int haet_time_embed(const float *t_d, int64_t B, int32_t dim, const float *w1_d, const float *b1_d, const float *w2_d,
+                    const float *b2_d, const float *base_d, float *add_d, void *stream);
+/* y[m, :] = W . LayerNorm(x[m, :]) + b  -- the last block's mlp2(ln_3(fx)) (HAETransolver_Irregular_Mesh.py:131-132) in one
+ * pass over x.  dim a multiple of 128 (<= 1024), out_dim 1..8, else HAET_ENOSUP. */
+int haet_head_ln_linear(const float *x_d, int64_t M, int32_t dim, const float *ln_g_d, const float *ln_b_d, float ln_eps,
+                        const float *w_d, const float *b_d, int32_t out_dim, float *y_d, void *stream);
 
 /* ---- whole layer on HOST buffers (copies inside) ------------------------------------
  * The call a non-torch host (C, C++, ctypes) makes: x_h / out_h are host pointers (pinned for
