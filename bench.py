@@ -282,6 +282,111 @@ def block_times(m, x, mlp_ratio, iters=10):
             "points_per_s": x.shape[0] * x.shape[1] / (t_block * 1e-3)}
 
 
+def timed_replay(fn, steps, warmup, dev):
+    """ms per call of fn() on the current stream: CUDA-graph replay when fn captures, else eager launches; CUDA events."""
+    for _ in range(max(warmup, 1)):
+        fn()
+    torch.cuda.synchronize()
+    step, mode = fn, "eager"
+    try:
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            fn()
+        graph.replay()
+        torch.cuda.synchronize()
+        step, mode = graph.replay, "cuda graph replay"
+    except Exception as ex:
+        print(f"bench.py: graph capture failed ({type(ex).__name__}: {ex}); timing eager launches", file=sys.stderr)
+        torch.cuda.synchronize()
+    step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps, mode
+
+
+def config_records(dev, pk, steps):
+    """The other BASELINE configs on one GPU, each timed like the headline (device-resident inputs, CUDA events):
+    cfg2 (Darcy 85 x 85, batch 4, 128 hidden, 64 slices), cfg3 (64^3 grid, 256 hidden, 64 slices), the per-GPU shard of cfg5
+    (1M points, 512 slices) and cfg4's full model (8 blocks, 1M points, 256 slices, prologue + head)."""
+    import haet_b200 as hb
+    from tests.helpers import trained_like_
+    rec = {}
+
+    def layer(cls, kw, B, N, name, flop_per_pt, bytes_per_pt):
+        torch.manual_seed(0)
+        m = cls(**kw).eval()
+        trained_like_(m, 1)
+        m = m.to(dev)
+        x = torch.nn.functional.layer_norm(torch.randn(B, N, kw["dim"], device=dev), (kw["dim"],))
+        ms, mode = timed_replay(lambda: m(x), steps, 3, dev)
+        t_roof = max(B * N * flop_per_pt / (pk["tf"] * 1e12), B * N * bytes_per_pt / (pk["hbm"] * 1e9)) * 1e3
+        rec[name] = {"ms_per_step": ms, "points_per_s": B * N / (ms * 1e-3), "launch": mode, "t_roof_ms": t_roof,
+                     "roofline_frac": t_roof / ms, "shape": {"B": B, "N": N, **{k: v for k, v in kw.items() if k != "rotate"}}}
+        del m, x
+        torch.cuda.empty_cache()
+    D = 128
+    layer(hb.Physics_Attention_Structured_Mesh_2D, dict(dim=D, heads=8, dim_head=16, slice_num=64, H=85, W=85, rotate=45, mlp_ratio=1),
+          4, 85 * 85, "cfg2", 2 * 10 * D * D + 6 * D * 64 + 2 * D, 8 * D)
+    D = 256
+    layer(hb.Physics_Attention_Structured_Mesh_3D, dict(dim=D, heads=8, dim_head=32, slice_num=64, H=64, W=64, D=64, rotate=45, mlp_ratio=2),
+          1, 64 ** 3, "cfg3", 2 * 28 * D * D + 6 * D * 64 + 2 * D, 8 * D)
+    layer(hb.Physics_Attention_Irregular_Mesh, dict(dim=D, heads=8, dim_head=32, slice_num=512, rotate=45, mlp_ratio=2),
+          1, 1_000_000, "cfg5_shard", 4 * D * D + 6 * D * 512 + 2 * D, 8 * D)
+    # cfg4 "full model": 8 blocks as the reference's velocity-mem-checker builds them (n_hidden 256, 8 heads, mlp_ratio 2,
+    # space_dim 3, fun_dim 1, out_dim 4), 256 slices, 1M points
+    torch.manual_seed(0)
+    mm = hb.HAETransolver_Irregular_Mesh(space_dim=3, fun_dim=1, n_hidden=256, n_layers=8, n_head=8, mlp_ratio=2, out_dim=4,
+                                         slice_num=256).eval()
+    for blk in mm.blocks:
+        trained_like_(blk.Attn, 1)
+    mm = mm.to(dev)
+    N = 1_000_000
+    xc, fc = torch.rand(1, N, 3, device=dev), torch.rand(1, N, 1, device=dev)
+    ms, mode = timed_replay(lambda: mm(xc, fc), max(3, steps // 3), 2, dev)
+    rec["cfg4_full_model"] = {"ms_per_forward": ms, "points_per_s": N / (ms * 1e-3), "launch": mode, "n_layers": 8,
+                              "what": "HAETransolver_Irregular_Mesh.forward(x, fx): prologue kernel + 8 fused blocks + head kernel"}
+    pro = timed_replay(lambda: hb.model_prologue(mm, xc, fc), 5, 2, dev)[0]
+    hx = torch.randn(1, N, 256, device=dev)
+    head = timed_replay(lambda: hb.head_ln_linear(hx, mm.blocks[-1].ln_3, mm.blocks[-1].mlp2), 5, 2, dev)[0]
+    rec["cfg4_full_model"].update(prologue_ms=pro, head_ms=head)
+    del mm, xc, fc, hx
+    torch.cuda.empty_cache()
+    return rec
+
+
+def cpu_model_record():
+    """BASELINE config 1 as stated: the 8-layer HAETransolver_Irregular_Mesh forward on a 32,186-point mesh (256 hidden, 8 heads,
+    32 slices) on the host cores -- the oracle's Model.forward restatement (kind "port"), one warm-up + one timed run."""
+    import haet_b200 as hb
+    from oracle import haet_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    torch.manual_seed(0)
+    kw = dict(space_dim=3, fun_dim=1, n_hidden=256, n_layers=8, n_head=8, mlp_ratio=2, out_dim=4, slice_num=32)
+    m = hb.HAETransolver_Irregular_Mesh(**kw).eval()
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    N = 32186
+    x, fx = torch.rand(1, N, 3), torch.rand(1, N, 1)
+    okw = dict(variant="irregular", n_layers=8, n_head=8, slice_num=32, mlp_ratio=2)
+    ts = []
+    with torch.no_grad():
+        for _ in range(2):
+            t0 = time.perf_counter()
+            O.model_forward(sd, x, fx, None, **okw)
+            ts.append(time.perf_counter() - t0)
+    return {"seconds_per_forward": ts[-1], "points_per_s": N / ts[-1], "cores": torch.get_num_threads(), "kind": "port",
+            "what": "cfg1: 8-layer HAETransolver_Irregular_Mesh forward, 32,186 points, 256 hidden, 32 slices, oracle on the host cores"}
+
+
 def ncu_traffic():
     """DRAM bytes per launch of each kernel from the committed ncu --set full summary (profiles/), or {}."""
     p = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
@@ -352,52 +457,70 @@ def run_gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        m(x)
-    barrier()
     lib = _lib.lib()
-    # One step = one layer forward.  The layer is 21 launches, all enqueued on the caller's stream with no host sync, so it is
-    # captured once into a CUDA graph and replayed ("graph-replayed iterations"): the clock queries the contract
-    # asks for inside the timed region take the driver lock for milliseconds and would otherwise stall the launches.
-    step, per_step, launch_mode = (lambda: m(x)), None, "eager"
-    # N > 1: capturable when the slice state is exchanged by the peer-memory kernel (a captured NCCL all-gather hung on replay)
-    if not args.no_graph and (world == 1 or getattr(m, "_px", None) is not None):
-        try:
-            side = torch.cuda.Stream(dev)
-            side.wait_stream(torch.cuda.current_stream(dev))
-            with torch.cuda.stream(side):
-                m(x)
-            torch.cuda.current_stream(dev).wait_stream(side)
-            graph = torch.cuda.CUDAGraph()
-            c0 = lib.haet_launch_count()
-            with torch.cuda.graph(graph):
-                out = m(x)
-            per_step = lib.haet_launch_count() - c0
-            graph.replay()
-            barrier()
-            step, launch_mode = graph.replay, "cuda graph replay"
-        except Exception as ex:   # capture not possible (e.g. a collective that cannot be captured): eager launches
-            print(f"bench.py: graph capture failed ({type(ex).__name__}: {ex}); timing eager launches", file=sys.stderr)
-            torch.cuda.synchronize()
-            step, per_step, launch_mode = (lambda: m(x)), None, "eager"
-    for _ in range(2):
-        step()
-    barrier()
-    n0 = lib.haet_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
-        e0.record()
-        for _ in range(args.steps):
-            step()
-        e1.record()
-        clk.start()
+
+    def time_layer(mod, xin, steps):
+        """(ms per step = max over ranks, launches, launch mode, clocks) of `steps` forwards of mod(xin).
+        One step = one layer forward.  The layer is ~20 launches, all enqueued on the caller's stream with no host sync, so it is
+        captured once into a CUDA graph and replayed ("graph-replayed iterations"): the clock queries the contract
+        asks for inside the timed region take the driver lock for milliseconds and would otherwise stall the launches."""
+        for _ in range(args.warmup):
+            mod(xin)
         barrier()
-    ms = e0.elapsed_time(e1) / args.steps
-    launches = per_step * args.steps if per_step is not None else lib.haet_launch_count() - n0
-    if world > 1:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t)
+        step, per_step, launch_mode = (lambda: mod(xin)), None, "eager"
+        # N > 1: capturable when the slice state is exchanged by the peer-memory kernel (a captured NCCL all-gather hung on replay)
+        if not args.no_graph and (world == 1 or getattr(mod, "_px", None) is not None):
+            try:
+                side = torch.cuda.Stream(dev)
+                side.wait_stream(torch.cuda.current_stream(dev))
+                with torch.cuda.stream(side):
+                    mod(xin)
+                torch.cuda.current_stream(dev).wait_stream(side)
+                graph = torch.cuda.CUDAGraph()
+                c0 = lib.haet_launch_count()
+                with torch.cuda.graph(graph):
+                    mod(xin)
+                per_step = lib.haet_launch_count() - c0
+                graph.replay()
+                barrier()
+                step, launch_mode = graph.replay, "cuda graph replay"
+            except Exception as ex:   # capture not possible (e.g. a collective that cannot be captured): eager launches
+                print(f"bench.py: graph capture failed ({type(ex).__name__}: {ex}); timing eager launches", file=sys.stderr)
+                torch.cuda.synchronize()
+                step, per_step, launch_mode = (lambda: mod(xin)), None, "eager"
+        for _ in range(2):
+            step()
+        barrier()
+        n0 = lib.haet_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as clk:
+            e0.record()
+            for _ in range(steps):
+                step()
+            e1.record()
+            clk.start()
+            barrier()
+        ms = e0.elapsed_time(e1) / steps
+        launches = per_step * steps if per_step is not None else lib.haet_launch_count() - n0
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms, launches, launch_mode, clk
+
+    ms, launches, launch_mode, clk = time_layer(m, x, args.steps)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    cfg5 = None
+    if world > 1 and not args.no_configs:
+        # BASELINE config 5 as stated: 512 slices, 1M points per GPU (8M points at 8 GPUs), point-sharded, the same exchange
+        m5 = make_module(512, dev)
+        m5.point_group = dist.group.WORLD
+        ms5, _, mode5, _ = time_layer(m5, x, args.steps)
+        cfg5 = {"ms_per_step": ms5, "points_per_s": N * world / (ms5 * 1e-3), "slices": 512, "points_per_gpu": N,
+                "total_points": N * world, "launch": mode5,
+                "exchange_bytes_per_rank": int(lib.haet_partial_floats(C.byref(m5._shape(1, N)))) * 4}
+        del m5
+        torch.cuda.empty_cache()
     value = N * world / (ms * 1e-3)
 
     # ---- end to end through the public host API (haet_b200.HostStream) with HOST buffers (pinned): every step uploads
@@ -453,13 +576,21 @@ def run_gpu_arm(args):
             "gpu_launches": int(launches), "roofline": roof,
             "layer_roofline": {"t_roof_ms": t_roof, "frac": t_roof / ms, "peak_source": pk["src"]},
             "stages_ms": stages}
+    if cfg5 is not None:
+        line["cfg5"] = cfg5
     if world == 1:
         line["block"] = block_times(m, x, MLP_RATIO)
+        if not args.no_configs:
+            del x
+            torch.cuda.empty_cache()
+            line["configs"] = config_records(dev, pk, args.steps)
     if world == 1 and not args.no_cpu:
         sec, cores = cpu_layer_time(args.slices, args.cpu_points, 2, 1)
         line["cpu_baseline"] = {"value": args.cpu_points / sec, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"oracle (CPU restatement of the reference PyTorch layer) on "
                                           f"{args.cpu_points} of the {N} points, {args.slices} slices, mean of 2"}
+        if not args.no_configs:
+            line["cpu_baseline"]["cfg1_full_model"] = cpu_model_record()
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -477,6 +608,7 @@ def main():
     ap.add_argument("--cpu-points", type=int, default=131072, help="bounded CPU sample (points)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
+    ap.add_argument("--no-configs", action="store_true", help="skip the sub-records of the other BASELINE configs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":

@@ -269,22 +269,15 @@ def block_mlp(fx: torch.Tensor, ln_2: nn.LayerNorm, mlp: nn.Module) -> torch.Ten
     return mlp(ln_2(fx)) + fx
 
 
-def _fused_block_forward(self, fx):
-    """TransolverErwinBlock.forward (models/HAETransolver_Irregular_Mesh.py:112-135): ``Attn(ln_1(fx)) + fx`` as one
-    fused call, ``mlp(ln_2(fx)) + fx`` as the fused GEMM pair (block_mlp)."""
-    fx = self.Attn.forward_block(fx, self.ln_1)
-    fx = block_mlp(fx, self.ln_2, self.mlp)
-    if self.last_layer:
-        return self.mlp2(self.ln_3(fx))
-    return fx
-
-
-def patch_model(model: nn.Module, fuse_blocks: bool = False) -> nn.Module:
+def patch_model(model: nn.Module, fuse_blocks: bool = False, fuse_io: bool = None) -> nn.Module:
     """Swap every reference ``Physics_Attention_*`` inside ``model`` (a reference-constructed HAETransolver_*)
     for the haet_b200 module of the same name, carrying the state_dict over (strict).  With ``fuse_blocks`` every
     block that holds one (attributes ``ln_1, Attn, ln_2, mlp, last_layer`` as in TransolverErwinBlock) also gets the
-    fused forward above (eval / inference only)."""
+    fused block forward (models.fused_block_forward; eval / inference only), and with ``fuse_io`` (default: the same as
+    ``fuse_blocks``) a model with the reference's ``preprocess / placeholder / blocks`` attributes gets the fused
+    ``forward(x, fx, T)`` (models.fused_model_forward: prologue and last-layer head kernels)."""
     import types
+    from . import models as _models
     mapping = {c.__name__: c for c in (Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D,
                                        Physics_Attention_Structured_Mesh_3D)}
     for parent in list(model.modules()):
@@ -298,7 +291,10 @@ def patch_model(model: nn.Module, fuse_blocks: bool = False) -> nn.Module:
         for blk in model.modules():
             if isinstance(getattr(blk, "Attn", None), _PhysicsAttentionBase) and \
                     all(hasattr(blk, a) for a in ("ln_1", "ln_2", "mlp", "last_layer")):
-                blk.forward = types.MethodType(_fused_block_forward, blk)
+                blk.forward = types.MethodType(_models.fused_block_forward, blk)
+    if (fuse_blocks if fuse_io is None else fuse_io) and all(hasattr(model, a) for a in ("preprocess", "placeholder", "blocks",
+                                                                                         "unified_pos")):
+        model.forward = types.MethodType(_models.fused_model_forward, model)
     return model
 
 

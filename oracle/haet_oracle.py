@@ -422,3 +422,83 @@ def streamed_output_rows(sd, st, S_out, rows, *, heads, dim_head, epsilon=1e-6, 
     W = torch.exp(z - lse[:, None])                                                            # [B, n, H, G]
     o = torch.einsum("bnhg,bhgc->bnhc", W, S_out.to(dtype).reshape(B, heads, G, C)).reshape(B, len(rows), heads * C)
     return F.linear(o, own["to_out.0.weight"], own["to_out.0.bias"])
+
+
+# ---- Model.forward around the blocks --------------------------------------------------------------------
+def timestep_embedding(timesteps, dim, max_period=10000):
+    """models/components/embedding.py:72-99"""
+    half = dim // 2
+    freqs = torch.exp(-math.log(max_period) * torch.arange(start=0, end=half, dtype=torch.float32) / half)
+    args = timesteps[:, None].float() * freqs[None]
+    emb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+    if dim % 2:
+        emb = torch.cat([emb, torch.zeros_like(emb[:, :1])], dim=-1)
+    return emb
+
+
+def grid_distances(x, ref):
+    """get_grid of the irregular model (HAETransolver_Irregular_Mesh.py:297-336): distances of the 2-D points x [B, N, 2]
+    to the ref x ref reference grid on [0, 1]^2, reference point k = (k // ref, k % ref)."""
+    g = torch.tensor(np.linspace(0, 1, ref), dtype=torch.float)
+    gx = g.reshape(1, ref, 1, 1).repeat([1, 1, ref, 1])
+    gy = g.reshape(1, 1, ref, 1).repeat([1, ref, 1, 1])
+    gref = torch.cat((gx, gy), dim=-1).reshape(1, ref * ref, 2)
+    return torch.sqrt(torch.sum((x[:, :, None, :] - gref[:, None, :, :]) ** 2, dim=-1))
+
+
+def structured_grid_distances(sizes, ref):
+    """get_grid of the structured models (HAETransolver_Structured_Mesh_2D.py:330-382; _3D.py:340-416) -> [1, N, ref^nd]."""
+    nd = len(sizes)
+    axes = [torch.tensor(np.linspace(0, 1, s), dtype=torch.float) for s in sizes]
+    raxes = [torch.tensor(np.linspace(0, 1, ref), dtype=torch.float) for _ in sizes]
+    grid = torch.stack(torch.meshgrid(*axes, indexing="ij"), dim=-1).reshape(-1, 1, nd)
+    gref = torch.stack(torch.meshgrid(*raxes, indexing="ij"), dim=-1).reshape(1, -1, nd)
+    return torch.sqrt(torch.sum((grid - gref) ** 2, dim=-1))[None]
+
+
+def _mlp0(sd, pre, x):
+    """components/mlp.py:75-96 with n_layers = 0, act = gelu: linear_post(gelu(linear_pre(x)))"""
+    return F.linear(F.gelu(F.linear(x, sd[pre + ".linear_pre.0.weight"], sd[pre + ".linear_pre.0.bias"])),
+                    sd[pre + ".linear_post.weight"], sd[pre + ".linear_post.bias"])
+
+
+def model_forward(sd, x, fx, T=None, *, variant="irregular", n_layers, n_head, slice_num, mlp_ratio=1, ref=8,
+                  unified_pos=False, grid=None, rotate=45, layer_hook=None):
+    """Model.forward(x, fx, T) of HAETransolver_Irregular_Mesh (:338-376) / _Structured_Mesh_2D (:384-410) / _3D (:418-461)
+    driven by the model's state_dict (fp32, CPU).  ``layer_hook(i)`` may return dict(tree=..., pos_override=...) for block i
+    (the device's positions / tree, SURVEY 7.3 hard part 2)."""
+    sd = {k: v.detach().cpu().float() if v.is_floating_point() else v.detach().cpu() for k, v in sd.items()}
+    x = x.detach().cpu().float()
+    B = x.shape[0]
+    structured = variant != "irregular"
+    if unified_pos:
+        x = structured_grid_distances(grid, ref).expand(B, -1, -1) if structured else grid_distances(x, ref)
+    N = x.shape[1]
+    if fx is not None:
+        h = _mlp0(sd, "preprocess", torch.cat((x, fx.detach().cpu().float()), -1))
+        if not structured:
+            h = h + sd["placeholder"][None, None, :]
+    else:
+        h = _mlp0(sd, "preprocess", x) + sd["placeholder"][None, None, :]
+    n_hidden = h.shape[-1]
+    if T is not None:
+        emb = timestep_embedding(T.detach().cpu(), n_hidden).repeat(1, N, 1)
+        h = h + F.linear(F.silu(F.linear(emb, sd["time_fc.0.weight"], sd["time_fc.0.bias"])), sd["time_fc.2.weight"],
+                         sd["time_fc.2.bias"])
+    dim_head = n_hidden // n_head
+    dimensionality = 2 if variant == "2d" else 3
+    for i in range(n_layers):
+        p = f"blocks.{i}."
+        attn_sd = {k[len(p) + 5:]: v for k, v in sd.items() if k.startswith(p + "Attn.")}
+        kw = dict(heads=n_head, dim_head=dim_head, slice_num=slice_num, dimensionality=dimensionality, grid=grid,
+                  rotate=rotate, mlp_ratio=mlp_ratio)
+        if layer_hook is not None:
+            kw.update(layer_hook(i) or {})
+        h = block_attention_half(attn_sd, h, sd[p + "ln_1.weight"], sd[p + "ln_1.bias"], **kw)           # :125
+        h = block_mlp_half(h, sd[p + "ln_2.weight"], sd[p + "ln_2.bias"], sd[p + "mlp.linear_pre.0.weight"],
+                           sd[p + "mlp.linear_pre.0.bias"], sd[p + "mlp.linear_post.weight"],
+                           sd[p + "mlp.linear_post.bias"], dtype=torch.float32)                             # :128
+        if i == n_layers - 1:                                                                                # :131-132
+            h = F.linear(F.layer_norm(h, (n_hidden,), sd[p + "ln_3.weight"], sd[p + "ln_3.bias"], 1e-5),
+                         sd[p + "mlp2.weight"], sd[p + "mlp2.bias"])
+    return h

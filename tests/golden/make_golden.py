@@ -132,8 +132,74 @@ def save_erwin_bias(name, seed, T_trees=4, G=64, d=3):
     print(name, "out absmax", float(out.abs().max()))
 
 
+class _cpu_cuda:
+    """get_grid hard-codes ``.cuda()`` (HAETransolver_Irregular_Mesh.py:323).  While a golden is generated on
+    this GPU-less machine ``Tensor.cuda`` is the identity: a device move, not arithmetic."""
+
+    def __enter__(self):
+        self._orig = torch.Tensor.cuda
+        torch.Tensor.cuda = lambda t, *a, **k: t
+
+    def __exit__(self, *a):
+        torch.Tensor.cuda = self._orig
+
+
+def save_model(name, variant, kwargs, B, N, seed, with_fx=True, with_T=False):
+    """A whole HAETransolver_* forward(x, fx, T) of the unmodified reference: inputs, state_dict, output."""
+    ref = ref_loader.load_reference()
+    mod = {"irregular": ref.HAETransolver_Irregular_Mesh, "2d": ref.HAETransolver_Structured_Mesh_2D,
+           "3d": ref.HAETransolver_Structured_Mesh_3D}[variant]
+    torch.manual_seed(seed)
+    with _cpu_cuda():
+        m = mod(**kwargs).eval()
+        g = torch.Generator().manual_seed(seed + 1)
+        for blk in m.blocks:
+            trained_like_(blk.Attn, int(torch.randint(0, 1 << 30, (1,), generator=g)))
+        with torch.no_grad():
+            for n, p in m.named_parameters():
+                if ".Attn." in n:
+                    continue
+                if n.endswith(".weight") and p.dim() == 2:
+                    p.copy_(torch.randn(p.shape, generator=g) * (1.0 / p.shape[1] ** 0.5))
+                elif n.endswith(".bias"):
+                    p.copy_(torch.randn(p.shape, generator=g) * 0.1)
+                elif n.endswith(".weight") and p.dim() == 1:
+                    p.copy_(1 + 0.2 * torch.randn(p.shape, generator=g))
+        x = torch.rand(B, N, kwargs["space_dim"], generator=g)
+        fx = torch.randn(B, N, kwargs["fun_dim"], generator=g) if with_fx else None
+        T = torch.rand(B, 1, generator=g) * 10 if with_T else None
+        with torch.no_grad():
+            out = m(x, fx, T)
+    blob = {"x": x.numpy(), "out": out.numpy(),
+            "cfg": np.frombuffer(json.dumps({"variant": variant, "kwargs": kwargs}).encode(), dtype=np.uint8)}
+    if fx is not None:
+        blob["fx"] = fx.numpy()
+    if T is not None:
+        blob["T"] = T.numpy()
+    for k, v in m.state_dict().items():
+        blob["sd/" + k] = v.numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **blob)
+    print(name, "out absmax", float(out.abs().max()), "bytes", os.path.getsize(os.path.join(OUT, name + ".npz")))
+
+
+def save_models():
+    save_model("model_irregular_small", "irregular",
+               dict(space_dim=3, n_layers=2, n_hidden=64, n_head=4, Time_Input=True, mlp_ratio=2, fun_dim=1, out_dim=4,
+                    slice_num=32, rotate=45), B=2, N=700, seed=31, with_T=True)
+    save_model("model_irregular_256", "irregular",
+               dict(space_dim=3, n_layers=2, n_hidden=256, n_head=8, Time_Input=True, mlp_ratio=1, fun_dim=1, out_dim=4,
+                    slice_num=32, rotate=45), B=2, N=900, seed=32, with_T=True)
+    save_model("model_irregular_256_upos", "irregular",
+               dict(space_dim=2, n_layers=1, n_hidden=256, n_head=8, mlp_ratio=1, fun_dim=0, out_dim=3,
+                    slice_num=64, ref=8, unified_pos=True, rotate=45), B=1, N=1100, seed=33, with_fx=False)
+    save_model("model_2d_small", "2d",
+               dict(space_dim=2, n_layers=2, n_hidden=32, n_head=4, mlp_ratio=2, fun_dim=1, out_dim=1, slice_num=32,
+                    ref=4, unified_pos=True, H=17, W=13, rotate=45), B=2, N=17 * 13, seed=34)
+
+
 if __name__ == "__main__":
     save_erwin_bias("erwin_bias_small", seed=21)
+    save_models()
     save_layer("layer_irregular_small", "Physics_Attention_Irregular_Mesh",
                dict(dim=64, heads=4, dim_head=16, slice_num=32, rotate=45, mlp_ratio=2), B=2, N=1031, seed=10)
     save_layer("layer_irregular_g64_fresh", "Physics_Attention_Irregular_Mesh",

@@ -69,3 +69,24 @@ def trained_like_(module, seed):
                 b.copy_(0.2 * torch.randn(b.shape, generator=g))
             elif n.endswith("running_var"):
                 b.copy_(0.5 + torch.rand(b.shape, generator=g))
+
+
+def load_model_golden(name):
+    """(cfg dict(variant, kwargs), state_dict, x, fx | None, T | None, out) of a whole-model golden (make_golden.save_model)."""
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    cfg = json.loads(bytes(z["cfg"]).decode())
+    sd = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd/")}
+    t = lambda k: torch.from_numpy(z[k]) if k in z.files else None
+    return cfg, sd, t("x"), t("fx"), t("T"), t("out")
+
+
+def model_oracle_kwargs(cfg):
+    kw = cfg["kwargs"]
+    out = dict(variant=cfg["variant"], n_layers=kw["n_layers"], n_head=kw["n_head"], slice_num=kw["slice_num"],
+               mlp_ratio=kw.get("mlp_ratio", 1), ref=kw.get("ref", 8), unified_pos=kw.get("unified_pos", False),
+               rotate=kw.get("rotate", 45))
+    if cfg["variant"] == "2d":
+        out["grid"] = (kw["H"], kw["W"])
+    elif cfg["variant"] == "3d":
+        out["grid"] = (kw["H"], kw["W"], kw["D"])
+    return out

@@ -529,6 +529,123 @@ def test_erwin_distance_bias_variant_matches_nonflash_reference_golden():
     assert rel_l2(gotm, want) < TOL
 
 
+# ------------------------------------------------------------------------------------------------
+# whole models: prologue + fused blocks + head against whole-model goldens of the reference
+# ------------------------------------------------------------------------------------------------
+def _model_from_golden(name):
+    import haet_b200 as hb
+    from tests.helpers import load_model_golden
+    cfg, sd, x, fx, T, out = load_model_golden(name)
+    cls = {"irregular": hb.HAETransolver_Irregular_Mesh, "2d": hb.HAETransolver_Structured_Mesh_2D,
+           "3d": hb.HAETransolver_Structured_Mesh_3D}[cfg["variant"]]
+    m = cls(**cfg["kwargs"])
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda().eval()
+    for blk in m.blocks:
+        blk.Attn.keep_taps = True
+    return cfg, sd, x, fx, T, out, m
+
+
+@pytest.mark.parametrize("name", ["model_irregular_small", "model_irregular_256", "model_irregular_256_upos", "model_2d_small"])
+def test_model_forward_matches_reference_golden(name):
+    """HAETransolver_*.forward(x, fx, T) end to end on the device -- prologue kernel (preprocess MLP, placeholder, get_grid
+    distances, time embedding), fused blocks, ln_3 + mlp2 head kernel -- against (a) the oracle's Model.forward fed the
+    device's per-layer positions / trees and (b) the reference's own whole-model output when no tree split flipped."""
+    import haet_b200 as hb
+    from tests.helpers import model_oracle_kwargs
+    cfg, sd, x, fx, T, out, m = _model_from_golden(name)
+    c = lambda t: t.cuda() if t is not None else None
+    n0 = hb.lib().haet_launch_count()
+    got = m(c(x), c(fx), c(T))
+    assert hb.lib().haet_launch_count() > n0
+    assert got.shape == out.shape and got.dtype == torch.float32
+    taps = [blk.Attn.last_taps for blk in m.blocks]
+
+    def hook(i):
+        t = taps[i]
+        return dict(tree=(t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]]),
+                    pos_override=t["pos"].cpu())
+    want = O.model_forward(sd, x, fx, T, layer_hook=hook, **model_oracle_kwargs(cfg))
+    e = rel_l2(got, want)
+    print(f"\n[model {name}] rel-L2 vs oracle (device trees) {e:.2e}, vs reference golden {rel_l2(got, out):.2e}")
+    assert e < TOL
+    # same trees as the reference built => the golden itself must be matched
+    ref_taps = []
+    O.model_forward(sd, x, fx, T, layer_hook=lambda i: dict(taps=ref_taps.append({}) or ref_taps[-1]), **model_oracle_kwargs(cfg))
+    same = all(torch.equal(rt["tree_idx"], t["tree_idx"].cpu()) and
+               all((a is None and b is None) or torch.equal(a, b.cpu()) for a, b in zip(rt["rot_idx"], t["rot_idx"]))
+               for rt, t in zip(ref_taps, taps))
+    if same:
+        assert rel_l2(got, out) < TOL
+
+
+def test_model_prologue_and_head_kernels_match_torch():
+    """The prologue / head entry points alone against the same modules as torch ops (fp32, TF32 off): every input-feature
+    combination (coordinates + function values, coordinates only, on-the-fly get_grid distances, time embedding)."""
+    import haet_b200 as hb
+    from haet_b200 import models as M
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(5)
+    for kw, with_fx, with_T in [(dict(space_dim=3, fun_dim=2), True, True), (dict(space_dim=3, fun_dim=1), False, False),
+                                (dict(space_dim=2, fun_dim=1, unified_pos=True, ref=8), True, True),
+                                (dict(space_dim=2, fun_dim=0, unified_pos=True, ref=5), False, False)]:
+        m = hb.HAETransolver_Irregular_Mesh(n_layers=1, n_hidden=256, n_head=8, Time_Input=with_T, out_dim=3, slice_num=32,
+                                            mlp_ratio=1, **kw).cuda().eval()
+        with torch.no_grad():
+            for p in m.preprocess.parameters():
+                p.copy_(torch.randn_like(p) * (0.5 if p.dim() == 2 else 0.1))
+        B, N = 2, 1237
+        x = torch.rand(B, N, kw["space_dim"], device="cuda")
+        fx = torch.randn(B, N, kw["fun_dim"], device="cuda") if with_fx else None
+        T = torch.rand(B, 1, device="cuda") * 7 if with_T else None
+        n0 = hb.lib().haet_launch_count()
+        got = M.model_prologue(m, x, fx, T)
+        assert hb.lib().haet_launch_count() > n0, "the prologue kernels did not run"
+        with torch.no_grad():
+            feat = m.get_grid(x, B) if m.unified_pos else x
+            want = m.preprocess(torch.cat((feat, fx), -1) if fx is not None else feat).double() + m.placeholder.double()
+            if T is not None:
+                want = want + m.time_fc(M.timestep_embedding(T, 256).repeat(1, N, 1)).double()
+        assert rel_l2(got, want) < 2e-5, kw
+        blk = m.blocks[0]
+        h = torch.randn(B, N, 256, device="cuda") * 2 + 0.3
+        with torch.no_grad():
+            blk.ln_3.weight.copy_(1 + 0.2 * torch.randn(256, device="cuda")); blk.ln_3.bias.copy_(0.1 * torch.randn(256, device="cuda"))
+            want_h = blk.mlp2(blk.ln_3(h))
+        assert rel_l2(M.head_ln_linear(h, blk.ln_3, blk.mlp2), want_h) < 1e-5
+
+
+def test_patch_model_fuses_a_reference_shaped_model():
+    """patch_model(model, fuse_blocks=True) on a module tree with the reference's attribute names (here: the host mirror,
+    un-fused by hand) installs the fused block / model forwards and keeps the result."""
+    import types
+    import haet_b200 as hb
+    cfg, sd, x, fx, T, out, m = _model_from_golden("model_irregular_256")
+    want = m(x.cuda(), fx.cuda(), T.cuda())
+    # give every block and the model a plain torch-composed forward, as a reference-constructed model has
+    def plain_block(self, h):
+        h = self.Attn(self.ln_1(h)) + h
+        h = self.mlp(self.ln_2(h)) + h
+        return self.mlp2(self.ln_3(h)) if self.last_layer else h
+
+    def plain_model(self, x, fx, T=None):
+        h = self.preprocess(torch.cat((x, fx), -1)) + self.placeholder[None, None, :]
+        h = h + self.time_fc(hb.models.timestep_embedding(T, self.n_hidden).repeat(1, x.shape[1], 1))
+        for b in self.blocks:
+            h = b(h)
+        return h
+    for b in m.blocks:
+        b.forward = types.MethodType(plain_block, b)
+    m.forward = types.MethodType(plain_model, m)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    with torch.no_grad():
+        plain = m(x.cuda(), fx.cuda(), T.cuda())
+    hb.patch_model(m, fuse_blocks=True)
+    fused = m(x.cuda(), fx.cuda(), T.cuda())
+    assert torch.equal(fused, want)
+    assert rel_l2(plain, want) < 5e-4
+
+
 def test_errors_are_loud():
     import haet_b200 as hb
     m = hb.Physics_Attention_Irregular_Mesh(64, heads=4, dim_head=16, slice_num=32, rotate=45)

@@ -87,3 +87,37 @@ def test_erwin_distance_bias_oracle_matches_nonflash_reference_golden():
     assert rel_l2(got, out) < 2e-6
     # and the bias matters: the flash arithmetic on the same weights is far away
     assert rel_l2(O.erwin_forward(sd, dict(cfg, variant="flash"), x, pos, bidx), out) > 1e-2
+
+
+MODELS = ["model_irregular_small", "model_irregular_256", "model_irregular_256_upos", "model_2d_small"]
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_model_oracle_matches_reference_golden(name):
+    """the oracle's Model.forward restatement (preprocess MLP, get_grid, placeholder, time embedding, blocks,
+    ln_3 + mlp2) against whole-model outputs of the unmodified reference."""
+    from tests.helpers import load_model_golden, model_oracle_kwargs
+    cfg, sd, x, fx, T, out = load_model_golden(name)
+    got = O.model_forward(sd, x, fx, T, **model_oracle_kwargs(cfg))
+    assert got.shape == out.shape
+    assert rel_l2(got, out) < 5e-6
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_model_containers_load_reference_state_dict(name):
+    """haet_b200.HAETransolver_* take the reference's constructor arguments and its state_dict, strictly."""
+    import haet_b200 as hb
+    from tests.helpers import load_model_golden
+    cfg, sd, *_ = load_model_golden(name)
+    cls = {"irregular": hb.HAETransolver_Irregular_Mesh, "2d": hb.HAETransolver_Structured_Mesh_2D,
+           "3d": hb.HAETransolver_Structured_Mesh_3D}[cfg["variant"]]
+    m = cls(**cfg["kwargs"])
+    assert set(m.state_dict()) == set(sd)
+    m.load_state_dict(sd, strict=True)
+    with pytest.raises(hb.HaetError):
+        m.eval()(torch.zeros(1, 10, cfg["kwargs"]["space_dim"]), None)    # CPU tensors: no fallback
+    if cfg["variant"] != "irregular" and cfg["kwargs"].get("unified_pos"):
+        kw = cfg["kwargs"]
+        sizes = (kw["H"], kw["W"]) + ((kw["D"],) if cfg["variant"] == "3d" else ())
+        want = O.structured_grid_distances(sizes, kw["ref"])             # pinned by the golden above
+        assert torch.equal(m.pos.reshape(want.shape), want)
