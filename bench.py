@@ -361,6 +361,16 @@ def config_records(dev, pk, steps):
     rec["cfg4_full_model"].update(prologue_ms=pro, head_ms=head)
     del mm, xc, fc, hx
     torch.cuda.empty_cache()
+    # cfg1's model on the GPU (the reference's CPU-runnable case: 32,186 points, 32 slices, 8 layers); its CPU time is
+    # cpu_baseline.cfg1_full_model
+    torch.manual_seed(0)
+    m1 = hb.HAETransolver_Irregular_Mesh(space_dim=3, fun_dim=1, n_hidden=256, n_layers=8, n_head=8, mlp_ratio=2, out_dim=4,
+                                         slice_num=32).eval().to(dev)
+    x1, f1 = torch.rand(1, 32186, 3, device=dev), torch.rand(1, 32186, 1, device=dev)
+    ms, mode = timed_replay(lambda: m1(x1, f1), steps, 3, dev)
+    rec["cfg1_full_model_gpu"] = {"ms_per_forward": ms, "points_per_s": 32186 / (ms * 1e-3), "launch": mode, "n_layers": 8}
+    del m1, x1, f1
+    torch.cuda.empty_cache()
     return rec
 
 

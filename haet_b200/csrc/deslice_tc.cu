@@ -51,7 +51,8 @@ __host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
-                  int64_t N, int64_t npad, int H, int G, int64_t chunk_pts, float *__restrict__ o, int o_image) {
+                  int64_t N, int64_t npad, int H, int G, int C, int64_t chunk_pts, float *__restrict__ o, int o_image) {
+    // C = dim_head: 32, or 16 -- then the image rows, Ws and S' are zero-padded to 32 channels and only 16 are written out
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int g_pad = dt_gpad(G), cw = g_pad < DT_GCMAX ? g_pad : DT_GCMAX;   // chunk width: slices per item
@@ -68,7 +69,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     DesliceCtl *ctl = reinterpret_cast<DesliceCtl *>(sS + DT_STAGES * DT_TILE);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
     const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
-    const int inner = H * DT_C;
+    const int inner = H * C;
     const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
     const int64_t n_end = min(N, n_begin + chunk_pts);
     const int n_tiles = (int)((n_end - n_begin + DT_TILE - 1) / DT_TILE);
@@ -86,8 +87,8 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     // power-of-two scale of S'_h: 2^(14 - e) with max |S'_h| in [2^(e-1), 2^e)
     {
         float amax = 0.f;
-        const float *sp = states + (size_t)bh * G * DT_C;
-        for (int idx = threadIdx.x; idx < G * DT_C; idx += DT_THREADS) amax = fmaxf(amax, fabsf(sp[idx]));
+        const float *sp = states + (size_t)bh * G * C;
+        for (int idx = threadIdx.x; idx < G * C; idx += DT_THREADS) amax = fmaxf(amax, fabsf(sp[idx]));
 #pragma unroll
         for (int o2 = 16; o2; o2 >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o2));
         if (lane == 0) ctl->red[threadIdx.x >> 5] = amax;
@@ -111,10 +112,11 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         __align__(16) __half sv[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const float v = g < G ? ws[(size_t)g * DT_C + ck * 8 + i] : 0.f;
+            const bool live = g < G && ck * 8 + i < C;
+            const float v = live ? ws[(size_t)g * C + ck * 8 + i] : 0.f;
             hi[i] = __float2half_rn(v);
             lo[i] = __float2half_rn(v - __half2float(hi[i]));
-            const float s = g < G ? states[((size_t)bh * G + g) * DT_C + ck * 8 + i] : 0.f;
+            const float s = live ? states[((size_t)bh * G + g) * C + ck * 8 + i] : 0.f;
             sv[i] = __float2half_rn(s * v_scale);
         }
         *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(hi);
@@ -150,7 +152,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         const int r = threadIdx.x - 384;   // row of the tile == TMEM lane
         const float o_scale = ctl->o_scale;
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-        float *dst = o + ((int64_t)b * N) * inner + h * DT_C;
+        float *dst = o + ((int64_t)b * N) * inner + h * C;
         for (int te = 0; te < n_tiles; ++te) {
             const int ob = te & 1;
             mbar_wait(&ctl->o_full[ob], (uint32_t)((te >> 1) & 1));
@@ -172,7 +174,8 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 xpose_stage<0, 3>(v, lane);
                 xpose_stage<1, 4>(v, lane);
                 const int64_t n0 = n_begin + (int64_t)te * DT_TILE + (r & ~3);
-                const int l4 = lane & 3, cc = (h & 1) * 4 + l4, panels = inner >> 6;
+                // global 16-byte chunk (8 channels) of this lane inside the row of `inner` channels
+                const int l4 = lane & 3, gch = (h * C >> 3) + l4, cc = gch & 7, pan = gch >> 3, panels = inner >> 6;
                 uint8_t *oimg = reinterpret_cast<uint8_t *>(o);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -186,10 +189,10 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                         hi[c] = ub;
                         lo[c] = *reinterpret_cast<const uint32_t *>(&lb);
                     }
-                    if (n0 + i < n_end) {
+                    if (n0 + i < n_end && 8 * l4 < C) {
                         const int64_t m = (int64_t)b * N + n0 + i;
                         const int rr = (int)(m & 127);
-                        uint8_t *blk = oimg + (((m >> 7) * panels + (h >> 1)) * 2) * (int64_t)(128 * 128) + sw128_off(rr, cc);
+                        uint8_t *blk = oimg + (((m >> 7) * panels + pan) * 2) * (int64_t)(128 * 128) + sw128_off(rr, cc);
                         *reinterpret_cast<uint4 *>(blk) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                         *reinterpret_cast<uint4 *>(blk + 128 * 128) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                     }
@@ -208,8 +211,9 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                     float *p = dst + (n0 + i) * inner + 4 * l4;
                     *reinterpret_cast<float4 *>(p) = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
                                                                  __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
-                    *reinterpret_cast<float4 *>(p + 16) = make_float4(__uint_as_float(v[4 * i + 16]), __uint_as_float(v[4 * i + 17]),
-                                                                      __uint_as_float(v[4 * i + 18]), __uint_as_float(v[4 * i + 19]));
+                    if (C > 16)
+                        *reinterpret_cast<float4 *>(p + 16) = make_float4(__uint_as_float(v[4 * i + 16]), __uint_as_float(v[4 * i + 17]),
+                                                                          __uint_as_float(v[4 * i + 18]), __uint_as_float(v[4 * i + 19]));
                 }
             }
         }
@@ -335,7 +339,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     }
 }
 
-bool deslice_tc_supported(const haet_layer_shape *s) { return s->dim_head == DT_C && s->slice_num <= DT_MAX_G; }
+bool deslice_tc_supported(const haet_layer_shape *s) { return (s->dim_head == DT_C || s->dim_head == 16) && s->slice_num <= DT_MAX_G; }
 
 int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
                       const float *states, const float *ws, const float *bs, float *o, int o_image, cudaStream_t st) {
@@ -355,7 +359,7 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
     deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                       xpi_npad(s->N), s->heads, s->slice_num, chunk_pts, o, o_image);
+                                                       xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
     HAET_LAUNCHED();
     return HAET_OK;
 }

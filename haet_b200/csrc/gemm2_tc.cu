@@ -66,7 +66,7 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
         mbar_wait(&cb->w_full, 0);
     }
     for (int i = threadIdx.x; i < G2_N; i += G2_THREADS) sBias[i] = bias ? bias[i] : 0.f;
-    if (EPI == EPI_IMG && threadIdx.x < 32) sWt[threadIdx.x] = ep.wt[threadIdx.x];
+    if (EPI == EPI_IMG && threadIdx.x < 32) sWt[threadIdx.x] = ep.wt[ep.c16 ? (threadIdx.x & 15) : threadIdx.x];
     // barriers initialised, TMEM allocated and W resident in BOTH CTAs before any remote arrive / pair MMA
     tc_fence_before();
     cluster_sync_all();

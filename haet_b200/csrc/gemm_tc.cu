@@ -294,8 +294,9 @@ int launch_add_rows(float *y, const float *resid, int64_t n, cudaStream_t st) {
 // in_project_x of the tensor-core path: X [B*N, dim] -> the spill's operand image + scales (no fp32 x_proj)
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
                      uint8_t *xpi, float *scale, void *img, cudaStream_t st, const LnArgs *ln) {
-    HAET_CHECK_ARG(s->dim_head == 32, "the operand image needs dim_head == 32");
+    HAET_CHECK_ARG(s->dim_head == 32 || s->dim_head == 16, "the operand image needs dim_head 16 or 32");
     GemmEpi ep{};
+    ep.c16 = s->dim_head == 16;
     if (ln) {
         HAET_CHECK_ARG(ln_fused_supported(s), "fused LayerNorm: unsupported shape");
         const int inner = s->heads * s->dim_head;

@@ -25,6 +25,8 @@ struct GemmEpi {   // EPI_IMG arguments
     int64_t N, npad;   // rows m = b * N + n
     int H;
     int dbg;   // development switches (HAET_GEMM_DBG): 1 = no epilogue stores, 2 = no global loads
+    int c16;   // EPI_IMG: dim_head == 16 -- a 32-column chunk holds TWO heads; each head's image row keeps its 16 channels in
+               // chunks 0, 1 (hi) and 4, 5 (lo), the other chunks are zero (the passes run their dim_head-32 kernels on it)
     int a_img; // X is the bf16 hi/lo operand image written by pass 2 (common.cuh: OPI), bulk-copied instead of converted
     // Block fusion (HAETransolver_Irregular_Mesh.py:125  fx = Attn(ln_1(fx)) + fx):
     //   EPI_F32: resid [M, ldy] is added to the output rows (nullptr: none)
@@ -276,10 +278,11 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
         xpose_stage<1, 4>(r, lane);
         // register 8 i + c = row m0 + i, column 8 l4 + c: lane l4 owns 16-byte chunk l4 (hi) and 4 + l4 (lo) of the image row
         const float4 ba = *reinterpret_cast<const float4 *>(bias32 + 8 * l4), bb = *reinterpret_cast<const float4 *>(bias32 + 8 * l4 + 4);
-        const float4 wa = *reinterpret_cast<const float4 *>(wt32 + 8 * l4), wb = *reinterpret_cast<const float4 *>(wt32 + 8 * l4 + 4);
+        const int c16 = ep.c16, lc = c16 ? (l4 & 1) : l4;   // this lane's 16-byte chunk inside its head's row
+        const float4 wa = *reinterpret_cast<const float4 *>(wt32 + 8 * lc), wb = *reinterpret_cast<const float4 *>(wt32 + 8 * lc + 4);
         const float bs[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
         const float ws[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
-        const int h = col0 >> 5;
+        const int h = c16 ? (col0 >> 4) + (l4 >> 1) : col0 >> 5;
         int64_t bi = bi0, n = n0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -307,15 +310,19 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
                 lo[c] = *reinterpret_cast<const uint32_t *>(&ll);
             }
             d += __shfl_xor_sync(0xffffffffu, d, 1);
-            d += __shfl_xor_sync(0xffffffffu, d, 2);
+            if (!c16) d += __shfl_xor_sync(0xffffffffu, d, 2);
             if (m0 + i < M && !(ep.dbg & 1)) {
                 // one head: Ada-Temp, fp16 hi/lo image row (chunk j -> position j ^ (n & 7))
                 const int64_t row = (bi * ep.H + h) * ep.npad + n;
                 uint8_t *dst = ep.img + row * XPI_ROW_BYTES;
                 const int sw = (int)(n & 7);
-                *reinterpret_cast<uint4 *>(dst + ((l4 ^ sw) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4 *>(dst + (((4 + l4) ^ sw) << 4)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                if (l4 == 0) {
+                *reinterpret_cast<uint4 *>(dst + ((lc ^ sw) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4 *>(dst + (((4 + lc) ^ sw) << 4)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                if (c16) {   // channels 16 .. 31 of the padded head do not exist
+                    *reinterpret_cast<uint4 *>(dst + (((2 + lc) ^ sw) << 4)) = make_uint4(0, 0, 0, 0);
+                    *reinterpret_cast<uint4 *>(dst + (((6 + lc) ^ sw) << 4)) = make_uint4(0, 0, 0, 0);
+                }
+                if (lc == 0) {
                     const float tau = ep.base_temp + fminf(fmaxf(d + ep.bt, -0.4f), 0.4f);   // Ada-Temp (IrregularMesh.py:168)
                     ep.scale[row] = kLog2e / tau;
                 }

@@ -159,7 +159,8 @@ __global__ void add_batch_vec_kernel(float *__restrict__ y, const float *__restr
 
 // y[m, o] = b[o] + sum_k W[o, k] LN(x[m, :])[k]   (last block: mlp2(ln_3(fx)), HAETransolver_Irregular_Mesh.py:131-132).
 // One warp per row (dim % 128 == 0, dim <= 1024: 8 float4 per lane at most), out_dim <= 8.
-template <int OUT>
+// N4 = float4 per lane held in registers: 2 for dim == 256 (few registers -> enough loads in flight), 8 for any dim <= 1024
+template <int OUT, int N4>
 __global__ void __launch_bounds__(256)
 head_ln_linear_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta, float eps,
                       const float *__restrict__ w, const float *__restrict__ bias, float *__restrict__ y, int64_t M, int dim) {
@@ -167,10 +168,10 @@ head_ln_linear_kernel(const float *__restrict__ x, const float *__restrict__ gam
     const int64_t m = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (m >= M) return;
     const int n4 = dim >> 7;   // float4 per lane
-    float4 v[8];
+    float4 v[N4];
     float s1 = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < N4; ++i)
         if (i < n4) {
             v[i] = __ldg(reinterpret_cast<const float4 *>(x + m * dim) + i * 32 + lane);
             s1 += (v[i].x + v[i].y) + (v[i].z + v[i].w);
@@ -180,7 +181,7 @@ head_ln_linear_kernel(const float *__restrict__ x, const float *__restrict__ gam
     const float mean = s1 / (float)dim;
     float s2 = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < N4; ++i)
         if (i < n4) {
             v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
             s2 = fmaf(v[i].x, v[i].x, s2); s2 = fmaf(v[i].y, v[i].y, s2); s2 = fmaf(v[i].z, v[i].z, s2); s2 = fmaf(v[i].w, v[i].w, s2);
@@ -192,7 +193,7 @@ head_ln_linear_kernel(const float *__restrict__ x, const float *__restrict__ gam
 #pragma unroll
     for (int o = 0; o < OUT; ++o) acc[o] = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < N4; ++i)
         if (i < n4) {
             const int k = (i * 32 + lane) * 4;
             const float4 g = __ldg(reinterpret_cast<const float4 *>(gamma + k)), bt = __ldg(reinterpret_cast<const float4 *>(beta + k));
@@ -305,7 +306,11 @@ int haet_head_ln_linear(const float *x_d, int64_t M, int32_t dim, const float *l
     if (M == 0) return HAET_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const unsigned grid = (unsigned)cdiv(M, 8);
-#define HAET_HEAD(O) case O: head_ln_linear_kernel<O><<<grid, 256, 0, st>>>(x_d, ln_g_d, ln_b_d, ln_eps, w_d, b_d, y_d, M, dim); break
+#define HAET_HEAD(O)                                                                                                  \
+    case O:                                                                                                           \
+        if (dim == 256) head_ln_linear_kernel<O, 2><<<grid, 256, 0, st>>>(x_d, ln_g_d, ln_b_d, ln_eps, w_d, b_d, y_d, M, dim); \
+        else head_ln_linear_kernel<O, 8><<<grid, 256, 0, st>>>(x_d, ln_g_d, ln_b_d, ln_eps, w_d, b_d, y_d, M, dim);            \
+        break
     switch (out_dim) {
         HAET_HEAD(1); HAET_HEAD(2); HAET_HEAD(3); HAET_HEAD(4); HAET_HEAD(5); HAET_HEAD(6); HAET_HEAD(7); HAET_HEAD(8);
     }

@@ -51,8 +51,8 @@ __device__ __forceinline__ uint32_t st_dbuf_col(int w, int buf) { return 128u + 
 
 __global__ void __launch_bounds__(ST_THREADS, 1)
 slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
-                const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int64_t chunk_pts,
-                float raise_thr, float *__restrict__ parts) {
+                const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int C, int64_t chunk_pts,
+                float raise_thr, float *__restrict__ parts) {   // C = dim_head: 32, or 16 (zero-padded to 32 in the image)
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int n_gb = (G + ST_GB - 1) / ST_GB;
@@ -88,7 +88,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         __align__(16) __half hi[8], lo[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const float v = g < G ? ws[(size_t)g * ST_C + ck * 8 + i] : 0.f;
+            const float v = (g < G && ck * 8 + i < C) ? ws[(size_t)g * C + ck * 8 + i] : 0.f;
             hi[i] = __float2half_rn(v);
             lo[i] = __float2half_rn(v - __half2float(hi[i]));
         }
@@ -312,7 +312,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         // ---- write this warpgroup's partial (m2, l, S[C]) per slice of its block: chunk slot 2 * blockIdx.x + c ----
         if (pw > 0) {
             const int slot = pw == 1 ? sub : 0;
-            float *o = parts + ((((int64_t)blockIdx.x * 2 + slot) * BH + bh) * G + g) * (ST_C + 2);
+            float *o = parts + ((((int64_t)blockIdx.x * 2 + slot) * BH + bh) * G + g) * (C + 2);
             if (i > 0) {
                 mbar_wait(&ctl->all_done[w], 0);
                 tc_fence_after();
@@ -322,18 +322,18 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 if (g < G) {
                     o[0] = m_run; o[1] = l_run;
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) o[2 + c] = __uint_as_float(s0[c]);
+                    for (int c = 0; c < 32; ++c) if (c < C) o[2 + c] = __uint_as_float(s0[c]);
                 }
             } else if (g < G) {   // no tile for this warpgroup: neutral partial
                 o[0] = -INFINITY; o[1] = 0.f;
 #pragma unroll
-                for (int c = 0; c < 32; ++c) o[2 + c] = 0.f;
+                for (int c = 0; c < 32; ++c) if (c < C) o[2 + c] = 0.f;
             }
             if (pw == 2 && g < G) {   // the other slot of this block's rows is nobody's: neutral
-                float *o2 = o + BH * (int64_t)G * (ST_C + 2);
+                float *o2 = o + BH * (int64_t)G * (C + 2);
                 o2[0] = -INFINITY; o2[1] = 0.f;
 #pragma unroll
-                for (int c = 0; c < 32; ++c) o2[2 + c] = 0.f;
+                for (int c = 0; c < 32; ++c) if (c < C) o2[2 + c] = 0.f;
             }
         }
     }
@@ -345,7 +345,9 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     }
 }
 
-bool slice_tc_supported(const haet_layer_shape *s) { return s->dim_head == ST_C && s->slice_num <= ST_MAX_GB * ST_GB; }
+bool slice_tc_supported(const haet_layer_shape *s) {   // dim_head 16 runs as zero-padded dim_head 32 (the kernels are bound by the N H G exponentials, not by C)
+    return (s->dim_head == ST_C || s->dim_head == 16) && s->slice_num <= ST_MAX_GB * ST_GB;
+}
 
 static int64_t slice_tc_chunk_pts(const haet_layer_shape *s) {
     int dev = 0, sms = 148;
@@ -370,7 +372,7 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
     const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : ST_RAISE;   // haet_set_raise_threshold: tests force the accumulator-rescale path
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads));
     slice_tc_kernel<<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
-                                                     s->slice_num, chunk_pts, raise_thr, chunk_parts);
+                                                     s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
     HAET_LAUNCHED();
     return HAET_OK;
 }

@@ -28,9 +28,10 @@ SpillView spill_view(const haet_layer_shape *s, void *base) {
     return v;
 }
 
-// one thread per (b, h, row): 32 projected channels -> hi/lo fp16 image row + s_n
+// one thread per (b, h, row): C (16 or 32) projected channels -> hi/lo fp16 image row + s_n; with C == 16 the chunks of the
+// missing channels 16 .. 31 are zero (the passes run their dim_head-32 kernels on zero-padded heads)
 __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__ xp, const float *__restrict__ wt, float bt,
-                                                       float base_temp, int64_t N, int64_t npad, int H, int64_t rows,
+                                                       float base_temp, int64_t N, int64_t npad, int H, int C, int64_t rows,
                                                        uint8_t *__restrict__ img, float *__restrict__ scale) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= rows) return;
@@ -39,10 +40,11 @@ __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__
     uint4 out[8];
     float sn = 0.f;
     if (n < N) {
-        const float4 *src = reinterpret_cast<const float4 *>(xp + ((int64_t)b * N + n) * (H * 32) + h * 32);
+        const float4 *src = reinterpret_cast<const float4 *>(xp + ((int64_t)b * N + n) * (H * C) + h * C);
         float d = bt;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {   // chunk j: channels 8j .. 8j+7
+            if (8 * j >= C) { out[j] = out[4 + j] = make_uint4(0, 0, 0, 0); continue; }
             const float4 a = __ldg(src + 2 * j), c = __ldg(src + 2 * j + 1);
             float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
 #pragma unroll
@@ -76,10 +78,10 @@ __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__
 
 int launch_xpi_pack(const haet_layer_shape *s, const float *xp, const float *wt, float bt, uint8_t *img, float *scale,
                     cudaStream_t st) {
-    HAET_CHECK_ARG(s->dim_head == 32, "the operand image needs dim_head == 32");
+    HAET_CHECK_ARG(s->dim_head == 32 || s->dim_head == 16, "the operand image needs dim_head 16 or 32");
     const int64_t npad = xpi_npad(s->N), rows = s->B * s->heads * npad;
     if (rows == 0) return HAET_OK;
-    xpi_pack_kernel<<<(unsigned)cdiv(rows, 256), 256, 0, st>>>(xp, wt, bt, s->base_temp, s->N, npad, s->heads, rows, img, scale);
+    xpi_pack_kernel<<<(unsigned)cdiv(rows, 256), 256, 0, st>>>(xp, wt, bt, s->base_temp, s->N, npad, s->heads, s->dim_head, rows, img, scale);
     HAET_LAUNCHED();
     return HAET_OK;
 }

@@ -100,8 +100,10 @@ def test_slice_state_matches_oracle(name):
     O.physics_attention_forward(sd, x, taps=taps, **oracle_kwargs(cfg))
     m(x.cuda())
     got = m.last_taps
-    assert rel_l2(got["S"], taps["S"]) < TOL_FP32
-    assert rel_l2(got["pos"], taps["pos"]) < 1e-4
+    # dim_head 16 / 32 run the tcgen05 passes (fp16 P and hi operand: S to ~2e-4 on peaky columns), the others exact fp32
+    tc = cfg["kwargs"]["dim_head"] in (16, 32)
+    assert rel_l2(got["S"], taps["S"]) < (5e-4 if tc else TOL_FP32)
+    assert rel_l2(got["pos"], taps["pos"]) < (5e-4 if tc else 1e-4)
     # global softmax normaliser: lse2 = log2 sum_n exp(z)
     if "W" in taps:
         B, H, N, G = taps["W"].shape
@@ -113,7 +115,7 @@ def test_slice_state_matches_oracle(name):
         z = (torch.nn.functional.linear(xp.double(), own["in_project_slice.weight"].double(),
                                         own["in_project_slice.bias"].double()) - c.double()) / tau.double()
         lse2 = torch.logsumexp(z, dim=2) / np.log(2.0)
-        assert float((got["lse2"].cpu().double() - lse2).abs().max()) < 1e-3
+        assert float((got["lse2"].cpu().double() - lse2).abs().max()) < (5e-3 if tc else 1e-3)
 
 
 @pytest.mark.parametrize("name", LAYERS)
@@ -586,7 +588,7 @@ def test_model_prologue_and_head_kernels_match_torch():
     from haet_b200 import models as M
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.manual_seed(5)
-    for kw, with_fx, with_T in [(dict(space_dim=3, fun_dim=2), True, True), (dict(space_dim=3, fun_dim=1), False, False),
+    for kw, with_fx, with_T in [(dict(space_dim=3, fun_dim=2), True, True), (dict(space_dim=3, fun_dim=0), False, False),
                                 (dict(space_dim=2, fun_dim=1, unified_pos=True, ref=8), True, True),
                                 (dict(space_dim=2, fun_dim=0, unified_pos=True, ref=5), False, False)]:
         m = hb.HAETransolver_Irregular_Mesh(n_layers=1, n_hidden=256, n_head=8, Time_Input=with_T, out_dim=3, slice_num=32,
@@ -751,7 +753,8 @@ def test_point_sharded_equals_single(monkeypatch):
         lse = torch.empty(T, device="cuda")
         pos = torch.empty(T, 3, device="cuda")
         _lib.check(l.haet_slice_merge(C.byref(sh), allp.data_ptr(), R, eid.data_ptr(), lse.data_ptr(), pos.data_ptr(), st))
-        assert rel_l2(eid, full["S"].reshape(T, -1)) < 1e-5
+        # tensor-core passes (dim_head 16 here): other chunk boundaries = other fp16 roundings of P, same ~2e-4 floor
+        assert rel_l2(eid, full["S"].reshape(T, -1)) < 5e-4
         assert float((lse - full["lse2"].reshape(-1)).abs().max()) < 1e-4
 
 
