@@ -455,6 +455,8 @@ def run_gpu_arm(args):
         args.gpus = world
     dev = torch.device("cuda", local)
     _lib.check(_lib.lib().haet_device_check())
+    from haet_b200 import bind_host_to_gpu_numa
+    numa = bind_host_to_gpu_numa(dev) if world > 1 else {"bound": False, "note": "single process: affinity left alone"}
     m = make_module(args.slices, dev)
     if world > 1:
         m.point_group = dist.group.WORLD
@@ -569,7 +571,8 @@ def run_gpu_arm(args):
         ms2, single_ms = float(t[0]), float(t[1])
     e2e = {"value": N * world / (ms2 * 1e-3), "unit": UNIT, "ms_per_step": ms2, "steps": k2,
            "h2d_bytes_per_step": xh.numel() * 4, "d2h_bytes_per_step": ohs[0].numel() * 4,
-           "api": "haet_b200.HostStream(depth=3).submit(pinned x, pinned out)", "single_call_ms": single_ms}
+           "api": "haet_b200.HostStream(depth=3).submit(pinned x, pinned out)", "single_call_ms": single_ms,
+           "host_numa": numa}
 
     if rank != 0:
         if world > 1:

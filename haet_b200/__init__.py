@@ -11,7 +11,7 @@ All arithmetic runs in libhaet_b200.so (hand-written CUDA behind the C-ABI of in
 from ._lib import HaetError, lib  # noqa: F401
 from .balltree import build_balltree, build_balltree_with_rotations  # noqa: F401
 from .erwin import ErwinTransformer  # noqa: F401
-from .host_stream import HostStream  # noqa: F401
+from .host_stream import HostStream, bind_host_to_gpu_numa  # noqa: F401
 from .physics_attention import (Physics_Attention_Irregular_Mesh, Physics_Attention_Structured_Mesh_2D,  # noqa: F401
                                 Physics_Attention_Structured_Mesh_3D, block_mlp, from_reference, patch_model)
 from .models import (HAETransolver_Irregular_Mesh, HAETransolver_Structured_Mesh_2D,  # noqa: F401
@@ -19,6 +19,6 @@ from .models import (HAETransolver_Irregular_Mesh, HAETransolver_Structured_Mesh
 
 __all__ = ["Physics_Attention_Irregular_Mesh", "Physics_Attention_Structured_Mesh_2D",
            "Physics_Attention_Structured_Mesh_3D", "ErwinTransformer", "build_balltree_with_rotations",
-           "build_balltree", "patch_model", "block_mlp", "from_reference", "HostStream", "HaetError", "lib",
+           "build_balltree", "patch_model", "block_mlp", "from_reference", "HostStream", "bind_host_to_gpu_numa", "HaetError", "lib",
            "HAETransolver_Irregular_Mesh", "HAETransolver_Structured_Mesh_2D", "HAETransolver_Structured_Mesh_3D",
            "fused_model_forward", "head_ln_linear", "model_prologue"]

@@ -158,62 +158,73 @@ __global__ void add_batch_vec_kernel(float *__restrict__ y, const float *__restr
 }
 
 // y[m, o] = b[o] + sum_k W[o, k] LN(x[m, :])[k]   (last block: mlp2(ln_3(fx)), HAETransolver_Irregular_Mesh.py:131-132).
-// One warp per row (dim % 128 == 0, dim <= 1024: 8 float4 per lane at most), out_dim <= 8.
-// N4 = float4 per lane held in registers: 2 for dim == 256 (few registers -> enough loads in flight), 8 for any dim <= 1024
+// One warp per row (dim % 128 == 0, dim <= 1024), out_dim <= 8; persistent grid, the next row's loads are in flight while
+// the current row is reduced (one short-lived block per 8 rows measured 2.4 TB/s: block turnover, not bandwidth).
+// N4 = float4 per lane held in registers: 2 for dim == 256, 8 for any dim <= 1024
 template <int OUT, int N4>
 __global__ void __launch_bounds__(256)
 head_ln_linear_kernel(const float *__restrict__ x, const float *__restrict__ gamma, const float *__restrict__ beta, float eps,
                       const float *__restrict__ w, const float *__restrict__ bias, float *__restrict__ y, int64_t M, int dim) {
     const int lane = threadIdx.x & 31;
-    const int64_t m = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (m >= M) return;
     const int n4 = dim >> 7;   // float4 per lane
-    float4 v[N4];
-    float s1 = 0.f;
+    const int64_t stride = (int64_t)gridDim.x * 8;
+    int64_t m = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    float4 nxt[N4];
+    auto load = [&](int64_t row) {
 #pragma unroll
-    for (int i = 0; i < N4; ++i)
-        if (i < n4) {
-            v[i] = __ldg(reinterpret_cast<const float4 *>(x + m * dim) + i * 32 + lane);
-            s1 += (v[i].x + v[i].y) + (v[i].z + v[i].w);
-        }
+        for (int i = 0; i < N4; ++i)
+            if (i < n4 && row < M) nxt[i] = __ldg(reinterpret_cast<const float4 *>(x + row * dim) + i * 32 + lane);
+    };
+    load(m);
+    for (; m < M; m += stride) {
+        float4 v[N4];
+        float s1 = 0.f;
 #pragma unroll
-    for (int o = 16; o; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-    const float mean = s1 / (float)dim;
-    float s2 = 0.f;
-#pragma unroll
-    for (int i = 0; i < N4; ++i)
-        if (i < n4) {
-            v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
-            s2 = fmaf(v[i].x, v[i].x, s2); s2 = fmaf(v[i].y, v[i].y, s2); s2 = fmaf(v[i].z, v[i].z, s2); s2 = fmaf(v[i].w, v[i].w, s2);
-        }
-#pragma unroll
-    for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-    const float rstd = rsqrtf(s2 / (float)dim + eps);
-    float acc[OUT];
-#pragma unroll
-    for (int o = 0; o < OUT; ++o) acc[o] = 0.f;
-#pragma unroll
-    for (int i = 0; i < N4; ++i)
-        if (i < n4) {
-            const int k = (i * 32 + lane) * 4;
-            const float4 g = __ldg(reinterpret_cast<const float4 *>(gamma + k)), bt = __ldg(reinterpret_cast<const float4 *>(beta + k));
-            const float n0 = fmaf(v[i].x * rstd, g.x, bt.x), n1 = fmaf(v[i].y * rstd, g.y, bt.y);
-            const float n2 = fmaf(v[i].z * rstd, g.z, bt.z), n3 = fmaf(v[i].w * rstd, g.w, bt.w);
-#pragma unroll
-            for (int o = 0; o < OUT; ++o) {
-                const float4 wv = __ldg(reinterpret_cast<const float4 *>(w + (size_t)o * dim + k));
-                acc[o] = fmaf(n0, wv.x, acc[o]); acc[o] = fmaf(n1, wv.y, acc[o]);
-                acc[o] = fmaf(n2, wv.z, acc[o]); acc[o] = fmaf(n3, wv.w, acc[o]);
+        for (int i = 0; i < N4; ++i)
+            if (i < n4) {
+                v[i] = nxt[i];
+                s1 += (v[i].x + v[i].y) + (v[i].z + v[i].w);
             }
+        load(m + stride);
+#pragma unroll
+        for (int o = 16; o; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        const float mean = s1 / (float)dim;
+        float s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < N4; ++i)
+            if (i < n4) {
+                v[i].x -= mean; v[i].y -= mean; v[i].z -= mean; v[i].w -= mean;
+                s2 = fmaf(v[i].x, v[i].x, s2); s2 = fmaf(v[i].y, v[i].y, s2); s2 = fmaf(v[i].z, v[i].z, s2); s2 = fmaf(v[i].w, v[i].w, s2);
+            }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+        const float rstd = rsqrtf(s2 / (float)dim + eps);
+        float acc[OUT];
+#pragma unroll
+        for (int o = 0; o < OUT; ++o) acc[o] = 0.f;
+#pragma unroll
+        for (int i = 0; i < N4; ++i)
+            if (i < n4) {
+                const int k = (i * 32 + lane) * 4;
+                const float4 g = __ldg(reinterpret_cast<const float4 *>(gamma + k)), bt = __ldg(reinterpret_cast<const float4 *>(beta + k));
+                const float n0 = fmaf(v[i].x * rstd, g.x, bt.x), n1 = fmaf(v[i].y * rstd, g.y, bt.y);
+                const float n2 = fmaf(v[i].z * rstd, g.z, bt.z), n3 = fmaf(v[i].w * rstd, g.w, bt.w);
+#pragma unroll
+                for (int o = 0; o < OUT; ++o) {
+                    const float4 wv = __ldg(reinterpret_cast<const float4 *>(w + (size_t)o * dim + k));
+                    acc[o] = fmaf(n0, wv.x, acc[o]); acc[o] = fmaf(n1, wv.y, acc[o]);
+                    acc[o] = fmaf(n2, wv.z, acc[o]); acc[o] = fmaf(n3, wv.w, acc[o]);
+                }
+            }
+#pragma unroll
+        for (int o = 0; o < OUT; ++o) {
+#pragma unroll
+            for (int s = 16; s; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
         }
+        if (lane == 0) {
 #pragma unroll
-    for (int o = 0; o < OUT; ++o) {
-#pragma unroll
-        for (int s = 16; s; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
-    }
-    if (lane == 0) {
-#pragma unroll
-        for (int o = 0; o < OUT; ++o) y[m * OUT + o] = acc[o] + bias[o];
+            for (int o = 0; o < OUT; ++o) y[m * OUT + o] = acc[o] + bias[o];
+        }
     }
 }
 
@@ -305,7 +316,11 @@ int haet_head_ln_linear(const float *x_d, int64_t M, int32_t dim, const float *l
     }
     if (M == 0) return HAET_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    const unsigned grid = (unsigned)cdiv(M, 8);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int64_t want = cdiv(M, 8);
+    const unsigned grid = (unsigned)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
 #define HAET_HEAD(O)                                                                                                  \
     case O:                                                                                                           \
         if (dim == 256) head_ln_linear_kernel<O, 2><<<grid, 256, 0, st>>>(x_d, ln_g_d, ln_b_d, ln_eps, w_d, b_d, y_d, M, dim); \

@@ -12,7 +12,44 @@ download concurrently on `depth` CUDA streams (PCIe is full duplex, the two copy
         hs.submit(xh, oh)             # asynchronous; returns the event that marks `oh` complete
     hs.drain()
 """
+import os
+
 import torch
+
+
+def bind_host_to_gpu_numa(device=None) -> dict:
+    """Restrict this process to the CPUs of the NUMA node its GPU hangs off, so that the pinned host buffers it allocates
+    afterwards (first-touch placement) and the threads that fill them are local to the GPU's PCIe root.  With one process per
+    GPU this spreads the host-memory traffic of N ranks over the sockets instead of piling it on the node the launcher
+    started on -- the end-to-end (host-resident) path is bound by PCIe and host-memory bandwidth, not by the kernels.
+    A no-op (reported as such) when the platform exposes no NUMA information or the node's CPUs are outside the
+    process' allowed set (a container pinned to one node)."""
+    info = {"bound": False}
+    try:
+        idx = torch.device(device).index if device is not None else torch.cuda.current_device()
+        if idx is None:
+            idx = torch.cuda.current_device()
+        p = torch.cuda.get_device_properties(idx)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as fh:
+            node = int(fh.read().strip())
+        info.update(gpu=idx, pci=bdf, numa_node=node)
+        if node < 0:
+            return info
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as fh:
+            cpus = set()
+            for part in fh.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        info.update(node_cpus=len(cpus), allowed_cpus=len(allowed), usable_cpus=len(use))
+        if use and use != allowed:
+            os.sched_setaffinity(0, use)
+            info["bound"] = True
+    except Exception as ex:   # no sysfs / no such attribute: leave the affinity alone
+        info["error"] = f"{type(ex).__name__}: {ex}"
+    return info
 
 
 class HostStream:

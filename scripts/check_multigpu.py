@@ -79,5 +79,19 @@ torch.cuda.synchronize()
 err_b = float((out_b - full_b[:, lo:hi]).norm() / full_b[:, lo:hi].norm())
 print(f"rank {rank}/{world}: fused block sharded vs single rel_l2 = {err_b:.3e}", flush=True)
 assert err_b < 2e-4
+# a whole model point-sharded end to end: prologue, blocks and head are row-local, one exchange per layer
+from haet_b200.distributed import set_point_group
+torch.manual_seed(9)
+mm = hb.HAETransolver_Irregular_Mesh(space_dim=3, fun_dim=1, n_hidden=256, n_layers=3, n_head=8, mlp_ratio=2, out_dim=4,
+                                     slice_num=64).to(dev).eval()
+xc = torch.rand(1, N, 3, generator=g).to(dev)
+fc = torch.rand(1, N, 1, generator=g).to(dev)
+full_m = mm(xc, fc)
+set_point_group(mm, dist.group.WORLD)
+out_m = mm(xc[:, lo:hi].contiguous(), fc[:, lo:hi].contiguous())
+torch.cuda.synchronize()
+err_m = float((out_m - full_m[:, lo:hi]).norm() / full_m[:, lo:hi].norm())
+print(f"rank {rank}/{world}: 3-layer model sharded vs single rel_l2 = {err_m:.3e}", flush=True)
+assert err_m < 5e-4
 dist.barrier()
 dist.destroy_process_group()
