@@ -23,7 +23,6 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.conv_simt = env_on("HAET_CONV_SIMT");
         v.conv_nh1 = env_on("HAET_CONV_NH1");
         v.no_pdl = env_on("HAET_NO_PDL");
-        v.f2fp_pack = env_on("HAET_F2FP_PACK");
         const char *e = getenv("HAET_TREE_ROLES");
         v.tree_roles = e ? atoi(e) : 0;
         e = getenv("HAET_PEER_TIMEOUT_S");

@@ -48,7 +48,6 @@ struct DesliceCtl {
 __device__ __forceinline__ uint32_t dt_dbuf_col(int buf) { return 128u + (uint32_t)buf * DT_GCMAX; }
 __host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (G + 127) / 128 * 128; }
 
-template <bool ALU_PACK>   // P packed to fp16 on the integer pipes (tc.cuh: pack_h2_biased) instead of F2FP on the MUFU pipe
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
@@ -126,7 +125,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         *reinterpret_cast<uint4 *>(sV + sw128_off(g, ck + 4)) = make_uint4(0, 0, 0, 0);
     }
     for (int g = threadIdx.x; g < g_pad; g += DT_THREADS) {
-        sL[g] = g < G ? DT_PSHIFT - (ALU_PACK ? PACK_BIAS : 0.f) - lse2[(size_t)bh * G + g] : -INFINITY;
+        sL[g] = g < G ? DT_PSHIFT - lse2[(size_t)bh * G + g] : -INFINITY;
         uint32_t b2 = 0;
         if (g < G) {
             const float bc = bs[g] - shift;
@@ -321,14 +320,9 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                     const float4 k4 = ll[hh * 8 + (c >> 2)];   // 14 - lse2 of four slices
                     const float p0 = fast_ex2(fmaf(__uint_as_float(r[c]), sn, k4.x)), p1 = fast_ex2(fmaf(__uint_as_float(r[c + 1]), sn, k4.y));
                     const float p2 = fast_ex2(fmaf(__uint_as_float(r[c + 2]), sn, k4.z)), p3 = fast_ex2(fmaf(__uint_as_float(r[c + 3]), sn, k4.w));
-                    if (ALU_PACK) {
-                        pk[c >> 1] = pack_h2_biased(p0, p1);
-                        pk[(c >> 1) + 1] = pack_h2_biased(p2, p3);
-                    } else {
-                        const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
-                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
-                        pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
-                    }
+                    const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                    pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
                 }
                 tmem_st16(dcol + hh * 16, pk);   // packed P trails the logits it replaces (columns already read)
             }
@@ -353,9 +347,7 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const int g_pad = dt_gpad(s->slice_num);
     const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
                         sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
-    const bool alu = !options().f2fp_pack;
-    if (alu) HAET_DYN_SMEM(deslice_tc_kernel<true>, smem);
-    else HAET_DYN_SMEM(deslice_tc_kernel<false>, smem);
+    HAET_DYN_SMEM(deslice_tc_kernel, smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -366,12 +358,8 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     if (n_chunks > max_chunks) n_chunks = max_chunks;
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
-    if (alu)
-        deslice_tc_kernel<true><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                                 xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
-    else
-        deslice_tc_kernel<false><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                                  xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
+    deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
+                                                       xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
     HAET_LAUNCHED();
     return HAET_OK;
 }

@@ -37,11 +37,6 @@ constexpr int ST_SCOLS = 32;        // TMEM columns of one warpgroup's accumulat
 constexpr int ST_NBUF = 3;          // D / P buffers per issue stream
 constexpr float ST_RAISE = 15.0f;   // lazy-max threshold (log2 units): P <= 2^15 fits fp16
 constexpr float ST_HEAD = 7.0f;     // a (re)set reference sits this far below the max that caused it
-// ALU_PACK variant (P packed on the integer pipes, tc.cuh: pack_h2_biased): fp16 subnormals are not produced, P flushes to
-// zero below 2^-14 -- and so does the p that feeds l (ex2.approx.ftz on the biased argument), so S and l lose the SAME mass.
-// The reference therefore sits 14 units below the max (flush at 2^-28 of the largest weight seen) and is raised past 2^15.9.
-constexpr float ST_RAISE_ALU = 15.9f;
-constexpr float ST_HEAD_ALU = 14.0f;
 
 struct SliceCtl {
     uint64_t b_full[ST_STAGES], b_empty[ST_STAGES];
@@ -54,7 +49,6 @@ struct SliceCtl {
 // TMEM columns: accumulators of the 4 softmax warpgroups at 0..127, D / P buffers [stream][3] x 64 at 128..511
 __device__ __forceinline__ uint32_t st_dbuf_col(int w, int buf) { return 128u + (uint32_t)(w * ST_NBUF + buf) * ST_TILE; }
 
-template <bool ALU_PACK>
 __global__ void __launch_bounds__(ST_THREADS, 1)
 slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
                 const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int C, int64_t chunk_pts,
@@ -243,28 +237,20 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 // below recomputes P from the kept t.
                 float tmax = -INFINITY, l0 = 0.f, l1 = 0.f;
                 uint32_t pk[16];   // P as packed fp16: word c = points (2c, 2c+1) of this half
-                constexpr float kBias = ALU_PACK ? PACK_BIAS : 0.f, kHead = ALU_PACK ? ST_HEAD_ALU : ST_HEAD;
-                const float nm = -(m_run + kBias);   // ALU_PACK: every exponent argument carries -112 (l is un-biased at the end)
 #pragma unroll
                 for (int c = 0; c < 32; c += 4) {
                     const float4 sa = s4[hh * 8 + (c >> 2)];
-                    const float v0 = fmaf(__uint_as_float(r[c]), sa.x, nm), v1 = fmaf(__uint_as_float(r[c + 1]), sa.y, nm);
-                    const float v2 = fmaf(__uint_as_float(r[c + 2]), sa.z, nm), v3 = fmaf(__uint_as_float(r[c + 3]), sa.w, nm);
+                    const float v0 = fmaf(__uint_as_float(r[c]), sa.x, -m_run), v1 = fmaf(__uint_as_float(r[c + 1]), sa.y, -m_run);
+                    const float v2 = fmaf(__uint_as_float(r[c + 2]), sa.z, -m_run), v3 = fmaf(__uint_as_float(r[c + 3]), sa.w, -m_run);
                     r[c] = __float_as_uint(v0); r[c + 1] = __float_as_uint(v1); r[c + 2] = __float_as_uint(v2); r[c + 3] = __float_as_uint(v3);
                     tmax = fmaxf(fmaxf(tmax, v0), v1);   // FMNMX3
                     tmax = fmaxf(fmaxf(tmax, v2), v3);
                     const float p0 = fast_ex2(v0), p1 = fast_ex2(v1), p2 = fast_ex2(v2), p3 = fast_ex2(v3);
                     l0 += p0; l1 += p1; l0 += p2; l1 += p3;
-                    if (ALU_PACK) {
-                        pk[c >> 1] = pack_h2_biased(p0, p1);
-                        pk[(c >> 1) + 1] = pack_h2_biased(p2, p3);
-                    } else {
-                        const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
-                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
-                        pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
-                    }
+                    const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                    pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
                 }
-                tmax += kBias;   // back to "log2 units above the running reference"
                 if (ragged) {   // columns past the chunk's last point: weight 0 (their image rows are zero)
                     tmax = -INFINITY;
 #pragma unroll
@@ -272,13 +258,12 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                         if (hh * 32 + c >= last_valid) r[c] = __float_as_uint(-INFINITY);
                         tmax = fmaxf(tmax, __uint_as_float(r[c]));
                     }
-                    tmax += kBias;
                 }
                 // lazy running reference: the very first half fixes it (max - ST_HEAD), later ones raise it only past 2^raise_thr
                 const bool first = (i == 0 && hh == 0);
                 const bool need = first || tmax > raise_thr;
                 if (ragged || __any_sync(0xffffffffu, need)) {   // warp-uniform (ragged is per tile)
-                    const float delta = need ? tmax - kHead : 0.f;   // m_new = m_run + delta: the new max maps to 2^head
+                    const float delta = need ? tmax - ST_HEAD : 0.f;   // m_new = m_run + delta: the new max maps to 2^ST_HEAD
                     const float sc = first ? 0.f : fast_ex2(-delta);
                     m_run += delta;
                     l_run *= sc;
@@ -287,12 +272,8 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                     for (int c = 0; c < 32; c += 2) {   // P again, at the raised max (and with the ragged columns masked)
                         const float p0 = fast_ex2(__uint_as_float(r[c]) - delta), p1 = fast_ex2(__uint_as_float(r[c + 1]) - delta);
                         l0 += p0; l1 += p1;
-                        if (ALU_PACK) {
-                            pk[c >> 1] = pack_h2_biased(p0, p1);
-                        } else {
-                            const __half2 h2 = __floats2half2_rn(p0, p1);
-                            pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&h2);
-                        }
+                        const __half2 h2 = __floats2half2_rn(p0, p1);
+                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&h2);
                     }
                     if (i > 0) {   // rescale this warpgroup's TMEM accumulator (its earlier MMA2s are done)
                         mbar_wait(&ctl->mma2_done[w][sub], (uint32_t)((i - 1) & 1));
@@ -339,7 +320,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 tmem_ld32(scol, s0);
                 tmem_wait_ld();
                 if (g < G) {
-                    o[0] = m_run; o[1] = ALU_PACK ? l_run * PACK_UNBIAS : l_run;
+                    o[0] = m_run; o[1] = l_run;
 #pragma unroll
                     for (int c = 0; c < 32; ++c) if (c < C) o[2 + c] = __uint_as_float(s0[c]);
                 }
@@ -386,18 +367,12 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
     const int n_gb = (s->slice_num + ST_GB - 1) / ST_GB;
     const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
-    const bool alu = !options().f2fp_pack;
-    if (alu) HAET_DYN_SMEM(slice_tc_kernel<true>, smem);
-    else HAET_DYN_SMEM(slice_tc_kernel<false>, smem);
+    HAET_DYN_SMEM(slice_tc_kernel, smem);
     const int64_t chunk_pts = slice_tc_chunk_pts(s);
-    const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : (alu ? ST_RAISE_ALU : ST_RAISE);   // haet_set_raise_threshold: tests force the accumulator-rescale path
+    const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : ST_RAISE;   // haet_set_raise_threshold: tests force the accumulator-rescale path
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads));
-    if (alu)
-        slice_tc_kernel<true><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
-                                                               s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
-    else
-        slice_tc_kernel<false><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
-                                                                s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
+    slice_tc_kernel<<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
+                                                     s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
     HAET_LAUNCHED();
     return HAET_OK;
 }

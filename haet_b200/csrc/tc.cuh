@@ -287,18 +287,6 @@ __device__ __forceinline__ float fast_ex2(float x) {   // MUFU.EX2 (2 ulp), flus
     return y;
 }
 
-// Two fp32 values that were computed 2^-112 too small (so that their fp32 exponent FIELD equals the fp16 exponent field of the
-// intended value; anything below the fp16 normal range has already been flushed to zero by ex2.approx.ftz) -> packed fp16x2,
-// rounded to nearest, WITHOUT the F2FP conversion instruction: F2FP shares the XU pipe with MUFU.EX2, which is what bounds the
-// slice / deslice passes.  (b << 3) + 0x8000 leaves the rounded half-precision bit pattern in the upper 16 bits (one IMAD / LEA
-// each), one byte permute packs the pair.  Requires 0 <= value < 2^16 * 2^-112 (bit 28 of the fp32 pattern clear).
-__device__ __forceinline__ uint32_t pack_h2_biased(float a, float b) {
-    const uint32_t x = __float_as_uint(a) * 8u + 0x8000u, y = __float_as_uint(b) * 8u + 0x8000u;
-    return __byte_perm(x, y, 0x7632);
-}
-constexpr float PACK_BIAS = 112.f;                        // fp32 exponent bias 127 - fp16 exponent bias 15
-constexpr float PACK_UNBIAS = 5.192296858534827628530496329220096e33f;   // 2^112
-
 // split an fp32 into bf16 hi + bf16 lo (hi + lo carries ~16 mantissa bits)
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16 &hi, __nv_bfloat16 &lo) {
     hi = __float2bfloat16_rn(v);
