@@ -225,7 +225,7 @@ def stage_times(m, x, iters=5):
             tree_idx, tree_mask, rots = balltree_device(pos, B * H, G, m.erwin.strides, m.erwin.ball_sizes,
                                                         float(m.erwin.rotate))
             e[4].record()
-            states = erwin_device(m.erwin, eid, pos, tree_idx, tree_mask, rots)
+            states = erwin_device(m.erwin, eid, pos, tree_idx, tree_mask, rots, B * H)
             e[5].record()
             deslice(4, states)
             e[6].record()

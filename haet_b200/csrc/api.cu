@@ -23,6 +23,7 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.conv_simt = env_on("HAET_CONV_SIMT");
         v.conv_nh1 = env_on("HAET_CONV_NH1");
         v.no_pdl = env_on("HAET_NO_PDL");
+        v.erwin_multi = env_on("HAET_ERWIN_MULTI");
         const char *e = getenv("HAET_TREE_ROLES");
         v.tree_roles = e ? atoi(e) : 0;
         e = getenv("HAET_PEER_TIMEOUT_S");
@@ -334,8 +335,8 @@ static int layer_forward_impl(const haet_layer_shape *s, const haet_erwin_cfg *c
     const int64_t T = s->B * s->heads * s->slice_num;
     if ((rc = haet_balltree_build(b.pos, s->B * s->heads, s->slice_num, s->dimensionality, c->strides, c->ball_sizes,
                                   c->n_levels, (double)c->rotate, b.tree_idx, b.tree_mask, b.rot, st))) return rc;
-    if ((rc = haet_erwin_forward(c, b.eidetic, b.pos, T, b.tree_idx, b.tree_mask, b.slots, b.rot, w->erwin_d, b.erwin_ws,
-                                 b.states, st))) return rc;
+    if ((rc = haet_erwin_forward_trees(c, b.eidetic, b.pos, T, s->B * s->heads, b.tree_idx, b.tree_mask, b.slots, b.rot, w->erwin_d,
+                                       b.erwin_ws, b.states, st))) return rc;
     return haet_deslice_out(s, b.spill, b.lse2, b.states, w->ws_d, w->bs_d, w->wt_d, w->bt, w->wo_d, w->bo_d, out_d, b.ws, st);
 }
 

@@ -190,33 +190,20 @@ __device__ void ball_attention_any(const float *qkv, int ldq, float *us, int ld,
 
 constexpr int EB_THREADS = 256;
 
-__global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restrict__ x, const float *__restrict__ pos,
-                                                                 const int64_t *__restrict__ perm,
-                                                                 const float *__restrict__ wts_g, BlockW w, int bs, int dim,
-                                                                 int heads, int hidden, int d, int w_lo, int w_n) {
-    extern __shared__ __align__(16) float sm[];
+// tokens / positions that OTHER CTAs of the same launch may have written in an earlier phase of the fused kernel are read
+// with ld.global.cg (L2, never the non-coherent path); the stand-alone kernel reads them through the read-only path
+template <bool COH> __device__ __forceinline__ float4 ld_tok4(const float4 *p) { return COH ? __ldcg(p) : __ldg(p); }
+template <bool COH> __device__ __forceinline__ float ld_tok(const float *p) { return COH ? __ldcg(p) : __ldg(p); }
+
+// One ErwinTransformerBlock (layers.py:30-32) on the ball of bs tokens starting at row `base` of the (possibly rotated)
+// sequence.  wts: the packed weights (the offsets of `w` are relative to it; shared or global memory); act: shared-memory
+// scratch of block_smem(bs, dim, hidden) bytes.  All threads of the CTA take part (contains __syncthreads).
+template <bool COH>
+__device__ void erwin_block_body(float *__restrict__ x, const float *__restrict__ pos, const int64_t *__restrict__ perm,
+                                 const float *wts, const BlockW &w, int bs, int dim, int heads, int hidden, int d, int64_t base,
+                                 float *act, uint64_t *wbar, uint32_t wparity) {
     const int ld = pad_dim(dim), ldq = pad_dim(3 * dim), ldh = pad_dim(hidden);
-    // the block's w_n packed weights (contiguous from float offset w_lo) are staged into shared memory by ONE bulk
-    // copy that overlaps the token gather: every linear layer then reads its weights at shared-memory latency (the
-    // kernel was bound by the L2 latency of those loads: 44 % long-scoreboard stalls, profiles/r1_ncu_summary.md)
-    uint64_t *wbar = reinterpret_cast<uint64_t *>(sm);   // sm[0..3]
-    float *wsm = sm + 4;                                  // [w_n]
-    const float *wts = wts_g;
-    // programmatic dependent launch (run_blocks sets the attribute): the NEXT kernel of the stream may start now -- its CTAs
-    // land on the idle SMs (64 balls on 148 SMs) and stage their weights while this one computes
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    if (w_n) {
-        if (threadIdx.x == 0) {
-            tc::mbar_init(wbar, 1);
-            tc::fence_barrier_init();
-            tc::mbar_arrive_expect_tx(wbar, (uint32_t)w_n * 4u);
-            tc::bulk_g2s(wsm, wts_g + w_lo, (uint32_t)w_n * 4u, wbar);   // weights are constants: no dependency on the previous kernel
-        }
-        wts = wsm - w_lo;
-    }
-    // everything below reads what the previous kernel of the stream wrote (tokens, positions, permutations)
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    float *xs = wsm + w_n;             // [bs][ld]   residual stream
+    float *xs = act;                   // [bs][ld]   residual stream
     float *us = xs + bs * ld;          // [bs][ld]   normed / attention output
     float *qkv = us + bs * ld;         // [bs][ldq]
     float *hid = qkv + bs * ldq;       // [bs][ldh]  gated SwiGLU product
@@ -224,26 +211,25 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restri
     float *cen = rel + bs * 4;         // [4]
     int *tok = reinterpret_cast<int *>(cen + 4);  // [bs]
     const int tid = threadIdx.x;
-    const int64_t base = (int64_t)blockIdx.x * bs;
     const bool vec = (dim & 3) == 0 && (hidden & 3) == 0;   // float4 paths
 
-    for (int i = tid; i < bs; i += blockDim.x) tok[i] = perm ? (int)perm[base + i] : (int)(base + i);
+    for (int i = tid; i < bs; i += blockDim.x) tok[i] = perm ? (int)(COH ? __ldcg(perm + base + i) : perm[base + i]) : (int)(base + i);
     __syncthreads();
     if (vec) {
         const int d4 = dim >> 2;
         for (int t = tid; t < bs * d4; t += blockDim.x) {
             const int i = t / d4, k = t - i * d4;
-            *reinterpret_cast<float4 *>(xs + i * ld + 4 * k) = __ldg(reinterpret_cast<const float4 *>(x + (int64_t)tok[i] * dim) + k);
+            *reinterpret_cast<float4 *>(xs + i * ld + 4 * k) = ld_tok4<COH>(reinterpret_cast<const float4 *>(x + (int64_t)tok[i] * dim) + k);
         }
     } else {
         for (int t = tid; t < bs * dim; t += blockDim.x) {
             const int i = t / dim, k = t - i * dim;
-            xs[i * ld + k] = x[(int64_t)tok[i] * dim + k];
+            xs[i * ld + k] = ld_tok<COH>(x + (int64_t)tok[i] * dim + k);
         }
     }
     for (int t = tid; t < bs * 4; t += blockDim.x) {
         const int i = t >> 2, j = t & 3;
-        rel[t] = j < d ? pos[(int64_t)tok[i] * d + j] : 0.f;
+        rel[t] = j < d ? ld_tok<COH>(pos + (int64_t)tok[i] * d + j) : 0.f;
     }
     __syncthreads();
     if (tid < d) {  // ball centre: mean over the ball (attention.py:35-40)
@@ -251,7 +237,7 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restri
         for (int i = 0; i < bs; ++i) s += rel[i * 4 + tid];
         cen[tid] = s / (float)bs;
     }
-    if (w_n) tc::mbar_wait(wbar, 0);   // initialised before the first __syncthreads above
+    if (wbar) tc::mbar_wait(wbar, wparity);   // the staged weights have landed
     ball_rmsnorm(xs, ld, wts + w.norm1, us, bs, dim);
     __syncthreads();
     for (int t = tid; t < bs * d; t += blockDim.x) { const int i = t / d, j = t - i * d; rel[i * 4 + j] -= cen[j]; }
@@ -303,6 +289,35 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restri
             x[(int64_t)tok[i] * dim + k] = xs[i * ld + k];
         }
     }
+}
+
+__global__ void __launch_bounds__(EB_THREADS) erwin_block_kernel(float *__restrict__ x, const float *__restrict__ pos,
+                                                                 const int64_t *__restrict__ perm,
+                                                                 const float *__restrict__ wts_g, BlockW w, int bs, int dim,
+                                                                 int heads, int hidden, int d, int w_lo, int w_n) {
+    extern __shared__ __align__(16) float sm[];
+    // the block's w_n packed weights (contiguous from float offset w_lo) are staged into shared memory by ONE bulk
+    // copy that overlaps the token gather: every linear layer then reads its weights at shared-memory latency (the
+    // kernel was bound by the L2 latency of those loads: 44 % long-scoreboard stalls, profiles/r1_ncu_summary.md)
+    uint64_t *wbar = reinterpret_cast<uint64_t *>(sm);   // sm[0..3]
+    float *wsm = sm + 4;                                  // [w_n]
+    const float *wts = wts_g;
+    // programmatic dependent launch (run_blocks sets the attribute): the NEXT kernel of the stream may start now -- its CTAs
+    // land on the idle SMs (64 balls on 148 SMs) and stage their weights while this one computes
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (w_n) {
+        if (threadIdx.x == 0) {
+            tc::mbar_init(wbar, 1);
+            tc::fence_barrier_init();
+            tc::mbar_arrive_expect_tx(wbar, (uint32_t)w_n * 4u);
+            tc::bulk_g2s(wsm, wts_g + w_lo, (uint32_t)w_n * 4u, wbar);   // weights are constants: no dependency on the previous kernel
+        }
+        wts = wsm - w_lo;
+    }
+    // everything below reads what the previous kernel of the stream wrote (tokens, positions, permutations)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    erwin_block_body<false>(x, pos, perm, wts, w, bs, dim, heads, hidden, d, (int64_t)blockIdx.x * bs, wsm + w_n,
+                            w_n ? wbar : nullptr, 0);
 }
 
 static size_t block_smem(int bs, int dim, int hidden) {
@@ -373,6 +388,168 @@ __global__ void erwin_unpool_kernel(const float *__restrict__ xp, const float *_
         for (int j = 0; j < d; ++j)
             acc = fmaf(pc[(n * s + mm) * d + j] - pp[n * d + j], wr[in_dim + mm * d + j], acc);
     xc[t] = fmaf(xc[t] + acc, wts[w.scale + c], wts[w.shift + c]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The whole Erwin pass as ONE cooperative kernel (round 2).  Everything in erwin_flash.py:176-193 is local to a TREE: balls,
+// rotated permutations, pooling and unpooling never cross trees, eval-mode BatchNorm is a per-channel affine.  So the CTAs
+// are grouped per tree (group = the tree's balls at the level with most balls) and the 10 launches become 10 phases separated
+// by per-tree barriers (a counter in global memory per tree; the launch is cooperative, so all CTAs are co-resident and a
+// spin on another CTA's arrival is legal).  Tokens that cross a phase are read with ld.global.cg after an acquire fence.
+// The next block's weights are bulk-copied into shared memory before the barrier wait, so the copy hides behind it.
+// ---------------------------------------------------------------------------------------------------------------------
+enum { PH_GATHER = 0, PH_BLOCK = 1, PH_POOL = 2, PH_UNPOOL = 3, PH_SCATTER = 4 };
+struct ErwinPhase {
+    int type, level;        // level of x / pos (PH_POOL, PH_UNPOOL: the CHILD level; parents live at level + 1)
+    int use_rot;            // PH_BLOCK: run on the rotated permutation of its level
+    int heads, w_lo, w_n;   // PH_BLOCK: heads, packed weights [w_lo, w_lo + w_n) staged in shared memory (w_n == 0: read from global)
+    BlockW bw;
+    PoolW pw;
+};
+constexpr int EF_MAX_PHASES = 24;
+constexpr int EF_MAX_TREES = 4096;
+struct ErwinProgram {
+    int n_phases, n_levels, d, mlp_ratio;
+    int n_trees, group_ctas;                 // CTAs per tree group; CTA c belongs to tree c / group_ctas
+    int dim[HAET_MAX_LEVELS], bs[HAET_MAX_LEVELS], stride[HAET_MAX_LEVELS];
+    int64_t npt[HAET_MAX_LEVELS];            // tokens per tree at each level
+    float *xs[HAET_MAX_LEVELS], *ps[HAET_MAX_LEVELS];
+    const int64_t *rot[HAET_MAX_LEVELS];
+    int act_off;                             // float offset of the activation scratch behind the staged weights
+    unsigned long long timeout_ns;
+    ErwinPhase ph[EF_MAX_PHASES];
+};
+
+__device__ __forceinline__ unsigned long long ef_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// barrier among the CTAs of one tree group: arrival k of this launch completes when the counter reaches k * group_ctas
+__device__ __forceinline__ void ef_group_barrier(unsigned int *counter, unsigned int target, unsigned long long timeout_ns) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        const unsigned long long t0 = ef_now();
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.gpu.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+            if (v < target && ef_now() - t0 > timeout_ns) {   // a missing CTA must not hang the GPU: fail loudly
+                printf("haet erwin_fused_kernel: tree barrier timed out (block %d, %u of %u)\n", blockIdx.x, v, target);
+                asm volatile("trap;");
+            }
+        } while (v < target);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(EB_THREADS) erwin_fused_kernel(const float *__restrict__ x_in, const float *__restrict__ pos_in,
+                                                                 const int64_t *__restrict__ tree_idx, const uint8_t *__restrict__ tree_mask,
+                                                                 const float *__restrict__ wts_g, float *__restrict__ out,
+                                                                 unsigned int *__restrict__ counters, const __grid_constant__ ErwinProgram P) {
+    extern __shared__ __align__(16) float sm[];
+    uint64_t *wbar = reinterpret_cast<uint64_t *>(sm);   // sm[0..3]
+    float *wsm = sm + 4;
+    float *act = sm + 4 + P.act_off;
+    const int tid = threadIdx.x;
+    const int tree = blockIdx.x / P.group_ctas, j = blockIdx.x - tree * P.group_ctas;   // j: this CTA inside its tree group
+    const int gthreads = P.group_ctas * EB_THREADS, gt = j * EB_THREADS + tid;          // thread index inside the group
+    unsigned int *ctr = counters + tree;
+    if (tid == 0) { tc::mbar_init(wbar, 1); tc::fence_barrier_init(); }
+    __syncthreads();
+    uint32_t wpar = 0;
+    auto stage_weights = [&](const ErwinPhase &ph) {   // issue the bulk copy of a block phase's weights (thread 0)
+        if (ph.type == PH_BLOCK && ph.w_n && tid == 0) {
+            tc::mbar_arrive_expect_tx(wbar, (uint32_t)ph.w_n * 4u);
+            tc::bulk_g2s(wsm, wts_g + ph.w_lo, (uint32_t)ph.w_n * 4u, wbar);
+        }
+    };
+    stage_weights(P.ph[0]);
+    const int d = P.d;
+    for (int k = 0; k < P.n_phases; ++k) {
+        const ErwinPhase &ph = P.ph[k];
+        const int L = ph.level;
+        if (ph.type == PH_GATHER) {   // erwin_flash.py:176-181: x[tree_idx], pos[tree_idx]
+            const int dim = P.dim[0], W = dim + d;
+            const int64_t n = P.npt[0], r0 = (int64_t)tree * n;
+            for (int64_t t = gt; t < n * W; t += gthreads) {
+                const int64_t i = r0 + t / W;
+                const int c = (int)(t % W);
+                const int64_t src = tree_idx[i];
+                if (c < dim) P.xs[0][i * dim + c] = x_in[src * dim + c];
+                else P.ps[0][i * d + (c - dim)] = pos_in[src * d + (c - dim)];
+            }
+        } else if (ph.type == PH_BLOCK) {
+            const int bs = P.bs[L], dim = P.dim[L];
+            const int64_t balls = P.npt[L] / bs;
+            const float *wts = ph.w_n ? wsm - ph.w_lo : wts_g;
+            // every CTA of the group waits for its staged weights (its own barrier) even if it has no ball at this level
+            if (j < balls)
+                erwin_block_body<true>(P.xs[L], P.ps[L], ph.use_rot ? P.rot[L] : nullptr, wts, ph.bw, bs, dim, ph.heads,
+                                       dim * P.mlp_ratio, d, ((int64_t)tree * balls + j) * bs, act, ph.w_n ? wbar : nullptr, wpar);
+            else if (ph.w_n)
+                tc::mbar_wait(wbar, wpar);
+            if (ph.w_n) wpar ^= 1;
+            __syncthreads();   // the weights in wsm are dead from here: the next phase's copy may overwrite them
+        } else if (ph.type == PH_POOL) {   // BallPooling (pooling.py:25-40), eval BatchNorm folded
+            const int s = P.stride[L], in_dim = P.dim[L], out_dim = P.dim[L + 1];
+            const int64_t n_par = P.npt[L + 1], p0 = (int64_t)tree * n_par;
+            const int K = s * in_dim + s * d;
+            const float *xc = P.xs[L], *pc = P.ps[L];
+            for (int64_t t = gt; t < n_par * out_dim; t += gthreads) {
+                const int64_t n = p0 + t / out_dim;
+                const int o = (int)(t % out_dim);
+                const float *wr = wts_g + ph.pw.w + (size_t)o * K;
+                float acc = wts_g[ph.pw.b + o];
+                const float *xr = xc + n * s * in_dim;
+                for (int kk = 0; kk < s * in_dim; ++kk) acc = fmaf(__ldcg(xr + kk), wr[kk], acc);
+                for (int jj = 0; jj < d; ++jj) {
+                    float c = 0.f;
+                    for (int m = 0; m < s; ++m) c += __ldcg(pc + (n * s + m) * d + jj);
+                    c = c / (float)s;
+                    if (o == 0) P.ps[L + 1][n * d + jj] = c;
+                    for (int m = 0; m < s; ++m) acc = fmaf(__ldcg(pc + (n * s + m) * d + jj) - c, wr[s * in_dim + m * d + jj], acc);
+                }
+                P.xs[L + 1][n * out_dim + o] = fmaf(acc, wts_g[ph.pw.scale + o], wts_g[ph.pw.shift + o]);
+            }
+        } else if (ph.type == PH_UNPOOL) {   // BallUnpooling (pooling.py:58-72)
+            const int s = P.stride[L], in_dim = P.dim[L + 1], out_dim = P.dim[L];
+            const int64_t n_par = P.npt[L + 1], p0 = (int64_t)tree * n_par;
+            const int K = in_dim + s * d;
+            const float *xp = P.xs[L + 1], *pp = P.ps[L + 1], *pc = P.ps[L];
+            float *xc = P.xs[L];
+            for (int64_t t = gt; t < n_par * s * out_dim; t += gthreads) {
+                const int64_t tokc = p0 * s + t / out_dim;
+                const int c = (int)(t % out_dim);
+                const int64_t n = tokc / s;
+                const int m = (int)(tokc - n * s);
+                const int row = m * out_dim + c;
+                const float *wr = wts_g + ph.pw.w + (size_t)row * K;
+                float acc = wts_g[ph.pw.b + row];
+                const float *xr = xp + n * in_dim;
+                for (int kk = 0; kk < in_dim; ++kk) acc = fmaf(__ldcg(xr + kk), wr[kk], acc);
+                for (int mm = 0; mm < s; ++mm)
+                    for (int jj = 0; jj < d; ++jj)
+                        acc = fmaf(__ldcg(pc + (n * s + mm) * d + jj) - __ldcg(pp + n * d + jj), wr[in_dim + mm * d + jj], acc);
+                const int64_t e = tokc * out_dim + c;
+                xc[e] = fmaf(__ldcg(xc + e) + acc, wts_g[ph.pw.scale + c], wts_g[ph.pw.shift + c]);
+            }
+        } else {   // PH_SCATTER: erwin_flash.py:193  out[tree_idx[i]] = x[i] where mask[i]
+            const int dim = P.dim[0];
+            const int64_t n = P.npt[0], r0 = (int64_t)tree * n;
+            for (int64_t t = gt; t < n * dim; t += gthreads) {
+                const int64_t i = r0 + t / dim;
+                const int c = (int)(t % dim);
+                if (tree_mask[i]) out[tree_idx[i] * dim + c] = __ldcg(P.xs[0] + i * dim + c);
+            }
+        }
+        if (k + 1 < P.n_phases) {
+            stage_weights(P.ph[k + 1]);   // constants: safe before the barrier, lands while we wait
+            ef_group_barrier(ctr, (unsigned int)(k + 1) * (unsigned int)P.group_ctas, P.timeout_ns);
+        }
+    }
 }
 
 // Launch with the programmatic-stream-serialization attribute: the kernel may be scheduled while its predecessor in the
@@ -464,7 +641,7 @@ extern "C" int64_t haet_erwin_workspace_bytes(const haet_erwin_cfg *c, int64_t n
         fl += align_up(n * c->c_hidden[i], 4) + align_up(n * c->dimensionality, 4);
         if (i + 1 < c->n_levels) n /= c->strides[i];
     }
-    return fl * (int64_t)sizeof(float);
+    return fl * (int64_t)sizeof(float) + EF_MAX_TREES * (int64_t)sizeof(unsigned int);   // + per-tree barrier counters (fused kernel)
 }
 
 static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64_t n, int level, int depth, int heads,
@@ -493,10 +670,143 @@ static int run_blocks(const haet_erwin_cfg *c, float *x, const float *pos, int64
     return HAET_OK;
 }
 
+// One cooperative launch for the whole pass (erwin_fused_kernel).  Returns 1 when the shape / device cannot take it (the caller
+// then uses the multi-launch path), a negative HAET_E* code on errors.
+static int erwin_forward_fused(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t n_trees,
+                               const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                               int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d, float *out_d,
+                               cudaStream_t st) {
+    const int d = c->dimensionality, L = c->n_levels - 1;
+    if (options().erwin_multi || !c->decode || n_trees < 1 || n_trees > EF_MAX_TREES || n_slots % n_trees) return 1;
+    ErwinProgram P{};
+    P.n_levels = c->n_levels; P.d = d; P.mlp_ratio = c->mlp_ratio; P.n_trees = (int)n_trees;
+    P.timeout_ns = 5000000000ull;
+    size_t act_max = 0;
+    int64_t w_max = 0, group = 1;
+    {
+        float *p = (float *)workspace_d;
+        int64_t n = n_slots;
+        for (int i = 0; i < c->n_levels; ++i) {
+            P.dim[i] = c->c_hidden[i]; P.bs[i] = c->ball_sizes[i]; P.stride[i] = i < L ? c->strides[i] : 1;
+            P.npt[i] = n / n_trees;
+            if (n % n_trees || P.npt[i] % P.bs[i]) return 1;           // balls must not straddle trees
+            if (P.npt[i] / P.bs[i] > group) group = P.npt[i] / P.bs[i];
+            P.xs[i] = p; p += align_up(n * c->c_hidden[i], 4); P.ps[i] = p; p += align_up(n * d, 4);
+            P.rot[i] = (c->rotate > 0 && rot_idx_d) ? rot_idx_d[i] : nullptr;
+            if (i < L) {
+                if (c->strides[i] == 1 || n % c->strides[i] || (n / n_trees) % c->strides[i]) return 1;
+                n /= c->strides[i];
+            }
+        }
+    }
+    P.group_ctas = (int)group;
+    Walker wk;
+    int np = 0;
+    auto push = [&](int type, int level) -> ErwinPhase * {
+        if (np >= EF_MAX_PHASES) return nullptr;
+        ErwinPhase &ph = P.ph[np++];
+        ph = ErwinPhase{};
+        ph.type = type; ph.level = level;
+        return &ph;
+    };
+    auto blocks = [&](int level, int depth, int heads) -> int {
+        const int dim = c->c_hidden[level], hidden = dim * c->mlp_ratio, bs = c->ball_sizes[level];
+        const bool rotate = c->rotate > 0 && depth > 1;
+        const size_t act = block_smem(bs, dim, hidden);
+        if (act > 200 * 1024) return 1;
+        if (act > act_max) act_max = act;
+        for (int k = 0; k < depth; ++k) {
+            ErwinPhase *ph = push(PH_BLOCK, level);
+            if (!ph) return 1;
+            ph->bw = wk.block(dim, hidden, d, c->attn_bias ? heads : 0);
+            ph->heads = heads;
+            ph->use_rot = rotate && (k & 1);
+            if (ph->use_rot && !P.rot[level]) return HAET_EINVAL;
+            Walker probe; probe.block(dim, hidden, d, c->attn_bias ? heads : 0);
+            ph->w_lo = ph->bw.norm1;
+            ph->w_n = (act + (size_t)probe.off * 4 + 64 <= 220 * 1024 && !((dim | hidden) & 3)) ? (int)probe.off : 0;
+            if (ph->w_n > w_max) w_max = ph->w_n;
+        }
+        return 0;
+    };
+    if (!push(PH_GATHER, 0)) return 1;
+    int rc;
+    for (int i = 0; i < L; ++i) {
+        if ((rc = blocks(i, c->enc_depths[i], c->enc_num_heads[i]))) return rc;
+        ErwinPhase *ph = push(PH_POOL, i);
+        if (!ph) return 1;
+        ph->pw = wk.pool(c->c_hidden[i + 1], (int64_t)c->strides[i] * (c->c_hidden[i] + d), c->c_hidden[i + 1]);
+    }
+    if ((rc = blocks(L, c->enc_depths[L], c->enc_num_heads[L]))) return rc;
+    for (int i = L - 1; i >= 0; --i) {
+        ErwinPhase *ph = push(PH_UNPOOL, i);
+        if (!ph) return 1;
+        ph->pw = wk.pool((int64_t)c->strides[i] * c->c_hidden[i], c->c_hidden[i + 1] + (int64_t)c->strides[i] * d, c->c_hidden[i]);
+        if ((rc = blocks(i, c->dec_depths[i], c->dec_num_heads[i]))) return rc;
+    }
+    if (!push(PH_SCATTER, 0)) return 1;
+    P.n_phases = np;
+    // a staged block must fit next to the LARGEST staged weights (fixed layout: [barrier | weights | activations])
+    P.act_off = (int)align_up(w_max, 4);
+    const size_t smem = 16 + (size_t)P.act_off * 4 + act_max + 64;
+    if (smem > 220 * 1024) return 1;
+    if (smem > 48 * 1024) HAET_DYN_SMEM(erwin_fused_kernel, smem);
+    int dev = 0, sms = 0, per_sm = 0, coop = 0;
+    HAET_CUDA(cudaGetDevice(&dev));
+    HAET_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    HAET_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    HAET_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, erwin_fused_kernel, EB_THREADS, smem));
+    const int64_t grid = n_trees * group;
+    if (!coop || grid > (int64_t)per_sm * sms) return 1;   // the tree barriers need every CTA resident
+    unsigned int *counters = reinterpret_cast<unsigned int *>((char *)workspace_d + haet_erwin_workspace_bytes(c, n_slots) -
+                                                               EF_MAX_TREES * (int64_t)sizeof(unsigned int));
+    HAET_CUDA(cudaMemsetAsync(counters, 0, (size_t)n_trees * sizeof(unsigned int), st));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(EB_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    HAET_CUDA(cudaLaunchKernelEx(&cfg, erwin_fused_kernel, x_d, pos_d, tree_idx_d, tree_mask_d, weights_d, out_d, counters, P));
+    HAET_LAUNCHED();
+    return HAET_OK;
+}
+
+static int erwin_forward_multi(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T,
+                               const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                               int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
+                               float *out_d, void *stream);
+
+extern "C" int haet_erwin_forward_trees(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T, int64_t n_trees,
+                                        const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                                        int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
+                                        float *out_d, void *stream) {
+    int rc = check_cfg(c);
+    if (rc) return rc;
+    if (n_slots == 0) return HAET_OK;
+    HAET_CHECK_ARG(n_trees >= 1, "haet_erwin_forward_trees: n_trees must be >= 1");
+    rc = erwin_forward_fused(c, x_d, pos_d, n_trees, tree_idx_d, tree_mask_d, n_slots, rot_idx_d, weights_d, workspace_d, out_d,
+                             (cudaStream_t)stream);
+    if (rc <= 0) return rc;
+    return erwin_forward_multi(c, x_d, pos_d, T, tree_idx_d, tree_mask_d, n_slots, rot_idx_d, weights_d, workspace_d, out_d, stream);
+}
+
+// Without the tree count every CTA belongs to one group (one barrier domain): still one launch, coarser barriers.
 extern "C" int haet_erwin_forward(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T,
                                   const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
                                   int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
                                   float *out_d, void *stream) {
+    return haet_erwin_forward_trees(c, x_d, pos_d, T, 1, tree_idx_d, tree_mask_d, n_slots, rot_idx_d, weights_d, workspace_d, out_d, stream);
+}
+
+static int erwin_forward_multi(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T,
+                               const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                               int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
+                               float *out_d, void *stream) {
     int rc = check_cfg(c);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;

@@ -216,10 +216,11 @@ class ErwinTransformer(nn.Module):
         T = x.shape[0]
         pts = pts_per_tree if pts_per_tree is not None else _uniform_pts(batch_idx, T)
         tree_idx, tree_mask, rots = balltree_device(pos, T // pts, pts, self.strides, self.ball_sizes, float(self.rotate))
-        return erwin_device(self, x, pos, tree_idx, tree_mask, rots)
+        return erwin_device(self, x, pos, tree_idx, tree_mask, rots, T // pts)
 
 
-def erwin_device(erwin: ErwinTransformer, x, pos, tree_idx, tree_mask, rots):
+def erwin_device(erwin: ErwinTransformer, x, pos, tree_idx, tree_mask, rots, n_trees: int = 1):
+    """haet_erwin_forward_trees: with the tree count the whole pass is one cooperative kernel with per-tree barriers."""
     l = _lib.lib()
     dev = x.device
     w = erwin.packed_weights(dev)
@@ -230,7 +231,7 @@ def erwin_device(erwin: ErwinTransformer, x, pos, tree_idx, tree_mask, rots):
     nl = erwin.cfg.n_levels
     rot_ptrs = (C.c_void_p * nl)(*[(r.data_ptr() if r is not None else None) for r in rots])
     st = torch.cuda.current_stream(dev).cuda_stream
-    _lib.check(l.haet_erwin_forward(C.byref(erwin.cfg), x.data_ptr(), pos.data_ptr(), x.shape[0], tree_idx.data_ptr(),
-                                    tree_mask.data_ptr(), n_slots, rot_ptrs, w.data_ptr(), ws.data_ptr(),
-                                    out.data_ptr(), st))
+    _lib.check(l.haet_erwin_forward_trees(C.byref(erwin.cfg), x.data_ptr(), pos.data_ptr(), x.shape[0], max(int(n_trees), 1),
+                                          tree_idx.data_ptr(), tree_mask.data_ptr(), n_slots, rot_ptrs, w.data_ptr(),
+                                          ws.data_ptr(), out.data_ptr(), st))
     return out

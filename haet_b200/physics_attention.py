@@ -149,7 +149,7 @@ class _PhysicsAttentionBase(nn.Module):
                                       "implemented); call .eval()")
         tree_idx, tree_mask, rots = balltree_device(pos, B * H, G, self.erwin.strides, self.erwin.ball_sizes,
                                                     float(self.erwin.rotate))
-        states = erwin_device(self.erwin, eidetic, pos, tree_idx, tree_mask, rots)
+        states = erwin_device(self.erwin, eidetic, pos, tree_idx, tree_mask, rots, B * H)
         out = torch.empty(B, N, self.dim, **f32)
         if residual and self.to_out[1].p > 0 and self.to_out[1].training:
             raise NotImplementedError("forward_block is eval-mode only (dropout sits between to_out and the residual)")

@@ -169,6 +169,15 @@ int haet_erwin_forward(const haet_erwin_cfg *c, const float *x_d, const float *p
                        int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
                        float *out_d, void *stream);
 
+/* The same with the number of trees given (n_slots / n_trees slots each): the pass then runs as ONE cooperative kernel whose
+ * phases (gather, blocks, pool / unpool, scatter) are separated by per-TREE barriers -- nothing in Erwin crosses a tree.
+ * haet_erwin_forward is this call with n_trees = 1 (one barrier domain).  Shapes the fused kernel cannot take (balls straddling
+ * trees, stride 1, more CTAs than can be co-resident) run the launch-per-block path; HAET_ERWIN_MULTI=1 forces it. */
+int haet_erwin_forward_trees(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T, int64_t n_trees,
+                             const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                             int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
+                             float *out_d, void *stream);
+
 /* ---- deslice + to_out (pass 2 over the points) -------------------------------------
  * states_d [B*heads*G, C] = Erwin output; lse2_d from haet_slice_merge; out_d [B, N, dim]. */
 int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float *lse2_d,

