@@ -23,7 +23,7 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.conv_simt = env_on("HAET_CONV_SIMT");
         v.conv_nh1 = env_on("HAET_CONV_NH1");
         v.no_pdl = env_on("HAET_NO_PDL");
-        v.erwin_multi = env_on("HAET_ERWIN_MULTI");
+        v.erwin_fused = env_on("HAET_ERWIN_FUSED");
         const char *e = getenv("HAET_TREE_ROLES");
         v.tree_roles = e ? atoi(e) : 0;
         e = getenv("HAET_PEER_TIMEOUT_S");

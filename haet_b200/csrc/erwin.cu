@@ -391,7 +391,10 @@ __global__ void erwin_unpool_kernel(const float *__restrict__ xp, const float *_
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// The whole Erwin pass as ONE cooperative kernel (round 2).  Everything in erwin_flash.py:176-193 is local to a TREE: balls,
+// The whole Erwin pass as ONE cooperative kernel (round 2; OPT-IN with HAET_ERWIN_FUSED=1 -- measured SLOWER than the
+// launch-per-block path with programmatic dependent launch: 0.193 against 0.165 ms at config 4 (64 CTAs, 10 phases): a per-tree
+// barrier costs what a dependent launch costs under graph replay, and the weights of a block cannot be staged while the previous
+// block of the same CTA still uses the staging buffer, which the separate launches overlap for free on idle SMs).  Everything in erwin_flash.py:176-193 is local to a TREE: balls,
 // rotated permutations, pooling and unpooling never cross trees, eval-mode BatchNorm is a per-channel affine.  So the CTAs
 // are grouped per tree (group = the tree's balls at the level with most balls) and the 10 launches become 10 phases separated
 // by per-tree barriers (a counter in global memory per tree; the launch is cooperative, so all CTAs are co-resident and a
@@ -466,11 +469,12 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_fused_kernel(const float *__
             tc::bulk_g2s(wsm, wts_g + ph.w_lo, (uint32_t)ph.w_n * 4u, wbar);
         }
     };
-    stage_weights(P.ph[0]);
     const int d = P.d;
     for (int k = 0; k < P.n_phases; ++k) {
         const ErwinPhase &ph = P.ph[k];
         const int L = ph.level;
+        const bool early = ph.type != PH_BLOCK && k + 1 < P.n_phases;   // the staging buffer is free during this phase
+        if (early) stage_weights(P.ph[k + 1]);
         if (ph.type == PH_GATHER) {   // erwin_flash.py:176-181: x[tree_idx], pos[tree_idx]
             const int dim = P.dim[0], W = dim + d;
             const int64_t n = P.npt[0], r0 = (int64_t)tree * n;
@@ -504,13 +508,13 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_fused_kernel(const float *__
                 const float *wr = wts_g + ph.pw.w + (size_t)o * K;
                 float acc = wts_g[ph.pw.b + o];
                 const float *xr = xc + n * s * in_dim;
-                for (int kk = 0; kk < s * in_dim; ++kk) acc = fmaf(__ldcg(xr + kk), wr[kk], acc);
+                for (int kk = 0; kk < s * in_dim; ++kk) acc = fmaf(xr[kk], wr[kk], acc);
                 for (int jj = 0; jj < d; ++jj) {
                     float c = 0.f;
-                    for (int m = 0; m < s; ++m) c += __ldcg(pc + (n * s + m) * d + jj);
+                    for (int m = 0; m < s; ++m) c += pc[(n * s + m) * d + jj];
                     c = c / (float)s;
                     if (o == 0) P.ps[L + 1][n * d + jj] = c;
-                    for (int m = 0; m < s; ++m) acc = fmaf(__ldcg(pc + (n * s + m) * d + jj) - c, wr[s * in_dim + m * d + jj], acc);
+                    for (int m = 0; m < s; ++m) acc = fmaf(pc[(n * s + m) * d + jj] - c, wr[s * in_dim + m * d + jj], acc);
                 }
                 P.xs[L + 1][n * out_dim + o] = fmaf(acc, wts_g[ph.pw.scale + o], wts_g[ph.pw.shift + o]);
             }
@@ -529,12 +533,12 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_fused_kernel(const float *__
                 const float *wr = wts_g + ph.pw.w + (size_t)row * K;
                 float acc = wts_g[ph.pw.b + row];
                 const float *xr = xp + n * in_dim;
-                for (int kk = 0; kk < in_dim; ++kk) acc = fmaf(__ldcg(xr + kk), wr[kk], acc);
+                for (int kk = 0; kk < in_dim; ++kk) acc = fmaf(xr[kk], wr[kk], acc);
                 for (int mm = 0; mm < s; ++mm)
                     for (int jj = 0; jj < d; ++jj)
-                        acc = fmaf(__ldcg(pc + (n * s + mm) * d + jj) - __ldcg(pp + n * d + jj), wr[in_dim + mm * d + jj], acc);
+                        acc = fmaf(pc[(n * s + mm) * d + jj] - pp[n * d + jj], wr[in_dim + mm * d + jj], acc);
                 const int64_t e = tokc * out_dim + c;
-                xc[e] = fmaf(__ldcg(xc + e) + acc, wts_g[ph.pw.scale + c], wts_g[ph.pw.shift + c]);
+                xc[e] = fmaf(xc[e] + acc, wts_g[ph.pw.scale + c], wts_g[ph.pw.shift + c]);
             }
         } else {   // PH_SCATTER: erwin_flash.py:193  out[tree_idx[i]] = x[i] where mask[i]
             const int dim = P.dim[0];
@@ -546,7 +550,7 @@ __global__ void __launch_bounds__(EB_THREADS) erwin_fused_kernel(const float *__
             }
         }
         if (k + 1 < P.n_phases) {
-            stage_weights(P.ph[k + 1]);   // constants: safe before the barrier, lands while we wait
+            if (!early) stage_weights(P.ph[k + 1]);   // constants: safe before the barrier, lands while we wait
             ef_group_barrier(ctr, (unsigned int)(k + 1) * (unsigned int)P.group_ctas, P.timeout_ns);
         }
     }
@@ -677,7 +681,7 @@ static int erwin_forward_fused(const haet_erwin_cfg *c, const float *x_d, const 
                                int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d, float *out_d,
                                cudaStream_t st) {
     const int d = c->dimensionality, L = c->n_levels - 1;
-    if (options().erwin_multi || !c->decode || n_trees < 1 || n_trees > EF_MAX_TREES || n_slots % n_trees) return 1;
+    if (!options().erwin_fused || !c->decode || n_trees < 1 || n_trees > EF_MAX_TREES || n_slots % n_trees) return 1;
     ErwinProgram P{};
     P.n_levels = c->n_levels; P.d = d; P.mlp_ratio = c->mlp_ratio; P.n_trees = (int)n_trees;
     P.timeout_ns = 5000000000ull;

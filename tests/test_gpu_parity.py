@@ -649,8 +649,8 @@ def test_patch_model_fuses_a_reference_shaped_model():
 
 
 def test_erwin_fused_kernel_equals_launch_per_block_path(tmp_path):
-    """The one-launch cooperative Erwin (per-tree barriers) against the launch-per-block path (HAET_ERWIN_MULTI=1, read once
-    per process, hence a child process): same arithmetic in the same order => bitwise equal, for power-of-two and ragged
+    """The opt-in one-launch cooperative Erwin (HAET_ERWIN_FUSED=1: per-tree barriers) against the default launch-per-block path
+    (the switch is read once per process, hence child processes): same arithmetic in the same order => bitwise equal, for power-of-two and ragged
     slice counts, with and without the tree count, and for the distance-bias variant."""
     import os
     import subprocess
@@ -674,16 +674,15 @@ for name, G, nt, variant in (("g256", 256, 8, "flash"), ("g100", 100, 3, "flash"
     e = e.cuda().eval()
     x = torch.randn(nt * G, 32, generator=g).cuda(); pos = torch.rand(nt * G, 3, generator=g).cuda()
     outs[name] = e(x, pos, pts_per_tree=G).cpu()
-    outs[name + "_1tree"] = e(x, pos, torch.arange(nt).repeat_interleave(G).cuda()).cpu() if False else outs[name]
 torch.save(outs, sys.argv[1])
 """ % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     res = {}
     for mode in ("fused", "multi"):
         env = dict(os.environ)
-        if mode == "multi":
-            env["HAET_ERWIN_MULTI"] = "1"
+        if mode == "fused":
+            env["HAET_ERWIN_FUSED"] = "1"
         else:
-            env.pop("HAET_ERWIN_MULTI", None)
+            env.pop("HAET_ERWIN_FUSED", None)
         path = str(tmp_path / (mode + ".pt"))
         r = subprocess.run([sys.executable, "-c", script, path], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
