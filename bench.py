@@ -399,7 +399,9 @@ def cpu_model_record():
 
 def ncu_traffic():
     """DRAM bytes per launch of each kernel from the committed ncu --set full summary (profiles/), or {}."""
-    p = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
+    p = os.path.join(ROOT, "profiles", "r2_ncu_summary.json")
+    if not os.path.exists(p):
+        p = os.path.join(ROOT, "profiles", "r1_ncu_summary.json")
     if not os.path.exists(p):
         return {}
     d = json.load(open(p))

@@ -106,6 +106,8 @@ class _PhysicsAttentionBase(nn.Module):
         x = x.contiguous().float()
         B, N, _ = x.shape
         dev = x.device
+        if B == 0:   # nothing to do (the C-ABI returns HAET_OK for an empty batch too)
+            return x.new_empty((0, N, self.dim), dtype=in_dtype)
         f32 = dict(dtype=torch.float32, device=dev)
         sh = self._shape(B, N)
         psh = C.byref(sh)

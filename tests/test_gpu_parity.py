@@ -692,6 +692,84 @@ torch.save(outs, sys.argv[1])
         assert torch.equal(res["fused"][k], res["multi"][k]), k
 
 
+@pytest.mark.parametrize("N", [1, 5, 63, 64, 65, 127, 129, 300])
+def test_tiny_and_ragged_meshes_on_the_tensor_core_shape(N):
+    """Meshes smaller than one tile / one chunk, and around the 64- and 128-point tile edges, on the tcgen05 shape (256 hidden,
+    8 x 32): most CTAs of the passes get no tile at all (neutral partials), the last tile is ragged."""
+    import haet_b200 as hb
+    kw = dict(dim=256, heads=8, dim_head=32, slice_num=32, rotate=45, mlp_ratio=2)
+    torch.manual_seed(100 + N)
+    m = hb.Physics_Attention_Irregular_Mesh(**kw).eval()
+    trained_like_(m, N)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    x = torch.nn.functional.layer_norm(torch.randn(2, N, 256), (256,))
+    m = m.cuda()
+    m.keep_taps = True
+    got = m(x.cuda())
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    taps = {}
+    want = O.physics_attention_forward(sd, x, tree=tree, pos_override=t["pos"].cpu(), taps=taps, heads=8, dim_head=32,
+                                       slice_num=32, rotate=45, mlp_ratio=2, dimensionality=3)
+    assert torch.isfinite(got).all()
+    assert rel_l2(t["S"], taps["S"]) < TOL and rel_l2(got, want) < TOL
+
+
+def test_empty_inputs():
+    """B == 0 is an empty result; a rank without points is an error (the softmax over the points has nothing to normalise)."""
+    import haet_b200 as hb
+    m = hb.Physics_Attention_Irregular_Mesh(256, heads=8, dim_head=32, slice_num=32, rotate=45, mlp_ratio=2).cuda().eval()
+    out = m(torch.zeros(0, 100, 256, device="cuda"))
+    assert out.shape == (0, 100, 256)
+    with pytest.raises(ValueError):
+        m(torch.zeros(1, 0, 256, device="cuda"))
+
+
+@pytest.mark.parametrize("N,G", [(1, 32), (130, 64), (4099, 256), (777, 100)])
+def test_layer_stays_inside_its_buffers(N, G):
+    """Canaries around every caller-owned buffer of the two passes (spill, workspace, partial, slice state, output) on ragged
+    meshes: compute-sanitizer is not usable on the GPU pool, so out-of-bounds writes are looked for this way."""
+    import haet_b200 as hb
+    from haet_b200 import _lib
+    l = _lib.lib()
+    torch.manual_seed(N)
+    m = hb.Physics_Attention_Irregular_Mesh(256, heads=8, dim_head=32, slice_num=G, rotate=45, mlp_ratio=2).eval()
+    trained_like_(m, 3)
+    m = m.cuda()
+    B, PAD = 2, 1 << 16
+    x = torch.nn.functional.layer_norm(torch.randn(B, N, 256, device="cuda"), (256,))
+    sh = m._shape(B, N)
+    psh = C.byref(sh)
+    st = torch.cuda.current_stream().cuda_stream
+    T = B * 8 * G
+
+    def guarded(nbytes):
+        big = torch.full((nbytes + 2 * PAD,), 0x5A, dtype=torch.uint8, device="cuda")
+        return big, big[PAD:PAD + nbytes]
+    wsz = max(l.haet_slice_workspace_bytes(psh), l.haet_deslice_workspace_bytes(psh))
+    bufs = {k: guarded(n) for k, n in dict(spill=l.haet_spill_bytes(psh), work=wsz, part=l.haet_partial_floats(psh) * 4,
+                                          eid=T * 32 * 4, lse=T * 4, pos=T * 3 * 4, out=B * N * 256 * 4).items()}
+    p = {k: v[1].data_ptr() for k, v in bufs.items()}
+    wx, bx = m._wx().float(), m.in_project_x.bias.detach()
+    ws, bs = m.in_project_slice.weight.detach().contiguous(), m.in_project_slice.bias.detach()
+    wt, bt = m.ada_temp_linear.weight.detach().view(-1).contiguous(), m._bt()
+    wo, bo = m.to_out[0].weight.detach().contiguous(), m.to_out[0].bias.detach()
+    x0 = x.clone()
+    _lib.check(l.haet_slice_reduce(psh, x.data_ptr(), wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(), wt.data_ptr(), bt,
+                                   p["spill"], p["part"], p["work"], st))
+    _lib.check(l.haet_slice_merge(psh, p["part"], 1, p["eid"], p["lse"], p["pos"], st))
+    states = torch.randn(T, 32, device="cuda")
+    _lib.check(l.haet_deslice_out(psh, p["spill"], p["lse"], states.data_ptr(), ws.data_ptr(), bs.data_ptr(), wt.data_ptr(), bt,
+                                  wo.data_ptr(), bo.data_ptr(), p["out"], p["work"], st))
+    torch.cuda.synchronize()
+    for k, (big, inner) in bufs.items():
+        n = inner.numel()
+        assert bool((big[:PAD] == 0x5A).all()) and bool((big[PAD + n:] == 0x5A).all()), f"{k}: write outside the buffer"
+    assert torch.equal(x, x0)
+    out = bufs["out"][1].view(torch.float32).view(B, N, 256)
+    assert torch.isfinite(out).all()
+
+
 def test_errors_are_loud():
     import haet_b200 as hb
     m = hb.Physics_Attention_Irregular_Mesh(64, heads=4, dim_head=16, slice_num=32, rotate=45)
