@@ -26,8 +26,6 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.erwin_fused = env_on("HAET_ERWIN_FUSED");
         const char *e = getenv("HAET_TREE_ROLES");
         v.tree_roles = e ? atoi(e) : 0;
-        e = getenv("HAET_POLY_COLS");
-        v.poly_cols = e ? atoi(e) : 0;
         e = getenv("HAET_PEER_TIMEOUT_S");
         v.peer_timeout_s = e ? atof(e) : 60.0;
         if (!(v.peer_timeout_s > 0.0)) v.peer_timeout_s = 60.0;

@@ -19,7 +19,6 @@ extern std::atomic<int64_t> g_launches;   // haet_launch_count()
 struct Options {
     bool gemm_1cta, no_opi, no_ln_fuse, conv_simt, conv_nh1, no_pdl, erwin_fused;
     int tree_roles;          // 0: one CTA per rotated level
-    int poly_cols;           // HAET_POLY_COLS: logits per 32 that the "FMA" softmax warpgroup exponentiates by polynomial
     double peer_timeout_s;
 };
 const Options &options();

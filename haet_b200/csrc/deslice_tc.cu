@@ -48,9 +48,6 @@ struct DesliceCtl {
 __device__ __forceinline__ uint32_t dt_dbuf_col(int buf) { return 128u + (uint32_t)buf * DT_GCMAX; }
 __host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (G + 127) / 128 * 128; }
 
-// PC: of every 32 logits of softmax warpgroup 2, the first PC are exponentiated by tc::poly_ex2 (FMA pipe), the rest -- and all
-// logits of warpgroups 0 and 1 -- by MUFU.EX2: one "FMA" warp and two "MUFU" warps per scheduler
-template <int PC>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
@@ -313,34 +310,19 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             tc_fence_after();
             const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(buf);
             const float4 *ll = reinterpret_cast<const float4 *>(sL + jc * cw);
-            const bool poly = PC > 0 && wg == 2;   // warp-uniform
 #pragma unroll 1
             for (int hh = 0; hh < halves; ++hh) {
                 uint32_t r[32], pk[16];
                 tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
-                if (poly) {
 #pragma unroll
-                    for (int c = 0; c < 32; c += 4) {
-                        const float4 k4 = ll[hh * 8 + (c >> 2)];   // 14 - lse2 of four slices
-                        const float t0 = fmaf(__uint_as_float(r[c]), sn, k4.x), t1 = fmaf(__uint_as_float(r[c + 1]), sn, k4.y);
-                        const float t2 = fmaf(__uint_as_float(r[c + 2]), sn, k4.z), t3 = fmaf(__uint_as_float(r[c + 3]), sn, k4.w);
-                        const float p0 = c < PC ? poly_ex2(t0) : fast_ex2(t0), p1 = c < PC ? poly_ex2(t1) : fast_ex2(t1);
-                        const float p2 = c < PC ? poly_ex2(t2) : fast_ex2(t2), p3 = c < PC ? poly_ex2(t3) : fast_ex2(t3);
-                        const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
-                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
-                        pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
-                    }
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 32; c += 4) {
-                        const float4 k4 = ll[hh * 8 + (c >> 2)];   // 14 - lse2 of four slices
-                        const float p0 = fast_ex2(fmaf(__uint_as_float(r[c]), sn, k4.x)), p1 = fast_ex2(fmaf(__uint_as_float(r[c + 1]), sn, k4.y));
-                        const float p2 = fast_ex2(fmaf(__uint_as_float(r[c + 2]), sn, k4.z)), p3 = fast_ex2(fmaf(__uint_as_float(r[c + 3]), sn, k4.w));
-                        const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
-                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
-                        pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
-                    }
+                for (int c = 0; c < 32; c += 4) {
+                    const float4 k4 = ll[hh * 8 + (c >> 2)];   // 14 - lse2 of four slices
+                    const float p0 = fast_ex2(fmaf(__uint_as_float(r[c]), sn, k4.x)), p1 = fast_ex2(fmaf(__uint_as_float(r[c + 1]), sn, k4.y));
+                    const float p2 = fast_ex2(fmaf(__uint_as_float(r[c + 2]), sn, k4.z)), p3 = fast_ex2(fmaf(__uint_as_float(r[c + 3]), sn, k4.w));
+                    const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                    pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
                 }
                 tmem_st16(dcol + hh * 16, pk);   // packed P trails the logits it replaces (columns already read)
             }
@@ -365,10 +347,7 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const int g_pad = dt_gpad(s->slice_num);
     const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
                         sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
-    const int pc = options().poly_cols;
-#define HAET_DT_CASE(P) case P: HAET_DYN_SMEM(deslice_tc_kernel<P>, smem); break
-    switch (pc) { HAET_DT_CASE(0); HAET_DT_CASE(16); HAET_DT_CASE(24); HAET_DT_CASE(32); default: HAET_CHECK_ARG(false, "HAET_POLY_COLS must be 0, 16, 24 or 32"); }
-#undef HAET_DT_CASE
+    HAET_DYN_SMEM(deslice_tc_kernel, smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -379,13 +358,8 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     if (n_chunks > max_chunks) n_chunks = max_chunks;
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
-#define HAET_DT_CASE(P)                                                                                                         \
-    case P:                                                                                                                     \
-        deslice_tc_kernel<P><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N, \
-                                                              xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image); \
-        break
-    switch (pc) { HAET_DT_CASE(0); HAET_DT_CASE(16); HAET_DT_CASE(24); HAET_DT_CASE(32); }
-#undef HAET_DT_CASE
+    deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
+                                                       xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
     HAET_LAUNCHED();
     return HAET_OK;
 }

@@ -20,8 +20,6 @@
 #include <cuda_fp16.h>
 #include <stdlib.h>
 
-#include <type_traits>
-
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -51,9 +49,6 @@ struct SliceCtl {
 // TMEM columns: accumulators of the 4 softmax warpgroups at 0..127, D / P buffers [stream][3] x 64 at 128..511
 __device__ __forceinline__ uint32_t st_dbuf_col(int w, int buf) { return 128u + (uint32_t)(w * ST_NBUF + buf) * ST_TILE; }
 
-// PC: of every 32 logits of softmax warpgroup 3, the first PC are exponentiated by tc::poly_ex2 (FMA pipe), everything else by
-// MUFU.EX2: one "FMA" warp beside three "MUFU" warps on every scheduler (deslice_tc.cu has the same split)
-template <int PC>
 __global__ void __launch_bounds__(ST_THREADS, 1)
 slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
                 const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int C, int64_t chunk_pts,
@@ -242,30 +237,20 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 // below recomputes P from the kept t.
                 float tmax = -INFINITY, l0 = 0.f, l1 = 0.f;
                 uint32_t pk[16];   // P as packed fp16: word c = points (2c, 2c+1) of this half
-                auto exps = [&](auto poly_tag) {   // the loop twice (compile-time flag) so that the MUFU warpgroups carry no branch
-                    constexpr bool POLY = decltype(poly_tag)::value;
 #pragma unroll
-                    for (int c = 0; c < 32; c += 4) {
-                        const float4 sa = s4[hh * 8 + (c >> 2)];
-                        const float v0 = fmaf(__uint_as_float(r[c]), sa.x, -m_run), v1 = fmaf(__uint_as_float(r[c + 1]), sa.y, -m_run);
-                        const float v2 = fmaf(__uint_as_float(r[c + 2]), sa.z, -m_run), v3 = fmaf(__uint_as_float(r[c + 3]), sa.w, -m_run);
-                        r[c] = __float_as_uint(v0); r[c + 1] = __float_as_uint(v1); r[c + 2] = __float_as_uint(v2); r[c + 3] = __float_as_uint(v3);
-                        tmax = fmaxf(fmaxf(tmax, v0), v1);   // FMNMX3
-                        tmax = fmaxf(fmaxf(tmax, v2), v3);
-                        float p0, p1, p2, p3;
-                        if (POLY && c < PC) {
-                            p0 = poly_ex2(v0); p1 = poly_ex2(v1); p2 = poly_ex2(v2); p3 = poly_ex2(v3);
-                        } else {
-                            p0 = fast_ex2(v0); p1 = fast_ex2(v1); p2 = fast_ex2(v2); p3 = fast_ex2(v3);
-                        }
-                        l0 += p0; l1 += p1; l0 += p2; l1 += p3;
-                        const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
-                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
-                        pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
-                    }
-                };
-                if (PC > 0 && wg == 3) exps(std::true_type{});
-                else exps(std::false_type{});
+                for (int c = 0; c < 32; c += 4) {
+                    const float4 sa = s4[hh * 8 + (c >> 2)];
+                    const float v0 = fmaf(__uint_as_float(r[c]), sa.x, -m_run), v1 = fmaf(__uint_as_float(r[c + 1]), sa.y, -m_run);
+                    const float v2 = fmaf(__uint_as_float(r[c + 2]), sa.z, -m_run), v3 = fmaf(__uint_as_float(r[c + 3]), sa.w, -m_run);
+                    r[c] = __float_as_uint(v0); r[c + 1] = __float_as_uint(v1); r[c + 2] = __float_as_uint(v2); r[c + 3] = __float_as_uint(v3);
+                    tmax = fmaxf(fmaxf(tmax, v0), v1);   // FMNMX3
+                    tmax = fmaxf(fmaxf(tmax, v2), v3);
+                    const float p0 = fast_ex2(v0), p1 = fast_ex2(v1), p2 = fast_ex2(v2), p3 = fast_ex2(v3);
+                    l0 += p0; l1 += p1; l0 += p2; l1 += p3;
+                    const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                    pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                    pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
+                }
                 if (ragged) {   // columns past the chunk's last point: weight 0 (their image rows are zero)
                     tmax = -INFINITY;
 #pragma unroll
@@ -382,20 +367,12 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
     const int n_gb = (s->slice_num + ST_GB - 1) / ST_GB;
     const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
-    const int pc = options().poly_cols;
-#define HAET_ST_CASE(P) case P: HAET_DYN_SMEM(slice_tc_kernel<P>, smem); break
-    switch (pc) { HAET_ST_CASE(0); HAET_ST_CASE(16); HAET_ST_CASE(24); HAET_ST_CASE(32); default: HAET_CHECK_ARG(false, "HAET_POLY_COLS must be 0, 16, 24 or 32"); }
-#undef HAET_ST_CASE
+    HAET_DYN_SMEM(slice_tc_kernel, smem);
     const int64_t chunk_pts = slice_tc_chunk_pts(s);
     const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : ST_RAISE;   // haet_set_raise_threshold: tests force the accumulator-rescale path
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads));
-#define HAET_ST_CASE(P)                                                                                                          \
-    case P:                                                                                                                      \
-        slice_tc_kernel<P><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N), \
-                                                            s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);       \
-        break
-    switch (pc) { HAET_ST_CASE(0); HAET_ST_CASE(16); HAET_ST_CASE(24); HAET_ST_CASE(32); }
-#undef HAET_ST_CASE
+    slice_tc_kernel<<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
+                                                     s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
     HAET_LAUNCHED();
     return HAET_OK;
 }

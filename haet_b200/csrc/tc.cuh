@@ -287,19 +287,6 @@ __device__ __forceinline__ float fast_ex2(float x) {   // MUFU.EX2 (2 ulp), flus
     return y;
 }
 
-// 2^t on the FMA / ALU pipes only (no MUFU): Cody-Waite split t = n + f with the 1.5 * 2^23 magic constant, a degree-3 minimax
-// polynomial for 2^f on [-0.5, 0.5] (max relative error 7.6e-5 -- a third of the fp16 half-ulp the result is rounded to
-// anyway) and n added to the exponent field (the low bits of t + magic ARE n).  t is clamped at -30 (2^-30 rounds to 0 in fp16);
-// valid for t < 127.  Used by ONE softmax warpgroup per pass so that, on every scheduler, a warp whose exponentials cost
-// FMA-pipe issue slots runs beside the warps whose exponentials cost MUFU-pipe cycles (the pipe that bounds the passes).
-__device__ __forceinline__ float poly_ex2(float t) {
-    t = fmaxf(t, -30.f);
-    const float r = t + 12582912.f;
-    const float f = t - (r - 12582912.f);
-    const float p = fmaf(fmaf(fmaf(0.05520550534129143f, f, 0.24261397123336792f), f, 0.6932547688484192f), f, 0.9999276995658875f);
-    return __uint_as_float(__float_as_uint(p) + (__float_as_uint(r) << 23));
-}
-
 // split an fp32 into bf16 hi + bf16 lo (hi + lo carries ~16 mantissa bits)
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16 &hi, __nv_bfloat16 &lo) {
     hi = __float2bfloat16_rn(v);
