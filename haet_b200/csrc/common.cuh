@@ -19,6 +19,7 @@ extern std::atomic<int64_t> g_launches;   // haet_launch_count()
 struct Options {
     bool gemm_1cta, no_opi, no_ln_fuse, conv_simt, conv_nh1, no_pdl, erwin_fused;
     int tree_roles;          // 0: one CTA per rotated level
+    int gemm_pf;             // HAET_GEMM_PF: L2 prefetch distance of the GEMM producers in (tile, panel) items
     double peer_timeout_s;
 };
 const Options &options();

@@ -116,12 +116,12 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
             gemm_produce<int>(X, M, K, panels, my_tiles, sA, row0,
                          [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
                          [&](int st) { mbar_arrive_remote(full0 + 8u * st); }, ep.dbg,
-                         [&](const float4 (&v)[GT_LD], int item) { ln.run(v, item, panels, row0, ep, M, K); });
+                         [&](const float4 (&v)[GT_LD], int item) { ln.run(v, item, panels, row0, ep, M, K); }, ep.pf);
         } else
         gemm_produce(X, M, K, panels, my_tiles, sA,
                      [&](int64_t ti) { return (pair + ti * n_pairs) * (int64_t)(2 * GT_M) + rank * GT_M; },
                      [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
-                     [&](int st) { mbar_arrive_remote(full0 + 8u * st); }, ep.dbg);
+                     [&](int st) { mbar_arrive_remote(full0 + 8u * st); }, ep.dbg, NoPanelHook(), ep.pf);
     } else if (warp == 8) {
         // ---------------- MMA issuer: the leader CTA only, whole warp in the loop, one elected lane issues ----------------
         if (rank == 0) {
@@ -235,6 +235,7 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     if (n_pairs > n_ptiles) n_pairs = (int)n_ptiles;
     if (n_pairs < 1) n_pairs = 1;
     GemmEpi epd = ep;
+    epd.pf = options().gemm_pf;
 #ifdef HAET_DEV_HOOKS   // timing ablations (results are garbage): never compiled into the shipped library
     if (const char *e = getenv("HAET_GEMM_DBG")) epd.dbg |= atoi(e);
 #endif

@@ -24,6 +24,7 @@ struct GemmEpi {   // EPI_IMG arguments
     float bt, base_temp;
     int64_t N, npad;   // rows m = b * N + n
     int H;
+    int pf;    // producers prefetch the fp32 rows of the item `pf` (tile, panel) items ahead of their register loads into L2 (0: off)
     int dbg;   // development switches (HAET_GEMM_DBG): 1 = no epilogue stores, 2 = no global loads
     int c16;   // EPI_IMG: dim_head == 16 -- a 32-column chunk holds TWO heads; each head's image row keeps its 16 channels in
                // chunks 0, 1 (hi) and 4, 5 (lo), the other chunks are zero (the passes run their dim_head-32 kernels on it)
@@ -72,7 +73,7 @@ struct NoPanelHook {
 //   (a 64-bit division is a subroutine call and the extra live registers pushed them into 100-230 B of spills: 0.72 -> 0.60 ms)
 template <class Idx = int64_t, class SrcFn, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
 __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uint8_t *sA, SrcFn srcf, WaitEmpty wait_empty,
-                                               ArriveFull arrive_full, PanelHook hook = PanelHook()) {
+                                               ArriveFull arrive_full, PanelHook hook = PanelHook(), int pf = 0) {
     using namespace tc;
     const int tid = threadIdx.x;
     const Idx total = (Idx)(my_tiles * panels);   // (tile, panel) items of this CTA, in order
@@ -89,6 +90,22 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
                 v[2 * i + 1] = __ldg(src + 1);
             } else {
                 v[2 * i] = v[2 * i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        // The register pipeline holds two panels (64 KB per SM) in flight: at a loaded HBM latency of ~2.7 us that is 3.5 TB/s
+        // of reads.  A short-distance L2 prefetch (one 128-byte line per 4 threads) turns the latency of the later register
+        // loads into L2 latency; the distance must stay within a few microseconds -- at 6.5 TB/s the 126 MB L2 turns over in
+        // ~20 us (round 1's bulk prefetch "tiles ahead" was evicted before use and read x from HBM twice).
+        if (pf > 0 && it + (Idx)pf < total) {
+            const Idx it2 = it + (Idx)pf, ti2 = it2 / (Idx)panels;
+            const int p2 = (int)(it2 - ti2 * panels);
+#pragma unroll
+            for (int i = 0; i < GT_LD / 2; ++i) {
+                const int idx = i * GT_PROD + tid, row = idx >> 3, c8 = idx & 7;
+                if ((c8 & 3) == 0) {
+                    const float *src = srcf(ti2, p2, i, row, c8);
+                    if (src) asm volatile("prefetch.global.L2 [%0];" ::"l"(src));
+                }
             }
         }
     };
@@ -136,13 +153,13 @@ __device__ __forceinline__ void gemm_produce_g(int panels, int64_t my_tiles, uin
 template <class Idx = int64_t, class Row0, class WaitEmpty, class ArriveFull, class PanelHook = NoPanelHook>
 __device__ __forceinline__ void gemm_produce(const float *__restrict__ X, int64_t M, int K, int panels, int64_t my_tiles,
                                              uint8_t *sA, Row0 row0, WaitEmpty wait_empty, ArriveFull arrive_full, int dbg = 0,
-                                             PanelHook hook = PanelHook()) {
+                                             PanelHook hook = PanelHook(), int pf = 0) {
     gemm_produce_g<Idx>(panels, my_tiles, sA,
                    [&](int64_t ti, int p, int, int row, int c8) -> const float * {
                        const int64_t m = row0(ti) + row;
                        return (m < M && !(dbg & 2)) ? X + m * K + p * GT_KP + c8 * 8 : nullptr;
                    },
-                   wait_empty, arrive_full, hook);
+                   wait_empty, arrive_full, hook, pf);
 }
 
 // LayerNorm statistics of the rows a producer thread touches (pair kernel, LN = true).  Thread tid holds, per panel, the 8
