@@ -213,7 +213,9 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
         int np = sms0 / 2;
         if (np > tiles) np = (int)tiles;
         if (np < 1) np = 1;
-        gemm2_tc_kernel<EPI_OPI, true, false><<<2 * np, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, np, ep);
+        GemmEpi epo = ep;
+        epo.pf = options().gemm_pf;
+        gemm2_tc_kernel<EPI_OPI, true, false><<<2 * np, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, np, epo);
         HAET_LAUNCHED();
         return HAET_OK;
     }

@@ -93,7 +93,7 @@ gemm_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
         gemm_produce(X, M, K, panels, my_tiles, sA,
                      [&](int64_t ti) { return (worker + ti * n_workers) * (int64_t)GT_M; },
                      [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
-                     [&](int st) { mbar_arrive(&cb->a_full[st]); });
+                     [&](int st) { mbar_arrive(&cb->a_full[st]); }, 0, NoPanelHook(), ep.pf);
     } else if (warp == 8) {
         // ---------------- MMA issuer ----------------
         if (lane == 0 && my_tiles > 0) {
@@ -191,7 +191,9 @@ static int launch_gemm_impl(const float *x, const float *w, const float *bias, f
     int n_workers = sm_count() / n_halves;
     if (n_workers < 1) n_workers = 1;
     if (n_workers > n_tiles) n_workers = (int)n_tiles;
-    gemm_tc_kernel<EPI><<<n_workers * n_halves, GT_THREADS, smem, st>>>(x, (const uint8_t *)img, bias, y, M, K, Nn, n_workers, ep);
+    GemmEpi epd = ep;
+    epd.pf = options().gemm_pf;
+    gemm_tc_kernel<EPI><<<n_workers * n_halves, GT_THREADS, smem, st>>>(x, (const uint8_t *)img, bias, y, M, K, Nn, n_workers, epd);
     HAET_LAUNCHED();
     if (EPI == EPI_F32 && ep.resid) return launch_add_rows(y, ep.resid, M * Nn, st);   // only the pair kernel fuses the residual
     return HAET_OK;
