@@ -186,6 +186,8 @@ head_ln_linear_kernel(const float *__restrict__ x, const float *__restrict__ gam
                 s1 += (v[i].x + v[i].y) + (v[i].z + v[i].w);
             }
         load(m + stride);
+        // two more rows ahead into L2 (the register pipeline alone keeps ~64 KB per SM in flight: latency, not bandwidth, bound)
+        if (m + 3 * stride < M && lane * 32 < dim) asm volatile("prefetch.global.L2 [%0];" ::"l"(x + (m + 3 * stride) * dim + lane * 32));
 #pragma unroll
         for (int o = 16; o; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
         const float mean = s1 / (float)dim;
