@@ -315,16 +315,12 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
                     v0 = __uint_as_float(r[8 * i + 2 * c]) + bs[2 * c];
                     v1 = __uint_as_float(r[8 * i + 2 * c + 1]) + bs[2 * c + 1];
                 }
-                // the image is fp16 hi + lo: saturate at the largest finite half instead of storing (inf, -inf) -> NaN logits
-                v0 = fminf(fmaxf(v0, -65504.f), 65504.f);
-                v1 = fminf(fmaxf(v1, -65504.f), 65504.f);
                 d = fmaf(v0, ws[2 * c], d);
                 d = fmaf(v1, ws[2 * c + 1], d);
-                const __half2 hh = __floats2half2_rn(v0, v1);
-                const float2 hf = __half22float2(hh);
-                const __half2 ll = __floats2half2_rn(v0 - hf.x, v1 - hf.y);
-                hi[c] = *reinterpret_cast<const uint32_t *>(&hh);
-                lo[c] = *reinterpret_cast<const uint32_t *>(&ll);
+                // the image is fp16 hi + lo: the conversions saturate at the largest finite half instead of storing (inf, -inf) -> NaN
+                hi[c] = tc::pack_h2_sat(v0, v1);
+                const float2 hf = __half22float2(*reinterpret_cast<const __half2 *>(&hi[c]));
+                lo[c] = tc::pack_h2_sat(v0 - hf.x, v1 - hf.y);
             }
             d += __shfl_xor_sync(0xffffffffu, d, 1);
             if (!c16) d += __shfl_xor_sync(0xffffffffu, d, 2);

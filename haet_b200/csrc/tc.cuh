@@ -287,6 +287,14 @@ __device__ __forceinline__ float fast_ex2(float x) {   // MUFU.EX2 (2 ulp), flus
     return y;
 }
 
+// (lo, hi) -> packed fp16x2, round to nearest, SATURATING at +-65504 instead of producing inf (SASS: F2FP.SATFINITE): the
+// operand images are fp16 hi + lo, and (inf, -inf) would turn into NaN logits
+__device__ __forceinline__ uint32_t pack_h2_sat(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
 // split an fp32 into bf16 hi + bf16 lo (hi + lo carries ~16 mantissa bits)
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16 &hi, __nv_bfloat16 &lo) {
     hi = __float2bfloat16_rn(v);

@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 
 #include "common.cuh"
+#include "tc.cuh"
 
 namespace haet {
 
@@ -46,19 +47,15 @@ __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__
         for (int j = 0; j < 4; ++j) {   // chunk j: channels 8j .. 8j+7
             if (8 * j >= C) { out[j] = out[4 + j] = make_uint4(0, 0, 0, 0); continue; }
             const float4 a = __ldg(src + 2 * j), c = __ldg(src + 2 * j + 1);
-            float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = fminf(fmaxf(v[i], -65504.f), 65504.f);   // fp16 hi + lo image: saturate, never (inf, -inf)
+            const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
             uint32_t hi[4], lo[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 d = fmaf(v[2 * i], __ldg(wt + 8 * j + 2 * i), d);
                 d = fmaf(v[2 * i + 1], __ldg(wt + 8 * j + 2 * i + 1), d);
-                const __half2 hh = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
-                const float2 hf = __half22float2(hh);
-                const __half2 ll = __floats2half2_rn(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
-                hi[i] = *reinterpret_cast<const uint32_t *>(&hh);
-                lo[i] = *reinterpret_cast<const uint32_t *>(&ll);
+                hi[i] = tc::pack_h2_sat(v[2 * i], v[2 * i + 1]);   // saturating: never (inf, -inf)
+                const float2 hf = __half22float2(*reinterpret_cast<const __half2 *>(&hi[i]));
+                lo[i] = tc::pack_h2_sat(v[2 * i] - hf.x, v[2 * i + 1] - hf.y);
             }
             out[j] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             out[4 + j] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
