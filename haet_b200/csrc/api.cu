@@ -22,7 +22,6 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.no_ln_fuse = env_on("HAET_NO_LN_FUSE");
         v.conv_simt = env_on("HAET_CONV_SIMT");
         v.conv_nh1 = env_on("HAET_CONV_NH1");
-        v.conv_mt1 = env_on("HAET_CONV_MT1");
         v.no_pdl = env_on("HAET_NO_PDL");
         v.erwin_fused = env_on("HAET_ERWIN_FUSED");
         const char *e = getenv("HAET_TREE_ROLES");

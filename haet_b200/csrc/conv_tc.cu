@@ -183,174 +183,6 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     }
 }
 
-// Two 128-row tiles per streamed W panel (256 output columns, both 256-column accumulators of TMEM in use).  The single-tile
-// kernel above re-reads the whole weight image (taps * dim * 256 * 4 bytes: 7 MB at 64^3 x 256) from L2 for EVERY tile: 2,048
-// tiles x 7 MB + the gathered rows = 21 GB of L2 -> shared traffic per launch, and L2 bandwidth -- not the tensor pipe -- set its
-// 3.4 ms.  Here every W panel that lands in shared memory feeds the MMAs of two tiles (A stages alternate between the tiles of the
-// pair), which halves the W traffic; the accumulators are no longer double-buffered across tiles, so the epilogue of a pair is
-// exposed (~4 % of the 108-panel main loop).
-__global__ void __launch_bounds__(CT_THREADS, 1)
-conv2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
-                float *__restrict__ Y, int64_t M, int Nn, int n_workers, ConvGeom geo) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    constexpr int NH = 2, CN = NH * GT_N, WST = 2;
-    constexpr size_t WSTAGE = (size_t)NH * 2 * GT_PANEL_BYTES;
-    const int kp = geo.din / GT_KP;
-    const int taps = geo.nd == 3 ? geo.ks * geo.ks * geo.ks : geo.ks * geo.ks;
-    const int panels = taps * kp;
-    const int n_groups = Nn / CN;
-    uint8_t *sA = smem;
-    uint8_t *sWs = sA + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES;
-    ConvSmem *cb = reinterpret_cast<ConvSmem *>(sWs + (size_t)WST * WSTAGE);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int group = blockIdx.x % n_groups, worker = blockIdx.x / n_groups;
-    const int64_t n_pairs = ((M + GT_M - 1) / GT_M + 1) / 2;
-    const int64_t my_pairs = worker < n_pairs ? (n_pairs - worker + n_workers - 1) / n_workers : 0;
-
-    if (warp == 8) {
-        if (lane == 0) {
-            for (int s = 0; s < GT_STAGES; ++s) {
-                mbar_init(&cb->a_full[s], GT_PROD); mbar_init(&cb->a_empty[s], 1);
-                mbar_init(&cb->w_full[s], 1); mbar_init(&cb->w_empty[s], 1);
-            }
-            for (int b = 0; b < 2; ++b) { mbar_init(&cb->t_full[b], 1); mbar_init(&cb->t_empty[b], 128); }
-            fence_barrier_init();
-        }
-        __syncwarp();
-        tmem_alloc<2 * CN>(&cb->tmem_base);
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = cb->tmem_base;
-
-    if (warp < 8) {
-        // ---------------- producers: item (pair, 2 * panel + h) = panel of tile 2 * pair + h ----------------
-        int64_t cur_pair = -1;
-        int ci_[2][GT_LD / 2], cj_[2][GT_LD / 2], ck_[2][GT_LD / 2];
-        int64_t base_[2][GT_LD / 2];
-        const int pad = geo.ks / 2;
-        auto src = [&](int64_t pi, int vp, int i, int row, int c8) -> const float * {
-            if (pi != cur_pair) {   // first item of a new pair (called with i = 0..3 in order): grid coordinates of both tiles' rows
-                if (i == GT_LD / 2 - 1) cur_pair = pi;
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int64_t m = ((worker + pi * n_workers) * 2 + h) * (int64_t)GT_M + row;
-                    if (m < M) {
-                        const int64_t b = m / geo.N, n = m - b * geo.N;
-                        const int64_t ij = n / geo.g2;
-                        ck_[h][i] = (int)(n - ij * geo.g2);
-                        ci_[h][i] = (int)(ij / geo.g1);
-                        cj_[h][i] = (int)(ij - (int64_t)ci_[h][i] * geo.g1);
-                        base_[h][i] = m;
-                    } else {
-                        base_[h][i] = -1;
-                    }
-                }
-            }
-            const int h = vp & 1, p = vp >> 1;
-            if (base_[h][i] < 0) return nullptr;
-            const int tap = p / kp, c0 = (p - tap * kp) * GT_KP;
-            int di, dj, dk = 0;
-            if (geo.nd == 3) { di = tap / (geo.ks * geo.ks) - pad; dj = (tap / geo.ks) % geo.ks - pad; dk = tap % geo.ks - pad; }
-            else { di = tap / geo.ks - pad; dj = tap % geo.ks - pad; }
-            const int ii = ci_[h][i] + di, jj = cj_[h][i] + dj, kk = ck_[h][i] + dk;
-            if (ii < 0 || ii >= geo.g0 || jj < 0 || jj >= geo.g1 || kk < 0 || kk >= geo.g2) return nullptr;   // zero padding
-            const int64_t nbr = base_[h][i] + ((int64_t)di * geo.g1 + dj) * geo.g2 + dk;
-            return X + nbr * geo.din + c0 + c8 * 8;
-        };
-        gemm_produce_g(2 * panels, my_pairs, sA, src,
-                       [&](int st, int parity) { mbar_wait(&cb->a_empty[st], (uint32_t)parity); },
-                       [&](int st) { mbar_arrive(&cb->a_full[st]); });
-    } else if (warp == 13) {
-        // ---------------- W loader: one 64 KB panel [hi | lo] x 256 columns per (pair, panel) ----------------
-        if (lane == 0) {
-            int stage = 0, phase = 0;
-            for (int64_t it = 0; it < my_pairs; ++it)
-                for (int p = 0; p < panels; ++p) {
-                    mbar_wait(&cb->w_empty[stage], (uint32_t)(phase ^ 1));
-                    mbar_arrive_expect_tx(&cb->w_full[stage], (uint32_t)WSTAGE);
-                    uint8_t *dst = sWs + (size_t)stage * WSTAGE;
-#pragma unroll
-                    for (int h = 0; h < NH; ++h) {
-                        const uint8_t *src = Wimg + ((size_t)(group * NH + h) * panels + p) * (2 * GT_PANEL_BYTES);
-                        bulk_g2s(dst + (size_t)h * GT_PANEL_BYTES, src, GT_PANEL_BYTES, &cb->w_full[stage]);
-                        bulk_g2s(dst + (size_t)(NH + h) * GT_PANEL_BYTES, src + GT_PANEL_BYTES, GT_PANEL_BYTES, &cb->w_full[stage]);
-                    }
-                    if (++stage == WST) { stage = 0; phase ^= 1; }
-                }
-        }
-        __syncwarp();
-    } else if (warp == 8) {
-        // ---------------- MMA issuer: per W panel, the panel's MMAs of tile 0 (accumulator 0) then of tile 1 (accumulator 1) ----------------
-        if (lane == 0 && my_pairs > 0) {
-            const uint32_t idesc = instr_desc(FMT_BF16, GT_M, CN, false, false);
-            int stage = 0, phase = 0, wst = 0, wph = 0;
-            for (int64_t it = 0; it < my_pairs; ++it) {
-                // both accumulators drained by the epilogue of the previous pair
-                mbar_wait(&cb->t_empty[0], (uint32_t)((it & 1) ^ 1));
-                mbar_wait(&cb->t_empty[1], (uint32_t)((it & 1) ^ 1));
-                tc_fence_after();
-                for (int p = 0; p < panels; ++p) {
-                    mbar_wait(&cb->w_full[wst], wph);
-                    const uint32_t b_hi = smem_u32(sWs + (size_t)wst * WSTAGE), b_lo = b_hi + NH * GT_PANEL_BYTES;
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        mbar_wait(&cb->a_full[stage], phase);
-                        tc_fence_after();
-                        const uint32_t d = tmem_base + (uint32_t)h * CN;
-                        const uint32_t a_hi = smem_u32(sA + (size_t)stage * 2 * GT_PANEL_BYTES), a_lo = a_hi + GT_PANEL_BYTES;
-#pragma unroll
-                        for (int ks = 0; ks < GT_KP / 16; ++ks) {
-                            const uint64_t dah = smem_desc_sw128(a_hi + ks * 32, 16, 1024);
-                            const uint64_t dal = smem_desc_sw128(a_lo + ks * 32, 16, 1024);
-                            const uint64_t dbh = smem_desc_sw128(b_hi + ks * 32, 16, 1024);
-                            const uint64_t dbl = smem_desc_sw128(b_lo + ks * 32, 16, 1024);
-                            mma_bf16_ss(d, dah, dbh, idesc, (p | ks) != 0);
-                            mma_bf16_ss(d, dal, dbh, idesc, true);
-                            mma_bf16_ss(d, dah, dbl, idesc, true);
-                        }
-                        tc_commit(&cb->a_empty[stage]);
-                        if (p == panels - 1) tc_commit(&cb->t_full[h]);
-                        if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
-                    }
-                    tc_commit(&cb->w_empty[wst]);
-                    if (++wst == WST) { wst = 0; wph ^= 1; }
-                }
-            }
-        }
-        __syncwarp();
-    } else {
-        // ---------------- epilogue: accumulator h -> tile 2 * pair + h ----------------
-        const int q = warp & 3;
-        GemmEpi ep{};
-        for (int64_t it = 0; it < my_pairs; ++it) {
-            for (int h = 0; h < 2; ++h) {
-                const int64_t tile = (worker + it * n_workers) * 2 + h;
-                mbar_wait(&cb->t_full[h], (uint32_t)(it & 1));
-                tc_fence_after();
-                const int64_t m0 = tile * GT_M + q * 32 + (lane & ~3);
-#pragma unroll 1
-                for (int c0 = 0; c0 < CN; c0 += 32) {
-                    uint32_t r[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CN + c0), r);
-                    tmem_wait_ld();
-                    gemm_epilogue_chunk<EPI_F32>(r, lane, m0, 0, 0, M, bias + group * CN + c0, nullptr, Y, Nn, group * CN + c0, ep);
-                }
-                tc_fence_before();
-                mbar_arrive(&cb->t_empty[h]);
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 8) {
-        tc_fence_after();
-        tmem_dealloc<2 * CN>(tmem_base);
-    }
-}
-
 bool conv_tc_supported(const haet_layer_shape *s) {
     const int inner = s->heads * s->dim_head;
     return (s->conv_nd == 2 || s->conv_nd == 3) && s->dim % GT_KP == 0 && inner % GT_N == 0 && (s->kernel & 1) == 1 && s->kernel <= 7;
@@ -388,14 +220,7 @@ int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, c
     int n_workers = sms / n_groups;
     if (n_workers < 1) n_workers = 1;
     if (n_workers > n_tiles) n_workers = (int)n_tiles;
-    if (nh == 2 && !options().conv_mt1) {   // two tiles per streamed W panel
-        HAET_DYN_SMEM(conv2_tc_kernel, smem);
-        const int64_t n_pairs = (n_tiles + 1) / 2;
-        int nw = sms / n_groups;
-        if (nw < 1) nw = 1;
-        if (nw > n_pairs) nw = (int)n_pairs;
-        conv2_tc_kernel<<<nw * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, nw, geo);
-    } else if (nh == 2) conv_tc_kernel<2><<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
+    if (nh == 2) conv_tc_kernel<2><<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
     else conv_tc_kernel<1><<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
     HAET_LAUNCHED();
     return HAET_OK;
