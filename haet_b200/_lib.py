@@ -66,6 +66,8 @@ SYMBOLS = {
                                      _P, _P]),
     "haet_erwin_forward_trees": (C.c_int, [_EC, _P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int64, C.POINTER(C.c_void_p), _P,
                                            _P, _P, _P]),
+    "haet_erwin_forward_static": (C.c_int, [_EC, _P, _P, C.c_int64, C.c_int64, _P, _P, C.c_int64, C.POINTER(C.c_void_p), _P,
+                                            _P, _P]),
     "haet_deslice_out": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P]),
     "haet_deslice_out_res": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P, _P]),
     "haet_block_mlp_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),

@@ -871,3 +871,52 @@ static int erwin_forward_multi(const haet_erwin_cfg *c, const float *x_d, const 
     HAET_LAUNCHED();
     return HAET_OK;
 }
+
+// ---- allocation-free variant (no counterpart in the reference) ----------------
+// Callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get
+// the Erwin pass with its scratch in a file-scope device array instead of a caller-provided workspace.  Every GPU that
+// loads the library holds these HAET_ERWIN_STATIC_SCRATCH_BYTES until exit.  In HOST code `g_erwin_static_scratch` is only a
+// stand-in for the symbol, not a device address: the address is taken with cudaGetSymbolAddress, once per device, with that
+// device current (cached below), and that pointer is what the kernels receive.
+static __device__ __align__(256) unsigned char g_erwin_static_scratch[HAET_ERWIN_STATIC_SCRATCH_BYTES];
+
+static int erwin_static_scratch(void **out) {
+    static std::atomic<void *> cache[64];
+    int dev = 0;
+    HAET_CUDA(cudaGetDevice(&dev));
+    HAET_CHECK_ARG(dev >= 0 && dev < 64, "haet_erwin_forward_static: device ordinal %d is beyond the 64 this library tracks", dev);
+    void *p = cache[dev].load(std::memory_order_acquire);
+    if (!p) {   // a race between two threads only repeats the (idempotent) query
+        HAET_CUDA(cudaGetSymbolAddress(&p, g_erwin_static_scratch));
+        HAET_CHECK_ARG(p != nullptr && ((uintptr_t)p & 255) == 0, "haet_erwin_forward_static: bad scratch symbol address");
+        cache[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return HAET_OK;
+}
+
+extern "C" int haet_erwin_forward_static(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T,
+                                         int64_t n_trees, const int64_t *tree_idx_d, const uint8_t *tree_mask_d,
+                                         int64_t n_slots, int64_t *const *rot_idx_d, const float *weights_d, float *out_d,
+                                         void *stream) {
+    int rc = check_cfg(c);
+    if (rc) return rc;
+    HAET_CHECK_ARG(n_slots >= 0 && n_trees >= 1, "haet_erwin_forward_static: n_slots must be >= 0 and n_trees >= 1");
+    const int64_t need = haet_erwin_workspace_bytes(c, n_slots);
+    if (need < 0 || need > (int64_t)HAET_ERWIN_STATIC_SCRATCH_BYTES) {
+        set_error("haet_erwin_forward_static: %lld tree slots of this configuration need %lld bytes of scratch, the built-in array "
+                  "holds %lld (HAET_ERWIN_STATIC_SCRATCH_BYTES); use haet_erwin_forward_trees with a caller workspace",
+                  (long long)n_slots, (long long)need, (long long)HAET_ERWIN_STATIC_SCRATCH_BYTES);
+        return HAET_ENOSUP;
+    }
+    if (n_slots == 0) return HAET_OK;
+    void *scratch = nullptr;
+    if ((rc = erwin_static_scratch(&scratch))) return rc;
+    // The array keeps the previous call's contents.  The activations of every level are fully written (gather / pool / unpool)
+    // before they are read, so only the per-tree barrier counters of the one-launch kernel must start at zero: they sit at the
+    // end of the workspace layout and are cleared on the stream here, whichever path runs.
+    HAET_CUDA(cudaMemsetAsync((char *)scratch + need - EF_MAX_TREES * (int64_t)sizeof(unsigned int), 0,
+                              EF_MAX_TREES * sizeof(unsigned int), (cudaStream_t)stream));
+    return haet_erwin_forward_trees(c, x_d, pos_d, T, n_trees, tree_idx_d, tree_mask_d, n_slots, rot_idx_d, weights_d, scratch,
+                                    out_d, stream);
+}

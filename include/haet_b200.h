@@ -178,6 +178,22 @@ int haet_erwin_forward_trees(const haet_erwin_cfg *c, const float *x_d, const fl
                              int64_t *const *rot_idx_d, const float *weights_d, void *workspace_d,
                              float *out_d, void *stream);
 
+/* haet_erwin_forward_trees WITHOUT a caller workspace.  No counterpart in the reference: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The scratch is a file-scope device array of HAET_ERWIN_STATIC_SCRATCH_BYTES inside the library (csrc/erwin.cu):
+ * every GPU that loads the library holds it until exit, and the call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine).  Inputs and outputs are still the caller's.  Fails with HAET_ENOSUP -- and launches nothing --
+ * when haet_erwin_workspace_bytes(c, n_slots) exceeds the array (the default HAET configuration, c_hidden {C, 2C} with C = 32,
+ * takes 274 bytes per slot: ~30,000 slots = B*heads*G slice tokens; the layer's own sizes are 512..4096).
+ * EVERY call on a device shares the one array, which keeps the previous call's contents (the call clears the part that must
+ * start at zero): two calls that overlap on the GPU -- different streams, or graphs replayed concurrently -- RACE; serialise
+ * them, or use haet_erwin_forward_trees with one workspace per stream.  The array's address is looked up on the first call on
+ * each device (make one un-captured call per device before capturing a graph). */
+#define HAET_ERWIN_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+int haet_erwin_forward_static(const haet_erwin_cfg *c, const float *x_d, const float *pos_d, int64_t T, int64_t n_trees,
+                              const int64_t *tree_idx_d, const uint8_t *tree_mask_d, int64_t n_slots,
+                              int64_t *const *rot_idx_d, const float *weights_d, float *out_d, void *stream);
+
 /* ---- deslice + to_out (pass 2 over the points) -------------------------------------
  * states_d [B*heads*G, C] = Erwin output; lse2_d from haet_slice_merge; out_d [B, N, dim]. */
 int haet_deslice_out(const haet_layer_shape *s, const void *spill_d, const float *lse2_d,
