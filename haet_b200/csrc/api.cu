@@ -24,6 +24,7 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.conv_nh1 = env_on("HAET_CONV_NH1");
         v.no_pdl = env_on("HAET_NO_PDL");
         v.erwin_fused = env_on("HAET_ERWIN_FUSED");
+        v.no_f32x2 = env_on("HAET_NO_F32X2");
         const char *e = getenv("HAET_TREE_ROLES");
         v.tree_roles = e ? atoi(e) : 0;
         e = getenv("HAET_GEMM_PF");

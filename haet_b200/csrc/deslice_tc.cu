@@ -48,6 +48,7 @@ struct DesliceCtl {
 __device__ __forceinline__ uint32_t dt_dbuf_col(int buf) { return 128u + (uint32_t)buf * DT_GCMAX; }
 __host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (G + 127) / 128 * 128; }
 
+template <bool F2>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
@@ -315,6 +316,20 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 uint32_t r[32], pk[16];
                 tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
+                if (F2) {   // packed fp32 pairs: 2 FFMA2 instead of 4 FFMA per 4 logits, bitwise the same values
+                    const uint64_t sn2 = f2_pack(sn, sn);
+#pragma unroll
+                    for (int c = 0; c < 32; c += 4) {
+                        const float4 k4 = ll[hh * 8 + (c >> 2)];   // 14 - lse2 of four slices
+                        float v0, v1, v2, v3;
+                        f2_unpack(f2_fma(f2_pack(__uint_as_float(r[c]), __uint_as_float(r[c + 1])), sn2, f2_pack(k4.x, k4.y)), v0, v1);
+                        f2_unpack(f2_fma(f2_pack(__uint_as_float(r[c + 2]), __uint_as_float(r[c + 3])), sn2, f2_pack(k4.z, k4.w)), v2, v3);
+                        const float p0 = fast_ex2(v0), p1 = fast_ex2(v1), p2 = fast_ex2(v2), p3 = fast_ex2(v3);
+                        const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                        pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
+                    }
+                } else {
 #pragma unroll
                 for (int c = 0; c < 32; c += 4) {
                     const float4 k4 = ll[hh * 8 + (c >> 2)];   // 14 - lse2 of four slices
@@ -323,6 +338,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                     const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
                     pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
                     pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
+                }
                 }
                 tmem_st16(dcol + hh * 16, pk);   // packed P trails the logits it replaces (columns already read)
             }
@@ -347,7 +363,8 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const int g_pad = dt_gpad(s->slice_num);
     const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
                         sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
-    HAET_DYN_SMEM(deslice_tc_kernel, smem);
+    HAET_DYN_SMEM(deslice_tc_kernel<true>, smem);
+    HAET_DYN_SMEM(deslice_tc_kernel<false>, smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -358,8 +375,12 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     if (n_chunks > max_chunks) n_chunks = max_chunks;
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
-    deslice_tc_kernel<<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                       xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
+    if (options().no_f32x2)
+        deslice_tc_kernel<false><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
+                                                                  xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
+    else
+        deslice_tc_kernel<true><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
+                                                                 xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
     HAET_LAUNCHED();
     return HAET_OK;
 }

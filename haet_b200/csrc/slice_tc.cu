@@ -49,6 +49,7 @@ struct SliceCtl {
 // TMEM columns: accumulators of the 4 softmax warpgroups at 0..127, D / P buffers [stream][3] x 64 at 128..511
 __device__ __forceinline__ uint32_t st_dbuf_col(int w, int buf) { return 128u + (uint32_t)(w * ST_NBUF + buf) * ST_TILE; }
 
+template <bool F2>
 __global__ void __launch_bounds__(ST_THREADS, 1)
 slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
                 const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int C, int64_t chunk_pts,
@@ -237,6 +238,28 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 // below recomputes P from the kept t.
                 float tmax = -INFINITY, l0 = 0.f, l1 = 0.f;
                 uint32_t pk[16];   // P as packed fp16: word c = points (2c, 2c+1) of this half
+                if (F2) {   // the same arithmetic on packed fp32 pairs: 2 FFMA2 + 2 FADD2 instead of 4 FFMA + 4 FADD per 4 logits
+                    const uint64_t nm = f2_pack(-m_run, -m_run);
+                    uint64_t l01 = f2_pack(0.f, 0.f);
+#pragma unroll
+                    for (int c = 0; c < 32; c += 4) {
+                        const float4 sa = s4[hh * 8 + (c >> 2)];
+                        const uint64_t va = f2_fma(f2_pack(__uint_as_float(r[c]), __uint_as_float(r[c + 1])), f2_pack(sa.x, sa.y), nm);
+                        const uint64_t vb = f2_fma(f2_pack(__uint_as_float(r[c + 2]), __uint_as_float(r[c + 3])), f2_pack(sa.z, sa.w), nm);
+                        float v0, v1, v2, v3;
+                        f2_unpack(va, v0, v1); f2_unpack(vb, v2, v3);
+                        r[c] = __float_as_uint(v0); r[c + 1] = __float_as_uint(v1); r[c + 2] = __float_as_uint(v2); r[c + 3] = __float_as_uint(v3);
+                        tmax = fmaxf(fmaxf(tmax, v0), v1);   // FMNMX3
+                        tmax = fmaxf(fmaxf(tmax, v2), v3);
+                        const float p0 = fast_ex2(v0), p1 = fast_ex2(v1), p2 = fast_ex2(v2), p3 = fast_ex2(v3);
+                        l01 = f2_add(l01, f2_pack(p0, p1));
+                        l01 = f2_add(l01, f2_pack(p2, p3));
+                        const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
+                        pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
+                        pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
+                    }
+                    f2_unpack(l01, l0, l1);
+                } else {
 #pragma unroll
                 for (int c = 0; c < 32; c += 4) {
                     const float4 sa = s4[hh * 8 + (c >> 2)];
@@ -250,6 +273,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                     const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
                     pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
                     pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
+                }
                 }
                 if (ragged) {   // columns past the chunk's last point: weight 0 (their image rows are zero)
                     tmax = -INFINITY;
@@ -367,12 +391,17 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
     const int n_gb = (s->slice_num + ST_GB - 1) / ST_GB;
     const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
-    HAET_DYN_SMEM(slice_tc_kernel, smem);
+    HAET_DYN_SMEM(slice_tc_kernel<true>, smem);
+    HAET_DYN_SMEM(slice_tc_kernel<false>, smem);
     const int64_t chunk_pts = slice_tc_chunk_pts(s);
     const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : ST_RAISE;   // haet_set_raise_threshold: tests force the accumulator-rescale path
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads));
-    slice_tc_kernel<<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
-                                                     s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
+    if (options().no_f32x2)
+        slice_tc_kernel<false><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
+                                                                s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
+    else
+        slice_tc_kernel<true><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
+                                                               s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
     HAET_LAUNCHED();
     return HAET_OK;
 }

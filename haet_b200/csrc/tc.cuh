@@ -287,6 +287,26 @@ __device__ __forceinline__ float fast_ex2(float x) {   // MUFU.EX2 (2 ulp), flus
     return y;
 }
 
+// Packed fp32 pairs (sm_100: FFMA2 / FADD2, one issue slot for two IEEE operations -- each half rounds exactly like the scalar
+// instruction, so a loop rewritten with them is bitwise unchanged).  The softmax loops of the two passes sit on the issue limit
+// of their 3-4 warps per scheduler; a pair is an aligned register pair, which the TMEM loads and LDS.128 already produce.
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
 // (lo, hi) -> packed fp16x2, round to nearest, SATURATING at +-65504 instead of producing inf (SASS: F2FP.SATFINITE): the
 // operand images are fp16 hi + lo, and (inf, -inf) would turn into NaN logits
 __device__ __forceinline__ uint32_t pack_h2_sat(float lo, float hi) {
