@@ -183,7 +183,7 @@ int64_t haet_deslice_workspace_bytes(const haet_layer_shape *s) { return deslice
 
 // ln_1 scratch behind the regular slice workspace: folded weights + row statistics when the in-projection fuses it, else normalised x
 static bool ln_fuse_ok(const haet_layer_shape *s) {
-    return hooks().path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && s->conv_nd == 0 &&
+    return hooks().path == 0 && slice_tc_supported(s) && deslice_tc_supported(s) && s->conv_nd == 0 && s->dim_head != 64 &&
            gemm_tc_supported(s->dim, s->heads * s->dim_head) && ln_fused_supported(s);
 }
 int64_t haet_slice_ln_workspace_bytes(const haet_layer_shape *s) {
@@ -235,7 +235,7 @@ static int slice_reduce_impl(const haet_layer_shape *s, const float *x_d, const 
     }
     if (!(hooks().stage_mask & 1)) {
         rc = HAET_OK;   // bench hook: the spill of an earlier call is reused
-    } else if (tc && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner)) {
+    } else if (tc && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner) && s->dim_head != 64) {
         // Linear front-end: the GEMM epilogue writes the operand image directly
         rc = launch_inproj_tc(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st, ln_fused ? &ln : nullptr);
     } else {

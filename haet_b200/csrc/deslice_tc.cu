@@ -53,24 +53,31 @@ __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
                   int64_t N, int64_t npad, int H, int G, int C, int64_t chunk_pts, float *__restrict__ o, int o_image) {
-    // C = dim_head: 32, or 16 -- then the image rows, Ws and S' are zero-padded to 32 channels and only 16 are written out
+    // C = dim_head: 32, or 16 -- then the image rows, Ws and S' are zero-padded to 32 channels and only 16 are written out --
+    // or 64 ("pair mode", slice_tc.cu): H counts pseudo-heads of 32 channels, the logits run over both sub-row tiles of the
+    // head, and this CTA produces the 32 output channels of its own sub-row from S'[.., 32 srow : 32 srow + 32]
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int g_pad = dt_gpad(G), cw = g_pad < DT_GCMAX ? g_pad : DT_GCMAX;   // chunk width: slices per item
     const int n_gc = g_pad / cw;
-    uint8_t *sW = smem;                                     // [g_pad rows][hi(32 fp16) | lo(32 fp16)]  K-major SW128
-    uint8_t *sV = sW + (size_t)g_pad * 128;                 // [g_pad rows][32 fp32]  S'_h, MN-major SW128_BASE32B
-    uint8_t *sA = sV + (size_t)g_pad * 128;                 // [stages][128 rows][hi | lo]
+    const bool pair = C == 64;
+    const int Cw = pair ? 32 : C;                           // channels per image row / output channels of this CTA
+    const int n_stages = pair ? DT_STAGES - 1 : DT_STAGES;  // pair mode: a stage holds the tiles of both sub-rows
+    const uint32_t stage_bytes = pair ? 2 * DT_TILE_BYTES : DT_TILE_BYTES;
+    uint8_t *sW = smem;                                     // [sub-row][g_pad rows][hi(32 fp16) | lo(32 fp16)]  K-major SW128
+    uint8_t *sV = sW + (size_t)g_pad * 128 * (pair ? 2 : 1);   // [g_pad rows][32 fp32]  S'_h, MN-major SW128_BASE32B
+    uint8_t *sA = sV + (size_t)g_pad * 128;                 // [stages][128 rows][hi | lo] (x 2 sub-rows)
     // bias operands of MMA1's extra K step (no swizzle: 8-row x 16-B core matrices, K halves 128 B apart, 8-row groups 256 B
     // apart): sBb row g = {bc_g hi, bc_g lo, 0 ..} with bc = bs_g - log(-log eps), sOne row n = {1, 1, 0 ..}
-    uint8_t *sBb = sA + (size_t)DT_STAGES * DT_TILE_BYTES;  // [g_pad / 8][256 B]
+    uint8_t *sBb = sA + (size_t)n_stages * stage_bytes;     // [g_pad / 8][256 B]
     uint8_t *sOne = sBb + (size_t)g_pad * 32;               // [128 / 8][256 B]
     float *sL = reinterpret_cast<float *>(sOne + DT_TILE * 32);                        // [g_pad] -lse2_g
     float *sS = sL + g_pad;                                                            // [stages][128] s_n
     DesliceCtl *ctl = reinterpret_cast<DesliceCtl *>(sS + DT_STAGES * DT_TILE);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
-    const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
-    const int inner = H * C;
+    const int bh = blockIdx.y, b = bh / H, h = bh - b * H;   // pair mode: h = pseudo-head 2 h_real + srow
+    const int bhr = pair ? (bh >> 1) : bh, srow = pair ? (bh & 1) : 0;
+    const int inner = H * Cw;
     const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
     const int64_t n_end = min(N, n_begin + chunk_pts);
     const int n_tiles = (int)((n_end - n_begin + DT_TILE - 1) / DT_TILE);
@@ -88,8 +95,11 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     // power-of-two scale of S'_h: 2^(14 - e) with max |S'_h| in [2^(e-1), 2^e)
     {
         float amax = 0.f;
-        const float *sp = states + (size_t)bh * G * C;
-        for (int idx = threadIdx.x; idx < G * C; idx += DT_THREADS) amax = fmaxf(amax, fabsf(sp[idx]));
+        const float *sp = states + (size_t)bhr * G * C + srow * 32;
+        for (int idx = threadIdx.x; idx < G * Cw; idx += DT_THREADS) {
+            const int g = idx / Cw, c = idx - g * Cw;
+            amax = fmaxf(amax, fabsf(sp[(size_t)g * C + c]));
+        }
 #pragma unroll
         for (int o2 = 16; o2; o2 >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o2));
         if (lane == 0) ctl->red[threadIdx.x >> 5] = amax;
@@ -113,20 +123,31 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         __align__(16) __half sv[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const bool live = g < G && ck * 8 + i < C;
+            const bool live = g < G && ck * 8 + i < Cw;
             const float v = live ? ws[(size_t)g * C + ck * 8 + i] : 0.f;
             hi[i] = __float2half_rn(v);
             lo[i] = __float2half_rn(v - __half2float(hi[i]));
-            const float s = live ? states[((size_t)bh * G + g) * C + ck * 8 + i] : 0.f;
+            const float s = live ? states[((size_t)bhr * G + g) * C + srow * 32 + ck * 8 + i] : 0.f;
             sv[i] = __float2half_rn(s * v_scale);
         }
         *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(hi);
         *reinterpret_cast<uint4 *>(sW + sw128_off(g, ck + 4)) = *reinterpret_cast<const uint4 *>(lo);
+        if (pair) {   // Ws channels 32 .. 63: the second sub-row's image
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float v = g < G ? ws[(size_t)g * C + 32 + ck * 8 + i] : 0.f;
+                hi[i] = __float2half_rn(v);
+                lo[i] = __float2half_rn(v - __half2float(hi[i]));
+            }
+            uint8_t *sW1 = sW + (size_t)g_pad * 128;
+            *reinterpret_cast<uint4 *>(sW1 + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(hi);
+            *reinterpret_cast<uint4 *>(sW1 + sw128_off(g, ck + 4)) = *reinterpret_cast<const uint4 *>(lo);
+        }
         *reinterpret_cast<uint4 *>(sV + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(sv);   // MN-major operand: row g = 32 fp16 channels
         *reinterpret_cast<uint4 *>(sV + sw128_off(g, ck + 4)) = make_uint4(0, 0, 0, 0);
     }
     for (int g = threadIdx.x; g < g_pad; g += DT_THREADS) {
-        sL[g] = g < G ? DT_PSHIFT - lse2[(size_t)bh * G + g] : -INFINITY;
+        sL[g] = g < G ? DT_PSHIFT - lse2[(size_t)bhr * G + g] : -INFINITY;
         uint32_t b2 = 0;
         if (g < G) {
             const float bc = bs[g] - shift;
@@ -153,7 +174,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         const int r = threadIdx.x - 384;   // row of the tile == TMEM lane
         const float o_scale = ctl->o_scale;
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-        float *dst = o + ((int64_t)b * N) * inner + h * C;
+        float *dst = o + ((int64_t)b * N) * inner + h * Cw;
         for (int te = 0; te < n_tiles; ++te) {
             const int ob = te & 1;
             mbar_wait(&ctl->o_full[ob], (uint32_t)((te >> 1) & 1));
@@ -176,7 +197,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 xpose_stage<1, 4>(v, lane);
                 const int64_t n0 = n_begin + (int64_t)te * DT_TILE + (r & ~3);
                 // global 16-byte chunk (8 channels) of this lane inside the row of `inner` channels
-                const int l4 = lane & 3, gch = (h * C >> 3) + l4, cc = gch & 7, pan = gch >> 3, panels = inner >> 6;
+                const int l4 = lane & 3, gch = (h * Cw >> 3) + l4, cc = gch & 7, pan = gch >> 3, panels = inner >> 6;
                 uint8_t *oimg = reinterpret_cast<uint8_t *>(o);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -190,7 +211,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                         hi[c] = ub;
                         lo[c] = *reinterpret_cast<const uint32_t *>(&lb);
                     }
-                    if (n0 + i < n_end && 8 * l4 < C) {
+                    if (n0 + i < n_end && 8 * l4 < Cw) {
                         const int64_t m = (int64_t)b * N + n0 + i;
                         const int rr = (int)(m & 127);
                         uint8_t *blk = oimg + (((m >> 7) * panels + pan) * 2) * (int64_t)(128 * 128) + sw128_off(rr, cc);
@@ -212,7 +233,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                     float *p = dst + (n0 + i) * inner + 4 * l4;
                     *reinterpret_cast<float4 *>(p) = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
                                                                  __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
-                    if (C > 16)
+                    if (Cw > 16)
                         *reinterpret_cast<float4 *>(p + 16) = make_float4(__uint_as_float(v[4 * i + 16]), __uint_as_float(v[4 * i + 17]),
                                                                           __uint_as_float(v[4 * i + 18]), __uint_as_float(v[4 * i + 19]));
                 }
@@ -221,15 +242,19 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     } else if (warp == 17) {
         // =========================== loader: one bulk copy per 128-point tile (+ its s_n) ===========================
         if (lane == 0) {
-            const uint8_t *src = img + ((int64_t)bh * npad + n_begin) * XPI_ROW_BYTES;
+            const int64_t bh0 = pair ? (bh & ~1) : bh;   // pair mode: sub-row 0 of this head; sub-row 1 follows npad rows later
+            const uint8_t *src = img + ((int64_t)bh0 * npad + n_begin) * XPI_ROW_BYTES;
             const float *ssrc = scale + (int64_t)bh * npad + n_begin;
             int stage = 0, phase = 0;
             for (int t = 0; t < n_tiles; ++t) {
                 mbar_wait(&ctl->a_empty[stage], phase ^ 1);
-                mbar_arrive_expect_tx(&ctl->a_full[stage], DT_TILE_BYTES + DT_TILE * 4);
-                bulk_g2s(sA + (size_t)stage * DT_TILE_BYTES, src + (size_t)t * DT_TILE_BYTES, DT_TILE_BYTES, &ctl->a_full[stage]);
+                mbar_arrive_expect_tx(&ctl->a_full[stage], stage_bytes + DT_TILE * 4);
+                bulk_g2s(sA + (size_t)stage * stage_bytes, src + (size_t)t * DT_TILE_BYTES, DT_TILE_BYTES, &ctl->a_full[stage]);
+                if (pair)
+                    bulk_g2s(sA + (size_t)stage * stage_bytes + DT_TILE_BYTES, src + ((size_t)npad + (size_t)t * DT_TILE) * XPI_ROW_BYTES,
+                             DT_TILE_BYTES, &ctl->a_full[stage]);
                 bulk_g2s(sS + stage * DT_TILE, ssrc + (size_t)t * DT_TILE, DT_TILE * 4, &ctl->a_full[stage]);
-                if (++stage == DT_STAGES) { stage = 0; phase ^= 1; }
+                if (++stage == n_stages) { stage = 0; phase ^= 1; }
             }
         }
         __syncwarp();
@@ -251,7 +276,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             if (jc1 == 0) mbar_wait(&ctl->a_full[st1], (uint32_t)ph1);
             tc_fence_after();
             if (elect_one()) {
-                const uint32_t a = abase + (uint32_t)st1 * (DT_TILE_BYTES >> 4);
+                const uint32_t a = abase + (uint32_t)st1 * (stage_bytes >> 4);
                 const uint32_t wb = wbase + (uint32_t)jc1 * w_step;
                 const uint32_t d = tmem_base + dt_dbuf_col(buf1);
 #pragma unroll
@@ -262,11 +287,20 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 }
                 // + bc_g: ones[n, 0:16] . bias[g, 0:16]  (the softmax warps then need no per-element bias add)
                 mma_bf16_ss(d, desc_u(one_a, 128, 256, 0), desc_u(bb_a + (uint32_t)jc1 * b_step, 128, 256, 0), id1, true);
+                if (pair) {   // channels 32 .. 63: second tile of the stage against the second Ws image
+                    const uint32_t a1 = a + (DT_TILE_BYTES >> 4), wb1 = wb + ((uint32_t)g_pad * 128 >> 4);
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        mma_bf16_ss(d, desc_sw128_u(a1 + ks * 2, 16, 1024), desc_sw128_u(wb1 + ks * 2, 16, 1024), id1, true);
+                        mma_bf16_ss(d, desc_sw128_u(a1 + 4 + ks * 2, 16, 1024), desc_sw128_u(wb1 + ks * 2, 16, 1024), id1, true);
+                        mma_bf16_ss(d, desc_sw128_u(a1 + ks * 2, 16, 1024), desc_sw128_u(wb1 + 4 + ks * 2, 16, 1024), id1, true);
+                    }
+                }
                 tc_commit(&ctl->d_full[buf1]);
             }
             __syncwarp();
             if (++buf1 == DT_NBUF) { buf1 = 0; if (q >= DT_NBUF) fph ^= 1; }
-            if (++jc1 == n_gc) { jc1 = 0; if (++st1 == DT_STAGES) { st1 = 0; ph1 ^= 1; } }
+            if (++jc1 == n_gc) { jc1 = 0; if (++st1 == n_stages) { st1 = 0; ph1 ^= 1; } }
         }
     } else if (warp >= 18) {
         // =========================== MMA2 issuers: O_u += P . S'_h[chunk], K steps [u, u + 1) * cw / 16 ===========================
@@ -293,7 +327,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
             __syncwarp();
             if (++buf2 == DT_NBUF) { buf2 = 0; ph2 ^= 1; }
-            if (++jc2 == n_gc) { jc2 = 0; ++t2; if (++st2 == DT_STAGES) st2 = 0; }
+            if (++jc2 == n_gc) { jc2 = 0; ++t2; if (++st2 == n_stages) st2 = 0; }
         }
     } else if (warp < 12) {
         // =========================== softmax warpgroups ===========================
@@ -304,8 +338,8 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         const int Q = n_tiles * n_gc, halves = cw / 32;
         for (int q = wg; q < Q; q += DT_NBUF) {
             const int t = q / n_gc, jc = q - t * n_gc;
-            const int stage = t % DT_STAGES, buf = wg;
-            mbar_wait(&ctl->a_full[stage], (uint32_t)((t / DT_STAGES) & 1));
+            const int stage = t % n_stages, buf = wg;
+            mbar_wait(&ctl->a_full[stage], (uint32_t)((t / n_stages) & 1));
             const float sn = sS[stage * DT_TILE + row];
             mbar_wait(&ctl->d_full[buf], (uint32_t)((q / DT_NBUF) & 1));
             tc_fence_after();
@@ -355,20 +389,24 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     }
 }
 
-bool deslice_tc_supported(const haet_layer_shape *s) { return (s->dim_head == DT_C || s->dim_head == 16) && s->slice_num <= DT_MAX_G; }
+bool deslice_tc_supported(const haet_layer_shape *s) {
+    if (s->dim_head == 64) return s->slice_num <= 256;   // pair mode (two Ws images, double stages): shared memory holds G <= 256
+    return (s->dim_head == DT_C || s->dim_head == 16) && s->slice_num <= DT_MAX_G;
+}
 
 int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *lse2,
                       const float *states, const float *ws, const float *bs, float *o, int o_image, cudaStream_t st) {
     if (s->N == 0 || s->B == 0) return HAET_OK;
     const int g_pad = dt_gpad(s->slice_num);
-    const size_t smem = 1024 + (size_t)g_pad * 256 + (size_t)DT_STAGES * DT_TILE_BYTES + (size_t)g_pad * 32 + DT_TILE * 32 + sizeof(float) * g_pad +
-                        sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
+    const bool pair = s->dim_head == 64;
+    const size_t smem = 1024 + (size_t)g_pad * (pair ? 384 : 256) + (size_t)(pair ? 2 * (DT_STAGES - 1) : DT_STAGES) * DT_TILE_BYTES + (size_t)g_pad * 32 +
+                        DT_TILE * 32 + sizeof(float) * g_pad + sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
     HAET_DYN_SMEM(deslice_tc_kernel<true>, smem);
     HAET_DYN_SMEM(deslice_tc_kernel<false>, smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int64_t BH = s->B * s->heads;
+    const int64_t BH = s->B * s->heads * (pair ? 2 : 1);   // pair mode: one CTA per (head, sub-row)
     int64_t n_chunks = sms / BH;
     if (n_chunks < 1) n_chunks = 1;
     const int64_t max_chunks = cdiv(s->N, DT_TILE);
@@ -377,10 +415,10 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
     if (options().no_f32x2)
         deslice_tc_kernel<false><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                                  xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
+                                                                  xpi_npad(s->N), s->heads * (pair ? 2 : 1), s->slice_num, s->dim_head, chunk_pts, o, o_image);
     else
         deslice_tc_kernel<true><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                                 xpi_npad(s->N), s->heads, s->slice_num, s->dim_head, chunk_pts, o, o_image);
+                                                                 xpi_npad(s->N), s->heads * (pair ? 2 : 1), s->slice_num, s->dim_head, chunk_pts, o, o_image);
     HAET_LAUNCHED();
     return HAET_OK;
 }

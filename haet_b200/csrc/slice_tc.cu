@@ -15,6 +15,10 @@
 //        l (fp32, unrounded p) still counts and S (fp16 P) has lost is then < N_chunk 2^-31 of the column's mass.
 //   MMA2 (kind::f16, A = P from TMEM, B = the hi half of the tile read MN-major: 32 columns):
 //        S[g, c] += sum_n P[g,n] hi[n,c]      M = 128, N = 32, K = 64   (hi carries x_proj to 2^-12: ample for S)
+// dim_head 64 ("pair mode"): a head is run as TWO pseudo-heads of 32 channels (image rows of pseudo-head 2h + sub = channels
+// [32 sub, 32 sub + 32) of head h).  Both CTAs of a head compute the SAME logits -- MMA1 runs over both sub-row tiles, always
+// sub-row 0 first, so D, the lazy reference and l are bit-identical in the two -- and each accumulates S for its own 32 channels
+// (MMA2 on its own tile).  The exponentials are computed twice; everything else is shared with the dim_head-32 code.
 // Warp roles: 4 softmax warpgroups (4 warps per scheduler hide the TMEM / MUFU latencies), 1 loader warp (bulk copies),
 // 2 MMA-issuing warps (a single issuing thread was the bottleneck of the first version).
 #include <cuda_fp16.h>
@@ -53,17 +57,23 @@ template <bool F2>
 __global__ void __launch_bounds__(ST_THREADS, 1)
 slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
                 const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int C, int64_t chunk_pts,
-                float raise_thr, float *__restrict__ parts) {   // C = dim_head: 32, or 16 (zero-padded to 32 in the image)
+                float raise_thr, float *__restrict__ parts) {   // C = dim_head: 32, 16 (zero-padded to 32 in the image) or 64 (pair mode)
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS / STS)
     const int n_gb = (G + ST_GB - 1) / ST_GB;
-    uint8_t *sW = smem;                                              // [n_gb][2][16 KB]: [hi|hi] rows, [lo|0] rows
-    uint8_t *sOne = sW + (size_t)n_gb * 2 * (ST_GB * 128);           // [64 points][128 B]: k = 0, 1 are 1.0 (bias operand)
-    uint8_t *sB = sOne + ST_TILE_BYTES;                              // [stages][8 KB] point tiles
+    const bool pair = C == 64;
+    const int Cw = pair ? 32 : C;                                    // channels of this CTA's image rows
+    const int n_stages = pair ? ST_STAGES / 2 : ST_STAGES;           // pair mode: a stage holds the tiles of both sub-rows
+    const uint32_t stage_bytes = pair ? 2 * ST_TILE_BYTES : ST_TILE_BYTES;
+    const uint32_t blk_bytes = (pair ? 4u : 2u) * (ST_GB * 128);     // Ws images of one slice block
+    uint8_t *sW = smem;                                              // [n_gb][sub-row][2][16 KB]: [hi|hi] rows, [lo|bias] rows
+    uint8_t *sOne = sW + (size_t)n_gb * blk_bytes;                   // [64 points][128 B]: k = 0, 1 are 1.0 (bias operand)
+    uint8_t *sB = sOne + ST_TILE_BYTES;                              // [stages][8 KB (x 2)] point tiles
     float *sS = reinterpret_cast<float *>(sB + (size_t)ST_STAGES * ST_TILE_BYTES);   // [stages][64] s_n
     SliceCtl *ctl = reinterpret_cast<SliceCtl *>(sS + ST_STAGES * ST_TILE);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
-    const int bh = blockIdx.y;
+    const int bh = blockIdx.y;                                       // (b, h), or (b, h, sub-row) in pair mode
+    const int srow = pair ? (bh & 1) : 0;                            // sub-row (channels 32 srow ..) this CTA accumulates
     const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
     const int64_t n_end = min(N, n_begin + chunk_pts);
     const int n_tiles = (int)((n_end - n_begin + ST_TILE - 1) / ST_TILE);
@@ -84,23 +94,24 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         __syncwarp();
         tmem_alloc<512>(&ctl->tmem_base);
     }
-    for (int idx = threadIdx.x; idx < n_gb * ST_GB * 4; idx += ST_THREADS) {   // one 16-B chunk (8 k) per step
-        const int row = idx >> 2, ck = idx & 3, g = row, j = row / ST_GB, r = row % ST_GB;
+    for (int idx = threadIdx.x; idx < n_gb * ST_GB * 4 * (pair ? 2 : 1); idx += ST_THREADS) {   // one 16-B chunk (8 k) per step
+        const int hf = idx / (n_gb * ST_GB * 4), id2 = idx - hf * (n_gb * ST_GB * 4);   // sub-row (pair mode)
+        const int row = id2 >> 2, ck = id2 & 3, g = row, j = row / ST_GB, r = row % ST_GB;
         __align__(16) __half hi[8], lo[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const float v = (g < G && ck * 8 + i < C) ? ws[(size_t)g * C + ck * 8 + i] : 0.f;
+            const float v = (g < G && ck * 8 + i < Cw) ? ws[(size_t)g * C + hf * 32 + ck * 8 + i] : 0.f;
             hi[i] = __float2half_rn(v);
             lo[i] = __float2half_rn(v - __half2float(hi[i]));
         }
-        uint8_t *w1 = sW + (size_t)j * 2 * (ST_GB * 128), *w2 = w1 + ST_GB * 128;
+        uint8_t *w1 = sW + (size_t)j * blk_bytes + (size_t)hf * 2 * (ST_GB * 128), *w2 = w1 + ST_GB * 128;
         *reinterpret_cast<uint4 *>(w1 + sw128_off(r, ck)) = *reinterpret_cast<const uint4 *>(hi);
         *reinterpret_cast<uint4 *>(w1 + sw128_off(r, ck + 4)) = *reinterpret_cast<const uint4 *>(hi);
         *reinterpret_cast<uint4 *>(w2 + sw128_off(r, ck)) = *reinterpret_cast<const uint4 *>(lo);
         // k = 32, 33 of the lo rows carry the logit bias bc = bs_g - log(-log eps) as fp16 hi + lo: one more K step of
         // MMA1 against the constant tile sOne adds it to D, so the softmax warps do not spend an FADD per element on it
         uint4 bias4 = make_uint4(0, 0, 0, 0);
-        if (ck == 0 && g < G) {
+        if (ck == 0 && g < G && hf == 0) {
             const float bc = bs[g] - shift;
             const __half bh = __float2half_rn(bc), bl = __float2half_rn(bc - __half2float(bh));
             bias4.x = (uint32_t)__half_as_ushort(bh) | ((uint32_t)__half_as_ushort(bl) << 16);
@@ -120,15 +131,19 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
     if (warp == 16) {
         // =========================== loader: one bulk copy per tile (+ its s_n) ===========================
         if (lane == 0) {
-            const uint8_t *src = img + ((int64_t)bh * npad + n_begin) * XPI_ROW_BYTES;
+            const int64_t bh0 = pair ? (bh & ~1) : bh;   // pair mode: sub-row 0 of this head, sub-row 1 follows npad rows later
+            const uint8_t *src = img + ((int64_t)bh0 * npad + n_begin) * XPI_ROW_BYTES;
             const float *ssrc = scale + (int64_t)bh * npad + n_begin;
             int stage = 0, phase = 0;
             for (int t = 0; t < n_tiles; ++t) {
                 mbar_wait(&ctl->b_empty[stage], phase ^ 1);
-                mbar_arrive_expect_tx(&ctl->b_full[stage], ST_TILE_BYTES + ST_TILE * 4);
-                bulk_g2s(sB + (size_t)stage * ST_TILE_BYTES, src + (size_t)t * ST_TILE_BYTES, ST_TILE_BYTES, &ctl->b_full[stage]);
+                mbar_arrive_expect_tx(&ctl->b_full[stage], stage_bytes + ST_TILE * 4);
+                bulk_g2s(sB + (size_t)stage * stage_bytes, src + (size_t)t * ST_TILE_BYTES, ST_TILE_BYTES, &ctl->b_full[stage]);
+                if (pair)
+                    bulk_g2s(sB + (size_t)stage * stage_bytes + ST_TILE_BYTES, src + ((size_t)npad + (size_t)t * ST_TILE) * XPI_ROW_BYTES,
+                             ST_TILE_BYTES, &ctl->b_full[stage]);
                 bulk_g2s(sS + stage * ST_TILE, ssrc + (size_t)t * ST_TILE, ST_TILE * 4, &ctl->b_full[stage]);
-                if (++stage == ST_STAGES) { stage = 0; phase ^= 1; }
+                if (++stage == n_stages) { stage = 0; phase ^= 1; }
             }
         }
         __syncwarp();
@@ -145,13 +160,15 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         // Low descriptor words (tc.cuh: desc_join): the issuing warp was ~70 % busy per item rebuilding and masking
         // descriptors, so they are kept as running sums -- one add per MMA.
         constexpr uint32_t HI = DESC_HI_SW128_SBO1024;
-        constexpr uint32_t STG = ST_TILE_BYTES >> 4;                        // one stage, in 16-byte units
+        const uint32_t STG = stage_bytes >> 4;                              // one stage, in 16-byte units
+        constexpr uint32_t TIL = ST_TILE_BYTES >> 4;                        // one tile
         const uint32_t sB_a = smem_u32(sB) >> 4;
         const uint32_t b1_lo0 = sB_a | (1u << 16);                          // point tile, K-major (LBO 16 B)
-        const uint32_t b2_lo0 = sB_a | (64u << 16);                         // the same tile MN-major (LBO 1024 B)
+        const uint32_t b2_lo0 = (sB_a + (uint32_t)srow * TIL) | (64u << 16);  // this CTA's own tile MN-major (LBO 1024 B)
         const uint32_t one_lo = (smem_u32(sOne) >> 4) | (1u << 16);
-        const uint32_t a_lo0 = ((smem_u32(sW) >> 4) + (uint32_t)w * (2 * ST_GB * 128 >> 4)) | (1u << 16);   // block j = w + 2 jj
-        constexpr uint32_t A_JJ = 2 * (2 * ST_GB * 128 >> 4), A_LO = ST_GB * 128 >> 4;   // next block of the stream; the [lo | bias] rows
+        const uint32_t a_lo0 = ((smem_u32(sW) >> 4) + (uint32_t)w * (blk_bytes >> 4)) | (1u << 16);   // block j = w + 2 jj
+        const uint32_t A_JJ = 2 * (blk_bytes >> 4);                                        // next block of the stream
+        constexpr uint32_t A_LO = ST_GB * 128 >> 4;                                        // the [lo | bias] rows
         int jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;           // MMA1 cursor: block within the stream, stage (+phase), D buffer
         int jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;           // MMA2 cursor
         uint32_t b1_lo = b1_lo0, b2_lo = b2_lo0;           // running stage descriptors of the two cursors
@@ -174,7 +191,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 if (++jj2 == pw) {
                     jj2 = 0;
                     b2_lo += STG;
-                    if (++st2 == ST_STAGES) { st2 = 0; b2_lo = b2_lo0; }
+                    if (++st2 == n_stages) { st2 = 0; b2_lo = b2_lo0; }
                 }
             }
             if (q < Qw) {    // ---- MMA1 of item q: D = Ws_j . x_proj^T (hi.hi + hi.lo + lo.hi) + bc_j
@@ -189,6 +206,15 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                     mma_bf16_ss(d, desc_join(al + A_LO, HI), desc_join(b1_lo, HI), id1, true);     // lo . x hi, k 0..31
                     mma_bf16_ss(d, desc_join(al + A_LO + 2, HI), desc_join(b1_lo + 2, HI), id1, true);
                     mma_bf16_ss(d, desc_join(al + A_LO + 4, HI), desc_join(one_lo, HI), id1, true);   // + bc_g (k = 32..47 of the lo rows)
+                    if (pair) {   // channels 32..63: the second sub-row's Ws images against the second tile of the stage
+                        const uint32_t a1 = al + 2 * A_LO, t1 = b1_lo + TIL;
+                        mma_bf16_ss(d, desc_join(a1, HI), desc_join(t1, HI), id1, true);
+                        mma_bf16_ss(d, desc_join(a1 + 2, HI), desc_join(t1 + 2, HI), id1, true);
+                        mma_bf16_ss(d, desc_join(a1 + 4, HI), desc_join(t1 + 4, HI), id1, true);
+                        mma_bf16_ss(d, desc_join(a1 + 6, HI), desc_join(t1 + 6, HI), id1, true);
+                        mma_bf16_ss(d, desc_join(a1 + A_LO, HI), desc_join(t1, HI), id1, true);
+                        mma_bf16_ss(d, desc_join(a1 + A_LO + 2, HI), desc_join(t1 + 2, HI), id1, true);
+                    }
                     tc_commit(&ctl->d_full[w][buf1]);
                 }
                 __syncwarp();
@@ -196,7 +222,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 if (++jj1 == pw) {
                     jj1 = 0;
                     b1_lo += STG;
-                    if (++st1 == ST_STAGES) { st1 = 0; ph1 ^= 1; b1_lo = b1_lo0; }
+                    if (++st1 == n_stages) { st1 = 0; ph1 ^= 1; b1_lo = b1_lo0; }
                 }
             }
         }
@@ -220,8 +246,8 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         int t = 0, jj = sub, i = 0;   // item k = t * pw + jj of the stream; i = items this warpgroup has done
         while (pw > 0 && jj >= pw) { jj -= pw; ++t; }
         for (int k = sub; k < Qw; k += 2, ++i) {
-            const int stage = t % ST_STAGES;
-            mbar_wait(&ctl->b_full[stage], (uint32_t)((t / ST_STAGES) & 1));
+            const int stage = t % n_stages;
+            mbar_wait(&ctl->b_full[stage], (uint32_t)((t / n_stages) & 1));
             const float4 *s4 = reinterpret_cast<const float4 *>(sS + stage * ST_TILE);
             const bool ragged = (t == n_tiles - 1) && last_valid < ST_TILE;
             mbar_wait(&ctl->d_full[w][buf], (uint32_t)bph);
@@ -336,7 +362,12 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         // ---- write this warpgroup's partial (m2, l, S[C]) per slice of its block: chunk slot 2 * blockIdx.x + c ----
         if (pw > 0) {
             const int slot = pw == 1 ? sub : 0;
-            float *o = parts + ((((int64_t)blockIdx.x * 2 + slot) * BH + bh) * G + g) * (C + 2);
+            // pair mode: both sub-row CTAs of a head hold the same (m, l); sub-row 0 writes them, each writes its 32 channels of S
+            const int64_t BHr = pair ? BH / 2 : BH, bhr = pair ? (bh >> 1) : bh;
+            const int64_t slot_stride = BHr * (int64_t)G * (C + 2);
+            float *o = parts + ((((int64_t)blockIdx.x * 2 + slot) * BHr + bhr) * G + g) * (C + 2);
+            float *oS = o + 2 + srow * 32;
+            const bool head_cols = srow == 0;
             if (i > 0) {
                 mbar_wait(&ctl->all_done[w], 0);
                 tc_fence_after();
@@ -344,20 +375,20 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 tmem_ld32(scol, s0);
                 tmem_wait_ld();
                 if (g < G) {
-                    o[0] = m_run; o[1] = l_run;
+                    if (head_cols) { o[0] = m_run; o[1] = l_run; }
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) if (c < C) o[2 + c] = __uint_as_float(s0[c]);
+                    for (int c = 0; c < 32; ++c) if (c < Cw) oS[c] = __uint_as_float(s0[c]);
                 }
             } else if (g < G) {   // no tile for this warpgroup: neutral partial
-                o[0] = -INFINITY; o[1] = 0.f;
+                if (head_cols) { o[0] = -INFINITY; o[1] = 0.f; }
 #pragma unroll
-                for (int c = 0; c < 32; ++c) if (c < C) o[2 + c] = 0.f;
+                for (int c = 0; c < 32; ++c) if (c < Cw) oS[c] = 0.f;
             }
             if (pw == 2 && g < G) {   // the other slot of this block's rows is nobody's: neutral
-                float *o2 = o + BH * (int64_t)G * (C + 2);
-                o2[0] = -INFINITY; o2[1] = 0.f;
+                float *o2 = o + slot_stride;
+                if (head_cols) { o2[0] = -INFINITY; o2[1] = 0.f; }
 #pragma unroll
-                for (int c = 0; c < 32; ++c) if (c < C) o2[2 + c] = 0.f;
+                for (int c = 0; c < 32; ++c) if (c < Cw) o2[2 + srow * 32 + c] = 0.f;
             }
         }
     }
@@ -370,6 +401,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
 }
 
 bool slice_tc_supported(const haet_layer_shape *s) {   // dim_head 16 runs as zero-padded dim_head 32 (the kernels are bound by the N H G exponentials, not by C)
+    if (s->dim_head == 64) return s->slice_num <= 2 * ST_GB;   // pair mode: the Ws images of both sub-rows must fit shared memory
     return (s->dim_head == ST_C || s->dim_head == 16) && s->slice_num <= ST_MAX_GB * ST_GB;
 }
 
@@ -377,7 +409,7 @@ static int64_t slice_tc_chunk_pts(const haet_layer_shape *s) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int64_t BH = s->B * s->heads;
+    const int64_t BH = s->B * s->heads * (s->dim_head == 64 ? 2 : 1);   // CTAs per chunk (pair mode: two sub-rows per head)
     int64_t n_chunks = sms / BH;
     if (n_chunks < 1) n_chunks = 1;
     const int64_t max_chunks = cdiv(s->N, ST_TILE);
@@ -389,13 +421,14 @@ int64_t slice_tc_chunks(const haet_layer_shape *s) { return s->N > 0 ? 2 * cdiv(
 int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,
                     const float *bs, float *chunk_parts, cudaStream_t st) {
     const int n_gb = (s->slice_num + ST_GB - 1) / ST_GB;
-    const size_t smem = 1024 + (size_t)n_gb * 2 * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
+    const bool pair = s->dim_head == 64;
+    const size_t smem = 1024 + (size_t)n_gb * (pair ? 4 : 2) * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
     HAET_DYN_SMEM(slice_tc_kernel<true>, smem);
     HAET_DYN_SMEM(slice_tc_kernel<false>, smem);
     const int64_t chunk_pts = slice_tc_chunk_pts(s);
     const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : ST_RAISE;   // haet_set_raise_threshold: tests force the accumulator-rescale path
-    dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads));
+    dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads * (pair ? 2 : 1)));
     if (options().no_f32x2)
         slice_tc_kernel<false><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
                                                                 s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);

@@ -269,6 +269,10 @@ def test_layer_deterministic_and_noncontiguous_input():
     ("Physics_Attention_Irregular_Mesh", 3, 1111, dict(dim=256, heads=8, dim_head=32, slice_num=64, rotate=45, mlp_ratio=2)),   # batches cross the 128-row GEMM tiles of the operand images
     ("Physics_Attention_Irregular_Mesh", 1, 3000, dict(dim=256, heads=8, dim_head=32, slice_num=512, rotate=45, mlp_ratio=1)),
     ("Physics_Attention_Irregular_Mesh", 1, 777, dict(dim=128, heads=2, dim_head=64, slice_num=64, rotate=0, mlp_ratio=4)),
+    # dim_head 64 (the reference constructor's default) on the tcgen05 passes: two 32-channel pseudo-heads per head ("pair mode")
+    ("Physics_Attention_Irregular_Mesh", 1, 4099, dict(dim=256, heads=4, dim_head=64, slice_num=256, rotate=45, mlp_ratio=2)),
+    ("Physics_Attention_Irregular_Mesh", 2, 1500, dict(dim=256, heads=4, dim_head=64, slice_num=100, rotate=45, mlp_ratio=2)),
+    ("Physics_Attention_Structured_Mesh_2D", 2, 21 * 13, dict(dim=128, heads=2, dim_head=64, slice_num=32, H=21, W=13, rotate=45, mlp_ratio=2)),
     ("Physics_Attention_Structured_Mesh_2D", 4, 85 * 85, dict(dim=128, heads=8, dim_head=16, slice_num=64, H=85, W=85, rotate=45, mlp_ratio=1)),
     ("Physics_Attention_Structured_Mesh_3D", 1, 16 * 12 * 10, dict(dim=64, heads=8, dim_head=8, slice_num=64, H=16, W=12, D=10, rotate=45, mlp_ratio=2)),
     # conv front-ends on the tcgen05 implicit-GEMM path (dim % 64 == 0, inner % 128 == 0, dim_head == 32), B > 1, odd grids
