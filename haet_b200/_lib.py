@@ -30,7 +30,8 @@ class ErwinCfg(C.Structure):
                 ("dec_num_heads", C.c_int32 * MAX_LEVELS), ("dec_depths", C.c_int32 * MAX_LEVELS),
                 ("strides", C.c_int32 * MAX_LEVELS),
                 ("rotate", C.c_float), ("decode", C.c_int32), ("mlp_ratio", C.c_int32),
-                ("dimensionality", C.c_int32), ("attn_bias", C.c_int32)]
+                ("dimensionality", C.c_int32), ("attn_bias", C.c_int32),
+                ("bn_train", C.c_int32), ("bn_eps", C.c_float), ("bn_stats_d", C.c_void_p)]
 
 
 class LayerWeights(C.Structure):
@@ -140,4 +141,4 @@ def make_erwin_cfg(c_hidden, ball_sizes, enc_num_heads, enc_depths, dec_num_head
     assert len(strides) == len(ball_sizes) - 1
     return ErwinCfg(len(ball_sizes), _arr(c_hidden), _arr(ball_sizes), _arr(enc_num_heads), _arr(enc_depths),
                     _arr(dec_num_heads), _arr(dec_depths), _arr(strides), float(rotate), int(bool(decode)),
-                    int(mlp_ratio), int(dimensionality), int(bool(attn_bias)))
+                    int(mlp_ratio), int(dimensionality), int(bool(attn_bias)), 0, 1e-5, None)

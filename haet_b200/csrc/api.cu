@@ -131,7 +131,7 @@ using namespace haet;
 
 extern "C" {
 
-int haet_version(void) { return 2; }
+int haet_version(void) { return 3; }   // 3: haet_erwin_cfg gained bn_train / bn_eps / bn_stats_d
 const char *haet_last_error(void) { return g_err; }
 int64_t haet_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 

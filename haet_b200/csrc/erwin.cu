@@ -351,7 +351,7 @@ __global__ void erwin_scatter_kernel(const float *__restrict__ x0, const int64_t
 // BallPooling (pooling.py:25-40) with eval BatchNorm folded to scale/shift
 __global__ void erwin_pool_kernel(const float *__restrict__ xc, const float *__restrict__ pc, int64_t n_par, int s,
                                   int in_dim, int out_dim, int d, const float *__restrict__ wts, PoolW w,
-                                  float *__restrict__ xo, float *__restrict__ po) {
+                                  float *__restrict__ xo, float *__restrict__ po, int raw = 0) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_par * out_dim) return;
     const int64_t n = t / out_dim; const int o = (int)(t - n * out_dim);
@@ -367,13 +367,13 @@ __global__ void erwin_pool_kernel(const float *__restrict__ xc, const float *__r
         if (o == 0) po[n * d + j] = c;
         for (int m = 0; m < s; ++m) acc = fmaf(pc[(n * s + m) * d + j] - c, wr[s * in_dim + m * d + j], acc);
     }
-    xo[t] = fmaf(acc, wts[w.scale + o], wts[w.shift + o]);
+    xo[t] = raw ? acc : fmaf(acc, wts[w.scale + o], wts[w.shift + o]);   // raw: train-mode BatchNorm follows (erwin_bn_train_kernel)
 }
 
 // BallUnpooling (pooling.py:58-72): children.x = BN(children.x + proj([x_parent | rel_children]))
 __global__ void erwin_unpool_kernel(const float *__restrict__ xp, const float *__restrict__ pp, int64_t n_par, int s,
                                     int in_dim, int out_dim, int d, const float *__restrict__ wts, PoolW w,
-                                    float *__restrict__ xc, const float *__restrict__ pc) {
+                                    float *__restrict__ xc, const float *__restrict__ pc, int raw = 0) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_par * s * out_dim) return;
     const int64_t tokc = t / out_dim; const int c = (int)(t - tokc * out_dim);
@@ -387,7 +387,38 @@ __global__ void erwin_unpool_kernel(const float *__restrict__ xp, const float *_
     for (int mm = 0; mm < s; ++mm)
         for (int j = 0; j < d; ++j)
             acc = fmaf(pc[(n * s + mm) * d + j] - pp[n * d + j], wr[in_dim + mm * d + j], acc);
-    xc[t] = fmaf(xc[t] + acc, wts[w.scale + c], wts[w.shift + c]);
+    xc[t] = raw ? xc[t] + acc : fmaf(xc[t] + acc, wts[w.scale + c], wts[w.shift + c]);
+}
+
+// Train-mode nn.BatchNorm1d over the n rows of x [n, C] (pooling.py:23,56 with module.training): batch mean and BIASED batch
+// variance per channel, y = (x - mean) / sqrt(var + eps) * gamma + beta in place; (mean, var) go to stats[0:C], stats[C:2C] so
+// that the host module can update running_mean / running_var (unbiased, momentum) as torch does.  One CTA per channel, fixed
+// reduction order (strided partials, shared-memory tree): bit-reproducible.  The packed weights carry (gamma, beta) in the
+// slots that hold the folded (scale, shift) in eval mode.
+__global__ void __launch_bounds__(256) erwin_bn_train_kernel(float *__restrict__ x, int64_t n, int C, const float *__restrict__ wts,
+                                                             PoolW w, float eps, float *__restrict__ stats) {
+    __shared__ float red[256];
+    const int c = blockIdx.x, tid = threadIdx.x;
+    auto block_sum = [&](float v) {
+        red[tid] = v;
+        __syncthreads();
+        for (int o = 128; o; o >>= 1) {
+            if (tid < o) red[tid] += red[tid + o];
+            __syncthreads();
+        }
+        const float r = red[0];
+        __syncthreads();
+        return r;
+    };
+    float a = 0.f;
+    for (int64_t i = tid; i < n; i += 256) a += x[i * C + c];
+    const float mean = block_sum(a) / (float)n;
+    float q = 0.f;
+    for (int64_t i = tid; i < n; i += 256) { const float dlt = x[i * C + c] - mean; q = fmaf(dlt, dlt, q); }
+    const float var = block_sum(q) / (float)n;
+    const float inv = 1.0f / sqrtf(var + eps), g = wts[w.scale + c], b = wts[w.shift + c];
+    for (int64_t i = tid; i < n; i += 256) x[i * C + c] = fmaf((x[i * C + c] - mean) * inv, g, b);
+    if (stats && tid == 0) { stats[c] = mean; stats[C + c] = var; }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -682,6 +713,7 @@ static int erwin_forward_fused(const haet_erwin_cfg *c, const float *x_d, const 
                                cudaStream_t st) {
     const int d = c->dimensionality, L = c->n_levels - 1;
     if (!options().erwin_fused || !c->decode || n_trees < 1 || n_trees > EF_MAX_TREES || n_slots % n_trees) return 1;
+    if (c->bn_train) return 1;   // batch statistics couple the trees: the per-tree barriers do not cover them
     ErwinProgram P{};
     P.n_levels = c->n_levels; P.d = d; P.mlp_ratio = c->mlp_ratio; P.n_trees = (int)n_trees;
     P.timeout_ns = 5000000000ull;
@@ -837,6 +869,12 @@ static int erwin_forward_multi(const haet_erwin_cfg *c, const float *x_d, const 
     }
     Walker wk;
     auto rot = [&](int i) -> const int64_t * { return (c->rotate > 0 && rot_idx_d) ? rot_idx_d[i] : nullptr; };
+    // train-mode BatchNorm (haet_erwin_cfg.bn_train): the pool / unpool kernels leave the pre-norm values, a per-channel kernel
+    // normalises with the batch statistics and reports them at bn_stats_d + 2 * (channels of the earlier BatchNorms)
+    const int bn_train = c->bn_train ? 1 : 0;
+    float *bn_stats = c->bn_stats_d;
+    int64_t bn_off = 0;
+    HAET_CHECK_ARG(!bn_train || c->bn_eps > 0.f, "bn_train needs bn_eps > 0");
     for (int i = 0; i < L; ++i) {   // encoder (erwin_flash.py:183-185)
         rc = run_blocks(c, xs[i], ps[i], ns[i], i, c->enc_depths[i], c->enc_num_heads[i], rot(i), weights_d, wk, st);
         if (rc) return rc;
@@ -845,8 +883,14 @@ static int erwin_forward_multi(const haet_erwin_cfg *c, const float *x_d, const 
             PoolW pw = wk.pool(c->c_hidden[i + 1], (int64_t)s * (c->c_hidden[i] + d), c->c_hidden[i + 1]);
             const int64_t tot = ns[i + 1] * c->c_hidden[i + 1];
             erwin_pool_kernel<<<(unsigned)cdiv(tot, 128), 128, 0, st>>>(xs[i], ps[i], ns[i + 1], s, c->c_hidden[i],
-                                                                       c->c_hidden[i + 1], d, weights_d, pw, xs[i + 1], ps[i + 1]);
+                                                                       c->c_hidden[i + 1], d, weights_d, pw, xs[i + 1], ps[i + 1], bn_train);
             HAET_LAUNCHED();
+            if (bn_train && ns[i + 1] > 0) {
+                erwin_bn_train_kernel<<<(unsigned)c->c_hidden[i + 1], 256, 0, st>>>(xs[i + 1], ns[i + 1], c->c_hidden[i + 1], weights_d, pw,
+                                                                                   c->bn_eps, bn_stats ? bn_stats + bn_off : nullptr);
+                HAET_LAUNCHED();
+            }
+            bn_off += 2 * c->c_hidden[i + 1];
         } else {
             HAET_CHECK_ARG(c->c_hidden[i] == c->c_hidden[i + 1], "stride 1 needs equal dims");
             HAET_CUDA(cudaMemcpyAsync(xs[i + 1], xs[i], sizeof(float) * ns[i] * c->c_hidden[i], cudaMemcpyDeviceToDevice, st));
@@ -861,8 +905,14 @@ static int erwin_forward_multi(const haet_erwin_cfg *c, const float *x_d, const 
         PoolW pw = wk.pool((int64_t)s * c->c_hidden[i], c->c_hidden[i + 1] + (int64_t)s * d, c->c_hidden[i]);
         const int64_t tot = ns[i + 1] * s * c->c_hidden[i];
         erwin_unpool_kernel<<<(unsigned)cdiv(tot, 128), 128, 0, st>>>(xs[i + 1], ps[i + 1], ns[i + 1], s, c->c_hidden[i + 1],
-                                                                     c->c_hidden[i], d, weights_d, pw, xs[i], ps[i]);
+                                                                     c->c_hidden[i], d, weights_d, pw, xs[i], ps[i], bn_train);
         HAET_LAUNCHED();
+        if (bn_train && ns[i] > 0) {
+            erwin_bn_train_kernel<<<(unsigned)c->c_hidden[i], 256, 0, st>>>(xs[i], ns[i], c->c_hidden[i], weights_d, pw, c->bn_eps,
+                                                                           bn_stats ? bn_stats + bn_off : nullptr);
+            HAET_LAUNCHED();
+        }
+        bn_off += 2 * c->c_hidden[i];
         rc = run_blocks(c, xs[i], ps[i], ns[i], i, c->dec_depths[i], c->dec_num_heads[i], rot(i), weights_d, wk, st);
         if (rc) return rc;
     }

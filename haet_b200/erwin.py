@@ -74,6 +74,9 @@ class ErwinTransformerBlock(nn.Module):
 class _PoolBase(nn.Module):
     def tensors(self):
         bn = self.norm
+        if bn.training or not bn.track_running_stats:
+            # train-mode semantics (haet_erwin_cfg.bn_train): the kernels normalise with batch statistics, the slots carry (gamma, beta)
+            return [self.proj.weight, self.proj.bias, bn.weight.detach().float(), bn.bias.detach().float()]
         scale = bn.weight.detach().double() / torch.sqrt(bn.running_var.detach().double() + bn.eps)
         shift = bn.bias.detach().double() - bn.running_mean.detach().double() * scale
         return [self.proj.weight, self.proj.bias, scale.float(), shift.float()]
@@ -202,14 +205,47 @@ class ErwinTransformer(nn.Module):
         self._packed, self._packed_key = packed, key
         return packed
 
+    # ---- train-mode BatchNorm (forward only) ------------------------------------------------
+    def batch_norms(self):
+        """The BatchNorm1d modules in the order the kernels run them: encoder pools (stride != 1), then decoder unpools."""
+        out = [layer.pool.norm for layer in self.encoder if layer.pool.stride != 1]
+        if self.decode:
+            out += [layer.unpool.norm for layer in self.decoder]
+        return out
+
+    @torch.no_grad()
+    def update_running_stats(self, norms, stats: torch.Tensor, n_slots: int):
+        """nn.BatchNorm1d's train-mode buffer update from the batch (mean, biased var) the kernels report: running_var takes the
+        UNBIASED variance, momentum None means a cumulative average (torch/nn/modules/batchnorm.py)."""
+        rows, n = [], n_slots
+        for i, layer in enumerate(self.encoder):          # rows entering each BatchNorm
+            n //= self.strides[i]
+            if layer.pool.stride != 1:
+                rows.append(n)
+        if self.decode:
+            for i in range(len(self.strides) - 1, -1, -1):
+                rows.append(n * self.strides[i])
+                n *= self.strides[i]
+        off = 0
+        for bn, cnt in zip(norms, rows):
+            Cn = bn.num_features
+            mean, var = stats[off:off + Cn], stats[off + Cn:off + 2 * Cn]
+            off += 2 * Cn
+            if not bn.track_running_stats or bn.running_mean is None:
+                continue
+            bn.num_batches_tracked += 1
+            f = 1.0 / float(bn.num_batches_tracked) if bn.momentum is None else float(bn.momentum)
+            unbiased = var * (cnt / max(cnt - 1, 1))
+            bn.running_mean.mul_(1 - f).add_(mean.to(bn.running_mean.dtype), alpha=f)
+            bn.running_var.mul_(1 - f).add_(unbiased.to(bn.running_var.dtype), alpha=f)
+
     # ---- forward --------------------------------------------------------------------------
     def forward(self, node_features: torch.Tensor, node_positions: torch.Tensor, batch_idx: torch.Tensor = None,
                 pts_per_tree: Optional[int] = None, **kwargs):
         """erwin_flash.py:138-195.  Trees must all have the same number of points (the HAET layer builds
         B*heads trees of slice_num tokens each); pass ``pts_per_tree`` to skip deriving it from batch_idx."""
-        if self.training and any(isinstance(m, nn.BatchNorm1d) for m in self.modules()):
-            raise NotImplementedError("haet_b200 is forward-only / eval mode: BatchNorm batch statistics "
-                                      "(train mode) are not implemented; call .eval()")
+        # train mode is FORWARD ONLY (SURVEY 8f-4, partial): BatchNorm1d normalises with batch statistics and updates its
+        # running buffers like torch; there is no backward pass, the result carries no grad_fn
         from .balltree import _uniform_pts, balltree_device
         x = node_features.contiguous().float()
         pos = node_positions.contiguous().float()
@@ -228,10 +264,25 @@ def erwin_device(erwin: ErwinTransformer, x, pos, tree_idx, tree_mask, rots, n_t
     ws_bytes = l.haet_erwin_workspace_bytes(C.byref(erwin.cfg), n_slots)
     ws = torch.empty(max(ws_bytes, 4) // 4, dtype=torch.float32, device=dev)
     out = torch.empty_like(x)
+    cfg, stats = erwin.cfg, None
+    norms = erwin.batch_norms()
+    batch = [bn.training or not bn.track_running_stats for bn in norms]
+    if any(batch) and not all(batch):
+        raise NotImplementedError("BatchNorm layers in mixed train / eval state are not supported")
+    if not any(batch):
+        norms = []
+    if norms:
+        if len({float(bn.eps) for bn in norms}) != 1:
+            raise NotImplementedError("train-mode BatchNorm: all pooling layers must share one eps")
+        cfg = _lib.ErwinCfg.from_buffer_copy(erwin.cfg)
+        stats = torch.zeros(2 * sum(bn.num_features for bn in norms), dtype=torch.float32, device=dev)
+        cfg.bn_train, cfg.bn_eps, cfg.bn_stats_d = 1, float(norms[0].eps), stats.data_ptr()
     nl = erwin.cfg.n_levels
     rot_ptrs = (C.c_void_p * nl)(*[(r.data_ptr() if r is not None else None) for r in rots])
     st = torch.cuda.current_stream(dev).cuda_stream
-    _lib.check(l.haet_erwin_forward_trees(C.byref(erwin.cfg), x.data_ptr(), pos.data_ptr(), x.shape[0], max(int(n_trees), 1),
+    _lib.check(l.haet_erwin_forward_trees(C.byref(cfg), x.data_ptr(), pos.data_ptr(), x.shape[0], max(int(n_trees), 1),
                                           tree_idx.data_ptr(), tree_mask.data_ptr(), n_slots, rot_ptrs, w.data_ptr(),
                                           ws.data_ptr(), out.data_ptr(), st))
+    if norms:
+        erwin.update_running_stats(norms, stats, n_slots)
     return out

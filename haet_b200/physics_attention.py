@@ -146,9 +146,8 @@ class _PhysicsAttentionBase(nn.Module):
         pos = torch.empty(T, self.dimensionality, **f32)
         _lib.check(l.haet_slice_merge(psh, parts.data_ptr(), n_ranks, eidetic.data_ptr(), lse2.data_ptr(),
                                       pos.data_ptr(), st))
-        if self.erwin.training:
-            raise NotImplementedError("haet_b200 is forward-only / eval mode (BatchNorm batch statistics are not "
-                                      "implemented); call .eval()")
+        # self.training: forward only (partial) -- Erwin's BatchNorm1d layers use batch statistics and update their
+        # running buffers (erwin.py); the result has no grad_fn, there is no backward pass
         tree_idx, tree_mask, rots = balltree_device(pos, B * H, G, self.erwin.strides, self.erwin.ball_sizes,
                                                     float(self.erwin.rotate))
         states = erwin_device(self.erwin, eidetic, pos, tree_idx, tree_mask, rots, B * H)

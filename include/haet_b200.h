@@ -84,6 +84,14 @@ typedef struct haet_erwin_cfg {
     int32_t attn_bias;                   /* 0: erwinflash BallMSA (no bias, the HAET default); 1: add the distance bias
                                           * sigma_att[h] * ||p_i - p_j|| of the non-flash copy (benchmarks/02-.../erwin/components/
                                           * attention.py:28-32,49-51); every block's packed weights then end with sigma_att[heads] */
+    int32_t bn_train;                    /* 0: eval-mode BatchNorm1d of BallPooling / BallUnpooling (pooling.py:23,56) folded into a per-channel
+                                          * (scale, shift) by the caller.  1: module.training semantics (forward only): the
+                                          * (scale, shift) slots of the packed weights hold (gamma, beta), every BatchNorm normalises with
+                                          * the batch mean / biased variance over ALL rows of its level (duplicated leaf slots included,
+                                          * as in the reference) */
+    float bn_eps;                        /* BatchNorm1d.eps (1e-5), used when bn_train */
+    float *bn_stats_d;                   /* bn_train: NULL, or device floats receiving (mean[C], biased var[C]) of every BatchNorm in
+                                          * execution order: encoder pools 0 .. L-1 (strides != 1), then decoder unpools L-1 .. 0 */
 } haet_erwin_cfg;
 
 int haet_version(void);

@@ -65,6 +65,28 @@ def save_layer(name, cls_name, kwargs, B, N, seed, trained=True):
     print(name, "out absmax", float(out.abs().max()), "bytes", os.path.getsize(os.path.join(OUT, name + ".npz")))
 
 
+def save_layer_train(name, cls_name, kwargs, B, N, seed):
+    """The reference layer in TRAIN mode (BatchNorm1d batch statistics in BallPooling / BallUnpooling,
+    pooling.py:23,56; dropout 0): weights BEFORE the call, the output, and the BatchNorm buffers AFTER it."""
+    ref = ref_loader.load_reference()
+    torch.manual_seed(seed)
+    m = getattr(ref.PhysicsAttention, cls_name)(**kwargs)
+    trained_like_(m, seed + 1)
+    x = torch.nn.functional.layer_norm(torch.randn(B, N, kwargs["dim"]), (kwargs["dim"],))
+    blob = {"x": x.numpy(), "cfg": np.frombuffer(json.dumps({"cls": cls_name, "kwargs": kwargs}).encode(), dtype=np.uint8)}
+    for k, v in m.state_dict().items():
+        blob["sd/" + k] = v.clone().numpy()
+    m.train()
+    with torch.no_grad():
+        out = m(x)
+    blob["out"] = out.numpy()
+    for k, v in m.state_dict().items():
+        if "running_" in k or "num_batches_tracked" in k:
+            blob["after/" + k] = v.clone().numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **blob)
+    print(name, "out absmax", float(out.abs().max()), "bytes", os.path.getsize(os.path.join(OUT, name + ".npz")))
+
+
 def save_balltree(name, d, n_trees, G, angle, mode, seed):
     bt = ref_loader.load_reference_balltree()
     g = torch.Generator().manual_seed(seed)
@@ -198,6 +220,10 @@ def save_models():
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "train":   # only the train-mode layer golden (added later than the others)
+        save_layer_train("layer_irregular_train", "Physics_Attention_Irregular_Mesh",
+                         dict(dim=64, heads=4, dim_head=16, slice_num=100, rotate=45, mlp_ratio=2), B=2, N=900, seed=41)
+        sys.exit(0)
     save_erwin_bias("erwin_bias_small", seed=21)
     save_models()
     save_layer("layer_irregular_small", "Physics_Attention_Irregular_Mesh",

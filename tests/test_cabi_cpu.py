@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol(lib):
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in the header but not exported"
     assert declared == set(_lib.SYMBOLS), "ctypes binding table and header disagree"
-    assert lib.haet_version() == 2
+    assert lib.haet_version() == 3
 
 
 def test_struct_layout_matches_c_header():

@@ -161,6 +161,46 @@ def test_layer_matches_reference_golden(name):
         assert rel_l2(got, out) < TOL
 
 
+def test_layer_train_mode_forward_matches_reference_golden():
+    """SURVEY 8f-4, the forward half: module.train() runs Erwin's BatchNorm1d layers on batch statistics (pooling.py:23,56) and
+    updates running_mean / running_var / num_batches_tracked like torch.  Golden = the unmodified reference in train mode."""
+    import numpy as np
+    import os
+    import haet_b200 as hb
+    from tests.helpers import GOLDEN
+    cfg, sd, x, out = load_layer_golden("layer_irregular_train")
+    z = np.load(os.path.join(GOLDEN, "layer_irregular_train.npz"))
+    after = {k[6:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("after/")}
+    m = getattr(hb, cfg["cls"])(**cfg["kwargs"])
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda().train()
+    m.keep_taps = True
+    got = m(x.cuda())
+    assert got.grad_fn is None   # forward only
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    want = O.physics_attention_forward(sd, x, tree=tree, pos_override=t["pos"].cpu(), bn_training=True, **oracle_kwargs(cfg))
+    assert rel_l2(got, want) < TOL
+    taps = {}
+    O.physics_attention_forward(sd, x, taps=taps, bn_training=True, **oracle_kwargs(cfg))
+    same_tree = torch.equal(taps["tree_idx"], tree[0]) and all(
+        (a is None and b is None) or torch.equal(a, b) for a, b in zip(taps["rot_idx"], tree[2]))
+    now = m.state_dict()
+    for k, v in after.items():
+        if k.endswith("num_batches_tracked"):
+            assert int(now[k]) == int(v), k
+        elif same_tree:
+            assert rel_l2(now[k], v) < 1e-4, k
+        assert not torch.equal(now[k].cpu(), sd[k]), k   # the buffer moved
+    if same_tree:
+        assert rel_l2(got, out) < TOL
+    # a second call keeps counting; eval mode afterwards uses the updated running statistics
+    m(x.cuda())
+    assert all(int(v) == 2 for k, v in m.state_dict().items() if k.endswith("num_batches_tracked"))
+    ev = m.eval()(x.cuda())
+    assert torch.isfinite(ev).all() and rel_l2(ev, got) > 1e-4
+
+
 @pytest.mark.parametrize("path", [0, 1])
 def test_both_device_paths_match_oracle(path):
     """The tcgen05 path (0) and the exact-fp32 SIMT cross-check path (1, haet_set_path) on the tensor-core shape."""
@@ -780,8 +820,8 @@ def test_errors_are_loud():
     with pytest.raises(hb.HaetError):
         m.eval()(torch.randn(1, 10, 64))                 # CPU tensor: no fallback
     m = m.cuda()
-    with pytest.raises(NotImplementedError):
-        m.train()(torch.randn(1, 100, 64).cuda())        # train-mode BatchNorm statistics
+    m.to_out[1].p = 0.0
+    assert m.train()(torch.randn(1, 100, 64).cuda()).grad_fn is None   # train mode is forward only: no autograd graph
     with pytest.raises(ValueError):
         m.eval()(torch.randn(1, 100, 32).cuda())         # wrong channel count
     with pytest.raises(NotImplementedError):

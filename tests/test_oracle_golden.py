@@ -34,6 +34,15 @@ def test_layer_oracle_matches_reference_golden(name):
     assert rel_l2(got, out) < 2e-6
 
 
+def test_layer_oracle_train_mode_matches_reference_golden():
+    """SURVEY 8f-4 (forward only): module.train() -- BatchNorm1d of BallPooling / BallUnpooling on batch statistics
+    (pooling.py:23,56); 100 slices, so the duplicated leaf slots of the padded tree enter the statistics as in the reference."""
+    cfg, sd, x, out = load_layer_golden("layer_irregular_train")
+    got = O.physics_attention_forward(sd, x, bn_training=True, **oracle_kwargs(cfg))
+    assert rel_l2(got, out) < 2e-6
+    assert rel_l2(O.physics_attention_forward(sd, x, **oracle_kwargs(cfg)), out) > 1e-3   # eval statistics give something else
+
+
 @pytest.mark.parametrize("name", ["layer_irregular_small", "layer_2d_small", "layer_3d_small"])
 def test_streamed_oracle_equals_materialising_oracle(name):
     """The streamed restatement used at the BASELINE sizes (no N x G weights in memory; conv front-ends tap by tap) is the
