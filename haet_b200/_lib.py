@@ -57,6 +57,9 @@ SYMBOLS = {
     "haet_slice_reduce": (C.c_int, [_SH, _P, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P]),
     "haet_slice_ln_workspace_bytes": (C.c_int64, [_SH]),
     "haet_slice_reduce_ln": (C.c_int, [_SH, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P, C.c_float, _P, _P, _P, _P]),
+    "haet_slice_halo_workspace_bytes": (C.c_int64, [_SH, C.c_int32, C.c_int32, C.c_int32]),
+    "haet_slice_reduce_halo": (C.c_int, [_SH, C.c_int32, C.c_int32, _P, _P, _P, C.c_float, _P, _P, _P, _P, _P, C.c_float, _P, _P,
+                                         _P, _P]),
     "haet_slice_merge": (C.c_int, [_SH, _P, C.c_int32, _P, _P, _P, _P]),
     "haet_peer_buffer_bytes": (C.c_int64, [_SH]),
     "haet_peer_exchange": (C.c_int, [_SH, C.POINTER(C.c_void_p), C.c_int32, C.c_int32, _P, _P, _P, _P]),

@@ -257,6 +257,70 @@ static int slice_reduce_impl(const haet_layer_shape *s, const float *x_d, const 
     return launch_slice_merge(s, parts, slice_chunks(s), partial_d, nullptr, nullptr, st);
 }
 
+// ---- halo-exchange sharding of the conv front-ends: a rank owns a slab of grid planes ----------------------
+static int halo_ext_shape(const haet_layer_shape *s, int32_t halo_lo, int32_t halo_hi, haet_layer_shape *ext) {
+    int rc = check_shape(s);
+    if (rc) return rc;
+    HAET_CHECK_ARG(s->conv_nd == 2 || s->conv_nd == 3, "haet_slice_reduce_halo: the shape has no conv front-end (conv_nd must be 2 or 3)");
+    const int64_t plane = (int64_t)s->grid[1] * (s->conv_nd == 3 ? s->grid[2] : 1);
+    HAET_CHECK_ARG(plane > 0 && s->grid[0] > 0 && s->N == (int64_t)s->grid[0] * plane,
+                   "haet_slice_reduce_halo: N = %lld is not grid[0] * grid[1] (* grid[2]) of the local slab", (long long)s->N);
+    const int r = s->kernel / 2;
+    HAET_CHECK_ARG((halo_lo == 0 || halo_lo == r) && (halo_hi == 0 || halo_hi == r),
+                   "haet_slice_reduce_halo: a halo is 0 (outer boundary of the grid) or kernel / 2 = %d planes", r);
+    *ext = *s;
+    ext->grid[0] = s->grid[0] + halo_lo + halo_hi;
+    ext->N = (int64_t)ext->grid[0] * plane;
+    return HAET_OK;
+}
+static bool halo_tc_ok(const haet_layer_shape *s) { return hooks().path == 0 && slice_tc_supported(s) && deslice_tc_supported(s); }
+
+int64_t haet_slice_halo_workspace_bytes(const haet_layer_shape *s, int32_t halo_lo, int32_t halo_hi, int32_t with_ln) {
+    haet_layer_shape ext;
+    if (halo_ext_shape(s, halo_lo, halo_hi, &ext) != HAET_OK) return HAET_EINVAL;
+    if (!halo_tc_ok(s)) { set_error("haet_slice_reduce_halo needs the tensor-core passes (dim_head 16 / 32 / 64)"); return HAET_ENOSUP; }
+    const int64_t ib = image_bytes(s) > image_bytes(&ext) ? image_bytes(s) : image_bytes(&ext);
+    const int64_t inner = (int64_t)s->heads * s->dim_head;
+    return align_up(slice_parts_bytes(s) + ib, 256) + align_up(s->B * ext.N * inner * 4, 256) +
+           (with_ln ? align_up(s->B * ext.N * (int64_t)s->dim * 4, 256) : 0);
+}
+
+int haet_slice_reduce_halo(const haet_layer_shape *s, int32_t halo_lo, int32_t halo_hi, const float *x_ext_d, const float *ln_g_d,
+                           const float *ln_b_d, float ln_eps, const float *wx_d, const float *bx_d, const float *ws_d,
+                           const float *bs_d, const float *wt_d, float bt, void *spill_d, float *partial_d, void *workspace_d,
+                           void *stream) {
+    haet_layer_shape ext;
+    int rc = halo_ext_shape(s, halo_lo, halo_hi, &ext);
+    if (rc) return rc;
+    if (!halo_tc_ok(s)) { set_error("haet_slice_reduce_halo needs the tensor-core passes (dim_head 16 / 32 / 64)"); return HAET_ENOSUP; }
+    if (s->B == 0) return HAET_OK;
+    HAET_CHECK_ARG((ln_g_d == nullptr) == (ln_b_d == nullptr) && (ln_g_d == nullptr || ln_eps > 0.f), "haet_slice_reduce_halo: bad LayerNorm arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    const SpillView sv = spill_view(s, spill_d);
+    const int64_t inner = (int64_t)s->heads * s->dim_head, plane = s->N / s->grid[0];
+    const int64_t ib = image_bytes(s) > image_bytes(&ext) ? image_bytes(s) : image_bytes(&ext);
+    float *parts = (float *)workspace_d;
+    void *img = (char *)workspace_d + slice_parts_bytes(s);
+    float *xp_ext = (float *)((char *)workspace_d + align_up(slice_parts_bytes(s) + ib, 256));
+    if (hooks().stage_mask & 1) {
+        const float *xin = x_ext_d;
+        if (ln_g_d) {   // the caller's ln_1 on every row of the extended slab (zero padding applies AFTER the LayerNorm, as in the reference)
+            float *xn = (float *)((char *)xp_ext + align_up(s->B * ext.N * inner * 4, 256));
+            if ((rc = launch_layernorm_rows(x_ext_d, ln_g_d, ln_b_d, ln_eps, xn, s->B * ext.N, s->dim, st))) return rc;
+            xin = xn;
+        }
+        // the conv over the slab PLUS its halo planes: the zero padding beyond the extended slab is the true padding at an outer
+        // boundary (halo 0) and only reaches halo rows otherwise, which the image pack below skips
+        if (conv_tc_supported(&ext) && !options().conv_simt) rc = launch_conv_tc(&ext, xin, wx_d, bx_d, xp_ext, img, st);
+        else rc = launch_in_project(&ext, xin, wx_d, bx_d, xp_ext, st);
+        if (rc) return rc;
+        if ((rc = launch_xpi_pack(s, xp_ext + (int64_t)halo_lo * plane * inner, wt_d, bt, sv.img, sv.scale, st, ext.N))) return rc;
+    }
+    if (!(hooks().stage_mask & 2)) return HAET_OK;
+    if ((rc = launch_slice_tc(s, sv.img, sv.scale, ws_d, bs_d, parts, st))) return rc;
+    return launch_slice_merge(s, parts, slice_tc_chunks(s), partial_d, nullptr, nullptr, st);
+}
+
 int haet_slice_merge(const haet_layer_shape *s, const float *partials_d, int32_t n_ranks, float *eidetic_d,
                      float *lse2_d, float *pos_d, void *stream) {
     int rc = check_shape(s);

@@ -97,7 +97,7 @@ struct SpillView {
 bool spill_needs_xp(const haet_layer_shape *s);
 SpillView spill_view(const haet_layer_shape *s, void *base);
 int launch_xpi_pack(const haet_layer_shape *s, const float *xp, const float *wt, float bt, uint8_t *img, float *scale,
-                    cudaStream_t st);
+                    cudaStream_t st, int64_t xp_rows_per_batch = 0);
 
 // ---- stage entry points implemented in the .cu files ------------------------------------
 int launch_in_project(const haet_layer_shape *s, const float *x, const float *wx, const float *bx,

@@ -35,7 +35,8 @@ SpillView spill_view(const haet_layer_shape *s, void *base) {
 // PSEUDO-heads (two per head), row (b, 2h + sub) carries channels [32 sub, 32 sub + 32) of head h and the head's s_n
 __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__ xp, const float *__restrict__ wt, float bt,
                                                        float base_temp, int64_t N, int64_t npad, int H, int C, int64_t rows,
-                                                       uint8_t *__restrict__ img, float *__restrict__ scale) {
+                                                       uint8_t *__restrict__ img, float *__restrict__ scale, int64_t Nxp) {
+    // Nxp: rows per batch item of xp (== N, or more when xp also holds the halo planes of a sharded grid: haet_slice_reduce_halo)
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= rows) return;
     const int64_t bh = t / npad, n = t - bh * npad;
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__
     float sn = 0.f;
     if (n < N) {
         const int Cr = C == 64 ? 32 : C;   // channels per image row
-        const float4 *src = reinterpret_cast<const float4 *>(xp + ((int64_t)b * N + n) * (H * Cr) + h * Cr);
+        const float4 *src = reinterpret_cast<const float4 *>(xp + ((int64_t)b * Nxp + n) * (H * Cr) + h * Cr);
         float d = bt;
         const float *wtr = wt;
         float d64 = 0.f;
@@ -52,7 +53,7 @@ __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__
             float dh[2];
 #pragma unroll
             for (int hf = 0; hf < 2; ++hf) {
-                const float4 *sp = reinterpret_cast<const float4 *>(xp + ((int64_t)b * N + n) * (H * Cr) + ((h & ~1) + hf) * Cr);
+                const float4 *sp = reinterpret_cast<const float4 *>(xp + ((int64_t)b * Nxp + n) * (H * Cr) + ((h & ~1) + hf) * Cr);
                 const float *wh = wt + hf * 32;
                 float acc = 0.f;
 #pragma unroll
@@ -98,12 +99,13 @@ __global__ void __launch_bounds__(256) xpi_pack_kernel(const float *__restrict__
 }
 
 int launch_xpi_pack(const haet_layer_shape *s, const float *xp, const float *wt, float bt, uint8_t *img, float *scale,
-                    cudaStream_t st) {
+                    cudaStream_t st, int64_t xp_rows_per_batch) {
     HAET_CHECK_ARG(s->dim_head == 32 || s->dim_head == 16 || s->dim_head == 64, "the operand image needs dim_head 16, 32 or 64");
     const int ph = s->heads * (s->dim_head == 64 ? 2 : 1);
     const int64_t npad = xpi_npad(s->N), rows = s->B * ph * npad;
     if (rows == 0) return HAET_OK;
-    xpi_pack_kernel<<<(unsigned)cdiv(rows, 256), 256, 0, st>>>(xp, wt, bt, s->base_temp, s->N, npad, ph, s->dim_head, rows, img, scale);
+    xpi_pack_kernel<<<(unsigned)cdiv(rows, 256), 256, 0, st>>>(xp, wt, bt, s->base_temp, s->N, npad, ph, s->dim_head, rows, img, scale,
+                                                                  xp_rows_per_batch > 0 ? xp_rows_per_batch : s->N);
     HAET_LAUNCHED();
     return HAET_OK;
 }

@@ -6,6 +6,9 @@ packed rank-partial slice state ``[B*heads*G, C+2]`` (<= 557 KB per rank at 8 he
 channels), after which every rank runs the same rank-ordered log-sum-exp merge, the same (replicated,
 deterministic) ball-tree build and Erwin pass, and deslices its own points.  LayerNorm / MLP of the
 surrounding block are row-local, so a whole HAETransolver stays sharded end to end.
+
+Structured meshes (Conv2d / Conv3d front-ends) shard by SLABS of grid planes: the same flow, preceded by one halo exchange
+of kernel // 2 planes with each neighbour (exchange_halo -> haet_slice_reduce_halo; SURVEY 8f-4).
 """
 from __future__ import annotations
 
@@ -28,6 +31,59 @@ def shard_range(n_points: int, rank: int, world: int) -> Tuple[int, int]:
 def shard_points(x: torch.Tensor, rank: int, world: int, dim: int = 1) -> torch.Tensor:
     lo, hi = shard_range(x.shape[dim], rank, world)
     return x.narrow(dim, lo, hi - lo).contiguous()
+
+
+def shard_planes(n_planes: int, rank: int, world: int) -> Tuple[int, int]:
+    """Slab sharding of a structured mesh: rank owns the planes [lo, hi) of the first grid axis (balanced like shard_range)."""
+    return shard_range(n_planes, rank, world)
+
+
+def shard_grid(x: torch.Tensor, grid, rank: int, world: int) -> torch.Tensor:
+    """The rows of ``x [B, H*W(*D), ...]`` that belong to ``rank``'s slab of planes (row-major grid: a contiguous row range)."""
+    plane = 1
+    for g in grid[1:]:
+        plane *= int(g)
+    lo, hi = shard_planes(int(grid[0]), rank, world)
+    return x.narrow(1, lo * plane, (hi - lo) * plane).contiguous()
+
+
+def exchange_halo(x: torch.Tensor, plane: int, r: int, group=None):
+    """Halo exchange of the conv front-ends of the structured meshes.
+
+    ``x [B, n_local, dim]`` holds this rank's slab of ``n_local / plane`` grid planes.  Returns ``(x_ext, halo_lo, halo_hi)``:
+    the slab preceded by the last ``r`` planes of rank - 1 and followed by the first ``r`` planes of rank + 1 (``r = kernel // 2``;
+    nothing at the outer boundaries, where the conv's zero padding is the true one) -- the input of haet_slice_reduce_halo.
+    One send and one receive per neighbour (NCCL point-to-point on GPUs, gloo on CPU)."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    B, n, dim = x.shape
+    if n % plane or n // plane < r:
+        raise ValueError(f"a slab must hold whole grid planes and at least kernel // 2 = {r} of them (got {n} rows, {plane} per plane)")
+    lo = r if rank > 0 else 0
+    hi = r if rank < world - 1 else 0
+    ext = x.new_empty(B, n + (lo + hi) * plane, dim)
+    ext[:, lo * plane:lo * plane + n] = x
+    if world == 1 or r == 0:
+        return ext, lo, hi
+    peer = (lambda k: dist.get_global_rank(group, k)) if group is not None else (lambda k: k)
+    ops, recv_lo, recv_hi, keep = [], None, None, []
+    if rank > 0:
+        first = x[:, :r * plane].contiguous()
+        recv_lo = x.new_empty(B, r * plane, dim)
+        keep.append(first)
+        ops += [dist.P2POp(dist.isend, first, peer(rank - 1), group), dist.P2POp(dist.irecv, recv_lo, peer(rank - 1), group)]
+    if rank < world - 1:
+        last = x[:, n - r * plane:].contiguous()
+        recv_hi = x.new_empty(B, r * plane, dim)
+        keep.append(last)
+        ops += [dist.P2POp(dist.isend, last, peer(rank + 1), group), dist.P2POp(dist.irecv, recv_hi, peer(rank + 1), group)]
+    for req in dist.batch_isend_irecv(ops):
+        req.wait()
+    if recv_lo is not None:
+        ext[:, :lo * plane] = recv_lo
+    if recv_hi is not None:
+        ext[:, lo * plane + n:] = recv_hi
+    return ext, lo, hi
 
 
 def gather_partials(partial: torch.Tensor, group=None) -> Tuple[torch.Tensor, int]:

@@ -73,12 +73,14 @@ class _PhysicsAttentionBase(nn.Module):
             self._wx_cache = (key, w.detach().reshape(inner, dim, -1).permute(0, 2, 1).contiguous())
         return self._wx_cache[1]
 
-    def _shape(self, B, N):
+    def _shape(self, B, N, planes=None):
         grid = (1, 1, 1)
         if self.conv_nd == 2:
             grid = (self.H, self.W, 1)
         elif self.conv_nd == 3:
             grid = (self.H, self.W, self.D)
+        if planes is not None:   # slab sharding: this rank's planes of the first grid axis
+            grid = (planes,) + grid[1:]
         k = self.in_project_x.weight.shape[-1] if self.conv_nd else 1
         return _lib.make_shape(B, N, self.dim, self.heads, self.dim_head, self.slice_num, self.conv_nd, grid, k,
                                self.dimensionality, self.base_temp, self.epsilon)
@@ -109,7 +111,14 @@ class _PhysicsAttentionBase(nn.Module):
         if B == 0:   # nothing to do (the C-ABI returns HAET_OK for an empty batch too)
             return x.new_empty((0, N, self.dim), dtype=in_dtype)
         f32 = dict(dtype=torch.float32, device=dev)
-        sh = self._shape(B, N)
+        slab = self.conv_nd != 0 and self.point_group is not None   # structured mesh sharded by slabs of planes + halo exchange
+        if slab:
+            plane = self.W * (self.D if self.conv_nd == 3 else 1)
+            if N % plane:
+                raise ValueError(f"slab sharding: a rank's {N} points are not whole planes of {plane} points")
+            sh = self._shape(B, N, N // plane)
+        else:
+            sh = self._shape(B, N)
         psh = C.byref(sh)
         st = torch.cuda.current_stream(dev).cuda_stream
         wx = self._wx().float()
@@ -124,11 +133,25 @@ class _PhysicsAttentionBase(nn.Module):
         H, G, Cc = self.heads, self.slice_num, self.dim_head
         T = B * H * G
         spill = torch.empty(max(l.haet_spill_bytes(psh), 4), dtype=torch.uint8, device=dev)
-        slice_ws = l.haet_slice_ln_workspace_bytes(psh) if ln_1 is not None else l.haet_slice_workspace_bytes(psh)
+        if slab:
+            from .distributed import exchange_halo
+            x_ext, h_lo, h_hi = exchange_halo(x, plane, int(self.in_project_x.weight.shape[-1]) // 2, self.point_group)
+            slice_ws = l.haet_slice_halo_workspace_bytes(psh, h_lo, h_hi, int(ln_1 is not None))
+            if slice_ws < 0:
+                _lib.check(int(slice_ws))
+        else:
+            slice_ws = l.haet_slice_ln_workspace_bytes(psh) if ln_1 is not None else l.haet_slice_workspace_bytes(psh)
         wsz = max(slice_ws, l.haet_deslice_workspace_bytes(psh), 4)
         work = torch.empty(wsz, dtype=torch.uint8, device=dev)
         partial = torch.empty(l.haet_partial_floats(psh), **f32)
-        if ln_1 is not None:
+        if slab:
+            lg = ln_1.weight.detach().float().contiguous() if ln_1 is not None else None
+            lb = ln_1.bias.detach().float().contiguous() if ln_1 is not None else None
+            _lib.check(l.haet_slice_reduce_halo(psh, h_lo, h_hi, x_ext.data_ptr(), lg.data_ptr() if lg is not None else None,
+                                                lb.data_ptr() if lb is not None else None, float(ln_1.eps) if ln_1 is not None else 0.0,
+                                                wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(), wt.data_ptr(), bt,
+                                                spill.data_ptr(), partial.data_ptr(), work.data_ptr(), st))
+        elif ln_1 is not None:
             lg = ln_1.weight.detach().float().contiguous()
             lb = ln_1.bias.detach().float().contiguous()
             _lib.check(l.haet_slice_reduce_ln(psh, x.data_ptr(), lg.data_ptr(), lb.data_ptr(), float(ln_1.eps),

@@ -138,6 +138,22 @@ int haet_slice_reduce_ln(const haet_layer_shape *s, const float *x_d, const floa
                          const float *wx_d, const float *bx_d, const float *ws_d, const float *bs_d, const float *wt_d,
                          float bt, void *spill_d, float *partial_d, void *workspace_d, void *stream);
 
+/* ---- slab sharding of the structured meshes (new; SURVEY 8e "2D/3D" + 8f-4 halo exchange) --------------------------
+ * A rank owns grid[0] consecutive planes of the (H, W[, D]) grid -- a contiguous run of rows of x -- and the conv front-end
+ * (StructuredMesh2D.py:173-189, StructuredMesh3D.py:177-193) needs kernel / 2 planes of its neighbours on either side.
+ * s describes the LOCAL slab (grid[0] = local planes, N = local points); x_ext_d [B, (halo_lo + grid[0] + halo_hi) * plane, dim]
+ * holds the neighbour's planes, then the slab, then the other neighbour's planes (the caller exchanges them: haet_b200/
+ * distributed.py: exchange_halo).  halo_lo / halo_hi are 0 at an outer boundary of the grid (the conv's zero padding is then the
+ * true padding) and kernel / 2 otherwise.  ln_g_d / ln_b_d (both NULL or both set): the caller's ln_1 applied to every row first.
+ * Outputs are those of haet_slice_reduce for the slab's own points; everything downstream (haet_peer_exchange / all-gather,
+ * haet_slice_merge with n_ranks = world, ball tree, Erwin, haet_deslice_out on the slab's spill) is the point-sharded flow of the
+ * irregular model.  Tensor-core passes only (dim_head 16 / 32 / 64; else HAET_ENOSUP). */
+int64_t haet_slice_halo_workspace_bytes(const haet_layer_shape *s, int32_t halo_lo, int32_t halo_hi, int32_t with_ln);
+int haet_slice_reduce_halo(const haet_layer_shape *s, int32_t halo_lo, int32_t halo_hi, const float *x_ext_d, const float *ln_g_d,
+                           const float *ln_b_d, float ln_eps, const float *wx_d, const float *bx_d, const float *ws_d,
+                           const float *bs_d, const float *wt_d, float bt, void *spill_d, float *partial_d, void *workspace_d,
+                           void *stream);
+
 /* Merge R packed rank-partials (rank-major, fixed order => bit-reproducible on every rank) into
  *   eidetic_d [B*heads*G, C]  = (S/l)/(1+1e-5)          (IrregularMesh.py:181-188; sum_n W == 1)
  *   lse2_d    [B*heads*G]     = m2 + log2(l)            (global softmax normaliser, base 2)

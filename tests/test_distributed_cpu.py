@@ -76,3 +76,63 @@ def test_gloo_world2_gather_and_merge():
         mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
         assert len(ret) == world
         assert all(e < 1e-9 for e in ret.values()), dict(ret)
+
+
+# ------------------------------------------------------------------------------------------------
+# slab sharding of the structured meshes: halo exchange of the conv front-end
+# ------------------------------------------------------------------------------------------------
+def test_plane_shards_tile_the_grid():
+    from haet_b200.distributed import shard_grid, shard_planes
+    for H in (2, 7, 64, 85):
+        for w in (1, 2, 3, 4):
+            if H < w:
+                continue
+            r = [shard_planes(H, k, w) for k in range(w)]
+            assert r[0][0] == 0 and r[-1][1] == H and all(r[k][1] == r[k + 1][0] for k in range(w - 1))
+    x = torch.arange(2 * 6 * 5 * 4 * 3, dtype=torch.float32).view(2, 6 * 5 * 4, 3)
+    parts = [shard_grid(x, (6, 5, 4), k, 3) for k in range(3)]
+    assert torch.equal(torch.cat(parts, 1), x) and all(p.shape[1] == 2 * 20 for p in parts)
+
+
+def _halo_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from haet_b200.distributed import exchange_halo, shard_grid, shard_planes
+        from oracle import haet_oracle as O
+        from tests.helpers import load_layer_golden, oracle_kwargs
+        errs = []
+        for name in ("layer_3d_small", "layer_2d_small"):
+            cfg, sd, x, out = load_layer_golden(name)
+            kw = oracle_kwargs(cfg)
+            grid = kw["grid"]
+            plane = 1
+            for g in grid[1:]:
+                plane *= g
+            own, _ = O.split_state_dict(sd, torch.float64)
+            xp_full = O.in_project(own, x.double(), kw["heads"], kw["dim_head"], grid=grid)     # [B, H, N, C]: the global conv
+            mine = shard_grid(x, grid, rank, world)
+            ext, lo, hi = exchange_halo(mine, plane, 1, None)
+            p_lo, p_hi = shard_planes(grid[0], rank, world)
+            assert lo == (1 if rank > 0 else 0) and hi == (1 if rank < world - 1 else 0)
+            # the extended slab is exactly the rows of the global mesh around this rank's planes
+            assert torch.equal(ext, x[:, (p_lo - lo) * plane:(p_hi + hi) * plane])
+            # conv over the extended slab (zero padding beyond it), halo rows dropped == the global conv on this rank's rows
+            g_ext = (p_hi - p_lo + lo + hi,) + tuple(grid[1:])
+            xp_ext = O.in_project(own, ext.double(), kw["heads"], kw["dim_head"], grid=g_ext)
+            got = xp_ext[:, :, lo * plane:lo * plane + mine.shape[1]]
+            want = xp_full[:, :, p_lo * plane:p_hi * plane]
+            errs.append(float((got - want).abs().max()))
+        ret[rank] = max(errs)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_halo_exchange_reproduces_the_global_conv(world):
+    port = 31500 + (os.getpid() % 2000) + world
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_halo_worker, args=(world, port, ret), nprocs=world, join=True)
+        assert len(ret) == world
+        assert all(e < 1e-12 for e in ret.values()), dict(ret)

@@ -1014,3 +1014,90 @@ def test_full_size_properties(N, G):
     Sv = S.view(8, G, 32)
     tol = 1e-3 * (hi - lo).max()
     assert bool((Sv >= lo[:, None] - tol).all()) and bool((Sv <= hi[:, None] + tol).all())   # (3)
+
+
+# ------------------------------------------------------------------------------------------------
+# slab sharding of the structured meshes (halo exchange of the conv front-ends), emulated on ONE GPU through the
+# C-ABI: every "rank" gets its planes plus the neighbours' halo planes, the rank partials are merged in rank order
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("variant,kw,B,R,ln", [
+    ("Physics_Attention_Structured_Mesh_3D", dict(dim=256, heads=8, dim_head=32, slice_num=64, H=12, W=10, D=9, rotate=45, mlp_ratio=2), 1, 3, False),
+    ("Physics_Attention_Structured_Mesh_2D", dict(dim=128, heads=8, dim_head=16, slice_num=64, H=21, W=13, rotate=45, mlp_ratio=1), 2, 2, True),
+    ("Physics_Attention_Structured_Mesh_3D", dict(dim=64, heads=2, dim_head=32, slice_num=32, H=5, W=6, D=7, rotate=45, mlp_ratio=2), 2, 5, False),
+])
+def test_slab_sharded_conv_layer_matches_full_grid(variant, kw, B, R, ln):
+    import haet_b200 as hb
+    from haet_b200 import _lib
+    from haet_b200.balltree import balltree_device
+    from haet_b200.distributed import shard_planes
+    from haet_b200.erwin import erwin_device
+    l = _lib.lib()
+    torch.manual_seed(R)
+    m = getattr(hb, variant)(**kw).eval()
+    trained_like_(m, R + 7)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    grid = (kw["H"], kw["W"]) + ((kw["D"],) if variant.endswith("3D") else ())
+    N = 1
+    for g in grid:
+        N *= g
+    plane = N // grid[0]
+    x_raw = torch.randn(B, N, kw["dim"]) * 1.5 + 0.3
+    ln_1 = torch.nn.LayerNorm(kw["dim"])
+    with torch.no_grad():
+        ln_1.weight.copy_(1 + 0.2 * torch.randn(kw["dim"]))
+        ln_1.bias.copy_(0.1 * torch.randn(kw["dim"]))
+    x = (ln_1(x_raw) if ln else torch.nn.functional.layer_norm(x_raw, (kw["dim"],))).detach()
+    m = m.cuda()
+    m.keep_taps = True
+    full = m(x.cuda())
+    t_full = m.last_taps
+    dev, st = torch.device("cuda"), torch.cuda.current_stream().cuda_stream
+    f32 = dict(dtype=torch.float32, device=dev)
+    wx, bx = m._wx().float(), m.in_project_x.bias.detach().float().contiguous()
+    ws, bs = m.in_project_slice.weight.detach().float().contiguous(), m.in_project_slice.bias.detach().float().contiguous()
+    wt, bt = m.ada_temp_linear.weight.detach().float().contiguous().view(-1), m._bt()
+    wo, bo = m.to_out[0].weight.detach().float().contiguous(), m.to_out[0].bias.detach().float().contiguous()
+    lg, lb = ln_1.weight.detach().cuda(), ln_1.bias.detach().cuda()
+    xin = (x_raw if ln else x).cuda()   # with ln the entry point normalises the raw rows itself (halo rows included)
+    ranks = []
+    for r in range(R):
+        p_lo, p_hi = shard_planes(grid[0], r, R)
+        lo, hi = (1 if r > 0 else 0), (1 if r < R - 1 else 0)
+        n_r = (p_hi - p_lo) * plane
+        sh = m._shape(B, n_r, p_hi - p_lo)
+        psh = C.byref(sh)
+        x_ext = xin[:, (p_lo - lo) * plane:(p_hi + hi) * plane].contiguous()
+        wsz = l.haet_slice_halo_workspace_bytes(psh, lo, hi, int(ln))
+        assert wsz > 0, l.haet_last_error()
+        work = torch.empty(max(wsz, l.haet_deslice_workspace_bytes(psh)), dtype=torch.uint8, device=dev)
+        spill = torch.empty(l.haet_spill_bytes(psh), dtype=torch.uint8, device=dev)
+        partial = torch.empty(l.haet_partial_floats(psh), **f32)
+        _lib.check(l.haet_slice_reduce_halo(psh, lo, hi, x_ext.data_ptr(), lg.data_ptr() if ln else None, lb.data_ptr() if ln else None,
+                                            float(ln_1.eps) if ln else 0.0, wx.data_ptr(), bx.data_ptr(), ws.data_ptr(), bs.data_ptr(),
+                                            wt.data_ptr(), bt, spill.data_ptr(), partial.data_ptr(), work.data_ptr(), st))
+        ranks.append(dict(sh=sh, spill=spill, work=work, partial=partial, n=n_r, keep=x_ext))
+    H, G, Cc = kw["heads"], kw["slice_num"], kw["dim_head"]
+    T = B * H * G
+    parts = torch.cat([r["partial"] for r in ranks])
+    eidetic, lse2, pos = torch.empty(T, Cc, **f32), torch.empty(T, **f32), torch.empty(T, m.dimensionality, **f32)
+    _lib.check(l.haet_slice_merge(C.byref(ranks[0]["sh"]), parts.data_ptr(), R, eidetic.data_ptr(), lse2.data_ptr(), pos.data_ptr(), st))
+    # other chunk boundaries -> other lazy references of the fp16 P: the two states agree at the precision of either (~1e-4), not bitwise
+    assert rel_l2(eidetic.view(B, H, G, Cc), t_full["S"]) < 2e-4 and float((lse2.view(B, H, G) - t_full["lse2"]).abs().max()) < 1e-3
+    tree_idx, tree_mask, rots = balltree_device(pos, B * H, G, m.erwin.strides, m.erwin.ball_sizes, float(m.erwin.rotate))
+    states = erwin_device(m.erwin, eidetic, pos, tree_idx, tree_mask, rots, B * H)
+    outs = []
+    for r in ranks:
+        out = torch.empty(B, r["n"], kw["dim"], **f32)
+        _lib.check(l.haet_deslice_out(C.byref(r["sh"]), r["spill"].data_ptr(), lse2.data_ptr(), states.data_ptr(), ws.data_ptr(),
+                                      bs.data_ptr(), wt.data_ptr(), bt, wo.data_ptr(), bo.data_ptr(), out.data_ptr(),
+                                      r["work"].data_ptr(), st))
+        outs.append(out)
+    got = torch.cat(outs, 1)
+    tree = (tree_idx.cpu(), tree_mask.cpu(), [q.cpu() if q is not None else None for q in rots])
+    okw = dict(heads=H, dim_head=Cc, slice_num=G, rotate=kw["rotate"], mlp_ratio=kw["mlp_ratio"], dimensionality=m.dimensionality, grid=grid)
+    want = O.physics_attention_forward(sd, x, tree=tree, pos_override=pos.cpu(), **okw)
+    assert torch.isfinite(got).all() and rel_l2(got, want) < TOL
+    if torch.equal(tree_idx, t_full["tree_idx"]) and all((a is None and b is None) or torch.equal(a, b) for a, b in zip(rots, t_full["rot_idx"])):
+        assert rel_l2(got, full) < 5e-4
+    # bad halo widths and shapes without a conv front-end are refused
+    assert l.haet_slice_halo_workspace_bytes(C.byref(ranks[0]["sh"]), 2, 0, 0) == _lib.HAET_EINVAL
