@@ -30,6 +30,7 @@
  *   haet_model_prologue / haet_time_embed / haet_head_ln_linear
  *                          Model.forward around the blocks: preprocess MLP + placeholder + time embedding
  *                          (HAETransolver_Irregular_Mesh.py:351-370, 297-336) and the last block's mlp2(ln_3(fx)) (:131-132)
+ *   haet_slice_reduce_halo   haet_slice_reduce for one slab of a structured mesh sharded over GPUs (new)
  *   haet_layer_forward_host  the whole Physics_Attention_*.forward
  *                          (IrregularMesh.py:141-235) on HOST buffers
  */
@@ -121,6 +122,8 @@ int64_t haet_balltree_slots(int64_t n_trees, int64_t pts);
  * spill_d  haet_spill_bytes() bytes (projected points kept for the deslice pass)
  * partial_d haet_partial_floats() floats: this rank's un-normalised slice state in the
  *          base-2 log domain: m2 = a reference exponent (<= max_n z*log2e), l = sum_n 2^(z2-m2), S = sum_n 2^(z2-m2) x_proj
+ * dim_head: 32 and 16 (zero-padded image rows) and 64 (two 32-channel pseudo-heads per head, slice_num <= 256) run on the
+ * tcgen05 passes; 4 / 8, and 64 with more slices, on the fp32 SIMT kernels.
  * Numeric range: the tensor-core path keeps x_proj as fp16 hi + lo (relative 2^-22 for |x_proj| in [2^-3, 65504]); values
  * beyond +-65504 SATURATE (they never become inf / NaN) and values below 2^-14 keep an absolute precision of 2^-25.
  */
