@@ -407,7 +407,9 @@ def ncu_traffic():
     d = json.load(open(p))
     key = {"in_project": "gemm2_tc_kernel<1, 0, 0>", "slice_pass1": "slice_tc_kernel", "deslice_pass2": "deslice_tc_kernel",
            "to_out": "gemm2_tc_kernel<0, 0, 0>"}
-    return {k: d[v]["traffic_bytes"] for k, v in key.items() if v in d}
+    def find(v):   # the passes are templates now: "slice_tc_kernel<1>"
+        return next((d[k] for k in d if k == v or k.startswith(v + "<")), None)
+    return {k: find(v)["traffic_bytes"] for k, v in key.items() if find(v) is not None}
 
 
 def roofline_for(stages, args, pk):

@@ -76,13 +76,29 @@ def main():
         a[1] += v
     ours = {k: a for k, a in agg.items() if not k.startswith("at::")}
     tot = sum(a[1] for a in ours.values())
+    # kernels of ONE plain layer forward (haet_b200 PhysicsAttention at the bench shape) and how often each runs in it; the
+    # LN / residual / MLP variants (gemm2_tc_kernel<1,1,0>, <0,0,1>, <2,1,0>, ln_fold) belong to the bench's fused-block leg
+    layer = [("gemm_tc_pack_kernel", 2), ("gemm2_tc_kernel<1, 0, 0>", 1), ("slice_tc_kernel<1>", 1), ("slice_merge_kernel", 2),
+             ("slice_pos_kernel", 1), ("balltree_kernel", 1), ("erwin_gather_kernel", 1), ("erwin_block_kernel", 6),
+             ("erwin_pool_kernel", 1), ("erwin_unpool_kernel", 1), ("erwin_scatter_kernel", 1), ("deslice_tc_kernel<1>", 1),
+             ("gemm2_tc_kernel<0, 0, 0>", 1)]
     with open(prefix + "_launches.md", "w") as f:
-        f.write("ncu --metrics gpu__time_duration.sum --clock-control none over scripts/profile_layer.py "
-                "(config 4 layer, 2 forwards): every haet_b200 launch, summed per kernel.\n\n")
-        f.write("| kernel | launches | total us | share |\n|---|---|---|---|\n")
+        f.write("ncu --metrics gpu__time_duration.sum --clock-control none over `python bench.py --steps 2 --warmup 3 --no-configs` "
+                "(the bench command: timed layer steps under graph replay, the e2e leg, the stage timings and the fused-block leg): "
+                "every haet_b200 launch, summed per kernel.\n\n")
+        f.write("| kernel | launches | total us | avg us | share of all |\n|---|---|---|---|---|\n")
         for k, a in ours.items():
-            f.write("| %s | %d | %.1f | %.1f%% |\n" % (k, a[0], a[1], 100 * a[1] / tot))
+            f.write("| %s | %d | %.1f | %.1f | %.1f%% |\n" % (k, a[0], a[1], a[1] / a[0], 100 * a[1] / tot))
         f.write("\nall haet_b200 kernels: %.1f us over %d launches\n" % (tot, sum(a[0] for a in ours.values())))
+        have = [(k, n) for k, n in layer if k in ours]
+        if have:
+            lt = sum(n * ours[k][1] / ours[k][0] for k, n in have)
+            f.write("\nOne layer forward (the timed step) = these kernels, at their average duration under ncu (cold cache, serialised):\n\n")
+            f.write("| kernel | per layer | us | share of the step |\n|---|---|---|---|\n")
+            for k, n in have:
+                v = n * ours[k][1] / ours[k][0]
+                f.write("| %s | %d | %.1f | %.1f%% |\n" % (k, n, v, 100 * v / lt))
+            f.write("\nsum: %.1f us per layer forward\n" % lt)
 
 
 if __name__ == "__main__":

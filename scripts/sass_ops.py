@@ -14,6 +14,7 @@ out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True
 demangle = lambda n: subprocess.run(["c++filt", n], capture_output=True, text=True).stdout.strip()
 pat = {"UTC*MMA": r"\bUTC[A-Z]*MMA\b", "LDTM": r"\bLDTM\b", "STTM": r"\bSTTM\b", "UBLKCP": r"\bUBLKCP\b",
        "UTMALDG/STG": r"\bUTMA(LDG|STG)\b", "HMMA": r"\bHMMA\b", "MUFU.EX2": r"\bMUFU\.EX2\b", "F2FP": r"\bF2FP\b",
+       "FFMA2/FADD2": r"\bF(FMA|ADD)2\b",
        "SYNCS (mbarrier)": r"\bSYNCS\b", "total": r"^\s+/\*[0-9a-f]{4,}\*/"}
 counts, cur = collections.OrderedDict(), None
 for line in out.splitlines():
@@ -31,7 +32,8 @@ cols = list(pat)
 print("# SASS evidence (round 2): `cuobjdump -sass haet_b200/libhaet_b200.so`, counted by scripts/sass_ops.py\n")
 print("sm_100a only (`-gencode arch=compute_100a,code=sm_100a`).  tcgen05.mma -> `UTC*MMA` (UTCHMMA = kind::f16), "
       "tcgen05.ld / st -> `LDTM` / `STTM`, `cp.async.bulk` -> `UBLKCP`.  No kernel uses tensor-map TMA (`UTMALDG`): every "
-      "operand tile is a contiguous pre-swizzled image, so a 1-D bulk copy moves it; none uses the legacy `HMMA` path.\n")
+      "operand tile is a contiguous pre-swizzled image, so a 1-D bulk copy moves it; none uses the legacy `HMMA` path.  `FFMA2` / `FADD2`: packed fp32 pairs (fma.rn.f32x2) in the softmax "
+      "loops of the two passes.\n")
 print("| kernel | " + " | ".join(cols) + " |")
 print("|---|" + "---|" * len(cols))
 for k, c in counts.items():
