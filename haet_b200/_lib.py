@@ -10,7 +10,7 @@ import os
 from typing import Sequence
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libhaet_b200.so")
+LIB_PATH = os.environ.get("HAET_B200_LIB") or os.path.join(HERE, "libhaet_b200.so")   # override: development builds (scripts/trace_pass2.py)
 MAX_LEVELS = 8
 
 HAET_OK, HAET_EINVAL, HAET_ECUDA, HAET_ENODEV, HAET_ENOSUP = 0, -1, -2, -3, -4

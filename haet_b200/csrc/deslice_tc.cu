@@ -24,6 +24,19 @@
 namespace haet {
 using namespace tc;
 
+#ifdef HAET_TRACE   // development build only (scripts/trace_pass2.py): cycle counters per warp role, never in the shipped library
+__device__ unsigned long long g_dt_trace[64];
+#define DT_T(var) const long long var = clock64()
+#define DT_DECL unsigned long long dt_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}
+#define DT_ACC(slot, v) dt_acc[(slot) & 7] += (unsigned long long)(v)
+#define DT_FLUSH(base) do { if (lane == 0) for (int i_ = 0; i_ < 8; ++i_) atomicAdd(&g_dt_trace[(base) + i_], dt_acc[i_]); } while (0)
+#else
+#define DT_T(var)
+#define DT_DECL
+#define DT_ACC(slot, v)
+#define DT_FLUSH(base)
+#endif
+
 constexpr int DT_C = 32;
 constexpr int DT_TILE = 128;        // points per tile (UMMA M)
 constexpr int DT_GCMAX = 128;       // slices per item (UMMA N of MMA1, K of MMA2): 128, or 64 when G <= 64
@@ -48,7 +61,11 @@ struct DesliceCtl {
 __device__ __forceinline__ uint32_t dt_dbuf_col(int buf) { return 128u + (uint32_t)buf * DT_GCMAX; }
 __host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (G + 127) / 128 * 128; }
 
-template <bool F2>
+// WG: softmax warpgroups (blockDim.x = (4 WG + 8) * 32).  3: warpgroup i owns D / P buffer i.  2: the warpgroups alternate over the
+// three buffers (item q: buffer q % 3, warpgroup q & 1), so a warpgroup never waits for the MMA phases of the buffer it just filled.
+// (Measured and dropped, DESIGN 10: WG = 2 removes the wait for d_full -- 1060 -> 126 cycles per item -- but two warps per scheduler
+// feed the MUFU pipe no better, 0.667 against 0.651 ms; software-pipelined TMEM reads in 16-column units were slower with either.)
+template <bool F2, int WG>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
@@ -75,14 +92,16 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     float *sS = sL + g_pad;                                                            // [stages][128] s_n
     DesliceCtl *ctl = reinterpret_cast<DesliceCtl *>(sS + DT_STAGES * DT_TILE);
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp-uniform role index
+    constexpr int W_EPI = 4 * WG, W_MMA1 = W_EPI + 4, W_LOAD = W_EPI + 5, W_MMA2 = W_EPI + 6, NTHR = (4 * WG + 8) * 32;
     const int bh = blockIdx.y, b = bh / H, h = bh - b * H;   // pair mode: h = pseudo-head 2 h_real + srow
     const int bhr = pair ? (bh >> 1) : bh, srow = pair ? (bh & 1) : 0;
     const int inner = H * Cw;
     const int64_t n_begin = (int64_t)blockIdx.x * chunk_pts;
     const int64_t n_end = min(N, n_begin + chunk_pts);
     const int n_tiles = (int)((n_end - n_begin + DT_TILE - 1) / DT_TILE);
+    DT_T(k_start);
 
-    if (warp == 16) {
+    if (warp == W_MMA1) {
         if (lane == 0) {
             for (int s = 0; s < DT_STAGES; ++s) { mbar_init(&ctl->a_full[s], 1); mbar_init(&ctl->a_empty[s], 2); }
             for (int k = 0; k < DT_NBUF; ++k) { mbar_init(&ctl->d_full[k], 1); mbar_init(&ctl->p_full[k], 128); mbar_init(&ctl->p_free[k], 2); }
@@ -96,7 +115,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     {
         float amax = 0.f;
         const float *sp = states + (size_t)bhr * G * C + srow * 32;
-        for (int idx = threadIdx.x; idx < G * Cw; idx += DT_THREADS) {
+        for (int idx = threadIdx.x; idx < G * Cw; idx += NTHR) {
             const int g = idx / Cw, c = idx - g * Cw;
             amax = fmaxf(amax, fabsf(sp[(size_t)g * C + c]));
         }
@@ -109,7 +128,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     {
         float amax = 0.f;
 #pragma unroll
-        for (int w2 = 0; w2 < DT_THREADS / 32; ++w2) amax = fmaxf(amax, ctl->red[w2]);
+        for (int w2 = 0; w2 < NTHR / 32; ++w2) amax = fmaxf(amax, ctl->red[w2]);
         int e = 14;
         if (amax > 0.f && amax <= 3.0e38f) frexpf(amax, &e);   // amax = f 2^e, f in [0.5, 1); zero / inf / NaN states: no scaling
         e = e < -90 ? -90 : e;
@@ -117,7 +136,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         if (threadIdx.x == 0) ctl->o_scale = ldexpf(1.f, e - 14 - (int)DT_PSHIFT);
     }
     // resident operand images: Ws rows [hi | lo] and S'_h rows (fp16), per-column constants
-    for (int idx = threadIdx.x; idx < g_pad * 4; idx += DT_THREADS) {
+    for (int idx = threadIdx.x; idx < g_pad * 4; idx += NTHR) {
         const int g = idx >> 2, ck = idx & 3;
         __align__(16) __half hi[8], lo[8];
         __align__(16) __half sv[8];
@@ -146,7 +165,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         *reinterpret_cast<uint4 *>(sV + sw128_off(g, ck)) = *reinterpret_cast<const uint4 *>(sv);   // MN-major operand: row g = 32 fp16 channels
         *reinterpret_cast<uint4 *>(sV + sw128_off(g, ck + 4)) = make_uint4(0, 0, 0, 0);
     }
-    for (int g = threadIdx.x; g < g_pad; g += DT_THREADS) {
+    for (int g = threadIdx.x; g < g_pad; g += NTHR) {
         sL[g] = g < G ? DT_PSHIFT - lse2[(size_t)bhr * G + g] : -INFINITY;
         uint32_t b2 = 0;
         if (g < G) {
@@ -158,7 +177,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         *reinterpret_cast<uint4 *>(dstb) = make_uint4(b2, 0, 0, 0);
         *reinterpret_cast<uint4 *>(dstb + 128) = make_uint4(0, 0, 0, 0);
     }
-    for (int n = threadIdx.x; n < DT_TILE; n += DT_THREADS) {
+    for (int n = threadIdx.x; n < DT_TILE; n += NTHR) {
         uint8_t *dst1 = sOne + (n >> 3) * 256 + (n & 7) * 16;
         *reinterpret_cast<uint4 *>(dst1) = make_uint4(0x3c003c00u, 0, 0, 0);   // fp16 1.0, 1.0
         *reinterpret_cast<uint4 *>(dst1 + 128) = make_uint4(0, 0, 0, 0);
@@ -169,9 +188,9 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
     tc_fence_after();
     const uint32_t tmem_base = ctl->tmem_base;
 
-    if (warp >= 12 && warp < 16) {
+    if (warp >= W_EPI && warp < W_EPI + 4) {
         // =========================== O epilogue: TMEM -> global ===========================
-        const int r = threadIdx.x - 384;   // row of the tile == TMEM lane
+        const int r = threadIdx.x - W_EPI * 32;   // row of the tile == TMEM lane
         const float o_scale = ctl->o_scale;
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
         float *dst = o + ((int64_t)b * N) * inner + h * Cw;
@@ -239,7 +258,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 }
             }
         }
-    } else if (warp == 17) {
+    } else if (warp == W_LOAD) {
         // =========================== loader: one bulk copy per 128-point tile (+ its s_n) ===========================
         if (lane == 0) {
             const int64_t bh0 = pair ? (bh & ~1) : bh;   // pair mode: sub-row 0 of this head; sub-row 1 follows npad rows later
@@ -258,7 +277,7 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
             }
         }
         __syncwarp();
-    } else if (warp == 16) {
+    } else if (warp == W_MMA1) {
         // =========================== MMA1 issuer ===========================
         // Items q = (tile t, slice chunk jc) in order; item q uses D / P buffer q % 3 = softmax warpgroup q % 3.  One warp can
         // issue a tcgen05.mma only every ~75 cycles whatever its size (clock64 trace: 7 + 8 small MMAs = 1300 cycles per item was
@@ -271,10 +290,15 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
         const uint32_t bb_a = smem_u32(sBb) >> 4, one_a = smem_u32(sOne) >> 4;
         const uint32_t w_step = (uint32_t)cw * 128 >> 4, b_step = (uint32_t)cw * 32 >> 4;   // one chunk of Ws rows, of bias rows
         int jc1 = 0, st1 = 0, ph1 = 0, buf1 = 0, fph = 0;   // chunk, stage (+phase), D buffer, phase of p_free
+        DT_DECL;
         for (int q = 0; q < Q; ++q) {    // D = x_proj . Ws[chunk]^T  (hi.hi + lo.hi + hi.lo) + bc
+            DT_T(m0);
             if (q >= DT_NBUF) mbar_wait(&ctl->p_free[buf1], (uint32_t)fph);   // both halves of P . S' of item q - 3 have completed
+            DT_T(m1);
             if (jc1 == 0) mbar_wait(&ctl->a_full[st1], (uint32_t)ph1);
             tc_fence_after();
+            DT_T(m2);
+            DT_ACC(16, m1 - m0); DT_ACC(17, m2 - m1); DT_ACC(19, 1);
             if (elect_one()) {
                 const uint32_t a = abase + (uint32_t)st1 * (stage_bytes >> 4);
                 const uint32_t wb = wbase + (uint32_t)jc1 * w_step;
@@ -299,23 +323,31 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 tc_commit(&ctl->d_full[buf1]);
             }
             __syncwarp();
+            DT_T(m3);
+            DT_ACC(18, m3 - m2);
             if (++buf1 == DT_NBUF) { buf1 = 0; if (q >= DT_NBUF) fph ^= 1; }
             if (++jc1 == n_gc) { jc1 = 0; if (++st1 == n_stages) { st1 = 0; ph1 ^= 1; } }
         }
-    } else if (warp >= 18) {
+        DT_FLUSH(16);
+    } else if (warp >= W_MMA2) {
         // =========================== MMA2 issuers: O_u += P . S'_h[chunk], K steps [u, u + 1) * cw / 16 ===========================
-        const int u = warp - 18;
+        const int u = warp - W_MMA2;
         const int Q = n_tiles * n_gc;
         const uint32_t id2 = instr_desc(FMT_F16, DT_TILE, DT_C, false, true);
         const uint32_t vbase = smem_u32(sV) >> 4;
         const uint32_t w_step = (uint32_t)cw * 128 >> 4;
         const int kh = cw / 32;   // K steps (of 16 slices) per warp
         int t2 = 0, jc2 = 0, st2 = 0, buf2 = 0, ph2 = 0;
+        DT_DECL;
         for (int k = 0; k < Q; ++k) {
             const int ob = t2 & 1;
+            DT_T(n0);
             if (jc2 == 0) mbar_wait(&ctl->o_empty[ob], (uint32_t)(((t2 >> 1) & 1) ^ 1));
+            DT_T(n1);
             mbar_wait(&ctl->p_full[buf2], (uint32_t)ph2);
             tc_fence_after();
+            DT_T(n2);
+            DT_ACC(24, n1 - n0); DT_ACC(25, n2 - n1); DT_ACC(27, 1);
             if (elect_one()) {
                 const uint32_t pa = tmem_base + dt_dbuf_col(buf2) + (uint32_t)(u * kh) * 8, od = tmem_base + (uint32_t)(u * 2 + ob) * DT_C;
                 const uint32_t vb = vbase + (uint32_t)jc2 * w_step + (uint32_t)(u * kh) * 128;
@@ -326,30 +358,42 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                 if (jc2 == n_gc - 1) { tc_commit(&ctl->o_full[ob]); tc_commit(&ctl->a_empty[st2]); }
             }
             __syncwarp();
+            DT_T(n3);
+            DT_ACC(26, n3 - n2);
             if (++buf2 == DT_NBUF) { buf2 = 0; ph2 ^= 1; }
             if (++jc2 == n_gc) { jc2 = 0; ++t2; if (++st2 == n_stages) st2 = 0; }
         }
-    } else if (warp < 12) {
+        DT_FLUSH(24);
+    } else if (warp < W_EPI) {
         // =========================== softmax warpgroups ===========================
         // 3 warpgroups, warpgroup i owns D / P buffer i and takes the items q = i, i + 3, ..: it sees EVERY phase of its two
         // barriers (a warpgroup that skipped phases could alias the mbarrier parity when it runs two uses ahead).
         const int wg = warp >> 2, q4 = warp & 3, row = q4 * 32 + lane;
         const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
         const int Q = n_tiles * n_gc, halves = cw / 32;
-        for (int q = wg; q < Q; q += DT_NBUF) {
-            const int t = q / n_gc, jc = q - t * n_gc;
-            const int stage = t % n_stages, buf = wg;
-            mbar_wait(&ctl->a_full[stage], (uint32_t)((t / n_stages) & 1));
+        DT_DECL;
+        DT_T(l_start);
+        // running item coordinates (tile t, slice chunk jc, stage + parity): the divisions they replace cost ~10 % of an item
+        int t = wg / n_gc, jc = wg - t * n_gc, stage = t % n_stages, sph = (t / n_stages) & 1, dph = 0, buf = wg;
+        for (int q = wg; q < Q; q += WG) {
+            DT_T(t0);
+            mbar_wait(&ctl->a_full[stage], (uint32_t)sph);
             const float sn = sS[stage * DT_TILE + row];
-            mbar_wait(&ctl->d_full[buf], (uint32_t)((q / DT_NBUF) & 1));
+            DT_T(t1);
+            mbar_wait(&ctl->d_full[buf], (uint32_t)dph);
             tc_fence_after();
+            DT_T(t2);
+            DT_ACC(0, t1 - t0); DT_ACC(1, t2 - t1); DT_ACC(7, 1);
             const uint32_t dcol = tmem_base + lane_base + dt_dbuf_col(buf);
             const float4 *ll = reinterpret_cast<const float4 *>(sL + jc * cw);
 #pragma unroll 1
             for (int hh = 0; hh < halves; ++hh) {
                 uint32_t r[32], pk[16];
+                DT_T(ta);
                 tmem_ld32(dcol + hh * 32, r);
                 tmem_wait_ld();
+                DT_T(tb);
+                DT_ACC(2, tb - ta);
                 if (F2) {   // packed fp32 pairs: 2 FFMA2 instead of 4 FFMA per 4 logits, bitwise the same values
                     const uint64_t sn2 = f2_pack(sn, sn);
 #pragma unroll
@@ -374,16 +418,37 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                     pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
                 }
                 }
+                DT_T(tc_);
                 tmem_st16(dcol + hh * 16, pk);   // packed P trails the logits it replaces (columns already read)
+                DT_T(td);
+                DT_ACC(3, tc_ - tb); DT_ACC(4, td - tc_);
             }
+            DT_T(t3);
             tmem_wait_st();
             tc_fence_before();
             mbar_arrive(&ctl->p_full[buf]);
+            DT_T(t4);
+            DT_ACC(5, t4 - t3); DT_ACC(6, t4 - t0);
+            buf += WG;
+            if (buf >= DT_NBUF) { buf -= DT_NBUF; dph ^= 1; }   // buffer q % 3 and the parity (q / 3) & 1 of its barriers
+            jc += WG;
+            while (jc >= n_gc) {
+                jc -= n_gc;
+                ++t;
+                if (++stage == n_stages) { stage = 0; sph ^= 1; }
+            }
         }
+        DT_FLUSH(0);
+#ifdef HAET_TRACE
+        { DT_T(l_end); if (lane == 0) { atomicAdd(&g_dt_trace[8], (unsigned long long)(l_start - k_start)); atomicAdd(&g_dt_trace[9], (unsigned long long)(l_end - l_start)); atomicAdd(&g_dt_trace[10], 1ull); } }
+#endif
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 16) {
+#ifdef HAET_TRACE
+    if (threadIdx.x == 0) { atomicAdd(&g_dt_trace[11], (unsigned long long)(clock64() - k_start)); atomicAdd(&g_dt_trace[12], 1ull); }
+#endif
+    if (warp == W_MMA1) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }
@@ -401,8 +466,8 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const bool pair = s->dim_head == 64;
     const size_t smem = 1024 + (size_t)g_pad * (pair ? 384 : 256) + (size_t)(pair ? 2 * (DT_STAGES - 1) : DT_STAGES) * DT_TILE_BYTES + (size_t)g_pad * 32 +
                         DT_TILE * 32 + sizeof(float) * g_pad + sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
-    HAET_DYN_SMEM(deslice_tc_kernel<true>, smem);
-    HAET_DYN_SMEM(deslice_tc_kernel<false>, smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<true, 3>), smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<false, 3>), smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -413,14 +478,20 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     if (n_chunks > max_chunks) n_chunks = max_chunks;
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
-    if (options().no_f32x2)
-        deslice_tc_kernel<false><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                                  xpi_npad(s->N), s->heads * (pair ? 2 : 1), s->slice_num, s->dim_head, chunk_pts, o, o_image);
-    else
-        deslice_tc_kernel<true><<<grid, DT_THREADS, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N,
-                                                                 xpi_npad(s->N), s->heads * (pair ? 2 : 1), s->slice_num, s->dim_head, chunk_pts, o, o_image);
+    constexpr int WG = 3;
+    auto kern = options().no_f32x2 ? deslice_tc_kernel<false, WG> : deslice_tc_kernel<true, WG>;
+    kern<<<grid, (4 * WG + 8) * 32, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
+                                               s->heads * (pair ? 2 : 1), s->slice_num, s->dim_head, chunk_pts, o, o_image);
     HAET_LAUNCHED();
     return HAET_OK;
 }
 
 }  // namespace haet
+
+#ifdef HAET_TRACE
+extern "C" int haet_debug_dt_trace(unsigned long long *out64, int reset) {
+    if (out64 && cudaMemcpyFromSymbol(out64, haet::g_dt_trace, sizeof(unsigned long long) * 64) != cudaSuccess) return -2;
+    if (reset) { unsigned long long z[64] = {0}; if (cudaMemcpyToSymbol(haet::g_dt_trace, z, sizeof(z)) != cudaSuccess) return -2; }
+    return 0;
+}
+#endif

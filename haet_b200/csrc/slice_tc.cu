@@ -30,6 +30,19 @@
 namespace haet {
 using namespace tc;
 
+#ifdef HAET_TRACE   // development build only (scripts/trace_pass2.py): cycle counters per warp role, never in the shipped library
+__device__ unsigned long long g_st_trace[64];
+#define ST_T(var) const long long var = clock64()
+#define ST_DECL unsigned long long st_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}
+#define ST_ACC(slot, v) st_acc[(slot) & 7] += (unsigned long long)(v)
+#define ST_FLUSH(base) do { if (lane == 0) for (int i_ = 0; i_ < 8; ++i_) atomicAdd(&g_st_trace[(base) + i_], st_acc[i_]); } while (0)
+#else
+#define ST_T(var)
+#define ST_DECL
+#define ST_ACC(slot, v)
+#define ST_FLUSH(base)
+#endif
+
 constexpr int ST_C = 32;            // dim_head handled by this kernel
 constexpr int ST_TILE = 64;         // points per tile
 constexpr int ST_STAGES = 10;
@@ -172,11 +185,18 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         int jj1 = 0, st1 = 0, ph1 = 0, buf1 = 0;           // MMA1 cursor: block within the stream, stage (+phase), D buffer
         int jj2 = 0, st2 = 0, buf2 = 0, ph2 = 0;           // MMA2 cursor
         uint32_t b1_lo = b1_lo0, b2_lo = b2_lo0;           // running stage descriptors of the two cursors
+        ST_DECL;
         for (int q = 0; q < Qw + ST_NBUF; ++q) {
             if (q >= ST_NBUF) {   // ---- MMA2 of this stream's item k = q - 3: S_wg += P . hi   (wg = k & 1)
                 const int k = q - ST_NBUF;
+                ST_T(m0);
                 mbar_wait(&ctl->p_full[w][buf2], (uint32_t)ph2);
                 tc_fence_after();
+                ST_T(m1);
+                ST_ACC(0, m1 - m0); ST_ACC(7, 1);
+#ifdef HAET_TRACE
+                const long long m1c = m1;
+#endif
                 if (elect_one()) {
                     const uint32_t pa = tmem_base + st_dbuf_col(w, buf2), sd = tmem_base + (uint32_t)(w * 2 + (k & 1)) * ST_SCOLS;
                     mma_f16_ts(sd, pa, desc_join(b2_lo, HI), id2, k > 1);   // K = 16 points = two 8-row swizzle atoms per step
@@ -187,6 +207,9 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                     if (jj2 == pw - 1) tc_commit(&ctl->b_empty[st2]);
                 }
                 __syncwarp();
+#ifdef HAET_TRACE
+                ST_ACC(2, clock64() - m1c);
+#endif
                 if (++buf2 == ST_NBUF) { buf2 = 0; ph2 ^= 1; }
                 if (++jj2 == pw) {
                     jj2 = 0;
@@ -195,7 +218,10 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 }
             }
             if (q < Qw) {    // ---- MMA1 of item q: D = Ws_j . x_proj^T (hi.hi + hi.lo + lo.hi) + bc_j
+                ST_T(m2);
                 if (jj1 == 0) { mbar_wait(&ctl->b_full[st1], (uint32_t)ph1); tc_fence_after(); }
+                ST_T(m3);
+                ST_ACC(1, m3 - m2);
                 if (elect_one()) {
                     const uint32_t al = a_lo0 + (uint32_t)jj1 * A_JJ;
                     const uint32_t d = tmem_base + st_dbuf_col(w, buf1);
@@ -218,6 +244,9 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                     tc_commit(&ctl->d_full[w][buf1]);
                 }
                 __syncwarp();
+#ifdef HAET_TRACE
+                ST_ACC(3, clock64() - m3);
+#endif
                 if (++buf1 == ST_NBUF) buf1 = 0;
                 if (++jj1 == pw) {
                     jj1 = 0;
@@ -226,6 +255,7 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 }
             }
         }
+        ST_FLUSH(16);
         if (elect_one()) tc_commit(&ctl->all_done[w]);   // every MMA of this stream has completed when this phase flips
         __syncwarp();
     } else {
@@ -245,13 +275,19 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
         const int last_valid = (int)(n_end - n_begin) - (n_tiles - 1) * ST_TILE;   // points in the last tile
         int t = 0, jj = sub, i = 0;   // item k = t * pw + jj of the stream; i = items this warpgroup has done
         while (pw > 0 && jj >= pw) { jj -= pw; ++t; }
+        int stage = t % n_stages, sph = (t / n_stages) & 1;   // running stage + parity of tile t (no division per item)
+        ST_DECL;
+        ST_T(l_start);
         for (int k = sub; k < Qw; k += 2, ++i) {
-            const int stage = t % n_stages;
-            mbar_wait(&ctl->b_full[stage], (uint32_t)((t / n_stages) & 1));
+            ST_T(t0);
+            mbar_wait(&ctl->b_full[stage], (uint32_t)sph);
+            ST_T(t1);
             const float4 *s4 = reinterpret_cast<const float4 *>(sS + stage * ST_TILE);
             const bool ragged = (t == n_tiles - 1) && last_valid < ST_TILE;
             mbar_wait(&ctl->d_full[w][buf], (uint32_t)bph);
             tc_fence_after();
+            ST_T(t2);
+            ST_ACC(0, t1 - t0); ST_ACC(1, t2 - t1); ST_ACC(7, 1);
             const uint32_t dcol = tmem_base + lane_base + st_dbuf_col(w, buf);
 #pragma unroll 1
             for (int hh = 0; hh < 2; ++hh) {
@@ -351,14 +387,25 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                 l_run += l0 + l1;
                 tmem_st16(dcol + hh * 16, pk);
             }
+            ST_T(t3);
             tmem_wait_st();
             tc_fence_before();
             mbar_arrive(&ctl->p_full[w][buf]);
+            ST_T(t4);
+            ST_ACC(3, t3 - t2); ST_ACC(5, t4 - t3); ST_ACC(6, t4 - t0);
             buf += 2;
             if (buf >= ST_NBUF) { buf -= ST_NBUF; bph ^= 1; }
             jj += 2;
-            while (jj >= pw) { jj -= pw; ++t; }
+            while (jj >= pw) {
+                jj -= pw;
+                ++t;
+                if (++stage == n_stages) { stage = 0; sph ^= 1; }
+            }
         }
+        ST_FLUSH(0);
+#ifdef HAET_TRACE
+        { ST_T(l_end); if (lane == 0) { atomicAdd(&g_st_trace[9], (unsigned long long)(l_end - l_start)); atomicAdd(&g_st_trace[10], 1ull); } }
+#endif
         // ---- write this warpgroup's partial (m2, l, S[C]) per slice of its block: chunk slot 2 * blockIdx.x + c ----
         if (pw > 0) {
             const int slot = pw == 1 ? sub : 0;
@@ -440,3 +487,11 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
 }
 
 }  // namespace haet
+
+#ifdef HAET_TRACE
+extern "C" int haet_debug_st_trace(unsigned long long *out64, int reset) {
+    if (out64 && cudaMemcpyFromSymbol(out64, haet::g_st_trace, sizeof(unsigned long long) * 64) != cudaSuccess) return -2;
+    if (reset) { unsigned long long z[64] = {0}; if (cudaMemcpyToSymbol(haet::g_st_trace, z, sizeof(z)) != cudaSuccess) return -2; }
+    return 0;
+}
+#endif
