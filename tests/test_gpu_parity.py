@@ -1101,3 +1101,53 @@ def test_slab_sharded_conv_layer_matches_full_grid(variant, kw, B, R, ln):
         assert rel_l2(got, full) < 5e-4
     # bad halo widths and shapes without a conv front-end are refused
     assert l.haet_slice_halo_workspace_bytes(C.byref(ranks[0]["sh"]), 2, 0, 0) == _lib.HAET_EINVAL
+
+
+def test_dim_head_64_beyond_the_pair_mode_limit_uses_the_simt_kernels():
+    """dim_head 64 runs on the tcgen05 passes up to 256 slices (two Ws images per slice block must fit shared memory); 512 slices
+    take the exact-fp32 SIMT kernels behind the same entry points -- same answer, no silent shape restriction."""
+    import haet_b200 as hb
+    kw = dict(dim=128, heads=2, dim_head=64, slice_num=512, rotate=45, mlp_ratio=2)
+    torch.manual_seed(512)
+    m = hb.Physics_Attention_Irregular_Mesh(**kw).eval()
+    trained_like_(m, 64)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    x = torch.nn.functional.layer_norm(torch.randn(1, 2000, 128), (128,))
+    m = m.cuda()
+    m.keep_taps = True
+    got = m(x.cuda())
+    t = m.last_taps
+    tree = (t["tree_idx"].cpu(), t["tree_mask"].cpu(), [r.cpu() if r is not None else None for r in t["rot_idx"]])
+    want = O.physics_attention_forward(sd, x, tree=tree, pos_override=t["pos"].cpu(), heads=2, dim_head=64, slice_num=512,
+                                       rotate=45, mlp_ratio=2, dimensionality=3)
+    assert rel_l2(got, want) < TOL
+
+
+def test_slab_entry_point_refuses_shapes_it_cannot_run():
+    from haet_b200 import _lib
+    l = _lib.lib()
+    # no conv front-end
+    sh = _lib.make_shape(1, 640, 64, 2, 32, 32)
+    assert l.haet_slice_halo_workspace_bytes(C.byref(sh), 0, 1, 0) == _lib.HAET_EINVAL
+    # N is not whole planes of the slab
+    sh = _lib.make_shape(1, 100, 64, 2, 32, 32, conv_nd=3, grid=(4, 5, 6))
+    assert l.haet_slice_halo_workspace_bytes(C.byref(sh), 0, 1, 0) == _lib.HAET_EINVAL
+    # dim_head 8 has no tensor-core passes: the spill of the SIMT deslice would need the halo-free projection
+    sh = _lib.make_shape(1, 4 * 5 * 6, 64, 8, 8, 32, conv_nd=3, grid=(4, 5, 6))
+    assert l.haet_slice_halo_workspace_bytes(C.byref(sh), 0, 1, 0) == _lib.HAET_ENOSUP
+    assert b"tensor-core" in l.haet_last_error()
+
+
+def test_train_mode_with_dropout_applies_torch_dropout_after_to_out():
+    """IrregularMesh.py:139,235: to_out = Sequential(Linear, Dropout).  In train mode the Dropout module runs (torch's op, on the
+    GPU) on the kernels' output: zeros appear at rate p and the survivors are scaled by 1 / (1 - p)."""
+    import haet_b200 as hb
+    torch.manual_seed(3)
+    m = hb.Physics_Attention_Irregular_Mesh(64, heads=4, dim_head=16, dropout=0.5, slice_num=32, rotate=45, mlp_ratio=2).cuda()
+    x = torch.nn.functional.layer_norm(torch.randn(1, 3000, 64), (64,)).cuda()
+    ev = m.eval()(x)
+    torch.manual_seed(4)
+    tr = m.train()(x)
+    zero = (tr == 0).float().mean().item()
+    assert 0.45 < zero < 0.55
+    assert tr.grad_fn is None
