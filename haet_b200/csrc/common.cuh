@@ -18,6 +18,7 @@ extern std::atomic<int64_t> g_launches;   // haet_launch_count()
 // and immutable afterwards, so that a *_bytes() query and the launch that follows always agree.
 struct Options {
     bool gemm_1cta, no_opi, no_ln_fuse, conv_simt, conv_nh1, no_pdl, erwin_fused;
+    int poly_p1, poly_p2;    // HAET_POLY_P1 / HAET_POLY_P2: eighths (0..4) of pass 1's / pass 2's exponentials computed by the FMA-pipe polynomial
     bool no_f32x2;           // HAET_NO_F32X2: scalar FFMA / FADD in the softmax loops of the two passes (A/B of the packed pairs)
     int tree_roles;          // 0: one CTA per rotated level
     int gemm_pf;             // HAET_GEMM_PF: L2 prefetch distance of the GEMM producers in (tile, panel) items

@@ -65,7 +65,9 @@ __host__ __device__ __forceinline__ int dt_gpad(int G) { return G <= 64 ? 64 : (
 // three buffers (item q: buffer q % 3, warpgroup q & 1), so a warpgroup never waits for the MMA phases of the buffer it just filled.
 // (Measured and dropped, DESIGN 10: WG = 2 removes the wait for d_full -- 1060 -> 126 cycles per item -- but two warps per scheduler
 // feed the MUFU pipe no better, 0.667 against 0.651 ms; software-pipelined TMEM reads in 16-column units were slower with either.)
-template <bool F2, int WG>
+// POLY: eighths (0..4) of every thread's logits whose 2^t comes from poly_ex2_pair (FMA / ALU pipes) instead of MUFU.EX2, interleaved
+// pair by pair in the same instruction stream (0 = all MUFU).
+template <bool F2, int WG, int POLY>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ lse2,
                   const float *__restrict__ states, const float *__restrict__ ws, const float *__restrict__ bs, float shift,
@@ -402,7 +404,10 @@ deslice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ sca
                         float v0, v1, v2, v3;
                         f2_unpack(f2_fma(f2_pack(__uint_as_float(r[c]), __uint_as_float(r[c + 1])), sn2, f2_pack(k4.x, k4.y)), v0, v1);
                         f2_unpack(f2_fma(f2_pack(__uint_as_float(r[c + 2]), __uint_as_float(r[c + 3])), sn2, f2_pack(k4.z, k4.w)), v2, v3);
-                        const float p0 = fast_ex2(v0), p1 = fast_ex2(v1), p2 = fast_ex2(v2), p3 = fast_ex2(v3);
+                        // pair index within the half: 2 * (c / 4) and + 1; pair j goes to the polynomial when poly_pair<POLY>(j) (tc.cuh)
+                        float p0, p1, p2, p3;
+                        if (poly_pair<POLY>(c >> 1)) poly_ex2_pair(v0, v1, p0, p1); else { p0 = fast_ex2(v0); p1 = fast_ex2(v1); }
+                        if (poly_pair<POLY>((c >> 1) + 1)) poly_ex2_pair(v2, v3, p2, p3); else { p2 = fast_ex2(v2); p3 = fast_ex2(v3); }
                         const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
                         pk[c >> 1] = *reinterpret_cast<const uint32_t *>(&ha);
                         pk[(c >> 1) + 1] = *reinterpret_cast<const uint32_t *>(&hb);
@@ -466,8 +471,12 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const bool pair = s->dim_head == 64;
     const size_t smem = 1024 + (size_t)g_pad * (pair ? 384 : 256) + (size_t)(pair ? 2 * (DT_STAGES - 1) : DT_STAGES) * DT_TILE_BYTES + (size_t)g_pad * 32 +
                         DT_TILE * 32 + sizeof(float) * g_pad + sizeof(float) * DT_STAGES * DT_TILE + sizeof(DesliceCtl);
-    HAET_DYN_SMEM((deslice_tc_kernel<true, 3>), smem);
-    HAET_DYN_SMEM((deslice_tc_kernel<false, 3>), smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<true, 3, 0>), smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<true, 3, 1>), smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<true, 3, 2>), smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<true, 3, 3>), smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<true, 3, 4>), smem);
+    HAET_DYN_SMEM((deslice_tc_kernel<false, 3, 0>), smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -479,7 +488,10 @@ int launch_deslice_tc(const haet_layer_shape *s, const uint8_t *img, const float
     const int64_t chunk_pts = align_up(cdiv(s->N, n_chunks), DT_TILE);
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)BH);
     constexpr int WG = 3;
-    auto kern = options().no_f32x2 ? deslice_tc_kernel<false, WG> : deslice_tc_kernel<true, WG>;
+    const int poly = options().no_f32x2 ? 0 : options().poly_p2;
+    auto kern = options().no_f32x2 ? deslice_tc_kernel<false, WG, 0>
+                : poly == 1 ? deslice_tc_kernel<true, WG, 1> : poly == 2 ? deslice_tc_kernel<true, WG, 2>
+                : poly == 3 ? deslice_tc_kernel<true, WG, 3> : poly == 4 ? deslice_tc_kernel<true, WG, 4> : deslice_tc_kernel<true, WG, 0>;
     kern<<<grid, (4 * WG + 8) * 32, smem, st>>>(img, scale, lse2, states, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
                                                s->heads * (pair ? 2 : 1), s->slice_num, s->dim_head, chunk_pts, o, o_image);
     HAET_LAUNCHED();

@@ -66,7 +66,8 @@ struct SliceCtl {
 // TMEM columns: accumulators of the 4 softmax warpgroups at 0..127, D / P buffers [stream][3] x 64 at 128..511
 __device__ __forceinline__ uint32_t st_dbuf_col(int w, int buf) { return 128u + (uint32_t)(w * ST_NBUF + buf) * ST_TILE; }
 
-template <bool F2>
+// POLY: eighths (0..4) of every thread's logits whose 2^t comes from poly_ex2_pair (FMA / ALU pipes) instead of MUFU.EX2 (tc.cuh)
+template <bool F2, int POLY>
 __global__ void __launch_bounds__(ST_THREADS, 1)
 slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale, const float *__restrict__ ws,
                 const float *__restrict__ bs, float shift, int64_t N, int64_t npad, int G, int C, int64_t chunk_pts,
@@ -313,7 +314,9 @@ slice_tc_kernel(const uint8_t *__restrict__ img, const float *__restrict__ scale
                         r[c] = __float_as_uint(v0); r[c + 1] = __float_as_uint(v1); r[c + 2] = __float_as_uint(v2); r[c + 3] = __float_as_uint(v3);
                         tmax = fmaxf(fmaxf(tmax, v0), v1);   // FMNMX3
                         tmax = fmaxf(fmaxf(tmax, v2), v3);
-                        const float p0 = fast_ex2(v0), p1 = fast_ex2(v1), p2 = fast_ex2(v2), p3 = fast_ex2(v3);
+                        float p0, p1, p2, p3;   // pair j of the half goes to the polynomial when poly_pair<POLY>(j) (tc.cuh)
+                        if (poly_pair<POLY>(c >> 1)) poly_ex2_pair(v0, v1, p0, p1); else { p0 = fast_ex2(v0); p1 = fast_ex2(v1); }
+                        if (poly_pair<POLY>((c >> 1) + 1)) poly_ex2_pair(v2, v3, p2, p3); else { p2 = fast_ex2(v2); p3 = fast_ex2(v3); }
                         l01 = f2_add(l01, f2_pack(p0, p1));
                         l01 = f2_add(l01, f2_pack(p2, p3));
                         const __half2 ha = __floats2half2_rn(p0, p1), hb = __floats2half2_rn(p2, p3);
@@ -471,17 +474,21 @@ int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *
     const bool pair = s->dim_head == 64;
     const size_t smem = 1024 + (size_t)n_gb * (pair ? 4 : 2) * (ST_GB * 128) + (size_t)(ST_STAGES + 1) * ST_TILE_BYTES +
                         sizeof(float) * ST_STAGES * ST_TILE + sizeof(SliceCtl);
-    HAET_DYN_SMEM(slice_tc_kernel<true>, smem);
-    HAET_DYN_SMEM(slice_tc_kernel<false>, smem);
+    HAET_DYN_SMEM((slice_tc_kernel<true, 0>), smem);
+    HAET_DYN_SMEM((slice_tc_kernel<true, 1>), smem);
+    HAET_DYN_SMEM((slice_tc_kernel<true, 2>), smem);
+    HAET_DYN_SMEM((slice_tc_kernel<true, 3>), smem);
+    HAET_DYN_SMEM((slice_tc_kernel<true, 4>), smem);
+    HAET_DYN_SMEM((slice_tc_kernel<false, 0>), smem);
     const int64_t chunk_pts = slice_tc_chunk_pts(s);
     const float raise_thr = hooks().st_raise > 0.f ? hooks().st_raise : ST_RAISE;   // haet_set_raise_threshold: tests force the accumulator-rescale path
     dim3 grid((unsigned)cdiv(s->N, chunk_pts), (unsigned)(s->B * s->heads * (pair ? 2 : 1)));
-    if (options().no_f32x2)
-        slice_tc_kernel<false><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
-                                                                s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
-    else
-        slice_tc_kernel<true><<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N),
-                                                               s->slice_num, s->dim_head, chunk_pts, raise_thr, chunk_parts);
+    const int poly = options().no_f32x2 ? 0 : options().poly_p1;
+    auto kern = options().no_f32x2 ? slice_tc_kernel<false, 0>
+                : poly == 1 ? slice_tc_kernel<true, 1> : poly == 2 ? slice_tc_kernel<true, 2> : poly == 3 ? slice_tc_kernel<true, 3>
+                : poly == 4 ? slice_tc_kernel<true, 4> : slice_tc_kernel<true, 0>;
+    kern<<<grid, ST_THREADS, smem, st>>>(img, scale, ws, bs, rep_slice_shift(s->epsilon), s->N, xpi_npad(s->N), s->slice_num, s->dim_head,
+                                          chunk_pts, raise_thr, chunk_parts);
     HAET_LAUNCHED();
     return HAET_OK;
 }

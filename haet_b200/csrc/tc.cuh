@@ -307,6 +307,36 @@ __device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
     return d;
 }
 
+// 2^t for a PAIR of logits on the FMA / ALU pipes only (no MUFU): Cody-Waite split t = n + f with the 1.5 * 2^23 magic constant, a
+// degree-3 minimax polynomial for 2^f on [-0.5, 0.5] (max relative error 7.6e-5 -- a sixth of the fp16 half-ulp the result is
+// rounded to) and n added to the exponent field (the low mantissa bits of t + magic ARE n).  t is clamped at -30 (2^-30 rounds to
+// 0 in fp16); valid for t < 127.  11 instructions per pair (2 FMNMX, 2 FADD2, 4 FFMA2, 2 LEA + the pack moves the allocator
+// elides).  The softmax loops give a FIXED FRACTION of every thread's logits to this routine, interleaved with the MUFU ones in
+// the same instruction stream: the MUFU pipe bounds the passes while two thirds of the issue slots are free.
+__device__ __forceinline__ void poly_ex2_pair(float t0, float t1, float &p0, float &p1) {
+    t0 = fmaxf(t0, -30.f);
+    t1 = fmaxf(t1, -30.f);
+    const uint64_t t = f2_pack(t0, t1);
+    const uint64_t r = f2_add(t, f2_pack(12582912.f, 12582912.f));
+    const uint64_t n = f2_add(r, f2_pack(-12582912.f, -12582912.f));
+    const uint64_t f = f2_fma(n, f2_pack(-1.f, -1.f), t);
+    uint64_t p = f2_fma(f2_pack(0.05520550534129143f, 0.05520550534129143f), f, f2_pack(0.24261397123336792f, 0.24261397123336792f));
+    p = f2_fma(p, f, f2_pack(0.6932547688484192f, 0.6932547688484192f));
+    p = f2_fma(p, f, f2_pack(0.9999276995658875f, 0.9999276995658875f));
+    float q0, q1, r0, r1;
+    f2_unpack(p, q0, q1);
+    f2_unpack(r, r0, r1);
+    p0 = __uint_as_float(__float_as_uint(q0) + (__float_as_uint(r0) << 23));
+    p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(r1) << 23));
+}
+
+// which pairs of a 16-pair half go to the polynomial: POLY eighths of them, spread evenly
+template <int POLY>
+__device__ __forceinline__ constexpr bool poly_pair(int j) {
+    constexpr unsigned masks[5] = {0x00u, 0x01u, 0x11u, 0x49u, 0x55u};
+    return (masks[POLY] >> (j & 7)) & 1u;
+}
+
 // (lo, hi) -> packed fp16x2, round to nearest, SATURATING at +-65504 instead of producing inf (SASS: F2FP.SATFINITE): the
 // operand images are fp16 hi + lo, and (inf, -inf) would turn into NaN logits
 __device__ __forceinline__ uint32_t pack_h2_sat(float lo, float hi) {
