@@ -78,9 +78,9 @@ def main():
     tot = sum(a[1] for a in ours.values())
     # kernels of ONE plain layer forward (haet_b200 PhysicsAttention at the bench shape) and how often each runs in it; the
     # LN / residual / MLP variants (gemm2_tc_kernel<1,1,0>, <0,0,1>, <2,1,0>, ln_fold) belong to the bench's fused-block leg
-    layer = [("gemm_tc_pack_kernel", 2), ("gemm2_tc_kernel<1, 0, 0>", 1), ("slice_tc_kernel<1>", 1), ("slice_merge_kernel", 2),
+    layer = [("gemm_tc_pack_kernel", 2), ("gemm2_tc_kernel<1, 0, 0>", 1), ("slice_tc_kernel<1, 1>", 1), ("slice_merge_kernel", 2),
              ("slice_pos_kernel", 1), ("balltree_kernel", 1), ("erwin_gather_kernel", 1), ("erwin_block_kernel", 6),
-             ("erwin_pool_kernel", 1), ("erwin_unpool_kernel", 1), ("erwin_scatter_kernel", 1), ("deslice_tc_kernel<1>", 1),
+             ("erwin_pool_kernel", 1), ("erwin_unpool_kernel", 1), ("erwin_scatter_kernel", 1), ("deslice_tc_kernel<1, 3, 3>", 1),
              ("gemm2_tc_kernel<0, 0, 0>", 1)]
     with open(prefix + "_launches.md", "w") as f:
         f.write("ncu --metrics gpu__time_duration.sum --clock-control none over `python bench.py --steps 2 --warmup 3 --no-configs` "
