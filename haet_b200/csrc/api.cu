@@ -25,6 +25,7 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.no_pdl = env_on("HAET_NO_PDL");
         v.erwin_fused = env_on("HAET_ERWIN_FUSED");
         v.no_f32x2 = env_on("HAET_NO_F32X2");
+        v.conv_xp = env_on("HAET_CONV_XP");
         auto eighths = [](const char *name, int dflt) { const char *e2 = getenv(name); const int v2 = e2 ? atoi(e2) : dflt; return v2 < 0 || v2 > 4 ? dflt : v2; };
         v.poly_p1 = eighths("HAET_POLY_P1", 1);
         v.poly_p2 = eighths("HAET_POLY_P2", 3);
@@ -242,13 +243,18 @@ static int slice_reduce_impl(const haet_layer_shape *s, const float *x_d, const 
         // Linear front-end: the GEMM epilogue writes the operand image directly
         rc = launch_inproj_tc(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st, ln_fused ? &ln : nullptr);
     } else {
+        bool packed = false;
         if (hooks().path == 0 && s->conv_nd == 0 && gemm_tc_supported(s->dim, inner))
             rc = launch_gemm_tc(x_d, wx_d, bx_d, xp, s->B * s->N, s->dim, inner, img, st);
-        else if (hooks().path == 0 && s->conv_nd != 0 && conv_tc_supported(s) && !options().conv_simt)
-            rc = launch_conv_tc(s, x_d, wx_d, bx_d, xp, img, st);   // Conv2d / Conv3d front-end: implicit GEMM on tcgen05
+        else if (tc && s->conv_nd != 0 && conv_tc_supported(s) && !options().conv_simt && !options().conv_xp && (s->dim_head == 32 || s->dim_head == 16)) {
+            // Conv2d / Conv3d front-end: implicit GEMM on tcgen05 whose epilogue writes the operand image itself
+            rc = launch_conv_tc_img(s, x_d, wx_d, bx_d, wt_d, bt, sv.img, sv.scale, img, st);
+            packed = true;
+        } else if (hooks().path == 0 && s->conv_nd != 0 && conv_tc_supported(s) && !options().conv_simt)
+            rc = launch_conv_tc(s, x_d, wx_d, bx_d, xp, img, st);   // the same to fp32 x_proj (SIMT passes, dim_head 64: packed below)
         else
             rc = launch_in_project(s, x_d, wx_d, bx_d, xp, st);
-        if (!rc && tc) rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st);
+        if (!rc && tc && !packed) rc = launch_xpi_pack(s, xp, wt_d, bt, sv.img, sv.scale, st);
     }
     if (rc) return rc;
     if (!(hooks().stage_mask & 2)) return HAET_OK;

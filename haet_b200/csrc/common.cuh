@@ -19,6 +19,7 @@ extern std::atomic<int64_t> g_launches;   // haet_launch_count()
 struct Options {
     bool gemm_1cta, no_opi, no_ln_fuse, conv_simt, conv_nh1, no_pdl, erwin_fused;
     int poly_p1, poly_p2;    // HAET_POLY_P1 / HAET_POLY_P2: eighths (0..4) of pass 1's / pass 2's exponentials computed by the FMA-pipe polynomial
+    bool conv_xp;            // HAET_CONV_XP: conv front-ends write fp32 x_proj + a separate image pack (A/B of the image epilogue)
     bool no_f32x2;           // HAET_NO_F32X2: scalar FFMA / FADD in the softmax loops of the two passes (A/B of the packed pairs)
     int tree_roles;          // 0: one CTA per rotated level
     int gemm_pf;             // HAET_GEMM_PF: L2 prefetch distance of the GEMM producers in (tile, panel) items
@@ -139,8 +140,13 @@ int launch_add_rows(float *y, const float *resid, int64_t n, cudaStream_t st);
 // Conv2d / Conv3d front-end as an implicit GEMM on tcgen05 (conv_tc.cu); wx tap-major [inner, taps, dim]
 bool conv_tc_supported(const haet_layer_shape *s);
 int64_t conv_tc_image_bytes(const haet_layer_shape *s);
+struct GemmEpi;
 int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, float *xp, void *img,
-                   cudaStream_t st);
+                   cudaStream_t st, const GemmEpi *epi = nullptr);
+// the same with the operand image + scales of the spill written by the epilogue (dim_head 16 / 32): no fp32 x_proj, no pack kernel
+int launch_conv_tc_img(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
+                       uint8_t *xpi, float *scale, void *img, cudaStream_t st);
+int launch_xpi_pad(const haet_layer_shape *s, uint8_t *xpi, float *scale, cudaStream_t st);   // zero the image rows N .. npad
 bool slice_tc_supported(const haet_layer_shape *s);
 int64_t slice_tc_chunks(const haet_layer_shape *s);
 int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,

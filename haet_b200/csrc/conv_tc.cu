@@ -28,10 +28,14 @@ struct ConvGeom {
     int ks, nd, din;      // kernel size, 2 or 3, input channels
 };
 
-template <int NH>
+// IMG: the epilogue writes the spill's fp16 hi / lo operand image + Ada-Temp scales directly (gemm_tc.cuh: EPI_IMG, as the Linear
+// front-end does) instead of fp32 x_proj that xpi_pack_kernel would read back: no x_proj round trip, one launch less.
+template <int NH, bool IMG>
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
-               float *__restrict__ Y, int64_t M, int Nn, int n_workers, ConvGeom geo) {
+               float *__restrict__ Y, int64_t M, int Nn, int n_workers, ConvGeom geo, GemmEpi epi) {
+    __shared__ __align__(16) float sWtc[32];   // Ada-Temp weights of one head (twice for dim_head 16)
+    if (IMG && threadIdx.x < 32) sWtc[threadIdx.x] = epi.wt[epi.c16 ? (threadIdx.x & 15) : threadIdx.x];
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int kp = geo.din / GT_KP;                       // 64-channel panels per tap
@@ -164,7 +168,6 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     } else {
         // ---------------- epilogue: TMEM -> registers -> + bias -> xp [M, Nn] ----------------
         const int q = warp & 3;
-        GemmEpi ep{};
         for (int64_t it = 0; it < my_tiles; ++it) {
             const int64_t tile = worker + it * n_workers;
             const int buf = (int)(it & 1);
@@ -176,7 +179,12 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
                 uint32_t r[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * CN + c0), r);
                 tmem_wait_ld();
-                gemm_epilogue_chunk<EPI_F32>(r, lane, m0, 0, 0, M, bias + group * CN + c0, nullptr, Y, Nn, group * CN + c0, ep);
+                if (IMG) {
+                    const int64_t bi0 = m0 / epi.N, n0 = m0 - bi0 * epi.N;
+                    gemm_epilogue_chunk<EPI_IMG>(r, lane, m0, bi0, n0, M, bias + group * CN + c0, sWtc, nullptr, Nn, group * CN + c0, epi);
+                } else {
+                    gemm_epilogue_chunk<EPI_F32>(r, lane, m0, 0, 0, M, bias + group * CN + c0, nullptr, Y, Nn, group * CN + c0, epi);
+                }
             }
             tc_fence_before();
             mbar_arrive(&cb->t_empty[buf]);
@@ -203,8 +211,9 @@ int64_t conv_tc_image_bytes(const haet_layer_shape *s) {
 }
 
 // wx: [inner, taps, dim] (tap-major, as the SIMT path reads it); img: scratch of conv_tc_image_bytes(s)
+// epi != nullptr: write the operand image / scales it names instead of xp (dim_head 16 or 32)
 int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, float *xp, void *img,
-                   cudaStream_t st) {
+                   cudaStream_t st, const GemmEpi *epi) {
     HAET_CHECK_ARG(conv_tc_supported(s), "conv_tc: unsupported shape");
     const int inner = s->heads * s->dim_head;
     ConvGeom geo;
@@ -220,8 +229,12 @@ int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, c
     const int nh = (inner % (2 * GT_N) == 0 && !options().conv_nh1) ? 2 : 1;
     const size_t smem = 1024 + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES + (size_t)(nh == 2 ? 2 : GT_STAGES) * nh * 2 * GT_PANEL_BYTES + sizeof(ConvSmem) + 16 +
                         (size_t)(K / GT_KP) * sizeof(int4);
-    if (nh == 2) HAET_DYN_SMEM(conv_tc_kernel<2>, smem);
-    else HAET_DYN_SMEM(conv_tc_kernel<1>, smem);
+    GemmEpi ep{};
+    if (epi) ep = *epi;
+    void (*kern)(const float *, const uint8_t *, const float *, float *, int64_t, int, int, ConvGeom, GemmEpi) =
+        nh == 2 ? (epi ? conv_tc_kernel<2, true> : conv_tc_kernel<2, false>) : (epi ? conv_tc_kernel<1, true> : conv_tc_kernel<1, false>);
+    if (nh == 2) { if (epi) HAET_DYN_SMEM((conv_tc_kernel<2, true>), smem); else HAET_DYN_SMEM((conv_tc_kernel<2, false>), smem); }
+    else { if (epi) HAET_DYN_SMEM((conv_tc_kernel<1, true>), smem); else HAET_DYN_SMEM((conv_tc_kernel<1, false>), smem); }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -230,10 +243,20 @@ int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, c
     int n_workers = sms / n_groups;
     if (n_workers < 1) n_workers = 1;
     if (n_workers > n_tiles) n_workers = (int)n_tiles;
-    if (nh == 2) conv_tc_kernel<2><<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
-    else conv_tc_kernel<1><<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo);
+    kern<<<n_workers * n_groups, CT_THREADS, smem, st>>>(x, (const uint8_t *)img, bx, xp, M, inner, n_workers, geo, ep);
     HAET_LAUNCHED();
     return HAET_OK;
+}
+
+int launch_conv_tc_img(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
+                       uint8_t *xpi, float *scale, void *img, cudaStream_t st) {
+    HAET_CHECK_ARG(s->dim_head == 32 || s->dim_head == 16, "conv_tc: the image epilogue needs dim_head 16 or 32");
+    GemmEpi ep{};
+    ep.c16 = s->dim_head == 16;
+    ep.img = xpi; ep.scale = scale; ep.wt = wt; ep.bt = bt; ep.base_temp = s->base_temp;
+    ep.N = s->N; ep.npad = xpi_npad(s->N); ep.H = s->heads;
+    if (int rc = launch_xpi_pad(s, xpi, scale, st)) return rc;
+    return launch_conv_tc(s, x, wx, bx, nullptr, img, st, &ep);
 }
 
 }  // namespace haet

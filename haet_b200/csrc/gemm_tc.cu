@@ -293,6 +293,15 @@ int launch_add_rows(float *y, const float *resid, int64_t n, cudaStream_t st) {
     return HAET_OK;
 }
 
+int launch_xpi_pad(const haet_layer_shape *s, uint8_t *xpi, float *scale, cudaStream_t st) {
+    const int64_t npad = xpi_npad(s->N), pad = npad - s->N, bh = s->B * s->heads;
+    if (pad > 0 && bh > 0) {
+        xpi_pad_kernel<<<(unsigned)cdiv(bh * pad * 8, 256), 256, 0, st>>>(xpi, scale, s->N, npad, bh);
+        HAET_LAUNCHED();
+    }
+    return HAET_OK;
+}
+
 // in_project_x of the tensor-core path: X [B*N, dim] -> the spill's operand image + scales (no fp32 x_proj)
 int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
                      uint8_t *xpi, float *scale, void *img, cudaStream_t st, const LnArgs *ln) {
@@ -313,11 +322,7 @@ int launch_inproj_tc(const haet_layer_shape *s, const float *x, const float *wx,
     }
     ep.img = xpi; ep.scale = scale; ep.wt = wt; ep.bt = bt; ep.base_temp = s->base_temp;
     ep.N = s->N; ep.npad = xpi_npad(s->N); ep.H = s->heads;
-    const int64_t pad = ep.npad - ep.N, bh = s->B * s->heads;
-    if (pad > 0 && bh > 0) {
-        xpi_pad_kernel<<<(unsigned)cdiv(bh * pad * 8, 256), 256, 0, st>>>(xpi, scale, ep.N, ep.npad, bh);
-        HAET_LAUNCHED();
-    }
+    if (int rc = launch_xpi_pad(s, xpi, scale, st)) return rc;
     return launch_gemm_impl<EPI_IMG>(x, wx, bx, nullptr, s->B * s->N, s->dim, s->heads * s->dim_head, img, ep, st);
 }
 
