@@ -26,6 +26,7 @@ const Options &options() {   // function-local static: initialised once, thread-
         v.erwin_fused = env_on("HAET_ERWIN_FUSED");
         v.no_f32x2 = env_on("HAET_NO_F32X2");
         v.conv_xp = env_on("HAET_CONV_XP");
+        v.mlp_fc2_split = env_on("HAET_MLP_FC2_SPLIT");
         auto eighths = [](const char *name, int dflt) { const char *e2 = getenv(name); const int v2 = e2 ? atoi(e2) : dflt; return v2 < 0 || v2 > 4 ? dflt : v2; };
         v.poly_p1 = eighths("HAET_POLY_P1", 1);
         v.poly_p2 = eighths("HAET_POLY_P2", 3);

@@ -19,6 +19,7 @@ extern std::atomic<int64_t> g_launches;   // haet_launch_count()
 struct Options {
     bool gemm_1cta, no_opi, no_ln_fuse, conv_simt, conv_nh1, no_pdl, erwin_fused;
     int poly_p1, poly_p2;    // HAET_POLY_P1 / HAET_POLY_P2: eighths (0..4) of pass 1's / pass 2's exponentials computed by the FMA-pipe polynomial
+    bool mlp_fc2_split;      // HAET_MLP_FC2_SPLIT: block MLP fc2 as one CTA-pair launch per 256 hidden columns (A/B of the streamed single pass)
     bool conv_xp;            // HAET_CONV_XP: conv front-ends write fp32 x_proj + a separate image pack (A/B of the image epilogue)
     bool no_f32x2;           // HAET_NO_F32X2: scalar FFMA / FADD in the softmax loops of the two passes (A/B of the packed pairs)
     int tree_roles;          // 0: one CTA per rotated level
@@ -146,7 +147,10 @@ int launch_conv_tc(const haet_layer_shape *s, const float *x, const float *wx, c
 // the same with the operand image + scales of the spill written by the epilogue (dim_head 16 / 32): no fp32 x_proj, no pack kernel
 int launch_conv_tc_img(const haet_layer_shape *s, const float *x, const float *wx, const float *bx, const float *wt, float bt,
                        uint8_t *xpi, float *scale, void *img, cudaStream_t st);
-int launch_xpi_pad(const haet_layer_shape *s, uint8_t *xpi, float *scale, cudaStream_t st);   // zero the image rows N .. npad
+int launch_xpi_pad(const haet_layer_shape *s, uint8_t *xpi, float *scale, cudaStream_t st);
+bool gemm_stream_opi_supported(int K, int Nn);
+int launch_gemm_stream_opi(const uint8_t *opi, const float *w, const float *bias, const float *resid, float *out, int64_t M, int K, int Nn,
+                           void *img, cudaStream_t st);   // zero the image rows N .. npad
 bool slice_tc_supported(const haet_layer_shape *s);
 int64_t slice_tc_chunks(const haet_layer_shape *s);
 int launch_slice_tc(const haet_layer_shape *s, const uint8_t *img, const float *scale, const float *ws,

@@ -30,7 +30,10 @@ struct ConvGeom {
 
 // IMG: the epilogue writes the spill's fp16 hi / lo operand image + Ada-Temp scales directly (gemm_tc.cuh: EPI_IMG, as the Linear
 // front-end does) instead of fp32 x_proj that xpi_pack_kernel would read back: no x_proj round trip, one launch less.
-template <int NH, bool IMG>
+// AIMG: X is not fp32 rows but a bf16 hi / lo operand image (common.cuh: OPI, [tile][k panel][hi | lo][128 x 128 B]) whose
+// (tile, panel) blocks are bulk-copied straight into the A stages -- a plain GEMM with K too deep for resident weights
+// (block MLP fc2, K = hidden >= 512: W streamed from L2, one pass over A); the epilogue adds bias and the residual rows.
+template <int NH, bool IMG, bool AIMG = false>
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
                float *__restrict__ Y, int64_t M, int Nn, int n_workers, ConvGeom geo, GemmEpi epi) {
@@ -67,7 +70,7 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     if (warp == 8) {
         if (lane == 0) {
             for (int s = 0; s < GT_STAGES; ++s) {
-                mbar_init(&cb->a_full[s], GT_PROD); mbar_init(&cb->a_empty[s], 1);
+                mbar_init(&cb->a_full[s], AIMG ? 1 : GT_PROD); mbar_init(&cb->a_empty[s], 1);
                 mbar_init(&cb->w_full[s], 1); mbar_init(&cb->w_empty[s], 1);
             }
             for (int b = 0; b < 2; ++b) { mbar_init(&cb->t_full[b], 1); mbar_init(&cb->t_empty[b], 128); }
@@ -81,7 +84,24 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
     tc_fence_after();
     const uint32_t tmem_base = cb->tmem_base;
 
-    if (warp < 8) {
+    if (AIMG && warp < 8) {
+        // ---------------- A loader: one 32 KB [hi | lo] block of the operand image per stage ----------------
+        if (warp == 0 && lane == 0) {
+            const uint8_t *opi = reinterpret_cast<const uint8_t *>(X);
+            int stage = 0, phase = 0;
+            for (int64_t it = 0; it < my_tiles; ++it) {
+                const int64_t tile = worker + it * n_workers;
+                for (int p = 0; p < panels; ++p) {
+                    mbar_wait(&cb->a_empty[stage], (uint32_t)(phase ^ 1));
+                    mbar_arrive_expect_tx(&cb->a_full[stage], 2 * GT_PANEL_BYTES);
+                    bulk_g2s(sA + (size_t)stage * 2 * GT_PANEL_BYTES, opi + ((size_t)tile * panels + p) * (2 * GT_PANEL_BYTES), 2 * GT_PANEL_BYTES,
+                             &cb->a_full[stage]);
+                    if (++stage == GT_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp < 8) {
         // ---------------- producers: implicit im2col.  Each thread owns 4 (row, chunk) items of the tile; the grid coordinates
         // of its rows are recomputed when the tile changes, the tap offset per panel. ----------------
         int64_t cur_ti = -1;
@@ -179,7 +199,9 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
                 uint32_t r[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * CN + c0), r);
                 tmem_wait_ld();
-                if (IMG) {
+                if (AIMG) {
+                    gemm_epilogue_chunk<EPI_F32, false, true>(r, lane, m0, 0, 0, M, bias + group * CN + c0, nullptr, Y, Nn, group * CN + c0, epi);
+                } else if (IMG) {
                     const int64_t bi0 = m0 / epi.N, n0 = m0 - bi0 * epi.N;
                     gemm_epilogue_chunk<EPI_IMG>(r, lane, m0, bi0, n0, M, bias + group * CN + c0, sWtc, nullptr, Nn, group * CN + c0, epi);
                 } else {
@@ -257,6 +279,34 @@ int launch_conv_tc_img(const haet_layer_shape *s, const float *x, const float *w
     ep.N = s->N; ep.npad = xpi_npad(s->N); ep.H = s->heads;
     if (int rc = launch_xpi_pad(s, xpi, scale, st)) return rc;
     return launch_conv_tc(s, x, wx, bx, nullptr, img, st, &ep);
+}
+
+// out[M, 256] = A . W^T + bias + resid with A the operand image `opi` ([tile][K / 64 panels][hi | lo]) and W [256, K] fp32:
+// the block MLP's fc2 for hidden >= 512 in ONE pass (W streamed as 64 KB panels instead of one resident 256-column slice per launch)
+bool gemm_stream_opi_supported(int K, int Nn) { return Nn == 2 * GT_N && K % GT_KP == 0 && K >= GT_KP && K / GT_KP <= CT_MAX_PANELS; }
+int launch_gemm_stream_opi(const uint8_t *opi, const float *w, const float *bias, const float *resid, float *out, int64_t M, int K, int Nn,
+                           void *img, cudaStream_t st) {
+    HAET_CHECK_ARG(gemm_stream_opi_supported(K, Nn), "gemm_stream_opi: unsupported K=%d Nn=%d", K, Nn);
+    HAET_CHECK_ARG(bias != nullptr && resid != nullptr, "gemm_stream_opi: bias and residual rows are required");
+    if (M == 0) return HAET_OK;
+    if (int rc = launch_gemm_tc_pack(w, Nn, K, (uint8_t *)img, st)) return rc;
+    ConvGeom geo{};
+    geo.N = M; geo.g0 = 1; geo.g1 = 1; geo.g2 = 1; geo.ks = 1; geo.nd = 2; geo.din = K;
+    GemmEpi ep{};
+    ep.resid = resid;
+    const size_t smem = 1024 + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES + (size_t)2 * 2 * 2 * GT_PANEL_BYTES + sizeof(ConvSmem) + 16 +
+                        (size_t)(K / GT_KP) * sizeof(int4);
+    HAET_DYN_SMEM((conv_tc_kernel<2, false, true>), smem);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t n_tiles = (M + GT_M - 1) / GT_M;
+    int n_workers = sms;
+    if (n_workers > n_tiles) n_workers = (int)n_tiles;
+    conv_tc_kernel<2, false, true><<<n_workers, CT_THREADS, smem, st>>>(reinterpret_cast<const float *>(opi), (const uint8_t *)img, bias, out, M, Nn,
+                                                                        n_workers, geo, ep);
+    HAET_LAUNCHED();
+    return HAET_OK;
 }
 
 }  // namespace haet

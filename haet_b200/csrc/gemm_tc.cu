@@ -334,7 +334,8 @@ bool mlp_tc_supported(int dim, int hidden) {
     return hooks().path == 0 && dim == 256 && hidden >= 256 && hidden % 256 == 0 && hidden <= 2048 && !options().gemm_1cta;
 }
 int64_t mlp_tc_workspace_bytes(int64_t M, int dim, int hidden) {
-    return align_up(opi_bytes(M, hidden), 256) + align_up(gemm_tc_image_bytes(dim, 256), 256) +
+    const int64_t img_b = gemm_tc_image_bytes(dim, 256) > 4 * (int64_t)dim * hidden ? gemm_tc_image_bytes(dim, 256) : 4 * (int64_t)dim * hidden;
+    return align_up(opi_bytes(M, hidden), 256) + align_up(img_b, 256) +
            align_up((int64_t)(256 * dim + 2 * 256) * 4, 256) + align_up(M * (int64_t)sizeof(float2), 256);
 }
 int launch_mlp_tc(const float *x, int64_t M, int dim, int hidden, const float *ln_g, const float *ln_b, float ln_eps,
@@ -343,7 +344,8 @@ int launch_mlp_tc(const float *x, int64_t M, int dim, int hidden, const float *l
     if (M == 0) return HAET_OK;
     char *p = (char *)workspace;
     uint8_t *h = (uint8_t *)p;      p += align_up(opi_bytes(M, hidden), 256);
-    uint8_t *img = (uint8_t *)p;    p += align_up(gemm_tc_image_bytes(dim, 256), 256);
+    const int64_t img_b = gemm_tc_image_bytes(dim, 256) > 4 * (int64_t)dim * hidden ? gemm_tc_image_bytes(dim, 256) : 4 * (int64_t)dim * hidden;
+    uint8_t *img = (uint8_t *)p;    p += align_up(img_b, 256);
     float *wf = (float *)p;         p += align_up((int64_t)(256 * dim + 2 * 256) * 4, 256);
     float *bf = wf + 256 * dim, *wsum = bf + 256;
     float2 *stats = (float2 *)p;
@@ -358,6 +360,10 @@ int launch_mlp_tc(const float *x, int64_t M, int dim, int hidden, const float *l
         ep.opi = h; ep.opi_panels = hidden / 64; ep.opi_panel0 = 4 * j;
         if ((rc = launch_gemm2_tc(EPI_OPI, x, img, bf, nullptr, M, dim, 256, ep, st))) return rc;
     }
+    // fc2.  hidden >= 512: ONE pass with W2 streamed from L2 (conv_tc.cu: launch_gemm_stream_opi) -- h is read once, out written
+    // once: 4 GB per 1M rows instead of 6 GB for one CTA-pair launch per 256 hidden columns with `out` read back in between
+    if (blocks >= 2 && !options().mlp_fc2_split && gemm_stream_opi_supported(hidden, dim))
+        return launch_gemm_stream_opi(h, w2, b2, x, out, M, hidden, dim, img, st);
     for (int j = 0; j < blocks; ++j) {
         if ((rc = launch_gemm_tc_pack(w2 + j * 256, dim, 256, img, st, hidden))) return rc;
         GemmEpi ep{};
