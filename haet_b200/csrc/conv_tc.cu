@@ -33,7 +33,7 @@ struct ConvGeom {
 // AIMG: X is not fp32 rows but a bf16 hi / lo operand image (common.cuh: OPI, [tile][k panel][hi | lo][128 x 128 B]) whose
 // (tile, panel) blocks are bulk-copied straight into the A stages -- a plain GEMM with K too deep for resident weights
 // (block MLP fc2, K = hidden >= 512: W streamed from L2, one pass over A); the epilogue adds bias and the residual rows.
-template <int NH, bool IMG, bool AIMG = false>
+template <int NH, bool IMG, bool AIMG = false, bool RES = false>
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, const float *__restrict__ bias,
                float *__restrict__ Y, int64_t M, int Nn, int n_workers, ConvGeom geo, GemmEpi epi) {
@@ -200,7 +200,7 @@ conv_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, co
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * CN + c0), r);
                 tmem_wait_ld();
                 if (AIMG) {
-                    gemm_epilogue_chunk<EPI_F32, false, true>(r, lane, m0, 0, 0, M, bias + group * CN + c0, nullptr, Y, Nn, group * CN + c0, epi);
+                    gemm_epilogue_chunk<EPI_F32, false, RES>(r, lane, m0, 0, 0, M, bias + group * CN + c0, nullptr, Y, Nn, group * CN + c0, epi);
                 } else if (IMG) {
                     const int64_t bi0 = m0 / epi.N, n0 = m0 - bi0 * epi.N;
                     gemm_epilogue_chunk<EPI_IMG>(r, lane, m0, bi0, n0, M, bias + group * CN + c0, sWtc, nullptr, Nn, group * CN + c0, epi);
@@ -281,13 +281,13 @@ int launch_conv_tc_img(const haet_layer_shape *s, const float *x, const float *w
     return launch_conv_tc(s, x, wx, bx, nullptr, img, st, &ep);
 }
 
-// out[M, 256] = A . W^T + bias + resid with A the operand image `opi` ([tile][K / 64 panels][hi | lo]) and W [256, K] fp32:
+// out[M, 256] = A . W^T + bias (+ resid, may be NULL) with A the operand image `opi` ([tile][K / 64 panels][hi | lo]) and W [256, K] fp32:
 // the block MLP's fc2 for hidden >= 512 in ONE pass (W streamed as 64 KB panels instead of one resident 256-column slice per launch)
 bool gemm_stream_opi_supported(int K, int Nn) { return Nn == 2 * GT_N && K % GT_KP == 0 && K >= GT_KP && K / GT_KP <= CT_MAX_PANELS; }
 int launch_gemm_stream_opi(const uint8_t *opi, const float *w, const float *bias, const float *resid, float *out, int64_t M, int K, int Nn,
                            void *img, cudaStream_t st) {
     HAET_CHECK_ARG(gemm_stream_opi_supported(K, Nn), "gemm_stream_opi: unsupported K=%d Nn=%d", K, Nn);
-    HAET_CHECK_ARG(bias != nullptr && resid != nullptr, "gemm_stream_opi: bias and residual rows are required");
+    HAET_CHECK_ARG(bias != nullptr, "gemm_stream_opi: a bias is required");
     if (M == 0) return HAET_OK;
     if (int rc = launch_gemm_tc_pack(w, Nn, K, (uint8_t *)img, st)) return rc;
     ConvGeom geo{};
@@ -296,15 +296,16 @@ int launch_gemm_stream_opi(const uint8_t *opi, const float *w, const float *bias
     ep.resid = resid;
     const size_t smem = 1024 + (size_t)GT_STAGES * 2 * GT_PANEL_BYTES + (size_t)2 * 2 * 2 * GT_PANEL_BYTES + sizeof(ConvSmem) + 16 +
                         (size_t)(K / GT_KP) * sizeof(int4);
-    HAET_DYN_SMEM((conv_tc_kernel<2, false, true>), smem);
+    HAET_DYN_SMEM((conv_tc_kernel<2, false, true, true>), smem);
+    HAET_DYN_SMEM((conv_tc_kernel<2, false, true, false>), smem);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int64_t n_tiles = (M + GT_M - 1) / GT_M;
     int n_workers = sms;
     if (n_workers > n_tiles) n_workers = (int)n_tiles;
-    conv_tc_kernel<2, false, true><<<n_workers, CT_THREADS, smem, st>>>(reinterpret_cast<const float *>(opi), (const uint8_t *)img, bias, out, M, Nn,
-                                                                        n_workers, geo, ep);
+    auto kern = resid ? conv_tc_kernel<2, false, true, true> : conv_tc_kernel<2, false, true, false>;
+    kern<<<n_workers, CT_THREADS, smem, st>>>(reinterpret_cast<const float *>(opi), (const uint8_t *)img, bias, out, M, Nn, n_workers, geo, ep);
     HAET_LAUNCHED();
     return HAET_OK;
 }

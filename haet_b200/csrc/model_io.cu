@@ -248,7 +248,8 @@ int64_t haet_model_prologue_workspace_bytes(int64_t M, int32_t Ka, int32_t Kf, i
                   "<= %d input features, tensor-core path)", K, hidden, dim, PRO_MAXK);
         return HAET_ENOSUP;
     }
-    return align_up(opi_bytes(M, hidden), 256) + align_up(gemm_tc_image_bytes(256, dim), 256) + 256 * 4;
+    const int64_t img_b = gemm_tc_image_bytes(256, dim) > 4 * (int64_t)dim * hidden ? gemm_tc_image_bytes(256, dim) : 4 * (int64_t)dim * hidden;
+    return align_up(opi_bytes(M, hidden), 256) + align_up(img_b, 256) + 256 * 4;
 }
 
 int haet_model_prologue(const float *feat_a_d, int32_t Ka, const float *feat_f_d, int32_t Kf, int32_t ref, int64_t B, int64_t N,
@@ -268,7 +269,8 @@ int haet_model_prologue(const float *feat_a_d, int32_t Ka, const float *feat_f_d
     cudaStream_t st = (cudaStream_t)stream;
     char *p = (char *)workspace_d;
     uint8_t *h = (uint8_t *)p;      p += align_up(opi_bytes(M, hidden), 256);
-    uint8_t *img = (uint8_t *)p;    p += align_up(gemm_tc_image_bytes(256, dim), 256);
+    const int64_t img_b = gemm_tc_image_bytes(256, dim) > 4 * (int64_t)dim * hidden ? gemm_tc_image_bytes(256, dim) : 4 * (int64_t)dim * hidden;
+    uint8_t *img = (uint8_t *)p;    p += align_up(img_b, 256);
     float *bias0 = (float *)p;
     const size_t smem = (size_t)K * (hidden + 128) * sizeof(float);
     if (smem > 48 * 1024) HAET_DYN_SMEM(prologue_fc1_kernel, smem);
@@ -282,6 +284,10 @@ int haet_model_prologue(const float *feat_a_d, int32_t Ka, const float *feat_f_d
         bias = bias0;
     }
     int rc;
+    if (hidden >= 512 && !options().mlp_fc2_split && gemm_stream_opi_supported(hidden, dim)) {
+        // one pass over the hidden activations with W2 streamed from L2 (conv_tc.cu: launch_gemm_stream_opi), as the block MLP's fc2
+        if ((rc = launch_gemm_stream_opi(h, w2_d, bias, nullptr, out_d, M, hidden, dim, img, st))) return rc;
+    } else
     for (int j = 0; j < hidden / 256; ++j) {
         if ((rc = launch_gemm_tc_pack(w2_d + j * 256, dim, 256, img, st, hidden))) return rc;
         GemmEpi ep{};
