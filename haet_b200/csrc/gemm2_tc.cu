@@ -67,6 +67,19 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
     }
     for (int i = threadIdx.x; i < G2_N; i += G2_THREADS) sBias[i] = bias ? bias[i] : 0.f;
     if (EPI == EPI_IMG && threadIdx.x < 32) sWt[threadIdx.x] = ep.wt[ep.c16 ? (threadIdx.x & 15) : threadIdx.x];
+    // LN: the epilogue re-reads wsum[256] for every tile; from global memory those loads sat behind the streaming x rows in L1 / L2
+    // and their latency was 15 % of the kernel's stall samples.  The layout is 256 bytes short of holding a copy -- unless the
+    // 1 KB reserved for aligning the dynamic segment is not needed (its base is 1 KB aligned on this architecture): checked here,
+    // per launch, and used when it fits.
+    GemmEpi epl = ep;
+    if (LN) {
+        float *sWsum = sWt + 32;
+        const uint32_t used = (uint32_t)(reinterpret_cast<uint8_t *>(sWsum + G2_N) - smem_raw);
+        if (used <= (uint32_t)ep.smem_total) {
+            for (int i = threadIdx.x; i < G2_N; i += G2_THREADS) sWsum[i] = ep.wsum[i];
+            epl.wsum = sWsum;
+        }
+    }
     // barriers initialised, TMEM allocated and W resident in BOTH CTAs before any remote arrive / pair MMA
     tc_fence_before();
     cluster_sync_all();
@@ -181,7 +194,7 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
                 uint32_t r[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * G2_N + c0), r);
                 tmem_wait_ld();
-                gemm_epilogue_chunk<EPI, LN, RES>(r, lane, m0, bi0, n0, M, sBias + c0, sWt, Y, G2_N, c0, ep, rs);
+                gemm_epilogue_chunk<EPI, LN, RES>(r, lane, m0, bi0, n0, M, sBias + c0, sWt, Y, G2_N, c0, epl, rs);
             }
             tc_fence_before();
             mbar_arrive_remote(empty0 + 8u * buf);
@@ -202,7 +215,10 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
                     const GemmEpi &ep, cudaStream_t st) {
     HAET_CHECK_ARG(gemm2_tc_supported(K, Nn), "gemm2_tc: unsupported K=%d Nn=%d", K, Nn);
     const int panels = K / GT_KP;
-    const size_t smem = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + G2_CB_BYTES + sizeof(float) * (G2_N + 32);
+    const size_t smem_base = 1024 + (size_t)(panels + GT_STAGES) * 2 * GT_PANEL_BYTES + G2_CB_BYTES + sizeof(float) * (G2_N + 32);
+    // LN variants ask for up to 1 KB more (their shared-memory copy of wsum), capped at the 227 KB opt-in limit
+    const size_t smem_ln = smem_base + sizeof(float) * G2_N <= 232448 ? smem_base + sizeof(float) * G2_N : 232448;
+    const size_t smem = (epi == EPI_OPI || ep.wsum != nullptr) ? smem_ln : smem_base;
     if (epi == EPI_OPI) {   // block MLP fc1: ln_2 + GELU + operand image
         HAET_CHECK_ARG(ep.ln_stats != nullptr && ep.wsum != nullptr && ep.opi != nullptr, "EPI_OPI needs the LayerNorm scratch and an image");
         HAET_DYN_SMEM((gemm2_tc_kernel<EPI_OPI, true, false>), smem);
@@ -215,6 +231,7 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
         if (np < 1) np = 1;
         GemmEpi epo = ep;
         epo.pf = options().gemm_pf;
+        epo.smem_total = (int)smem;
         gemm2_tc_kernel<EPI_OPI, true, false><<<2 * np, G2_THREADS, smem, st>>>(x, wimg, bias, y, M, K, np, epo);
         HAET_LAUNCHED();
         return HAET_OK;
@@ -238,6 +255,7 @@ int launch_gemm2_tc(int epi, const float *x, const uint8_t *wimg, const float *b
     if (n_pairs < 1) n_pairs = 1;
     GemmEpi epd = ep;
     epd.pf = options().gemm_pf;
+    epd.smem_total = (int)smem;
 #ifdef HAET_DEV_HOOKS   // timing ablations (results are garbage): never compiled into the shipped library
     if (const char *e = getenv("HAET_GEMM_DBG")) epd.dbg |= atoi(e);
 #endif

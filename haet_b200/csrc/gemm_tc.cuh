@@ -36,6 +36,7 @@ struct GemmEpi {   // EPI_IMG arguments
     //   xp[m, o] = rstd_m (acc[m, o] - mean_m wsum[o]) + bias'[o],  wsum[o] = sum_k W'[o, k]
     const float *resid;
     const float *wsum;
+    int smem_total;   // pair kernel, LN: dynamic shared memory of the launch; the kernel keeps wsum in its tail when the alignment pad leaves room
     float2 *ln_stats;
     float ln_eps;
     int ln_reuse;   // ln_stats was filled by an earlier launch over the same X (later column blocks of the block MLP's fc1)
@@ -219,8 +220,9 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
     // overlaps the shuffles (the same fix as the residual loads below)
     float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (LN && EPI != EPI_F32 && !(ep.dbg & 64)) {
-        const float4 sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
-        const float4 sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
+        // ep.wsum may point to the CTA's shared-memory copy (gemm2_tc.cu): a generic load serves both
+        const float4 sa = *reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4);
+        const float4 sb = *reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4);
         su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
     }
     if (EPI == EPI_F32) {
