@@ -77,7 +77,7 @@ gemm2_tc_kernel(const float *__restrict__ X, const uint8_t *__restrict__ Wimg, c
         const uint32_t used = (uint32_t)(reinterpret_cast<uint8_t *>(sWsum + G2_N) - smem_raw);
         if (used <= (uint32_t)ep.smem_total) {
             for (int i = threadIdx.x; i < G2_N; i += G2_THREADS) sWsum[i] = ep.wsum[i];
-            epl.wsum = sWsum;
+            epl.wsum_s = smem_u32(sWsum);
         }
     }
     // barriers initialised, TMEM allocated and W resident in BOTH CTAs before any remote arrive / pair MMA

@@ -36,6 +36,7 @@ struct GemmEpi {   // EPI_IMG arguments
     //   xp[m, o] = rstd_m (acc[m, o] - mean_m wsum[o]) + bias'[o],  wsum[o] = sum_k W'[o, k]
     const float *resid;
     const float *wsum;
+    uint32_t wsum_s;  // shared-memory address of the CTA's copy of wsum (0: read ep.wsum from global memory); set by the kernel
     int smem_total;   // pair kernel, LN: dynamic shared memory of the launch; the kernel keeps wsum in its tail when the alignment pad leaves room
     float2 *ln_stats;
     float ln_eps;
@@ -220,9 +221,15 @@ __device__ __forceinline__ void gemm_epilogue_chunk(uint32_t (&r)[32], int lane,
     // overlaps the shuffles (the same fix as the residual loads below)
     float su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (LN && EPI != EPI_F32 && !(ep.dbg & 64)) {
-        // ep.wsum may point to the CTA's shared-memory copy (gemm2_tc.cu): a generic load serves both
-        const float4 sa = *reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4);
-        const float4 sb = *reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4);
+        float4 sa, sb;
+        if (ep.wsum_s) {   // the CTA's shared-memory copy (gemm2_tc.cu): LDS, not a generic load
+            const uint32_t a = ep.wsum_s + (uint32_t)(col0 + 8 * l4) * 4u;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(sa.x), "=f"(sa.y), "=f"(sa.z), "=f"(sa.w) : "r"(a));
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(sb.x), "=f"(sb.y), "=f"(sb.z), "=f"(sb.w) : "r"(a + 16u));
+        } else {
+            sa = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4));
+            sb = __ldg(reinterpret_cast<const float4 *>(ep.wsum + col0 + 8 * l4 + 4));
+        }
         su[0] = sa.x; su[1] = sa.y; su[2] = sa.z; su[3] = sa.w; su[4] = sb.x; su[5] = sb.y; su[6] = sb.z; su[7] = sb.w;
     }
     if (EPI == EPI_F32) {
